@@ -1,0 +1,744 @@
+/* fimo_worlds_b200.h — C ABI of the B200-native `fimo-worlds` system-group step.
+ *
+ * This header is the drop-in boundary.  It is a self-contained,
+ * C17 / C++17 / nvcc-clean mirror of the reference's interface packages:
+ *
+ *   pkgs/fimo_worlds_meta/include/fimo_worlds_meta/{jobs,resources,systems,worlds}.h
+ *   pkgs/fimo_tasks_meta/include/fimo_tasks_meta/{command_buffer,futex,pool,task}.h
+ *   pkgs/fimo_std/include/fimo_std/error.h (FimoStatus only)
+ *
+ * The reference's own headers do not compile (jobs.h:42,47; modules.h:284 — see
+ * SURVEY.md preamble), and where header and implementation disagree the Zig
+ * `symbols.zig` files are authoritative (pkgs/fimo_worlds_meta/src/symbols.zig:60-365,
+ * pkgs/fimo_tasks_meta/src/pool.zig:88-104).  Struct layouts are byte-identical to
+ * the reference on x86-64 and are pinned by the static asserts at the bottom.
+ *
+ * The reference exposes its 32 `fimo-worlds` symbols through the fimo module
+ * loader (name + namespace + version), not as C-linkage names.  This library
+ * exports each of them as `fimo_worlds_<symbol name>` and additionally as a
+ * table (`fimo_worlds_b200_exports`) in the order of `all_symbols`
+ * (symbols.zig:22-58), which is what a `fimo_exports` shim binds.
+ *
+ * The same header is implemented twice:
+ *   - libfimo_worlds_b200.so  the product: CUDA sm_100a device executor.
+ *   - oracle/_build/libfimo_worlds_oracle.so  the CPU restatement (test infrastructure only).
+ */
+#ifndef FIMO_WORLDS_B200_H
+#define FIMO_WORLDS_B200_H
+
+#include <stdbool.h>
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(__GNUC__)
+#define FIMO_B200_EXPORT __attribute__((visibility("default")))
+#else
+#define FIMO_B200_EXPORT
+#endif
+
+/* ------------------------------------------------------------------------- */
+/* fimo_std mirrors                                                           */
+/* ------------------------------------------------------------------------- */
+
+typedef size_t FimoUSize;
+typedef uint8_t FimoU8;
+typedef uint64_t FimoU64;
+typedef int32_t FimoI32;
+
+/* fimo_std/error.h:175-186 — status of a fallible call. */
+typedef FimoI32 FimoStatus;
+#define FIMO_STATUS_OK ((FimoStatus)0)
+/* error, details parked in the thread-local result (here: fimo_worlds_b200_last_error) */
+#define FIMO_STATUS_ERROR ((FimoStatus)-1)
+#define FIMO_STATUS_ERROR_NO_REPORT ((FimoStatus)-2)
+
+/* fimo_std/time.h — 16-byte instant / duration. */
+typedef struct FimoDuration {
+    FimoU64 secs;
+    uint32_t nanos;
+} FimoDuration;
+typedef struct FimoInstant {
+    FimoU64 secs;
+    uint32_t nanos;
+} FimoInstant;
+
+/* ------------------------------------------------------------------------- */
+/* fimo_tasks_meta mirrors (types on the boundary of the hot path)            */
+/* ------------------------------------------------------------------------- */
+
+typedef FimoUSize FimoTasksMeta_TaskId;
+typedef FimoUSize FimoTasksMeta_PoolId;
+typedef FimoUSize FimoTasksMeta_PoolWorker;
+typedef FimoUSize FimoTasksMeta_PoolStackSize;
+
+/* task.h:17-38 */
+typedef struct FimoTasksMeta_Task {
+    const char *label;
+    FimoUSize label_len;
+    void (*on_start)(struct FimoTasksMeta_Task *task);
+    void (*on_complete)(struct FimoTasksMeta_Task *task);
+    void (*on_abort)(struct FimoTasksMeta_Task *task);
+    void (*on_deinit)(struct FimoTasksMeta_Task *task);
+} FimoTasksMeta_Task;
+
+typedef struct FimoTasksMeta_CommandBuffer FimoTasksMeta_CommandBuffer;
+typedef struct FimoTasksMeta_CommandBufferHandle FimoTasksMeta_CommandBufferHandle;
+
+/* pool.h:27-62; enqueue_buffer returns Status as in pkgs/fimo_tasks_meta/src/pool.zig:99-103 */
+typedef struct FimoTasksMeta_PoolVTable {
+    FimoTasksMeta_PoolId (*id)(void *pool);
+    void (*acquire)(void *pool);
+    void (*release)(void *pool);
+    void (*request_close)(void *pool);
+    bool (*accepts_requests)(void *pool);
+    bool (*owns_current_thread)(void *pool);
+    const char *(*label)(void *pool, FimoUSize *len);
+    FimoUSize (*workers)(void *pool, FimoTasksMeta_PoolWorker *ptr, FimoUSize len);
+    FimoUSize (*stack_sizes)(void *pool, FimoTasksMeta_PoolStackSize *ptr, FimoUSize len);
+    FimoStatus (*enqueue_buffer)(void *pool, FimoTasksMeta_CommandBuffer *buffer,
+                                 FimoTasksMeta_CommandBufferHandle *handle /* nullable: detached */);
+} FimoTasksMeta_PoolVTable;
+
+/* pool.h:65-68 */
+typedef struct FimoTasksMeta_Pool {
+    void *data;
+    const FimoTasksMeta_PoolVTable *vtable;
+} FimoTasksMeta_Pool;
+
+/* command_buffer.h:17-41 */
+typedef enum FimoTasksMeta_CommandBufferHandleCompletionStatus {
+    FIMO_TASKS_META_COMMAND_BUFFER_HANDLE_COMPLETION_STATUS_COMPLETED,
+    FIMO_TASKS_META_COMMAND_BUFFER_HANDLE_COMPLETION_STATUS_ABORTED,
+} FimoTasksMeta_CommandBufferHandleCompletionStatus;
+
+typedef struct FimoTasksMeta_CommandBufferHandleVTable {
+    void (*acquire)(void *handle);
+    void (*release)(void *handle);
+    FimoTasksMeta_Pool (*owner_pool)(void *handle);
+    FimoTasksMeta_CommandBufferHandleCompletionStatus (*wait_on)(void *handle);
+} FimoTasksMeta_CommandBufferHandleVTable;
+
+struct FimoTasksMeta_CommandBufferHandle {
+    void *data;
+    const FimoTasksMeta_CommandBufferHandleVTable *vtable;
+};
+
+/* command_buffer.h:44-54 */
+typedef FimoI32 FimoTasksMeta_CommandBufferEntryType;
+enum {
+    FIMO_TASKS_META_COMMAND_BUFFER_ENTRY_TYPE_ABORT_ON_ERROR = 0,
+    FIMO_TASKS_META_COMMAND_BUFFER_ENTRY_TYPE_SET_MIN_STACK_SIZE = 1,
+    FIMO_TASKS_META_COMMAND_BUFFER_ENTRY_TYPE_SELECT_WORKER = 2,
+    FIMO_TASKS_META_COMMAND_BUFFER_ENTRY_TYPE_SELECT_ANY_WORKER = 3,
+    FIMO_TASKS_META_COMMAND_BUFFER_ENTRY_TYPE_ENQUEUE_TASK = 4,
+    FIMO_TASKS_META_COMMAND_BUFFER_ENTRY_TYPE_ENQUEUE_COMMAND_BUFFER = 5,
+    FIMO_TASKS_META_COMMAND_BUFFER_ENTRY_TYPE_WAIT_ON_BARRIER = 6,
+    FIMO_TASKS_META_COMMAND_BUFFER_ENTRY_TYPE_WAIT_ON_COMMAND_BUFFER = 7,
+    FIMO_TASKS_META_COMMAND_BUFFER_ENTRY_TYPE_WAIT_ON_COMMAND_INDIRECT = 8,
+};
+
+/* command_buffer.h:57-86 */
+typedef union FimoTasksMeta_CommandBufferEntryPayload {
+    bool abort_on_error;
+    FimoTasksMeta_PoolStackSize set_min_stack_size;
+    FimoTasksMeta_PoolWorker select_worker;
+    FimoU8 select_any_worker;
+    FimoTasksMeta_Task *enqueue_task;
+    FimoTasksMeta_CommandBuffer *enqueue_command_buffer;
+    FimoU8 wait_on_barrier;
+    FimoTasksMeta_CommandBufferHandle wait_on_command_buffer;
+    /* waits for the command at index `this_command - value` */
+    FimoUSize wait_on_command_indirect;
+} FimoTasksMeta_CommandBufferEntryPayload;
+
+/* command_buffer.h:92-96 */
+typedef struct FimoTasksMeta_CommandBufferEntry {
+    FimoTasksMeta_CommandBufferEntryType type;
+    FimoTasksMeta_CommandBufferEntryPayload payload;
+} FimoTasksMeta_CommandBufferEntry;
+
+/* command_buffer.h:99-122 */
+struct FimoTasksMeta_CommandBuffer {
+    const char *label;
+    FimoUSize label_len;
+    const FimoTasksMeta_CommandBufferEntry *entries;
+    FimoUSize entries_len;
+    void (*on_complete)(FimoTasksMeta_CommandBuffer *buffer);
+    void (*on_abort)(FimoTasksMeta_CommandBuffer *buffer);
+    void (*on_deinit)(FimoTasksMeta_CommandBuffer *buffer);
+};
+
+/* pool.h:71-106 */
+typedef struct FimoTasksMeta_PoolConfigStackConfig {
+    const void *next;
+    FimoTasksMeta_PoolStackSize size;
+    FimoUSize preallocated_count;
+    FimoUSize cold_count;
+    FimoUSize hot_count;
+    FimoUSize max_allocated;
+} FimoTasksMeta_PoolConfigStackConfig;
+
+typedef struct FimoTasksMeta_PoolConfig {
+    const void *next;
+    const char *label;
+    FimoUSize label_len;
+    const FimoTasksMeta_PoolConfigStackConfig *stacks;
+    FimoUSize stacks_len;
+    FimoUSize default_stack_index;
+    FimoUSize worker_count; /* 0 = number of CPUs (FimoTasks.zig:127-132) */
+    bool is_queryable;
+} FimoTasksMeta_PoolConfig;
+
+/* futex.h:14-19 */
+typedef FimoI32 FimoTasksMeta_FutexStatus;
+enum {
+    FIMO_TASKS_META_FUTEX_STATUS_OK = 0,
+    FIMO_TASKS_META_FUTEX_STATUS_INVALID = 1,
+    FIMO_TASKS_META_FUTEX_STATUS_TIMEOUT = 2,
+    FIMO_TASKS_META_FUTEX_STATUS_KEY_ERROR = 3,
+};
+
+/* futex.h:22-27 */
+typedef struct FimoTasksMeta_FutexKeyExpect {
+    const void *key;
+    FimoUSize key_size;
+    FimoU64 expect;
+    FimoUSize token;
+} FimoTasksMeta_FutexKeyExpect;
+
+/* futex.h:46-119: op = token_op | token_type<<1 | cmp_op<<3 | cmp_arg_op<<6 */
+typedef struct FimoTasksMeta_FutexFilter {
+    FimoUSize op;
+    FimoUSize token_mask;
+    FimoUSize cmp_arg;
+} FimoTasksMeta_FutexFilter;
+
+enum { FIMO_TASKS_META_FUTEX_FILTER_TOKEN_OP_NOOP = 0, FIMO_TASKS_META_FUTEX_FILTER_TOKEN_OP_DEREF = 1 };
+enum {
+    FIMO_TASKS_META_FUTEX_FILTER_TOKEN_TYPE_U8 = 0,
+    FIMO_TASKS_META_FUTEX_FILTER_TOKEN_TYPE_U16 = 1,
+    FIMO_TASKS_META_FUTEX_FILTER_TOKEN_TYPE_U32 = 2,
+    FIMO_TASKS_META_FUTEX_FILTER_TOKEN_TYPE_U64 = 3,
+};
+enum {
+    FIMO_TASKS_META_FUTEX_FILTER_CMP_OP_EQ = 0,
+    FIMO_TASKS_META_FUTEX_FILTER_CMP_OP_NE = 1,
+    FIMO_TASKS_META_FUTEX_FILTER_CMP_OP_LT = 2,
+    FIMO_TASKS_META_FUTEX_FILTER_CMP_OP_LE = 3,
+    FIMO_TASKS_META_FUTEX_FILTER_CMP_OP_GT = 4,
+    FIMO_TASKS_META_FUTEX_FILTER_CMP_OP_GE = 5,
+};
+enum { FIMO_TASKS_META_FUTEX_FILTER_CMP_ARG_OP_NOOP = 0, FIMO_TASKS_META_FUTEX_FILTER_CMP_ARG_OP_DEREF = 1 };
+
+static inline FimoUSize FimoTasksMeta_futex_filter_op_init(FimoUSize token_op, FimoUSize token_type, FimoUSize cmp_op,
+                                                           FimoUSize cmp_arg_op) {
+    return (token_op & 1u) | ((token_type & 3u) << 1) | ((cmp_op & 7u) << 3) | ((cmp_arg_op & 1u) << 6);
+}
+
+/* The two `fimo-tasks` futex symbols the path imports (pkgs/fimo_tasks_meta/src/symbols.zig:132-160). */
+typedef FimoTasksMeta_FutexStatus (*FimoTasksMeta_futex_wait)(const void *key, FimoUSize key_size, FimoU64 expect,
+                                                              FimoUSize token, const FimoInstant *timeout);
+typedef FimoUSize (*FimoTasksMeta_futex_wake)(const void *key, FimoUSize max_waiters, FimoTasksMeta_FutexFilter filter);
+
+/* ------------------------------------------------------------------------- */
+/* fimo_worlds_meta mirrors                                                   */
+/* ------------------------------------------------------------------------- */
+
+typedef struct FimoWorldsMeta_World FimoWorldsMeta_World;
+typedef struct FimoWorldsMeta_Resource *FimoWorldsMeta_ResourceHandle;
+typedef struct FimoWorldsMeta_System *FimoWorldsMeta_SystemHandle;
+typedef struct FimoWorldsMeta_SystemGroup FimoWorldsMeta_SystemGroup;
+typedef struct FimoWorldsMeta_SystemContext FimoWorldsMeta_SystemContext;
+
+/* jobs.h:15-21; Zig: pkgs/fimo_worlds_meta/src/Job.zig:20-26.
+ * One atomic byte: bit0 = signaled, bit1 = contended (a waiter is parked). */
+typedef struct FimoWorldsMeta_Fence {
+    FimoU8 state; /* accessed with __atomic builtins only */
+} FimoWorldsMeta_Fence;
+#define FIMO_WORLDS_META_FENCE_UNSIGNALED ((FimoU8)0)
+#define FIMO_WORLDS_META_FENCE_SIGNALED ((FimoU8)1)
+#define FIMO_WORLDS_META_FENCE_CONTENDED ((FimoU8)2)
+
+/* jobs.h:74-76; Job.zig:66-70 — monotonically increasing u64 counter. */
+typedef struct FimoWorldsMeta_TimelineSemaphore {
+    FimoU64 state; /* accessed with __atomic builtins only */
+} FimoWorldsMeta_TimelineSemaphore;
+
+/* jobs.h:24-71 restated with GCC atomics (the reference's C inline versions do not
+ * compile: jobs.h:42 passes &fence->state as a Fence*, jobs.h:47 passes a value as
+ * the `expected` pointer).  Semantics follow Job.zig:28-63. */
+static inline void FimoWorldsMeta_fence_init(FimoWorldsMeta_Fence *fence) {
+    __atomic_store_n(&fence->state, FIMO_WORLDS_META_FENCE_UNSIGNALED, __ATOMIC_RELAXED);
+}
+static inline bool FimoWorldsMeta_fence_is_signaled(const FimoWorldsMeta_Fence *fence) {
+    return (__atomic_load_n(&fence->state, __ATOMIC_ACQUIRE) & FIMO_WORLDS_META_FENCE_SIGNALED) != 0;
+}
+static inline void FimoWorldsMeta_fence_wait(FimoWorldsMeta_Fence *fence, FimoTasksMeta_futex_wait futex_wait) {
+    for (;;) {
+        FimoU8 state = __atomic_load_n(&fence->state, __ATOMIC_RELAXED);
+        if ((state & FIMO_WORLDS_META_FENCE_SIGNALED) != 0) {
+            if (FimoWorldsMeta_fence_is_signaled(fence)) return;
+        }
+        if ((state & FIMO_WORLDS_META_FENCE_CONTENDED) == 0) {
+            FimoU8 expected = FIMO_WORLDS_META_FENCE_UNSIGNALED;
+            if (!__atomic_compare_exchange_n(&fence->state, &expected, FIMO_WORLDS_META_FENCE_CONTENDED, true,
+                                             __ATOMIC_RELAXED, __ATOMIC_RELAXED))
+                continue;
+        }
+        futex_wait(&fence->state, sizeof(FimoU8), FIMO_WORLDS_META_FENCE_CONTENDED, 0, NULL);
+    }
+}
+static inline void FimoWorldsMeta_fence_signal(FimoWorldsMeta_Fence *fence, FimoTasksMeta_futex_wake futex_wake) {
+    const FimoU8 state = __atomic_exchange_n(&fence->state, FIMO_WORLDS_META_FENCE_SIGNALED, __ATOMIC_RELEASE);
+    if ((state & FIMO_WORLDS_META_FENCE_CONTENDED) != 0) {
+        FimoTasksMeta_FutexFilter all = {0, 0, 0}; /* FIMO_TASKS_META_FUTEX_FILTER_ALL */
+        futex_wake(&fence->state, ~(FimoUSize)0, all);
+    }
+}
+static inline void FimoWorldsMeta_fence_reset(FimoWorldsMeta_Fence *fence) {
+    (void)__atomic_fetch_and(&fence->state, (FimoU8)~FIMO_WORLDS_META_FENCE_SIGNALED, __ATOMIC_RELEASE);
+}
+
+/* jobs.h:79-144; Job.zig:72-173 */
+static inline void FimoWorldsMeta_timeline_semaphore_init(FimoWorldsMeta_TimelineSemaphore *s, FimoU64 value) {
+    __atomic_store_n(&s->state, value, __ATOMIC_RELAXED);
+}
+static inline FimoU64 FimoWorldsMeta_timeline_semaphore_counter(const FimoWorldsMeta_TimelineSemaphore *s) {
+    return __atomic_load_n(&s->state, __ATOMIC_ACQUIRE);
+}
+static inline bool FimoWorldsMeta_timeline_semaphore_is_signaled(const FimoWorldsMeta_TimelineSemaphore *s,
+                                                                 FimoU64 value) {
+    return __atomic_load_n(&s->state, __ATOMIC_ACQUIRE) >= value;
+}
+static inline void FimoWorldsMeta_timeline_semaphore_wait(const FimoWorldsMeta_TimelineSemaphore *s, FimoU64 value,
+                                                          FimoTasksMeta_futex_wait futex_wait) {
+    if (FimoWorldsMeta_timeline_semaphore_is_signaled(s, value)) return;
+    for (;;) {
+        const FimoU64 state = __atomic_load_n(&s->state, __ATOMIC_RELAXED);
+        if (state >= value) {
+            (void)__atomic_load_n(&s->state, __ATOMIC_ACQUIRE);
+            return;
+        }
+        futex_wait(&s->state, sizeof(FimoU64), state, (FimoUSize)value, NULL);
+    }
+}
+static inline void FimoWorldsMeta_timeline_semaphore_signal(FimoWorldsMeta_TimelineSemaphore *s, FimoU64 value,
+                                                            FimoTasksMeta_futex_wake futex_wake) {
+    __atomic_store_n(&s->state, value, __ATOMIC_RELEASE);
+    FimoTasksMeta_FutexFilter filter;
+    filter.token_mask = ~(FimoUSize)0;
+    filter.op = FimoTasksMeta_futex_filter_op_init(
+            FIMO_TASKS_META_FUTEX_FILTER_TOKEN_OP_NOOP, FIMO_TASKS_META_FUTEX_FILTER_TOKEN_TYPE_U64,
+            FIMO_TASKS_META_FUTEX_FILTER_CMP_OP_LE, FIMO_TASKS_META_FUTEX_FILTER_CMP_ARG_OP_NOOP);
+    filter.cmp_arg = (FimoUSize)value;
+    futex_wake(&s->state, ~(FimoUSize)0, filter);
+}
+
+/* resources.h:16-27 */
+typedef struct FimoWorldsMeta_ResourceDescriptor {
+    const void *next; /* reference: reserved, ignored (FimoWorlds.zig:108-122). Here: FimoB200_ResourceDeviceExt chain. */
+    const char *label;
+    FimoUSize label_len;
+    FimoUSize size;
+    FimoUSize alignment;
+} FimoWorldsMeta_ResourceDescriptor;
+
+/* systems.h:28-48 */
+typedef FimoUSize FimoWorldsMeta_SystemDependencyFlags;
+#define FIMO_WORLDS_META_SYSTEM_DEPENDENCY_FLAGS_WEAK ((FimoUSize)1)
+#define FIMO_WORLDS_META_SYSTEM_DEPENDENCY_FLAGS_IGNORE_DEFERRED ((FimoUSize)2)
+typedef struct FimoWorldsMeta_SystemDependency {
+    FimoWorldsMeta_SystemHandle system;
+    FimoWorldsMeta_SystemDependencyFlags flags;
+} FimoWorldsMeta_SystemDependency;
+
+/* systems.h:51-114.  NOTE the naming (Universe.zig:195-219, SystemGroup.zig:225-232):
+ * `before` = systems that run BEFORE this one (this system depends on them);
+ * `after`  = systems that run AFTER this one. */
+typedef struct FimoWorldsMeta_SystemDescriptor {
+    const void *next; /* reference: reserved. Here: FimoB200_SystemDeviceExt chain. */
+    const char *label;
+    FimoUSize label_len;
+    const FimoWorldsMeta_ResourceHandle *exclusive_handles;
+    FimoUSize exclusive_handles_len;
+    const FimoWorldsMeta_ResourceHandle *shared_handles;
+    FimoUSize shared_handles_len;
+    const FimoWorldsMeta_SystemDependency *before;
+    FimoUSize before_len;
+    const FimoWorldsMeta_SystemDependency *after;
+    FimoUSize after_len;
+    const void *factory;
+    FimoUSize factory_size;
+    FimoUSize factory_alignment;
+    void (*factory_destroy)(const void *factory);
+    FimoUSize system_size;
+    FimoUSize system_alignment;
+    bool (*system_create)(const void *factory, FimoWorldsMeta_SystemContext *context, void *system);
+    void (*system_destroy)(void *system);
+    void (*system_run)(void *system, void *const *exclusive_resources, void *const *shared_resources,
+                       FimoWorldsMeta_Fence *fence);
+} FimoWorldsMeta_SystemDescriptor;
+
+/* systems.h:117-131 */
+typedef struct FimoWorldsMeta_SystemGroupDescriptor {
+    const void *next;
+    const char *label;
+    FimoUSize label_len;
+    const FimoTasksMeta_Pool *pool;
+    FimoWorldsMeta_World *world;
+} FimoWorldsMeta_SystemGroupDescriptor;
+
+/* systems.h:134-155 */
+typedef FimoI32 FimoWorldsMeta_SystemAllocatorStrategy;
+enum {
+    FIMO_WORLDS_META_SYSTEM_ALLOCATOR_STRATEGY_TRANSIENT = 0,
+    FIMO_WORLDS_META_SYSTEM_ALLOCATOR_STRATEGY_SINGLE_GENERATION = 1,
+    FIMO_WORLDS_META_SYSTEM_ALLOCATOR_STRATEGY_MULTI_GENERATION = 2,
+    FIMO_WORLDS_META_SYSTEM_ALLOCATOR_STRATEGY_SYSTEM_PERSISTENT = 3,
+};
+
+/* worlds.h:20-32 */
+typedef struct FimoWorldsMeta_WorldDescriptor {
+    const void *next; /* reference: reserved. Here: FimoB200_WorldBatchExt chain. */
+    const char *label;
+    FimoUSize label_len;
+    const FimoTasksMeta_Pool *pool;
+} FimoWorldsMeta_WorldDescriptor;
+
+/* ------------------------------------------------------------------------- */
+/* B200 device extension structs (new; ABI-preserving)                        */
+/*                                                                            */
+/* The reference reserves a Vulkan-style `next` pointer on every descriptor   */
+/* and never reads it (FimoWorlds.zig:108-168), so the same descriptors stay  */
+/* valid on the reference's CPU path and on the oracle.  This library walks   */
+/* the chain and picks out the structs below by `s_type`.                     */
+/* ------------------------------------------------------------------------- */
+
+#define FIMO_B200_STYPE_WORLD_BATCH 0xB2000001u
+#define FIMO_B200_STYPE_RESOURCE_DEVICE 0xB2000002u
+#define FIMO_B200_STYPE_SYSTEM_DEVICE 0xB2000003u
+#define FIMO_B200_STYPE_GROUP_DEVICE 0xB2000004u
+
+typedef struct FimoB200_ExtHeader {
+    uint32_t s_type;
+    uint32_t reserved;
+    const void *next;
+} FimoB200_ExtHeader;
+
+/* WorldDescriptor.next: one `World` handle stands for `n_worlds` independent
+ * worlds of `entities_per_world` entities each, resident on CUDA device `device`.
+ * Without this struct a world is a batch of one world with zero entities. */
+typedef struct FimoB200_WorldBatchExt {
+    FimoB200_ExtHeader header;
+    uint64_t n_worlds;
+    uint64_t entities_per_world;
+    int32_t device; /* CUDA ordinal; -1 = current device */
+    uint32_t flags;
+} FimoB200_WorldBatchExt;
+
+/* How many elements of a device resource one world owns. */
+enum {
+    FIMO_B200_SCOPE_ENTITY = 0,      /* count = entities_per_world */
+    FIMO_B200_SCOPE_WORLD = 1,       /* count = 1 (per-world constants: frustum, dt, counters) */
+    FIMO_B200_SCOPE_ENTITY_BITS = 2, /* count = ceil(entities_per_world / 32) u32 words (bit masks) */
+    FIMO_B200_SCOPE_BATCH = 3,       /* count = 1 and a single instance for the whole batch (statistics) */
+};
+
+/* ResourceDescriptor.next: the resource is an SoA HBM buffer.  The registered
+ * `size` must be sizeof(FimoB200_ResourceView): the host-visible blob of a device
+ * resource is a fixed-size view, the data lives in HBM. */
+typedef struct FimoB200_ResourceDeviceExt {
+    FimoB200_ExtHeader header;
+    uint32_t scope;      /* FIMO_B200_SCOPE_* */
+    uint32_t components; /* 4-byte words per element: pos 3, rot 4, world 12, frustum 24 ... */
+    uint32_t elem_bytes; /* must be 4 */
+    uint32_t flags;
+} FimoB200_ResourceDeviceExt;
+
+/* The blob of a device resource.  Layout of the data, on host and device alike:
+ * dense 4-byte words [n_worlds][components][count] (world-major, then component
+ * plane, then element), i.e. comp_stride = 4*count, world_stride = 4*components*count.
+ *
+ * world_add_resource(world, handle, &view):   in: host_ptr = initial contents or NULL (zero-fill);
+ *                                             device_ptr = NULL (library allocates) or external HBM to adopt.
+ * world_lock_resources(...) -> FimoB200_ResourceView*: all fields valid, device idle for this resource.
+ * world_remove_resource(world, handle, &view): in: view.host_ptr = destination for a final D2H copy or NULL;
+ *                                             out: the view (device_ptr is dangling unless external).
+ * On the CPU path (reference / oracle) `host_ptr` IS the data and n_worlds == 1. */
+typedef struct FimoB200_ResourceView {
+    void *device_ptr;
+    void *host_ptr;
+    uint64_t n_worlds;
+    uint64_t count;
+    uint32_t components;
+    uint32_t elem_bytes;
+    uint64_t comp_stride;
+    uint64_t world_stride;
+    uint32_t scope;
+    uint32_t flags; /* bit0: device_ptr is external (not owned) */
+} FimoB200_ResourceView;
+#define FIMO_B200_VIEW_FLAG_EXTERNAL 1u
+
+typedef struct FimoB200_LaunchInfo {
+    void *stream; /* cudaStream_t to launch on */
+    uint64_t n_worlds;
+    uint64_t entities_per_world;
+    int32_t device;
+    uint32_t flags; /* bit0: stream is being captured into a CUDA graph (no syncs, no allocations) */
+    uint64_t reserved;
+} FimoB200_LaunchInfo;
+#define FIMO_B200_LAUNCH_FLAG_CAPTURING 1u
+
+/* Device entry point of a system: enqueue the system's kernels for ALL worlds of the
+ * batch on `info->stream`.  Same argument meaning and order as `system_run`
+ * (systems.h:103-113), with resource views instead of blob pointers and the
+ * stream taking the place of the deferred fence (stream order == completion). */
+typedef FimoStatus (*FimoB200_device_entry)(void *system, const FimoB200_ResourceView *const *exclusive_resources,
+                                            const FimoB200_ResourceView *const *shared_resources,
+                                            const FimoB200_LaunchInfo *info);
+
+/* Built-in synthetic systems.  A non-zero id lets the DAG
+ * compiler fuse neighbouring built-ins into one world-step kernel. */
+enum {
+    FIMO_B200_BUILTIN_NONE = 0,
+    FIMO_B200_BUILTIN_INTEGRATE = 1, /* X: pos            S: vel, dt */
+    FIMO_B200_BUILTIN_PROPAGATE = 2, /* X: world          S: pos, rot, scale, parent, level_start */
+    FIMO_B200_BUILTIN_CULL = 3,      /* X: vis_mask, vis_list, vis_count, stats   S: world, aabb_c, aabb_h, frustum */
+    FIMO_B200_BUILTIN_COUNT_
+};
+
+/* SystemDescriptor.next: the system runs on the device. `system_run` must still be
+ * non-null (ABI); this library never calls it for a device system. */
+typedef struct FimoB200_SystemDeviceExt {
+    FimoB200_ExtHeader header;
+    FimoB200_device_entry device_entry;
+    uint32_t builtin_id; /* FIMO_B200_BUILTIN_* */
+    uint32_t flags;
+} FimoB200_SystemDeviceExt;
+
+/* SystemGroupDescriptor.next: executor options. */
+typedef void (*FimoB200_post_step)(void *user, void *stream, uint64_t generation);
+typedef struct FimoB200_GroupDeviceExt {
+    FimoB200_ExtHeader header;
+    uint32_t flags;
+    uint32_t reserved;
+    /* Called on the launcher thread right after generation `generation` was enqueued on
+     * `stream` (e.g. to enqueue the end-of-step statistics allreduce). May be NULL. */
+    FimoB200_post_step post_step;
+    void *post_step_user;
+} FimoB200_GroupDeviceExt;
+#define FIMO_B200_GROUP_FLAG_NO_FUSION 1u /* one kernel per system (CUDA graph of the DAG) */
+#define FIMO_B200_GROUP_FLAG_NO_GRAPH 2u  /* plain stream launches, no CUDA graph */
+
+/* Statistics words written by BUILTIN_CULL into the `stats` resource (u64 each, 8 per batch). */
+enum {
+    FIMO_B200_STAT_VISIBLE = 0,  /* sum over worlds of vis_count, last step */
+    FIMO_B200_STAT_ENTITIES = 1, /* entities tested, last step */
+    FIMO_B200_STAT_MASK_SUM = 2, /* sum of all vis_mask words (as u64), last step */
+    FIMO_B200_STAT_WORLDS = 3,   /* worlds stepped, last step */
+    FIMO_B200_STAT_STEPS = 4,    /* world-steps accumulated since the resource was added (+1 per world per step) */
+    FIMO_B200_STAT_WORDS = 8
+};
+#define FIMO_B200_PARENT_ROOT 0xFFFFFFFFu
+
+/* ------------------------------------------------------------------------- */
+/* The 32 `fimo-worlds` entry points                                          */
+/* (pkgs/fimo_worlds_meta/src/symbols.zig:22-58 for the list, :60-365 for     */
+/*  the signatures; implementation shims modules/fimo_worlds/src/FimoWorlds.zig:108-447) */
+/* ------------------------------------------------------------------------- */
+
+/* symbols.zig:60-76   resources.h:32-39 */
+FIMO_B200_EXPORT FimoStatus fimo_worlds_resource_register(const FimoWorldsMeta_ResourceDescriptor *resource,
+                                                          FimoWorldsMeta_ResourceHandle *handle);
+FIMO_B200_EXPORT void fimo_worlds_resource_unregister(FimoWorldsMeta_ResourceHandle handle);
+
+/* symbols.zig:78-94   systems.h:160-167 */
+FIMO_B200_EXPORT FimoStatus fimo_worlds_system_register(const FimoWorldsMeta_SystemDescriptor *system,
+                                                        FimoWorldsMeta_SystemHandle *handle);
+FIMO_B200_EXPORT void fimo_worlds_system_unregister(FimoWorldsMeta_SystemHandle handle);
+
+/* symbols.zig:96-166   systems.h:170-223 */
+FIMO_B200_EXPORT FimoStatus fimo_worlds_system_group_create(const FimoWorldsMeta_SystemGroupDescriptor *descriptor,
+                                                            FimoWorldsMeta_SystemGroup **group);
+FIMO_B200_EXPORT void fimo_worlds_system_group_destroy(FimoWorldsMeta_SystemGroup *group);
+FIMO_B200_EXPORT FimoWorldsMeta_World *fimo_worlds_system_group_get_world(FimoWorldsMeta_SystemGroup *group);
+FIMO_B200_EXPORT const char *fimo_worlds_system_group_get_label(FimoWorldsMeta_SystemGroup *group, FimoUSize *len);
+FIMO_B200_EXPORT FimoTasksMeta_Pool fimo_worlds_system_group_get_pool(FimoWorldsMeta_SystemGroup *group);
+FIMO_B200_EXPORT FimoStatus fimo_worlds_system_group_add_systems(FimoWorldsMeta_SystemGroup *group,
+                                                                 const FimoWorldsMeta_SystemHandle *systems,
+                                                                 FimoUSize systems_len);
+FIMO_B200_EXPORT void fimo_worlds_system_group_remove_system(FimoWorldsMeta_SystemGroup *group,
+                                                             FimoWorldsMeta_SystemHandle handle,
+                                                             FimoWorldsMeta_Fence *signal);
+FIMO_B200_EXPORT FimoStatus fimo_worlds_system_group_schedule(FimoWorldsMeta_SystemGroup *group,
+                                                              FimoWorldsMeta_Fence *const *wait_on,
+                                                              FimoUSize wait_on_len, FimoWorldsMeta_Fence *signal);
+
+/* symbols.zig:168-235   systems.h:226-272 */
+FIMO_B200_EXPORT FimoWorldsMeta_SystemGroup *fimo_worlds_system_context_get_group(FimoWorldsMeta_SystemContext *context);
+FIMO_B200_EXPORT FimoUSize fimo_worlds_system_context_get_generation(FimoWorldsMeta_SystemContext *context);
+FIMO_B200_EXPORT void *fimo_worlds_system_context_allocator_alloc(FimoWorldsMeta_SystemContext *context,
+                                                                  FimoWorldsMeta_SystemAllocatorStrategy strategy,
+                                                                  FimoUSize size, FimoUSize alignment,
+                                                                  FimoUSize ret_addr);
+FIMO_B200_EXPORT bool fimo_worlds_system_context_allocator_resize(FimoWorldsMeta_SystemContext *context,
+                                                                  FimoWorldsMeta_SystemAllocatorStrategy strategy,
+                                                                  void *ptr, FimoUSize size, FimoUSize alignment,
+                                                                  FimoUSize new_size, FimoUSize ret_addr);
+FIMO_B200_EXPORT void *fimo_worlds_system_context_allocator_remap(FimoWorldsMeta_SystemContext *context,
+                                                                  FimoWorldsMeta_SystemAllocatorStrategy strategy,
+                                                                  void *ptr, FimoUSize size, FimoUSize alignment,
+                                                                  FimoUSize new_size, FimoUSize ret_addr);
+FIMO_B200_EXPORT void fimo_worlds_system_context_allocator_free(FimoWorldsMeta_SystemContext *context,
+                                                                FimoWorldsMeta_SystemAllocatorStrategy strategy,
+                                                                void *ptr, FimoUSize size, FimoUSize alignment,
+                                                                FimoUSize ret_addr);
+
+/* symbols.zig:237-365   worlds.h:35-118 */
+FIMO_B200_EXPORT FimoStatus fimo_worlds_world_create(const FimoWorldsMeta_WorldDescriptor *descriptor,
+                                                     FimoWorldsMeta_World **world);
+FIMO_B200_EXPORT void fimo_worlds_world_destroy(FimoWorldsMeta_World *world);
+FIMO_B200_EXPORT const char *fimo_worlds_world_get_label(FimoWorldsMeta_World *world, FimoUSize *len);
+FIMO_B200_EXPORT FimoTasksMeta_Pool fimo_worlds_world_get_pool(FimoWorldsMeta_World *world);
+FIMO_B200_EXPORT bool fimo_worlds_world_has_resource(FimoWorldsMeta_World *world, FimoWorldsMeta_ResourceHandle handle);
+FIMO_B200_EXPORT FimoStatus fimo_worlds_world_add_resource(FimoWorldsMeta_World *world,
+                                                           FimoWorldsMeta_ResourceHandle handle, const void *value);
+FIMO_B200_EXPORT FimoStatus fimo_worlds_world_remove_resource(FimoWorldsMeta_World *world,
+                                                              FimoWorldsMeta_ResourceHandle handle, void *value);
+FIMO_B200_EXPORT void fimo_worlds_world_lock_resources(FimoWorldsMeta_World *world,
+                                                       const FimoWorldsMeta_ResourceHandle *exclusive_handles,
+                                                       FimoUSize exclusive_handles_len,
+                                                       const FimoWorldsMeta_ResourceHandle *shared_handles,
+                                                       FimoUSize shared_handles_len, void **out_resources);
+FIMO_B200_EXPORT void fimo_worlds_world_unlock_resource_exclusive(FimoWorldsMeta_World *world,
+                                                                  FimoWorldsMeta_ResourceHandle handle);
+FIMO_B200_EXPORT void fimo_worlds_world_unlock_resource_shared(FimoWorldsMeta_World *world,
+                                                               FimoWorldsMeta_ResourceHandle handle);
+FIMO_B200_EXPORT void *fimo_worlds_world_allocator_alloc(FimoWorldsMeta_World *world, FimoUSize size,
+                                                         FimoUSize alignment, FimoUSize ret_addr);
+FIMO_B200_EXPORT bool fimo_worlds_world_allocator_resize(FimoWorldsMeta_World *world, void *ptr, FimoUSize size,
+                                                         FimoUSize alignment, FimoUSize new_size, FimoUSize ret_addr);
+FIMO_B200_EXPORT void *fimo_worlds_world_allocator_remap(FimoWorldsMeta_World *world, void *ptr, FimoUSize size,
+                                                         FimoUSize alignment, FimoUSize new_size, FimoUSize ret_addr);
+FIMO_B200_EXPORT void fimo_worlds_world_allocator_free(FimoWorldsMeta_World *world, void *ptr, FimoUSize size,
+                                                       FimoUSize alignment, FimoUSize ret_addr);
+
+/* ------------------------------------------------------------------------- */
+/* Module plumbing that the fimo loader provides in the reference             */
+/* ------------------------------------------------------------------------- */
+
+/* One row of the export table: what `fimo_exports` lists in FimoWorlds.zig:48-81. */
+typedef struct FimoB200_Export {
+    const char *name;       /* e.g. "system_group_schedule" */
+    const char *name_space; /* "fimo-worlds" (package.h:12) */
+    void (*function)(void);
+} FimoB200_Export;
+FIMO_B200_EXPORT const FimoB200_Export *fimo_worlds_b200_exports(FimoUSize *count);
+
+/* Name of the error behind the last FIMO_STATUS_ERROR on this thread
+ * ("NotFound", "Deadlock", "Duplicate", "InUse", "InitError", "OutOfMemory", ...).
+ * Stand-in for the thread-local context result (pkgs/fimo_std/src/ctx.zig:184-186). */
+FIMO_B200_EXPORT const char *fimo_worlds_b200_last_error(void);
+
+/* `fimo-tasks` futex symbols the path imports (symbols.zig:132-160).  The library
+ * ships a standalone parking-lot implementation; a host application that runs the
+ * real fimo_tasks module injects its own with `bind_tasks` so that fibers park
+ * through their pool. */
+FIMO_B200_EXPORT FimoTasksMeta_FutexStatus fimo_tasks_futex_wait(const void *key, FimoUSize key_size, FimoU64 expect,
+                                                                 FimoUSize token, const FimoInstant *timeout);
+FIMO_B200_EXPORT FimoUSize fimo_tasks_futex_wake(const void *key, FimoUSize max_waiters,
+                                                 FimoTasksMeta_FutexFilter filter);
+FIMO_B200_EXPORT void fimo_worlds_b200_bind_tasks(FimoTasksMeta_futex_wait futex_wait,
+                                                  FimoTasksMeta_futex_wake futex_wake);
+
+/* Fence helpers bound to the library's futex symbols (what Job.zig:33-62 does
+ * through `symbols.futex_*`). */
+FIMO_B200_EXPORT void fimo_worlds_b200_fence_wait(FimoWorldsMeta_Fence *fence);
+FIMO_B200_EXPORT void fimo_worlds_b200_fence_signal(FimoWorldsMeta_Fence *fence);
+
+/* `create_worker_pool` of fimo-tasks (symbols.zig:35-52, pool.h:145-148), Status-returning
+ * as in the Zig implementation.  Needed by worlds/groups that are given an explicit pool. */
+FIMO_B200_EXPORT FimoStatus fimo_tasks_create_worker_pool(const FimoTasksMeta_PoolConfig *config,
+                                                          FimoTasksMeta_Pool *pool);
+
+/* ------------------------------------------------------------------------- */
+/* Device-side helpers (product library only; absent from the CPU oracle)     */
+/* ------------------------------------------------------------------------- */
+
+/* Fills `desc` (system_size/alignment, create/destroy/run) and `ext` (device entry,
+ * builtin id) for a built-in synthetic system and chains `ext` on `desc->next`.
+ * The caller still fills label, resource handles and dependencies.  `system_run`
+ * is a stub that aborts: built-in systems exist on the device only (no CPU fallback). */
+FIMO_B200_EXPORT FimoStatus fimo_b200_builtin_system(uint32_t builtin_id, FimoWorldsMeta_SystemDescriptor *desc,
+                                                     FimoB200_SystemDeviceExt *ext);
+
+/* Synchronous copies between a locked device resource and dense host memory
+ * laid out as the view describes. */
+FIMO_B200_EXPORT FimoStatus fimo_b200_resource_upload(const FimoB200_ResourceView *view, const void *host_src);
+FIMO_B200_EXPORT FimoStatus fimo_b200_resource_download(const FimoB200_ResourceView *view, void *host_dst);
+
+/* What the DAG compiler produced for the group's current system set. */
+typedef struct FimoB200_ExecutorInfo {
+    uint32_t systems;          /* member systems */
+    uint32_t device_systems;   /* of which run on the device */
+    uint32_t nodes;            /* executor nodes after fusion */
+    uint32_t fused_world_step; /* 1 if integrate->propagate->cull was fused into one kernel */
+    uint32_t uses_cuda_graph;
+    uint32_t kernel_launches_per_generation;
+    uint64_t edges;                      /* dependency edges between nodes */
+    uint64_t algorithmic_bytes_per_step; /* live-in read once + live-out written once, 0 if unknown */
+    uint64_t reserved[4];
+} FimoB200_ExecutorInfo;
+FIMO_B200_EXPORT FimoStatus fimo_b200_group_executor_info(FimoWorldsMeta_SystemGroup *group,
+                                                          FimoB200_ExecutorInfo *info);
+
+/* The CUDA stream (cudaStream_t) generations of this group are enqueued on. */
+FIMO_B200_EXPORT void *fimo_b200_group_stream(FimoWorldsMeta_SystemGroup *group);
+
+/* Blocks until every scheduled generation of the group has finished on the device. */
+FIMO_B200_EXPORT void fimo_b200_group_wait_idle(FimoWorldsMeta_SystemGroup *group);
+
+/* Average device time of the group's last `n` generations in milliseconds, measured with
+ * CUDA events on the group's stream around each generation (0 if none recorded). */
+FIMO_B200_EXPORT double fimo_b200_group_device_ms(FimoWorldsMeta_SystemGroup *group, uint64_t *generations);
+
+/* ------------------------------------------------------------------------- */
+/* Layout pins (sizes measured with gcc on x86-64)       */
+/* ------------------------------------------------------------------------- */
+#ifdef __cplusplus
+#define FIMO_B200_STATIC_ASSERT(c, m) static_assert(c, m)
+#else
+#define FIMO_B200_STATIC_ASSERT(c, m) _Static_assert(c, m)
+#endif
+FIMO_B200_STATIC_ASSERT(sizeof(FimoWorldsMeta_SystemDescriptor) == 160, "SystemDescriptor");
+FIMO_B200_STATIC_ASSERT(sizeof(FimoWorldsMeta_ResourceDescriptor) == 40, "ResourceDescriptor");
+FIMO_B200_STATIC_ASSERT(sizeof(FimoWorldsMeta_SystemDependency) == 16, "SystemDependency");
+FIMO_B200_STATIC_ASSERT(sizeof(FimoWorldsMeta_SystemGroupDescriptor) == 40, "SystemGroupDescriptor");
+FIMO_B200_STATIC_ASSERT(sizeof(FimoWorldsMeta_WorldDescriptor) == 32, "WorldDescriptor");
+FIMO_B200_STATIC_ASSERT(sizeof(FimoWorldsMeta_Fence) == 1, "Fence");
+FIMO_B200_STATIC_ASSERT(sizeof(FimoWorldsMeta_TimelineSemaphore) == 8, "TimelineSemaphore");
+FIMO_B200_STATIC_ASSERT(sizeof(FimoTasksMeta_CommandBufferEntry) == 24, "CommandBufferEntry");
+FIMO_B200_STATIC_ASSERT(offsetof(FimoTasksMeta_CommandBufferEntry, payload) == 8, "CommandBufferEntry.payload");
+FIMO_B200_STATIC_ASSERT(sizeof(FimoTasksMeta_Task) == 48, "Task");
+FIMO_B200_STATIC_ASSERT(sizeof(FimoTasksMeta_CommandBuffer) == 56, "CommandBuffer");
+FIMO_B200_STATIC_ASSERT(sizeof(FimoTasksMeta_Pool) == 16, "Pool");
+FIMO_B200_STATIC_ASSERT(sizeof(FimoTasksMeta_PoolVTable) == 80, "PoolVTable");
+FIMO_B200_STATIC_ASSERT(sizeof(FimoTasksMeta_CommandBufferHandle) == 16, "Handle");
+FIMO_B200_STATIC_ASSERT(sizeof(FimoTasksMeta_CommandBufferHandleVTable) == 32, "HandleVTable");
+FIMO_B200_STATIC_ASSERT(sizeof(FimoTasksMeta_PoolConfig) == 64, "PoolConfig");
+FIMO_B200_STATIC_ASSERT(sizeof(FimoTasksMeta_PoolConfigStackConfig) == 48, "StackConfig");
+FIMO_B200_STATIC_ASSERT(sizeof(FimoTasksMeta_FutexFilter) == 24, "FutexFilter");
+FIMO_B200_STATIC_ASSERT(sizeof(FimoTasksMeta_FutexKeyExpect) == 32, "FutexKeyExpect");
+FIMO_B200_STATIC_ASSERT(sizeof(FimoStatus) == 4, "FimoStatus");
+FIMO_B200_STATIC_ASSERT(sizeof(FimoDuration) == 16 && sizeof(FimoInstant) == 16, "FimoDuration/Instant");
+FIMO_B200_STATIC_ASSERT(sizeof(FimoB200_ResourceView) == 64, "ResourceView");
+
+#ifdef __cplusplus
+}
+#endif
+
+#endif /* FIMO_WORLDS_B200_H */

@@ -1,0 +1,430 @@
+// oracle_pool.cpp — CPU restatement of the fimo_tasks dispatch path (TEST INFRASTRUCTURE ONLY).
+//
+// Follows the structure of modules/fimo_tasks/src:
+//   Pool.zig:275-294,660-765   one event-loop thread + N worker threads per pool; every command
+//                              buffer entry, completion and wake-up is processed on the event loop
+//   CommandBuffer.zig:150-201  in-order issue of entries; a blocked entry stalls all later entries
+//   CommandBuffer.zig:272-313  enqueue_task     :339-348 wait_on_barrier
+//   CommandBuffer.zig:390-411  wait_on_command_indirect (documented meaning, command_buffer.h:83-85;
+//                              NOT the double markStatus of SURVEY.md §5 quirk 1)
+//   CommandBuffer.zig:127-148,445-457  completeTask / progressCompleted
+//   Worker.zig:250-411         worker run loop (task fetch, run, report completion)
+// Difference from the reference, stated once: tasks run on OS threads, not on stackful fibers
+// (boost.context is an un-vendored network dependency, modules/fimo_tasks/build.zig.zon:8-11).
+// A task that blocks therefore blocks its thread; the pool compensates by keeping
+// `worker_count` runnable threads (pool_blocking_enter/exit), which is what a parked fiber
+// achieves in the reference.
+#include <deque>
+#include <memory>
+#include <string>
+#include <thread>
+#include <vector>
+
+#include "oracle_internal.h"
+
+namespace oracle {
+
+namespace {
+std::atomic<size_t> g_next_pool_id{1};
+thread_local Pool *t_pool = nullptr;      // pool owning this thread (worker or event loop)
+thread_local bool t_is_worker = false;    // true on worker threads only
+thread_local bool t_is_spare = false;     // compensation thread
+} // namespace
+
+struct RtBuffer;
+
+enum class EntryStatus : uint8_t { not_processed, running_task, running_buffer, processed };
+
+struct RtBuffer {
+    Pool *owner = nullptr;
+    FimoTasksMeta_CommandBuffer *buffer = nullptr;
+    std::vector<EntryStatus> status;
+    size_t entry_index = 0;     // next entry to issue
+    size_t completed_index = 0; // all entries below are processed
+    bool abort_on_error = false;
+    bool has_error = false;
+    bool in_process_list = false;
+    RtBuffer *parent = nullptr; // set for enqueue_command_buffer children
+    size_t parent_entry = 0;
+    std::vector<RtBuffer *> buffer_waiters; // buffers blocked in wait_on_command_buffer on us
+
+    std::atomic<size_t> refs{1};
+    std::mutex m; // guards `done` for Handle.waitOn
+    std::condition_variable cv;
+    int done = 0; // 0 running, 1 completed, 2 aborted
+};
+
+struct Msg {
+    enum Kind { enqueue, task_done, wake } kind;
+    RtBuffer *rb;
+    size_t entry;
+};
+
+struct WorkItem {
+    RtBuffer *rb;
+    size_t entry;
+    FimoTasksMeta_Task *task;
+};
+
+struct Pool {
+    size_t id;
+    std::string label;
+    size_t worker_count;
+    std::atomic<size_t> refs{1};
+    std::atomic<bool> closed{false};
+
+    // event loop mailbox (Pool.zig:386-401 IntrusiveMpsc + futex wake)
+    std::mutex mbox_m;
+    std::condition_variable mbox_cv;
+    std::deque<Msg> mbox;
+    size_t active_buffers = 0; // event-loop thread only
+    std::deque<RtBuffer *> process_list;
+
+    // global task queue (Pool.zig:417-430 SPMC)
+    std::mutex q_m;
+    std::condition_variable q_cv;
+    std::deque<WorkItem> queue;
+    bool stop_workers = false;
+    size_t runnable = 0;       // threads currently able to run tasks
+    size_t threads_total = 0;  // live worker + spare threads
+    std::vector<std::thread> threads;
+
+    std::thread event_thread;
+};
+
+static void post(Pool *p, Msg m) {
+    {
+        std::lock_guard<std::mutex> g(p->mbox_m);
+        p->mbox.push_back(m);
+    }
+    p->mbox_cv.notify_one();
+}
+
+static void rb_unref(RtBuffer *rb) {
+    if (rb->refs.fetch_sub(1, std::memory_order_acq_rel) == 1) delete rb;
+}
+
+// ---- worker threads (Worker.zig:250-411) ---------------------------------------
+static void worker_main(Pool *p, bool spare) {
+    t_pool = p;
+    t_is_worker = true;
+    t_is_spare = spare;
+    std::unique_lock<std::mutex> g(p->q_m);
+    for (;;) {
+        // A compensation thread retires as soon as the pool is back at its thread budget.
+        if (spare && p->runnable > p->worker_count) break;
+        if (p->queue.empty()) {
+            if (p->stop_workers) break;
+            p->q_cv.wait(g);
+            continue;
+        }
+        WorkItem w = p->queue.front();
+        p->queue.pop_front();
+        g.unlock();
+        // Task.zig:56-67 / Worker.taskEntry: run the task body, then its completion hooks.
+        w.task->on_start(w.task);
+        if (w.task->on_complete) w.task->on_complete(w.task);
+        if (w.task->on_deinit) w.task->on_deinit(w.task);
+        post(p, Msg{Msg::task_done, w.rb, w.entry}); // Worker.zig:306-321 "complete" message
+        g.lock();
+    }
+    p->runnable--;
+    p->threads_total--;
+}
+
+void pool_blocking_enter() {
+    Pool *p = t_pool;
+    if (!p || !t_is_worker) return;
+    std::lock_guard<std::mutex> g(p->q_m);
+    p->runnable--;
+    if (p->runnable < p->worker_count && !p->stop_workers) {
+        p->runnable++;
+        p->threads_total++;
+        std::thread(worker_main, p, true).detach();
+    }
+}
+
+void pool_blocking_exit() {
+    Pool *p = t_pool;
+    if (!p || !t_is_worker) return;
+    std::lock_guard<std::mutex> g(p->q_m);
+    p->runnable++;
+    p->q_cv.notify_all(); // lets a spare notice it is over budget and retire
+}
+
+// ---- command buffer interpreter (event-loop thread only) ------------------------
+static void enqueue_process(Pool *p, RtBuffer *rb) {
+    if (rb->in_process_list || rb->done) return;
+    rb->in_process_list = true;
+    p->process_list.push_back(rb);
+}
+
+static void progress_completed(RtBuffer *rb) {
+    // CommandBuffer.zig:445-457
+    while (rb->completed_index < rb->entry_index && rb->status[rb->completed_index] == EntryStatus::processed)
+        rb->completed_index++;
+}
+
+static void finish_buffer(Pool *p, RtBuffer *rb);
+
+static void complete_entry(Pool *p, RtBuffer *rb, size_t entry) {
+    rb->status[entry] = EntryStatus::processed;
+    progress_completed(rb);
+    enqueue_process(p, rb);
+}
+
+// Returns false if the buffer is blocked (error.Block in the reference).
+static bool process_buffer(Pool *p, RtBuffer *rb) {
+    const FimoTasksMeta_CommandBuffer *cb = rb->buffer;
+    while (rb->entry_index < cb->entries_len) {
+        const size_t idx = rb->entry_index;
+        const FimoTasksMeta_CommandBufferEntry &e = cb->entries[idx];
+        switch (e.type) {
+            case FIMO_TASKS_META_COMMAND_BUFFER_ENTRY_TYPE_ABORT_ON_ERROR:
+                rb->abort_on_error = e.payload.abort_on_error;
+                rb->status[idx] = EntryStatus::processed;
+                break;
+            case FIMO_TASKS_META_COMMAND_BUFFER_ENTRY_TYPE_SET_MIN_STACK_SIZE:
+            case FIMO_TASKS_META_COMMAND_BUFFER_ENTRY_TYPE_SELECT_WORKER:
+            case FIMO_TASKS_META_COMMAND_BUFFER_ENTRY_TYPE_SELECT_ANY_WORKER:
+                // Stack sizes and worker pinning have no meaning for OS-thread tasks.
+                rb->status[idx] = EntryStatus::processed;
+                break;
+            case FIMO_TASKS_META_COMMAND_BUFFER_ENTRY_TYPE_ENQUEUE_TASK: {
+                rb->status[idx] = EntryStatus::running_task;
+                {
+                    std::lock_guard<std::mutex> g(p->q_m);
+                    p->queue.push_back(WorkItem{rb, idx, e.payload.enqueue_task});
+                }
+                p->q_cv.notify_one();
+                break;
+            }
+            case FIMO_TASKS_META_COMMAND_BUFFER_ENTRY_TYPE_ENQUEUE_COMMAND_BUFFER: {
+                RtBuffer *child = new RtBuffer();
+                child->owner = p;
+                child->buffer = e.payload.enqueue_command_buffer;
+                child->status.assign(child->buffer->entries_len, EntryStatus::not_processed);
+                child->parent = rb;
+                child->parent_entry = idx;
+                rb->status[idx] = EntryStatus::running_buffer;
+                p->active_buffers++;
+                enqueue_process(p, child);
+                break;
+            }
+            case FIMO_TASKS_META_COMMAND_BUFFER_ENTRY_TYPE_WAIT_ON_BARRIER:
+                progress_completed(rb);
+                if (rb->completed_index != idx) return false;
+                rb->status[idx] = EntryStatus::processed;
+                break;
+            case FIMO_TASKS_META_COMMAND_BUFFER_ENTRY_TYPE_WAIT_ON_COMMAND_BUFFER: {
+                RtBuffer *other = (RtBuffer *)e.payload.wait_on_command_buffer.data;
+                bool other_done;
+                {
+                    std::lock_guard<std::mutex> g(other->m);
+                    other_done = other->done != 0;
+                }
+                if (!other_done) {
+                    if (other->owner != p) panic("wait_on_command_buffer across pools is not restated");
+                    other->buffer_waiters.push_back(rb);
+                    return false;
+                }
+                rb->status[idx] = EntryStatus::processed;
+                break;
+            }
+            case FIMO_TASKS_META_COMMAND_BUFFER_ENTRY_TYPE_WAIT_ON_COMMAND_INDIRECT: {
+                const size_t k = e.payload.wait_on_command_indirect;
+                if (k == 0 || k > idx) panic("wait_on_command_indirect out of range");
+                if (rb->status[idx - k] != EntryStatus::processed) return false; // error.Block
+                rb->status[idx] = EntryStatus::processed;
+                break;
+            }
+            default: panic("unknown command buffer entry");
+        }
+        rb->entry_index++;
+    }
+    progress_completed(rb);
+    if (rb->completed_index != rb->entry_index) return false; // CommandBuffer.zig:190-194
+    finish_buffer(p, rb);
+    return true;
+}
+
+static void finish_buffer(Pool *p, RtBuffer *rb) {
+    // CommandBuffer.zig:196-200: complete/abort, broadcast to waiters, drop the pool's reference.
+    FimoTasksMeta_CommandBuffer *cb = rb->buffer;
+    RtBuffer *parent = rb->parent;
+    const size_t parent_entry = rb->parent_entry;
+    std::vector<RtBuffer *> waiters;
+    waiters.swap(rb->buffer_waiters);
+    const bool err = rb->has_error;
+    if (err) {
+        if (cb->on_abort) cb->on_abort(cb);
+    } else {
+        if (cb->on_complete) cb->on_complete(cb);
+    }
+    auto on_deinit = cb->on_deinit;
+    {
+        std::lock_guard<std::mutex> g(rb->m);
+        rb->done = err ? 2 : 1;
+    }
+    rb->cv.notify_all();
+    if (on_deinit) on_deinit(cb);
+    for (RtBuffer *w : waiters) enqueue_process(p, w);
+    if (parent) complete_entry(p, parent, parent_entry);
+    p->active_buffers--;
+    rb_unref(rb);
+}
+
+// ---- event loop (Pool.zig:660-765) ----------------------------------------------
+static void event_loop(Pool *p) {
+    t_pool = p;
+    for (;;) {
+        std::deque<Msg> batch;
+        {
+            std::unique_lock<std::mutex> g(p->mbox_m);
+            p->mbox_cv.wait(g, [&] {
+                return !p->mbox.empty() || (p->closed.load() && p->refs.load() == 0 && p->active_buffers == 0);
+            });
+            batch.swap(p->mbox);
+        }
+        if (batch.empty()) break; // closed, unreferenced and drained
+        for (const Msg &m : batch) {
+            switch (m.kind) {
+                case Msg::enqueue:
+                    p->active_buffers++;
+                    enqueue_process(p, m.rb);
+                    break;
+                case Msg::task_done: complete_entry(p, m.rb, m.entry); break;
+                case Msg::wake: break;
+            }
+        }
+        while (!p->process_list.empty()) {
+            RtBuffer *rb = p->process_list.front();
+            p->process_list.pop_front();
+            rb->in_process_list = false;
+            process_buffer(p, rb);
+        }
+    }
+    // shut down workers
+    {
+        std::lock_guard<std::mutex> g(p->q_m);
+        p->stop_workers = true;
+    }
+    p->q_cv.notify_all();
+    for (auto &t : p->threads) t.join();
+    // wait for detached compensation threads to retire
+    for (;;) {
+        {
+            std::lock_guard<std::mutex> g(p->q_m);
+            if (p->threads_total == 0) break;
+        }
+        p->q_cv.notify_all();
+        std::this_thread::yield();
+    }
+    delete p;
+}
+
+// ---- vtables ----------------------------------------------------------------------
+static FimoTasksMeta_PoolId vt_id(void *d) { return ((Pool *)d)->id; }
+static void vt_acquire(void *d) { ((Pool *)d)->refs.fetch_add(1, std::memory_order_relaxed); }
+static void vt_release(void *d) {
+    Pool *p = (Pool *)d;
+    if (p->refs.fetch_sub(1, std::memory_order_acq_rel) == 1) {
+        p->closed.store(true);
+        post(p, Msg{Msg::wake, nullptr, 0});
+    }
+}
+static void vt_request_close(void *d) { ((Pool *)d)->closed.store(true); }
+static bool vt_accepts_requests(void *d) { return !((Pool *)d)->closed.load(); }
+static bool vt_owns_current_thread(void *d) { return t_pool == (Pool *)d; }
+static const char *vt_label(void *d, FimoUSize *len) {
+    Pool *p = (Pool *)d;
+    *len = p->label.size();
+    return p->label.data();
+}
+static FimoUSize vt_workers(void *d, FimoTasksMeta_PoolWorker *ptr, FimoUSize len) {
+    Pool *p = (Pool *)d;
+    for (size_t i = 0; ptr && i < len && i < p->worker_count; i++) ptr[i] = i;
+    return p->worker_count;
+}
+static FimoUSize vt_stack_sizes(void *, FimoTasksMeta_PoolStackSize *ptr, FimoUSize len) {
+    if (ptr && len > 0) ptr[0] = 8u << 20; // FimoTasks.zig:32 default_stack_size = 8 MiB
+    return 1;
+}
+
+static void h_acquire(void *d) { ((RtBuffer *)d)->refs.fetch_add(1, std::memory_order_relaxed); }
+static void h_release(void *d) { rb_unref((RtBuffer *)d); }
+static FimoTasksMeta_Pool h_owner_pool(void *d) {
+    Pool *p = ((RtBuffer *)d)->owner;
+    vt_acquire(p);
+    return pool_handle(p);
+}
+static FimoTasksMeta_CommandBufferHandleCompletionStatus h_wait_on(void *d) {
+    // CommandBuffer.zig:603-631
+    RtBuffer *rb = (RtBuffer *)d;
+    std::unique_lock<std::mutex> g(rb->m);
+    if (!rb->done) {
+        pool_blocking_enter();
+        rb->cv.wait(g, [&] { return rb->done != 0; });
+        g.unlock();
+        pool_blocking_exit();
+        g.lock();
+    }
+    return rb->done == 1 ? FIMO_TASKS_META_COMMAND_BUFFER_HANDLE_COMPLETION_STATUS_COMPLETED
+                         : FIMO_TASKS_META_COMMAND_BUFFER_HANDLE_COMPLETION_STATUS_ABORTED;
+}
+static const FimoTasksMeta_CommandBufferHandleVTable g_handle_vtable = {h_acquire, h_release, h_owner_pool, h_wait_on};
+
+static FimoStatus vt_enqueue_buffer(void *d, FimoTasksMeta_CommandBuffer *buffer,
+                                    FimoTasksMeta_CommandBufferHandle *handle) {
+    // Pool.zig:820-842: wrap in runtime state, hand to the event loop, optionally return a handle.
+    Pool *p = (Pool *)d;
+    if (p->closed.load()) {
+        set_last_error("Closed");
+        return FIMO_STATUS_ERROR;
+    }
+    RtBuffer *rb = new RtBuffer();
+    rb->owner = p;
+    rb->buffer = buffer;
+    rb->status.assign(buffer->entries_len, EntryStatus::not_processed);
+    if (handle) {
+        rb->refs.fetch_add(1, std::memory_order_relaxed);
+        handle->data = rb;
+        handle->vtable = &g_handle_vtable;
+    }
+    post(p, Msg{Msg::enqueue, rb, 0});
+    return FIMO_STATUS_OK;
+}
+
+static const FimoTasksMeta_PoolVTable g_pool_vtable = {
+        vt_id,    vt_acquire, vt_release,     vt_request_close, vt_accepts_requests, vt_owns_current_thread,
+        vt_label, vt_workers, vt_stack_sizes, vt_enqueue_buffer};
+
+FimoTasksMeta_Pool pool_handle(Pool *p) { return FimoTasksMeta_Pool{p, &g_pool_vtable}; }
+Pool *pool_current() { return t_pool; }
+
+Pool *pool_create(const char *label, size_t label_len, size_t workers) {
+    Pool *p = new Pool();
+    p->id = g_next_pool_id.fetch_add(1);
+    p->label = label && label_len ? std::string(label, label_len) : std::string("<unlabelled>");
+    if (workers == 0) workers = std::thread::hardware_concurrency(); // FimoTasks.zig:127-132
+    if (workers == 0) workers = 1;
+    p->worker_count = workers;
+    p->runnable = workers;
+    p->threads_total = workers;
+    for (size_t i = 0; i < workers; i++) p->threads.emplace_back(worker_main, p, false);
+    p->event_thread = std::thread(event_loop, p);
+    p->event_thread.detach();
+    return p;
+}
+
+} // namespace oracle
+
+extern "C" FimoStatus fimo_tasks_create_worker_pool(const FimoTasksMeta_PoolConfig *config, FimoTasksMeta_Pool *pool) {
+    // FimoTasks.zig:201-358 validates the config; the oracle honours label and worker_count.
+    if (config->next != nullptr) {
+        oracle::set_last_error("InvalidConfig"); // FimoTasks.zig:208-212 rejects a non-null `next`
+        return FIMO_STATUS_ERROR;
+    }
+    *pool = oracle::pool_handle(oracle::pool_create(config->label, config->label_len, config->worker_count));
+    return FIMO_STATUS_OK;
+}

@@ -1,0 +1,40 @@
+/* systems_ref.h — scalar CPU definition of the synthetic systems (TEST INFRASTRUCTURE ONLY).
+ *
+ * The reference contains no entity / transform / cull arithmetic at all (SURVEY.md §8 a14:
+ * grep for transform|aabb|frustum|cull|entity over /root/reference -> 0 hits), so this file is
+ * not a restatement of reference code: it is the DEFINITION of the three build-defined systems
+ * named in BASELINE.json (integrate -> transform propagate -> AABB frustum cull), written as
+ * plain scalar loops.  "Parity unpinned" for this arithmetic: nothing in the reference can pin it.
+ * The CUDA kernels must reproduce these results bit for bit (every float op below is a single
+ * IEEE-754 binary32 operation rounded to nearest-even, in exactly the order written; build with
+ * -ffp-contract=off, device with --fmad=false).
+ *
+ * Data layout of one world: component planes, plane k of a C-component
+ * resource with E elements is at words [k*E, (k+1)*E).
+ */
+#ifndef FIMO_ORACLE_SYSTEMS_REF_H
+#define FIMO_ORACLE_SYSTEMS_REF_H
+#include <stddef.h>
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* integrate   X: pos[3][E]   S: vel[3][E], dt */
+void fimo_ref_integrate(float *pos, const float *vel, float dt, size_t n);
+
+/* propagate   X: world[12][E] (3x4 row-major affine)   S: pos, rot[4][E] (x,y,z,w), scale[E], parent[E].
+ * Entities are sorted by hierarchy level, so parent[e] < e or parent[e] == 0xFFFFFFFF (root).
+ * Returns 0, or -1 if a parent index is not smaller than its child. */
+int fimo_ref_propagate(float *world, const float *pos, const float *rot, const float *scale, const uint32_t *parent,
+                       size_t n);
+
+/* cull   X: vis_mask[ceil(E/32)], vis_list[E], vis_count[1], stats[8 x u64]
+ *        S: world, aabb_c[3][E], aabb_h[3][E], frustum[6][4] (nx,ny,nz,d; inside = n.x + d >= 0) */
+void fimo_ref_cull(uint32_t *vis_mask, uint32_t *vis_list, uint32_t *vis_count, uint64_t *stats, const float *world,
+                   const float *aabb_c, const float *aabb_h, const float *frustum, size_t n);
+
+#ifdef __cplusplus
+}
+#endif
+#endif
