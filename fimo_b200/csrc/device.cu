@@ -1,0 +1,359 @@
+// device.cu — CUDA side of the scheduler: HBM resource store, the per-group executor that turns the
+// compiled system DAG into a CUDA graph, and the completion thread that turns "generation finished on
+// the device" into the reference's host-side protocol (generation counter, timeline semaphore, fence).
+//
+// Replaces, for device systems, the reference's per-system dispatch through the pool's event loop
+// (modules/fimo_tasks/src/Pool.zig:660-765, CommandBuffer.zig:150-201,390-411): dependencies between
+// systems become edges of a CUDA graph, so one generation is ONE graph launch and no host thread is
+// touched between systems.  Generations of a group serialise by stream order (SystemGroup.zig:430-452
+// does it with a timeline semaphore).
+#include <cuda_runtime.h>
+
+#include <atomic>
+#include <condition_variable>
+#include <deque>
+#include <mutex>
+#include <string>
+#include <thread>
+
+#include "device.h"
+
+namespace fb::dev {
+namespace {
+
+thread_local std::string t_cuda_error;
+
+bool ok(cudaError_t err, const char *what) {
+    if (err == cudaSuccess) return true;
+    t_cuda_error = std::string(what) + ": " + cudaGetErrorString(err);
+    std::fprintf(stderr, "fimo_worlds_b200: %s\n", t_cuda_error.c_str());
+    (void)cudaGetLastError();
+    return false;
+}
+
+struct DeviceGuard { // the calling thread may belong to anyone: restore its device
+    int previous = -1;
+    bool valid = false;
+    explicit DeviceGuard(int device) {
+        if (cudaGetDevice(&previous) != cudaSuccess) {
+            (void)cudaGetLastError();
+            previous = -1;
+        }
+        valid = cudaSetDevice(device) == cudaSuccess;
+        if (!valid) (void)cudaGetLastError();
+    }
+    ~DeviceGuard() {
+        if (previous >= 0 && valid) cudaSetDevice(previous);
+    }
+};
+
+// ---- completion thread ---------------------------------------------------------------------------
+struct Completion {
+    cudaEvent_t start, end;
+    Executor *ex;
+    void (*done)(void *);
+    void *user;
+};
+
+struct Completer {
+    std::mutex m;
+    std::condition_variable cv;
+    std::deque<Completion> pending;
+    bool started = false;
+    void run();
+    void post(const Completion &c) {
+        std::lock_guard<std::mutex> g(m);
+        pending.push_back(c);
+        if (!started) {
+            started = true;
+            std::thread([this] { run(); }).detach();
+        }
+        cv.notify_one();
+    }
+};
+Completer &completer() {
+    static Completer *c = new Completer(); // leaked on purpose: the thread may outlive static destructors
+    return *c;
+}
+
+} // namespace
+
+struct Executor {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    std::vector<cudaStream_t> lanes; // side streams for DAG fan-out
+    std::vector<cudaEvent_t> node_events;
+    cudaEvent_t fork_event = nullptr;
+    std::vector<Node> nodes;
+    FimoB200_LaunchInfo info{};
+    cudaGraph_t graph = nullptr;
+    cudaGraphExec_t graph_exec = nullptr;
+    bool use_graph = false;
+    uint32_t kernels = 0;
+
+    std::mutex m; // event pool, in-flight count, timing
+    std::condition_variable idle_cv;
+    std::vector<cudaEvent_t> free_events;
+    size_t in_flight = 0;
+    double ms_sum = 0.0;
+    uint64_t ms_count = 0;
+
+    cudaEvent_t take_event() {
+        {
+            std::lock_guard<std::mutex> g(m);
+            if (!free_events.empty()) {
+                cudaEvent_t e = free_events.back();
+                free_events.pop_back();
+                return e;
+            }
+        }
+        cudaEvent_t e = nullptr;
+        ok(cudaEventCreate(&e), "cudaEventCreate");
+        return e;
+    }
+};
+
+namespace {
+
+void Completer::run() {
+    for (;;) {
+        Completion c;
+        {
+            std::unique_lock<std::mutex> g(m);
+            cv.wait(g, [&] { return !pending.empty(); });
+            c = pending.front();
+            pending.pop_front();
+        }
+        cudaSetDevice(c.ex->device);
+        ok(cudaEventSynchronize(c.end), "cudaEventSynchronize");
+        float ms = 0.0f;
+        const bool timed = cudaEventElapsedTime(&ms, c.start, c.end) == cudaSuccess;
+        if (!timed) (void)cudaGetLastError();
+        if (c.done) c.done(c.user);
+        Executor *ex = c.ex;
+        std::lock_guard<std::mutex> g(ex->m);
+        if (timed) {
+            ex->ms_sum += ms;
+            ex->ms_count++;
+        }
+        ex->free_events.push_back(c.start);
+        ex->free_events.push_back(c.end);
+        if (--ex->in_flight == 0) ex->idle_cv.notify_all();
+    }
+}
+
+// Replays the DAG on ex->stream: node i runs on a lane stream, waits for its dependencies' events,
+// records its own; the origin stream joins every lane at the end.  Used both live (no graph) and
+// under stream capture (to build the graph).
+bool replay(Executor *ex, bool capturing) {
+    const size_t n = ex->nodes.size();
+    while (ex->node_events.size() < n) {
+        cudaEvent_t e = nullptr;
+        if (!ok(cudaEventCreateWithFlags(&e, cudaEventDisableTiming), "cudaEventCreate")) return false;
+        ex->node_events.push_back(e);
+    }
+    // lane assignment: a node continues the lane of its first dependency if nobody else has yet
+    std::vector<int> lane(n, -1);
+    std::vector<char> lane_continued(n, 0);
+    int lanes_used = 1;
+    for (size_t i = 0; i < n; i++) {
+        int pick = -1;
+        for (uint32_t d : ex->nodes[i].deps)
+            if (!lane_continued[d]) {
+                pick = lane[d];
+                lane_continued[d] = 1;
+                break;
+            }
+        if (pick < 0) pick = (i == 0) ? 0 : lanes_used++;
+        lane[i] = pick;
+    }
+    while ((int)ex->lanes.size() < lanes_used - 1) {
+        cudaStream_t s = nullptr;
+        if (!ok(cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking), "cudaStreamCreate")) return false;
+        ex->lanes.push_back(s);
+    }
+    auto stream_of = [&](int l) { return l == 0 ? ex->stream : ex->lanes[(size_t)l - 1]; };
+    if (lanes_used > 1) {
+        if (!ex->fork_event && !ok(cudaEventCreateWithFlags(&ex->fork_event, cudaEventDisableTiming), "cudaEventCreate"))
+            return false;
+        if (!ok(cudaEventRecord(ex->fork_event, ex->stream), "cudaEventRecord")) return false;
+    }
+    std::vector<char> lane_started(lanes_used, 0);
+    lane_started[0] = 1;
+    FimoB200_LaunchInfo info = ex->info;
+    info.flags = capturing ? FIMO_B200_LAUNCH_FLAG_CAPTURING : 0u;
+    for (size_t i = 0; i < n; i++) {
+        cudaStream_t s = stream_of(lane[i]);
+        if (!lane_started[lane[i]]) { // fork the lane from the origin so it belongs to this generation
+            if (!ok(cudaStreamWaitEvent(s, ex->fork_event, 0), "cudaStreamWaitEvent")) return false;
+            lane_started[lane[i]] = 1;
+        }
+        for (uint32_t d : ex->nodes[i].deps)
+            if (lane[d] != lane[i] && !ok(cudaStreamWaitEvent(s, ex->node_events[d], 0), "cudaStreamWaitEvent"))
+                return false;
+        info.stream = s;
+        if (ex->nodes[i].launch(&info) != FIMO_STATUS_OK) return false;
+        if (!ok(cudaEventRecord(ex->node_events[i], s), "cudaEventRecord")) return false;
+    }
+    // join: the last node of every side lane
+    std::vector<int> last_on_lane(lanes_used, -1);
+    for (size_t i = 0; i < n; i++) last_on_lane[lane[i]] = (int)i;
+    for (int l = 1; l < lanes_used; l++)
+        if (last_on_lane[l] >= 0 &&
+            !ok(cudaStreamWaitEvent(ex->stream, ex->node_events[(size_t)last_on_lane[l]], 0), "cudaStreamWaitEvent"))
+            return false;
+    return true;
+}
+
+void drop_graph(Executor *ex) {
+    if (ex->graph_exec) cudaGraphExecDestroy(ex->graph_exec);
+    if (ex->graph) cudaGraphDestroy(ex->graph);
+    ex->graph_exec = nullptr;
+    ex->graph = nullptr;
+}
+
+} // namespace
+
+const char *last_cuda_error() { return t_cuda_error.c_str(); }
+
+int resolve_device(int device) {
+    if (device >= 0) return device;
+    int current = 0;
+    if (cudaGetDevice(&current) != cudaSuccess) {
+        (void)cudaGetLastError();
+        return 0;
+    }
+    return current;
+}
+
+bool device_ok(int device) {
+    int count = 0;
+    if (cudaGetDeviceCount(&count) != cudaSuccess) {
+        t_cuda_error = "no CUDA device: the B200 path has no CPU fallback";
+        (void)cudaGetLastError();
+        return false;
+    }
+    device = resolve_device(device);
+    if (device >= count) {
+        t_cuda_error = "CUDA device ordinal out of range";
+        return false;
+    }
+    return true;
+}
+
+void *hbm_alloc(int device, size_t bytes) {
+    DeviceGuard guard(device);
+    void *p = nullptr;
+    if (!ok(cudaMalloc(&p, bytes ? bytes : 4), "cudaMalloc")) return nullptr;
+    if (!ok(cudaMemset(p, 0, bytes ? bytes : 4), "cudaMemset")) {
+        cudaFree(p);
+        return nullptr;
+    }
+    return p;
+}
+
+void hbm_free(int device, void *ptr) {
+    if (!ptr) return;
+    DeviceGuard guard(device);
+    ok(cudaFree(ptr), "cudaFree");
+}
+
+bool hbm_upload(int device, void *dst, const void *src, size_t bytes) {
+    DeviceGuard guard(device);
+    return ok(cudaMemcpy(dst, src, bytes, cudaMemcpyHostToDevice), "cudaMemcpy H2D");
+}
+
+bool hbm_download(int device, void *dst, const void *src, size_t bytes) {
+    DeviceGuard guard(device);
+    return ok(cudaMemcpy(dst, src, bytes, cudaMemcpyDeviceToHost), "cudaMemcpy D2H");
+}
+
+Executor *executor_create(int device) {
+    DeviceGuard guard(device);
+    Executor *ex = new Executor();
+    ex->device = device;
+    if (!ok(cudaStreamCreateWithFlags(&ex->stream, cudaStreamNonBlocking), "cudaStreamCreate")) {
+        delete ex;
+        return nullptr;
+    }
+    return ex;
+}
+
+void executor_wait_idle(Executor *ex) {
+    std::unique_lock<std::mutex> g(ex->m);
+    ex->idle_cv.wait(g, [&] { return ex->in_flight == 0; });
+}
+
+void executor_destroy(Executor *ex) {
+    if (!ex) return;
+    executor_wait_idle(ex);
+    DeviceGuard guard(ex->device);
+    cudaStreamSynchronize(ex->stream);
+    drop_graph(ex);
+    for (cudaEvent_t e : ex->free_events) cudaEventDestroy(e);
+    for (cudaEvent_t e : ex->node_events) cudaEventDestroy(e);
+    if (ex->fork_event) cudaEventDestroy(ex->fork_event);
+    for (cudaStream_t s : ex->lanes) cudaStreamDestroy(s);
+    cudaStreamDestroy(ex->stream);
+    delete ex;
+}
+
+bool executor_compile(Executor *ex, std::vector<Node> nodes, const FimoB200_LaunchInfo &info, bool use_graph) {
+    executor_wait_idle(ex); // never rebuild under a generation that is still running
+    DeviceGuard guard(ex->device);
+    drop_graph(ex);
+    ex->nodes = std::move(nodes);
+    ex->info = info;
+    ex->info.device = ex->device;
+    ex->use_graph = false;
+    ex->kernels = 0;
+    for (const Node &n : ex->nodes) ex->kernels += n.kernels;
+    if (!use_graph || ex->nodes.empty()) return true;
+    if (!ok(cudaStreamBeginCapture(ex->stream, cudaStreamCaptureModeRelaxed), "cudaStreamBeginCapture")) return false;
+    const bool replayed = replay(ex, true);
+    cudaGraph_t graph = nullptr;
+    const bool ended = ok(cudaStreamEndCapture(ex->stream, &graph), "cudaStreamEndCapture");
+    if (!replayed || !ended || !graph) {
+        if (graph) cudaGraphDestroy(graph);
+        return false;
+    }
+    ex->graph = graph;
+    if (!ok(cudaGraphInstantiate(&ex->graph_exec, ex->graph, 0), "cudaGraphInstantiate")) return false;
+    ok(cudaGraphUpload(ex->graph_exec, ex->stream), "cudaGraphUpload");
+    ex->use_graph = true;
+    return true;
+}
+
+bool executor_launch(Executor *ex, void (*done)(void *), void *user) {
+    DeviceGuard guard(ex->device);
+    Completion c{ex->take_event(), ex->take_event(), ex, done, user};
+    if (!c.start || !c.end) return false;
+    {
+        std::lock_guard<std::mutex> g(ex->m);
+        ex->in_flight++;
+    }
+    bool launched = ok(cudaEventRecord(c.start, ex->stream), "cudaEventRecord");
+    if (launched) {
+        if (ex->use_graph) launched = ok(cudaGraphLaunch(ex->graph_exec, ex->stream), "cudaGraphLaunch");
+        else launched = replay(ex, false);
+    }
+    launched = ok(cudaEventRecord(c.end, ex->stream), "cudaEventRecord") && launched;
+    if (!launched) c.done = nullptr; // the caller reports the failure itself
+    completer().post(c);
+    return launched;
+}
+
+void *executor_stream(Executor *ex) { return ex->stream; }
+bool executor_uses_graph(Executor *ex) { return ex->use_graph; }
+uint32_t executor_kernels_per_generation(Executor *ex) { return ex->kernels; }
+
+double executor_device_ms(Executor *ex, uint64_t *generations) {
+    std::lock_guard<std::mutex> g(ex->m);
+    if (generations) *generations = ex->ms_count;
+    const double avg = ex->ms_count ? ex->ms_sum / (double)ex->ms_count : 0.0;
+    ex->ms_sum = 0.0;
+    ex->ms_count = 0;
+    return avg;
+}
+
+} // namespace fb::dev

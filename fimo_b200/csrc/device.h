@@ -1,0 +1,75 @@
+// device.h — the seam between the host-side scheduler (worlds.cpp) and the CUDA side
+// (device.cu, kernels.cu).  Plain C++: worlds.cpp never sees a CUDA header.
+#pragma once
+
+#include <cstddef>
+#include <cstdint>
+#include <functional>
+#include <vector>
+
+#include "fimo_worlds_b200.h"
+
+namespace fb::dev {
+
+// ---- HBM resource store -----------------------------------------------------------------------
+// One allocation per (resource, batch of worlds): dense 4-byte words [n_worlds][components][count].
+// All calls throw nothing and return false / nullptr after recording the CUDA error text.
+bool device_ok(int device); // a usable CUDA device with that ordinal exists (-1 = current)
+int resolve_device(int device);
+void *hbm_alloc(int device, size_t bytes); // zero-filled
+void hbm_free(int device, void *ptr);
+bool hbm_upload(int device, void *dst, const void *src, size_t bytes);
+bool hbm_download(int device, void *dst, const void *src, size_t bytes);
+const char *last_cuda_error();
+
+// ---- executor ------------------------------------------------------------------------------------
+// A compiled system group: the DAG of device nodes, instantiated as a CUDA graph (or replayed with
+// stream fork/join when graphs are disabled), launched once per generation on the group's stream.
+struct Node {
+    // Enqueue the node's kernels on info->stream (FimoB200_device_entry with bound arguments).
+    std::function<FimoStatus(const FimoB200_LaunchInfo *)> launch;
+    std::vector<uint32_t> deps; // indices of nodes that must finish first
+    uint32_t kernels = 1;       // kernel launches this node issues (for ExecutorInfo / gpu_launches)
+};
+
+struct Executor;
+Executor *executor_create(int device);
+void executor_destroy(Executor *ex); // waits until idle
+bool executor_compile(Executor *ex, std::vector<Node> nodes, const FimoB200_LaunchInfo &info, bool use_graph);
+// Enqueue one generation.  `done(user)` runs on the completion thread once the device finished it
+// (never inside a CUDA callback, so it may take locks and wake futex waiters).
+bool executor_launch(Executor *ex, void (*done)(void *), void *user);
+void executor_wait_idle(Executor *ex);
+void *executor_stream(Executor *ex);
+bool executor_uses_graph(Executor *ex);
+uint32_t executor_kernels_per_generation(Executor *ex);
+double executor_device_ms(Executor *ex, uint64_t *generations);
+
+// ---- built-in systems (kernels.cu) -------------------------------------------------------------
+// device_entry of FIMO_B200_BUILTIN_{INTEGRATE,PROPAGATE,CULL}.
+FimoStatus builtin_integrate(void *system, const FimoB200_ResourceView *const *exclusive,
+                             const FimoB200_ResourceView *const *shared, const FimoB200_LaunchInfo *info);
+FimoStatus builtin_propagate(void *system, const FimoB200_ResourceView *const *exclusive,
+                             const FimoB200_ResourceView *const *shared, const FimoB200_LaunchInfo *info);
+FimoStatus builtin_cull(void *system, const FimoB200_ResourceView *const *exclusive,
+                        const FimoB200_ResourceView *const *shared, const FimoB200_LaunchInfo *info);
+uint32_t builtin_propagate_kernels(const FimoB200_ResourceView *world, const FimoB200_ResourceView *level_start);
+
+// State of a built-in system instance (what `system_create` builds into the system blob).
+struct BuiltinState {
+    void *scratch; // HBM: statistics accumulators + completion ticket (cull only)
+    int device;
+};
+
+// The fused world-step: integrate -> propagate -> cull of one batch in ONE kernel; every live-in
+// resource is read once and every live-out resource written once (SURVEY.md §8d, B3 bytes).
+struct WorldStepViews {
+    const FimoB200_ResourceView *pos, *vel, *dt;                            // integrate
+    const FimoB200_ResourceView *world, *rot, *scale, *parent, *level_start; // propagate
+    const FimoB200_ResourceView *vis_mask, *vis_list, *vis_count, *stats;    // cull (exclusive)
+    const FimoB200_ResourceView *aabb_c, *aabb_h, *frustum;                  // cull (shared)
+};
+bool world_step_supported(const WorldStepViews &v);
+FimoStatus world_step_launch(const WorldStepViews &v, void *cull_scratch, const FimoB200_LaunchInfo *info);
+
+} // namespace fb::dev

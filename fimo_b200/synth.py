@@ -1,0 +1,328 @@
+"""Synthetic worlds of the shape BASELINE.json names, and the rig that registers them on an
+implementation of include/fimo_worlds_b200.h exactly as a user module would on the reference:
+`resource_register` / `world_add_resource` / `system_register` / `system_group_add_systems` /
+`system_group_schedule` (pkgs/fimo_worlds_meta/src/{resources,systems,worlds}.zig).
+
+Harness-side only (tests, bench.py, smoke).  The generator is counter-based — every value is a pure
+function of (seed, global world index, entity, field) — so any shard of any GPU materialises exactly
+the data a single process would.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import math
+from dataclasses import dataclass
+
+import numpy as np
+
+from . import abi
+from .worlds import Fence, Resource, System, World
+
+SEED = 0x46494D4F  # "FIMO"
+DT = np.float32(1.0 / 60.0)
+
+# name -> (scope, components, dtype); `level_start` gets depth+1 components at build time
+LAYOUT = {
+    "pos": (abi.SCOPE_ENTITY, 3, np.float32),
+    "vel": (abi.SCOPE_ENTITY, 3, np.float32),
+    "dt": (abi.SCOPE_WORLD, 1, np.float32),
+    "rot": (abi.SCOPE_ENTITY, 4, np.float32),
+    "scale": (abi.SCOPE_ENTITY, 1, np.float32),
+    "parent": (abi.SCOPE_ENTITY, 1, np.uint32),
+    "level_start": (abi.SCOPE_WORLD, 0, np.uint32),
+    "world": (abi.SCOPE_ENTITY, 12, np.float32),
+    "aabb_c": (abi.SCOPE_ENTITY, 3, np.float32),
+    "aabb_h": (abi.SCOPE_ENTITY, 3, np.float32),
+    "frustum": (abi.SCOPE_WORLD, 24, np.float32),
+    "vis_mask": (abi.SCOPE_ENTITY_BITS, 1, np.uint32),
+    "vis_list": (abi.SCOPE_ENTITY, 1, np.uint32),
+    "vis_count": (abi.SCOPE_WORLD, 1, np.uint32),
+    "stats": (abi.SCOPE_BATCH, 2 * abi.STAT_WORDS, np.uint32),
+}
+LIVE_IN = ("pos", "vel", "rot", "scale", "parent", "aabb_c", "aabb_h")  # 72 B / entity
+LIVE_OUT = ("pos", "world", "vis_mask", "vis_list")  # 60.125 + 4 f_vis B / entity
+OUTPUTS = ("pos", "world", "vis_mask", "vis_list", "vis_count", "stats")
+
+_F = {  # field ids of the generator
+    "pos": 0, "vel": 3, "rot": 6, "scale": 10, "aabb_c": 11, "aabb_h": 14, "parent": 17, "yaw": 18, "rot_retry": 32,
+}
+
+
+def pcg_hash(x: np.ndarray) -> np.ndarray:
+    """PCG-RXS-M-XS 32 (one round), vectorised over uint32."""
+    x = x.astype(np.uint32, copy=False)
+    with np.errstate(over="ignore"):
+        state = x * np.uint32(747796405) + np.uint32(2891336453)
+        word = ((state >> ((state >> np.uint32(28)) + np.uint32(4))) ^ state) * np.uint32(277803737)
+        return (word >> np.uint32(22)) ^ word
+
+
+def _key(seed: int, world: np.ndarray, entity: np.ndarray, field: int) -> np.ndarray:
+    with np.errstate(over="ignore"):
+        return (np.uint32(seed) ^ (world.astype(np.uint32) * np.uint32(0x9E3779B9))
+                ^ (entity.astype(np.uint32) * np.uint32(0x85EBCA6B)) ^ np.uint32((field * 0xC2B2AE35) & 0xFFFFFFFF))
+
+
+def _uniform(seed, world, entity, field, lo, hi) -> np.ndarray:
+    u = (pcg_hash(_key(seed, world, entity, field)) >> np.uint32(8)).astype(np.float32) * np.float32(1.0 / (1 << 24))
+    return (np.float32(lo) + np.float32(hi - lo) * u).astype(np.float32)
+
+
+def level_starts(entities: int, depth: int) -> np.ndarray:
+    """Level sizes proportional to 3^l (depth <= 4) or 2^l (deeper), remainder to the last level."""
+    base = 3 if depth <= 4 else 2
+    weights = [base ** l for l in range(depth)]
+    total = sum(weights)
+    sizes = [max(1, entities * w // total) for w in weights] if entities >= depth else [0] * depth
+    if entities >= depth:
+        sizes[-1] = entities - sum(sizes[:-1])
+        assert sizes[-1] >= 1
+    else:  # degenerate tiny worlds: everything is a root
+        sizes[0] = entities
+    starts = np.zeros(depth + 1, dtype=np.uint32)
+    starts[1:] = np.cumsum(sizes)
+    return starts
+
+
+def generate(n_worlds: int, entities: int, depth: int, world0: int = 0, seed: int = SEED) -> dict[str, np.ndarray]:
+    """All resources of `n_worlds` worlds starting at global world index `world0`, each laid out
+    [n_worlds][components][count] (4-byte words), outputs zero-filled."""
+    W, E = n_worlds, entities
+    wi = (np.arange(W, dtype=np.uint32) + np.uint32(world0))[:, None]
+    ei = np.arange(E, dtype=np.uint32)[None, :]
+    out: dict[str, np.ndarray] = {}
+
+    def field3(name, lo, hi, n=3):
+        a = np.empty((W, n, E), dtype=np.float32)
+        for k in range(n):
+            a[:, k, :] = _uniform(seed, wi, ei, _F[name] + k, lo, hi)
+        return a
+
+    out["pos"] = field3("pos", -100.0, 100.0)
+    out["vel"] = field3("vel", -1.0, 1.0)
+    rot = field3("rot", -1.0, 1.0, 4)
+    for attempt in range(1, 8):  # re-draw degenerate quaternions, deterministically
+        bad = (rot.astype(np.float64) ** 2).sum(axis=1) < 1e-3
+        if not bad.any():
+            break
+        wb, eb = np.nonzero(bad)
+        for k in range(4):
+            rot[wb, k, eb] = _uniform(seed, wi[wb, 0], ei[0, eb], _F["rot_retry"] + 4 * attempt + k, -1.0, 1.0)
+    norm = np.sqrt((rot * rot).sum(axis=1, dtype=np.float32)).astype(np.float32)
+    out["rot"] = (rot / norm[:, None, :]).astype(np.float32)
+    out["scale"] = _uniform(seed, wi, ei, _F["scale"], 0.75, 1.25).reshape(W, 1, E)
+    out["aabb_c"] = field3("aabb_c", -0.5, 0.5)
+    out["aabb_h"] = field3("aabb_h", 0.1, 2.0)
+    out["dt"] = np.full((W, 1, 1), DT, dtype=np.float32)
+
+    starts = level_starts(E, depth)
+    out["level_start"] = np.broadcast_to(starts[None, :, None], (W, depth + 1, 1)).copy()
+    parent = np.full((W, E), abi.PARENT_ROOT, dtype=np.uint32)
+    h = pcg_hash(_key(seed, wi, ei, _F["parent"]))
+    for l in range(1, depth):
+        lo, hi = int(starts[l]), int(starts[l + 1])
+        n_prev = int(starts[l]) - int(starts[l - 1])
+        if hi > lo and n_prev > 0:
+            parent[:, lo:hi] = np.uint32(starts[l - 1]) + h[:, lo:hi] % np.uint32(n_prev)
+    out["parent"] = parent.reshape(W, 1, E)
+
+    # frustum: symmetric perspective, fov 90 deg, aspect 1, near 0.1, far 400, at the origin, yawed per world
+    u = (pcg_hash(_key(seed, wi[:, 0], np.zeros(W, np.uint32), _F["yaw"])) >> np.uint32(8)).astype(np.float64) / (1 << 24)
+    yaw = 2.0 * math.pi * u
+    f = np.stack([np.sin(yaw), np.zeros(W), np.cos(yaw)], axis=1)
+    r = np.stack([np.cos(yaw), np.zeros(W), -np.sin(yaw)], axis=1)
+    up = np.broadcast_to(np.array([0.0, 1.0, 0.0]), (W, 3))
+    planes = np.zeros((W, 6, 4), dtype=np.float64)
+
+    def unit(v):
+        return v / np.linalg.norm(v, axis=1, keepdims=True)
+
+    planes[:, 0, :3], planes[:, 0, 3] = f, -0.1  # near
+    planes[:, 1, :3], planes[:, 1, 3] = -f, 400.0  # far
+    planes[:, 2, :3] = unit(f + r)  # left
+    planes[:, 3, :3] = unit(f - r)  # right
+    planes[:, 4, :3] = unit(f + up)  # bottom
+    planes[:, 5, :3] = unit(f - up)  # top
+    out["frustum"] = planes.reshape(W, 24, 1).astype(np.float32)
+
+    out["world"] = np.zeros((W, 12, E), dtype=np.float32)
+    out["vis_mask"] = np.zeros((W, 1, (E + 31) // 32), dtype=np.uint32)
+    out["vis_list"] = np.zeros((W, 1, E), dtype=np.uint32)
+    out["vis_count"] = np.zeros((W, 1, 1), dtype=np.uint32)
+    out["stats"] = np.zeros((1, 2 * abi.STAT_WORDS, 1), dtype=np.uint32)
+    return {k: np.ascontiguousarray(v) for k, v in out.items()}
+
+
+def bytes_per_entity_step(f_vis: float) -> float:
+    """B3 of SURVEY.md §8d: live-in read once (72 B) + live-out written once (60.125 + 4 f_vis B)."""
+    return 72.0 + 60.125 + 4.0 * f_vis
+
+
+@dataclass
+class RigOptions:
+    fused: bool = True  # let the DAG compiler fuse integrate -> propagate -> cull into one world-step kernel
+    graph: bool = True  # CUDA graph executor (False: plain stream launches with fork/join events)
+    device: int = -1
+    keep_host_copy: bool = True
+
+
+class WorldStepRig:
+    """One batch world + one system group running the 3-system chain
+    integrate -> transform propagate -> AABB frustum cull on `lib`.
+
+    On the product the resources are HBM SoA buffers behind FimoB200_ResourceView blobs and the
+    systems are the built-in device systems; on the CPU oracle (tests / bench baseline only) the same
+    descriptors are registered, the view's host_ptr is the data and the systems are ordinary
+    `system_run` callbacks dispatched on the pool — the reference's CPU path."""
+
+    def __init__(self, lib: abi.WorldsLib, n_worlds: int, entities: int, depth: int, world0: int = 0,
+                 options: RigOptions | None = None, data: dict[str, np.ndarray] | None = None, pool: abi.Pool | None = None):
+        self.lib, self.W, self.E, self.depth = lib, n_worlds, entities, depth
+        self.opt = options or RigOptions()
+        self.on_device = lib.is_product
+        self.host = data if data is not None else generate(n_worlds, entities, depth, world0)
+        self._keep: list = []
+        self.resources: dict[str, Resource] = {}
+        self.views: dict[str, abi.ResourceView] = {}
+
+        batch = None
+        if self.on_device:
+            batch = abi.WorldBatchExt(abi.ExtHeader(abi.STYPE_WORLD_BATCH, 0, None), n_worlds, entities, self.opt.device, 0)
+        self.world = World.init(lib, "synthetic-batch", pool=pool, batch=batch)
+        for name, (scope, comps, _dtype) in LAYOUT.items():
+            if name == "level_start":
+                comps = depth + 1
+            arr = self.host[name]
+            assert arr.dtype.itemsize == 4 and arr.flags["C_CONTIGUOUS"]
+            ext = abi.ResourceDeviceExt(abi.ExtHeader(abi.STYPE_RESOURCE_DEVICE, 0, None), scope, comps, 4, 0)
+            res = Resource.register(lib, name, C.sizeof(abi.ResourceView), 8,
+                                    next_ptr=C.cast(C.pointer(ext), C.c_void_p), keep=(ext,))
+            count = arr.shape[2]
+            view = abi.ResourceView(None, arr.ctypes.data, arr.shape[0], count, comps, 4, 4 * count, 4 * comps * count, scope, 0)
+            res.add_to_world(self.world, view)
+            self.resources[name] = res
+            self.views[name] = view
+
+        gext = None
+        if self.on_device:
+            flags = (0 if self.opt.fused else abi.GROUP_FLAG_NO_FUSION) | (0 if self.opt.graph else abi.GROUP_FLAG_NO_GRAPH)
+            gext = abi.GroupDeviceExt(abi.ExtHeader(abi.STYPE_GROUP_DEVICE, 0, None), flags, 0, abi.PostStepFn(), None)
+        self.group = self.world.add_system_group("world-step", pool=pool, ext=gext)
+
+        R = self.resources
+        self.sys_integrate = self._system("integrate", abi.BUILTIN_INTEGRATE, [R["pos"]], [R["vel"], R["dt"]])
+        self.sys_propagate = self._system("propagate", abi.BUILTIN_PROPAGATE, [R["world"]],
+                                          [R["pos"], R["rot"], R["scale"], R["parent"], R["level_start"]],
+                                          before=[self.sys_integrate])
+        self.sys_cull = self._system("cull", abi.BUILTIN_CULL,
+                                     [R["vis_mask"], R["vis_list"], R["vis_count"], R["stats"]],
+                                     [R["world"], R["aabb_c"], R["aabb_h"], R["frustum"]], before=[self.sys_propagate])
+        self.systems = [self.sys_integrate, self.sys_propagate, self.sys_cull]
+        self.group.add_systems(self.systems)
+        self._fence = Fence(lib)
+        self.closed = False
+
+    def _system(self, label, builtin, exclusive, shared, before=()):
+        desc = abi.SystemDescriptor()
+        keep = [desc]
+        if self.on_device:
+            ext = abi.SystemDeviceExt()
+            self.lib.check(self.lib.fimo_b200_builtin_system(builtin, C.byref(desc), C.byref(ext)))
+            keep.append(ext)
+        else:
+            self.lib.check(self.lib.fimo_oracle_builtin_system(builtin, C.byref(desc)))
+        return System.register(self.lib, label, exclusive=exclusive, shared=shared, before=before, descriptor=desc, keep=keep)
+
+    # ---- stepping -----------------------------------------------------------------------------------
+    def schedule(self, steps: int = 1, signal_last: bool = True) -> None:
+        """`steps` x system_group_schedule; the last one signals the rig's fence."""
+        self._fence.reset()
+        for i in range(steps):
+            self.group.schedule(signal=self._fence if (signal_last and i == steps - 1) else None)
+
+    def wait(self) -> None:
+        self._fence.wait()
+
+    def step(self, steps: int = 1) -> None:
+        self.schedule(steps)
+        self.wait()
+
+    def executor_info(self) -> abi.ExecutorInfo:
+        info = abi.ExecutorInfo()
+        self.lib.check(self.lib.fimo_b200_group_executor_info(self.group.handle, C.byref(info)))
+        return info
+
+    def device_ms(self) -> tuple[float, int]:
+        n = C.c_uint64(0)
+        ms = self.lib.fimo_b200_group_device_ms(self.group.handle, C.byref(n))
+        return ms, n.value
+
+    # ---- host access through the ABI ----------------------------------------------------------------
+    def _locked_view(self, name: str, exclusive: bool) -> abi.ResourceView:
+        ptr = self.resources[name].lock_in_world(self.world, exclusive)
+        return C.cast(ptr, C.POINTER(abi.ResourceView)).contents
+
+    def download(self, names=OUTPUTS) -> dict[str, np.ndarray]:
+        """world_lock_resources (shared) -> copy out -> unlock, per resource."""
+        out = {}
+        for name in names:
+            view = self._locked_view(name, exclusive=False)
+            try:
+                if self.on_device:
+                    arr = np.empty_like(self.host[name])
+                    self.lib.check(self.lib.fimo_b200_resource_download(C.byref(view), arr.ctypes.data))
+                else:
+                    arr = self.host[name].copy()
+            finally:
+                self.resources[name].unlock_in_world(self.world, False)
+            out[name] = arr
+        return out
+
+    def upload(self, name: str, arr: np.ndarray) -> None:
+        """world_lock_resources (exclusive) -> copy in -> unlock."""
+        assert arr.dtype.itemsize == 4 and arr.flags["C_CONTIGUOUS"] and arr.shape == self.host[name].shape
+        view = self._locked_view(name, exclusive=True)
+        try:
+            if self.on_device:
+                self.lib.check(self.lib.fimo_b200_resource_upload(C.byref(view), arr.ctypes.data))
+            else:
+                self.host[name][...] = arr
+        finally:
+            self.resources[name].unlock_in_world(self.world, True)
+
+    def stats(self) -> np.ndarray:
+        return self.download(("stats",))["stats"].reshape(-1).view(np.uint64)
+
+    def close(self) -> None:
+        if self.closed:
+            return
+        self.closed = True
+        for s in self.systems:
+            self.group.remove_system(s)
+        for s in reversed(self.systems):
+            s.unregister()
+        self.group.deinit()
+        for name, res in self.resources.items():
+            out = abi.ResourceView()
+            res.remove_from_world(self.world, out)
+            res.unregister()
+        self.world.deinit()
+
+
+def compare_outputs(got: dict[str, np.ndarray], want: dict[str, np.ndarray], float_rtol: float = 0.0) -> list[str]:
+    """Integer / index / mask outputs must match bit for bit; float outputs within `float_rtol`
+    relative (0.0 = bit-exact, the design target; north_star allows 1e-5)."""
+    problems = []
+    for name, w in want.items():
+        g = got[name]
+        if g.shape != w.shape:
+            problems.append(f"{name}: shape {g.shape} != {w.shape}")
+            continue
+        if w.dtype == np.float32 and float_rtol > 0.0:
+            bad = ~np.isclose(g, w, rtol=float_rtol, atol=0.0, equal_nan=True)
+        else:
+            bad = g.view(np.uint32) != w.view(np.uint32)
+        if bad.any():
+            idx = tuple(int(i[0]) for i in np.nonzero(bad))
+            problems.append(f"{name}: {int(bad.sum())} of {bad.size} words differ, first at {idx}: got {g[idx]!r} want {w[idx]!r}")
+    return problems
