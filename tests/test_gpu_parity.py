@@ -1,0 +1,144 @@
+"""Parity of the CUDA path with the CPU oracle, through the C ABI, on a B200 (-m gpu).
+
+Bar (BASELINE.json north_star): integer / index / cull-mask outputs bit-exact; float transforms within
+1e-5 relative.  The kernels are written so that floats are bit-exact as well (FLOAT_RTOL = 0.0 below
+asserts exactly that; relax to 1e-5 only with a written reason)."""
+import numpy as np
+import pytest
+
+from fimo_b200 import abi, synth
+
+pytestmark = pytest.mark.gpu
+FLOAT_RTOL = 0.0  # bit-exact; north_star tolerance is 1e-5 relative
+
+
+def run_both(oracle, product, W, E, D, steps, options=None, world0=0):
+    data = synth.generate(W, E, D, world0=world0)
+    ref = synth.WorldStepRig(oracle, W, E, D, data={k: v.copy() for k, v in data.items()})
+    try:
+        ref.step(steps)
+        want = ref.download()
+    finally:
+        ref.close()
+    dev = synth.WorldStepRig(product, W, E, D, data={k: v.copy() for k, v in data.items()}, options=options)
+    try:
+        info = dev.executor_info()
+        dev.step(steps)
+        got = dev.download()
+    finally:
+        dev.close()
+    return got, want, info
+
+
+CASES = [
+    # (worlds, entities, depth, steps)
+    (1, 1024, 4, 16),     # BASELINE configs[0]: single world, 1k entities
+    (64, 1024, 4, 16),    # configs[1] shape at a size the oracle finishes in seconds
+    (7, 1000, 4, 5),      # ragged: entities not a multiple of 32 / 4
+    (3, 33, 4, 3),
+    (5, 1, 4, 2),         # one entity per world
+    (2, 4096, 4, 4),      # configs[3] world shape
+    (300, 96, 8, 3),      # more worlds than resident CTAs, depth 8
+]
+
+
+@pytest.mark.parametrize("W,E,D,steps", CASES)
+@pytest.mark.parametrize("mode", ["fused", "unfused-graph", "unfused-streams"])
+def test_three_system_chain_matches_oracle(oracle, product, W, E, D, steps, mode):
+    options = synth.RigOptions(fused=(mode == "fused"), graph=(mode != "unfused-streams"))
+    got, want, info = run_both(oracle, product, W, E, D, steps, options)
+    assert info.systems == 3 and info.device_systems == 3
+    if mode == "fused":
+        assert info.fused_world_step == 1 and info.nodes == 1 and info.kernel_launches_per_generation == 1
+    else:
+        assert info.fused_world_step == 0 and info.nodes == 3
+    assert info.uses_cuda_graph == (0 if mode == "unfused-streams" else 1)
+    problems = synth.compare_outputs(got, want, FLOAT_RTOL)
+    assert not problems, "\n".join(problems)
+    st = got["stats"].reshape(-1).view(np.uint64)
+    assert st[abi.STAT_STEPS] == W * steps and st[abi.STAT_WORLDS] == W
+
+
+def test_large_world_uses_per_level_propagate(oracle, product):
+    """configs[2] world shape (64k entities, depth 8): too large for one CTA's shared memory."""
+    got, want, info = run_both(oracle, product, 2, 65536, 8, 3)
+    assert info.fused_world_step == 0 and info.kernel_launches_per_generation == 1 + 8 + 1
+    problems = synth.compare_outputs(got, want, FLOAT_RTOL)
+    assert not problems, "\n".join(problems)
+
+
+def test_full_size_properties(product):
+    """BASELINE configs[1] at full size (4096 x 1k): size-independent properties instead of the oracle."""
+    W, E, D, K = 4096, 1024, 4, 4
+    rig = synth.WorldStepRig(product, W, E, D)
+    try:
+        rig.step(K)
+        out = rig.download()
+        host = rig.host
+    finally:
+        rig.close()
+    counts = out["vis_count"][:, 0, 0].astype(np.int64)
+    bits = np.unpackbits(out["vis_mask"][:, 0, :].view(np.uint8), axis=1, bitorder="little")
+    assert np.array_equal(bits.sum(axis=1), counts)                       # count == popcount(mask)
+    st = out["stats"].reshape(-1).view(np.uint64)
+    assert st[abi.STAT_VISIBLE] == counts.sum() and st[abi.STAT_ENTITIES] == W * E
+    assert st[abi.STAT_MASK_SUM] == out["vis_mask"].astype(np.uint64).sum()  # checksum of checksums
+    assert st[abi.STAT_STEPS] == W * K
+    for w in (0, 1, 2047, 4095):                                          # list == ascending indices of the mask
+        idx = np.nonzero(bits[w])[0].astype(np.uint32)
+        assert np.array_equal(out["vis_list"][w, 0, :counts[w]], idx)
+    expect = host["pos"].copy()                                           # integrate is exactly K fp32 steps
+    step = (host["vel"] * synth.DT).astype(np.float32)
+    for _ in range(K):
+        expect = (expect + step).astype(np.float32)
+    assert np.array_equal(expect.view(np.uint32), out["pos"].view(np.uint32))
+    roots = host["parent"][:, 0, :] == abi.PARENT_ROOT                    # roots: world translation == pos
+    for k in range(3):
+        assert np.array_equal(out["world"][:, 4 * k + 3, :][roots], out["pos"][:, k, :][roots])
+
+
+def test_generations_pipeline_and_fences(product):
+    """schedule is asynchronous; K queued generations run in order; the signal fence fires after the last."""
+    rig = synth.WorldStepRig(product, 32, 256, 4)
+    try:
+        rig.schedule(25)
+        rig.wait()
+        assert rig.stats()[abi.STAT_STEPS] == 32 * 25
+        # wait_on: a generation gated on an unsignaled fence must not run until it is signaled
+        from fimo_b200.worlds import Fence
+        gate, done = Fence(product), Fence(product)
+        rig.group.schedule(wait_on=[gate], signal=done)
+        import time
+        time.sleep(0.05)
+        assert not done.is_signaled()
+        gate.signal()
+        done.wait()
+        assert rig.stats()[abi.STAT_STEPS] == 32 * 26
+    finally:
+        rig.close()
+
+
+def test_host_upload_between_steps(oracle, product):
+    """world_lock_resources + upload of a per-step input (new frustum) is honoured by the next step."""
+    W, E, D = 8, 512, 4
+    data = synth.generate(W, E, D)
+    other = synth.generate(W, E, D, world0=1000)["frustum"]
+    outs = []
+    for lib in (oracle, product):
+        rig = synth.WorldStepRig(lib, W, E, D, data={k: v.copy() for k, v in data.items()})
+        try:
+            rig.step(2)
+            rig.upload("frustum", other)
+            rig.step(1)
+            outs.append(rig.download())
+        finally:
+            rig.close()
+    problems = synth.compare_outputs(outs[1], outs[0], FLOAT_RTOL)
+    assert not problems, "\n".join(problems)
+
+
+@pytest.mark.parametrize("case_name", ["group_schedule_counts_to_five", "context_generation_increments", "resource_unique_lock"])
+def test_reference_goldens_on_gpu_box(product, case_name):
+    import reference_goldens as G
+
+    getattr(G, case_name)(product)
