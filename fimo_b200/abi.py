@@ -366,6 +366,7 @@ PRODUCT_SYMBOLS = [
     ("fimo_b200_group_stream", c_void_p, [c_void_p]),
     ("fimo_b200_group_wait_idle", None, [c_void_p]),
     ("fimo_b200_group_device_ms", c_double, [c_void_p, POINTER(c_uint64)]),
+    ("fimo_b200_group_span_ms", c_double, [c_void_p]),
 ]
 
 # CPU-oracle-only helpers (tests / bench cpu_baseline only)

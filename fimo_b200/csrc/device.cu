@@ -97,6 +97,8 @@ struct Executor {
     size_t in_flight = 0;
     double ms_sum = 0.0;
     uint64_t ms_count = 0;
+    cudaEvent_t span_anchor = nullptr; // start of the first generation since the timers were read
+    double span_ms = 0.0;              // anchor -> end of the latest generation (includes inter-generation gaps)
 
     cudaEvent_t take_event() {
         {
@@ -136,7 +138,11 @@ void Completer::run() {
             ex->ms_sum += ms;
             ex->ms_count++;
         }
-        ex->free_events.push_back(c.start);
+        if (!ex->span_anchor) ex->span_anchor = c.start;
+        else ex->free_events.push_back(c.start);
+        float span = 0.0f;
+        if (cudaEventElapsedTime(&span, ex->span_anchor, c.end) == cudaSuccess) ex->span_ms = span;
+        else (void)cudaGetLastError();
         ex->free_events.push_back(c.end);
         if (--ex->in_flight == 0) ex->idle_cv.notify_all();
     }
@@ -354,6 +360,15 @@ double executor_device_ms(Executor *ex, uint64_t *generations) {
     ex->ms_sum = 0.0;
     ex->ms_count = 0;
     return avg;
+}
+
+double executor_span_ms(Executor *ex) {
+    std::lock_guard<std::mutex> g(ex->m);
+    const double span = ex->span_ms;
+    ex->span_ms = 0.0;
+    if (ex->span_anchor) ex->free_events.push_back(ex->span_anchor);
+    ex->span_anchor = nullptr;
+    return span;
 }
 
 } // namespace fb::dev

@@ -1564,4 +1564,15 @@ double fimo_b200_group_device_ms(FimoWorldsMeta_SystemGroup *group, uint64_t *ge
     dev::executor_wait_idle(ex);
     return dev::executor_device_ms(ex, generations);
 }
+double fimo_b200_group_span_ms(FimoWorldsMeta_SystemGroup *group) {
+    Group *g = (Group *)group;
+    dev::Executor *ex;
+    {
+        std::lock_guard<std::mutex> lock(g->m);
+        ex = g->executor_dev;
+    }
+    if (!ex) return 0.0;
+    dev::executor_wait_idle(ex);
+    return dev::executor_span_ms(ex);
+}
 }

@@ -176,7 +176,8 @@ class WorldStepRig:
     `system_run` callbacks dispatched on the pool — the reference's CPU path."""
 
     def __init__(self, lib: abi.WorldsLib, n_worlds: int, entities: int, depth: int, world0: int = 0,
-                 options: RigOptions | None = None, data: dict[str, np.ndarray] | None = None, pool: abi.Pool | None = None):
+                 options: RigOptions | None = None, data: dict[str, np.ndarray] | None = None, pool: abi.Pool | None = None,
+                 post_step=None):
         self.lib, self.W, self.E, self.depth = lib, n_worlds, entities, depth
         self.opt = options or RigOptions()
         self.on_device = lib.is_product
@@ -206,7 +207,8 @@ class WorldStepRig:
         gext = None
         if self.on_device:
             flags = (0 if self.opt.fused else abi.GROUP_FLAG_NO_FUSION) | (0 if self.opt.graph else abi.GROUP_FLAG_NO_GRAPH)
-            gext = abi.GroupDeviceExt(abi.ExtHeader(abi.STYPE_GROUP_DEVICE, 0, None), flags, 0, abi.PostStepFn(), None)
+            self._post_step = abi.PostStepFn(post_step) if post_step is not None else abi.PostStepFn()
+            gext = abi.GroupDeviceExt(abi.ExtHeader(abi.STYPE_GROUP_DEVICE, 0, None), flags, 0, self._post_step, None)
         self.group = self.world.add_system_group("world-step", pool=pool, ext=gext)
 
         R = self.resources
@@ -257,6 +259,9 @@ class WorldStepRig:
         ms = self.lib.fimo_b200_group_device_ms(self.group.handle, C.byref(n))
         return ms, n.value
 
+    def span_ms(self) -> float:
+        return self.lib.fimo_b200_group_span_ms(self.group.handle)
+
     # ---- host access through the ABI ----------------------------------------------------------------
     def _locked_view(self, name: str, exclusive: bool) -> abi.ResourceView:
         ptr = self.resources[name].lock_in_world(self.world, exclusive)
@@ -277,6 +282,17 @@ class WorldStepRig:
                 self.resources[name].unlock_in_world(self.world, False)
             out[name] = arr
         return out
+
+    def download_into(self, name: str, arr: np.ndarray) -> None:
+        """download() into a caller-provided (e.g. pinned) host buffer."""
+        view = self._locked_view(name, exclusive=False)
+        try:
+            if self.on_device:
+                self.lib.check(self.lib.fimo_b200_resource_download(C.byref(view), arr.ctypes.data))
+            else:
+                arr[...] = self.host[name]
+        finally:
+            self.resources[name].unlock_in_world(self.world, False)
 
     def upload(self, name: str, arr: np.ndarray) -> None:
         """world_lock_resources (exclusive) -> copy in -> unlock."""

@@ -702,9 +702,14 @@ FIMO_B200_EXPORT void *fimo_b200_group_stream(FimoWorldsMeta_SystemGroup *group)
 /* Blocks until every scheduled generation of the group has finished on the device. */
 FIMO_B200_EXPORT void fimo_b200_group_wait_idle(FimoWorldsMeta_SystemGroup *group);
 
-/* Average device time of the group's last `n` generations in milliseconds, measured with
- * CUDA events on the group's stream around each generation (0 if none recorded). */
+/* Average device time per generation in milliseconds over the `*generations` generations completed since
+ * the previous call, measured with CUDA events on the group's stream around each generation (0 if none). */
 FIMO_B200_EXPORT double fimo_b200_group_device_ms(FimoWorldsMeta_SystemGroup *group, uint64_t *generations);
+
+/* Device time in milliseconds (CUDA events on the group's stream) from the start of the first to the end
+ * of the last generation completed since the previous call — i.e. including any gap between generations.
+ * Resets the span; call fimo_b200_group_device_ms first if both are wanted for the same window. */
+FIMO_B200_EXPORT double fimo_b200_group_span_ms(FimoWorldsMeta_SystemGroup *group);
 
 /* ------------------------------------------------------------------------- */
 /* Layout pins (sizes measured with gcc on x86-64)       */
