@@ -243,7 +243,7 @@ def run_b200(args) -> None:
     except Exception:
         pass
     roofline = {"bound": "hbm", "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s", "frac": round(achieved / peak, 4),
-                "traffic": traffic, "kernel": "k_world_cta<256,true,true> (fused world-step)" if info.fused_world_step else "per-system kernels",
+                "traffic": traffic, "kernel": ("k_world_step_pipe (TMA-fed persistent fused world-step)" if E % 4 == 0 else "k_world_cta (fused, one CTA per world)") if info.fused_world_step else "per-system kernels",
                 "algorithmic_bytes_per_launch": int(alg_bytes), "bytes_per_entity_step": round(b3, 3), "f_vis": round(f_vis, 4),
                 "kernel_ms": round(kernel_ms, 5), "peak_source": peak_src, "traffic_source": "profiles/traffic.json (ncu --set full)"}
 

@@ -72,5 +72,9 @@ struct WorldStepViews {
 };
 bool world_step_supported(const WorldStepViews &v);
 FimoStatus world_step_launch(const WorldStepViews &v, void *cull_scratch, const FimoB200_LaunchInfo *info);
+const char *world_step_kernel_name(const WorldStepViews &v); // which kernel world_step_launch picks
+// v1: one CTA per world, whole world's matrices in shared memory, loads through registers (kernels.cu)
+bool world_step_supported_v1(const WorldStepViews &v);
+FimoStatus world_step_launch_v1(const WorldStepViews &v, void *cull_scratch, const FimoB200_LaunchInfo *info);
 
 } // namespace fb::dev

@@ -3,150 +3,20 @@
 //
 // The reference contains no entity / transform / cull arithmetic (a "system" there is an opaque
 // callback, pkgs/fimo_worlds_meta/include/fimo_worlds_meta/systems.h:103-113), so the arithmetic
-// below is defined by this build: every float operation is one IEEE-754 binary32 operation
-// (__fmul_rn/__fadd_rn/__fsub_rn, never contracted into an FMA), in a fixed order, so that results
-// are bit-identical to a scalar CPU evaluation of the same expressions.
+// is defined by this build (kernels_common.cuh): every float operation is one IEEE-754 binary32
+// operation — __fmul_rn / __fadd_rn / __fsub_rn, or __fmaf_rn exactly where the definition spells a
+// fused multiply-add — in a fixed order, never contracted or reassociated by the compiler, so that
+// results are bit-identical to a scalar CPU evaluation of the same expressions with fmaf().
 //
 // Data layout: every resource is dense 4-byte words [n_worlds][components][count];
 // component plane k of world w starts at word  w*world_words + k*count.
-#include <cuda_runtime.h>
 
-#include <cstdint>
-#include <cstdio>
 
-#include "device.h"
+
+#include "kernels_common.cuh"
 
 namespace fb::dev {
 namespace {
-
-constexpr uint32_t kRoot = FIMO_B200_PARENT_ROOT;
-constexpr int kMaxLevels = 32;
-constexpr unsigned kFull = 0xFFFFFFFFu;
-
-// ---------------------------------------------------------------------------------------------
-// math (each line is one rounding)
-// ---------------------------------------------------------------------------------------------
-__device__ __forceinline__ float mul(float a, float b) { return __fmul_rn(a, b); }
-__device__ __forceinline__ float add(float a, float b) { return __fadd_rn(a, b); }
-__device__ __forceinline__ float sub(float a, float b) { return __fsub_rn(a, b); }
-
-// local = T(pos) * R(quat x,y,z,w) * S(uniform s): 3x4 row-major affine
-__device__ __forceinline__ void local_trs(float (&L)[12], float px, float py, float pz, float x, float y, float z, float w,
-                                          float s) {
-    const float xx = mul(x, x), yy = mul(y, y), zz = mul(z, z);
-    const float xy = mul(x, y), xz = mul(x, z), yz = mul(y, z);
-    const float wx = mul(w, x), wy = mul(w, y), wz = mul(w, z);
-    const float r00 = sub(1.0f, mul(2.0f, add(yy, zz))), r01 = mul(2.0f, sub(xy, wz)), r02 = mul(2.0f, add(xz, wy));
-    const float r10 = mul(2.0f, add(xy, wz)), r11 = sub(1.0f, mul(2.0f, add(xx, zz))), r12 = mul(2.0f, sub(yz, wx));
-    const float r20 = mul(2.0f, sub(xz, wy)), r21 = mul(2.0f, add(yz, wx)), r22 = sub(1.0f, mul(2.0f, add(xx, yy)));
-    L[0] = mul(r00, s), L[1] = mul(r01, s), L[2] = mul(r02, s), L[3] = px;
-    L[4] = mul(r10, s), L[5] = mul(r11, s), L[6] = mul(r12, s), L[7] = py;
-    L[8] = mul(r20, s), L[9] = mul(r21, s), L[10] = mul(r22, s), L[11] = pz;
-}
-
-// W = P o L  (both 3x4 affine)
-__device__ __forceinline__ void compose(float (&W)[12], const float (&P)[12], const float (&L)[12]) {
-#pragma unroll
-    for (int r = 0; r < 3; r++) {
-        const float a = P[r * 4 + 0], b = P[r * 4 + 1], c = P[r * 4 + 2], t = P[r * 4 + 3];
-#pragma unroll
-        for (int col = 0; col < 3; col++)
-            W[r * 4 + col] = add(add(mul(a, L[col]), mul(b, L[4 + col])), mul(c, L[8 + col]));
-        W[r * 4 + 3] = add(add(add(mul(a, L[3]), mul(b, L[7])), mul(c, L[11])), t);
-    }
-}
-
-// world-space AABB of (c,h) under W, tested against 6 planes (nx,ny,nz,d), inside = n.x + d >= 0
-__device__ __forceinline__ bool aabb_visible(const float (&W)[12], float c0, float c1, float c2, float h0, float h1,
-                                             float h2, const float *__restrict__ fr /* 24 floats, shared memory */) {
-    float wc[3], wh[3];
-#pragma unroll
-    for (int r = 0; r < 3; r++) {
-        wc[r] = add(add(add(mul(W[r * 4 + 0], c0), mul(W[r * 4 + 1], c1)), mul(W[r * 4 + 2], c2)), W[r * 4 + 3]);
-        wh[r] = add(add(mul(fabsf(W[r * 4 + 0]), h0), mul(fabsf(W[r * 4 + 1]), h1)), mul(fabsf(W[r * 4 + 2]), h2));
-    }
-    bool visible = true;
-#pragma unroll
-    for (int p = 0; p < 6; p++) {
-        const float nx = fr[p * 4 + 0], ny = fr[p * 4 + 1], nz = fr[p * 4 + 2], d = fr[p * 4 + 3];
-        const float dist = add(add(add(mul(nx, wc[0]), mul(ny, wc[1])), mul(nz, wc[2])), d);
-        const float rad = add(add(mul(fabsf(nx), wh[0]), mul(fabsf(ny), wh[1])), mul(fabsf(nz), wh[2]));
-        if (!(add(dist, rad) >= 0.0f)) visible = false;
-    }
-    return visible;
-}
-
-// ---------------------------------------------------------------------------------------------
-// argument blocks (word strides; one block per kernel, passed by value)
-// ---------------------------------------------------------------------------------------------
-struct Plane { // a resource of the batch
-    uint32_t *base;
-    uint64_t world_words;
-};
-__device__ __forceinline__ float *fptr(const Plane &p, uint64_t w) { return (float *)(p.base + w * p.world_words); }
-__device__ __forceinline__ uint32_t *uptr(const Plane &p, uint64_t w) { return p.base + w * p.world_words; }
-
-struct StepArgs {
-    Plane pos, vel, dt;                             // integrate
-    Plane world, rot, scale, parent, level_start;   // propagate
-    Plane vis_mask, vis_list, vis_count;            // cull outputs
-    Plane aabb_c, aabb_h, frustum;                  // cull inputs
-    unsigned long long *stats;                      // FIMO_B200_STAT_* words of the batch
-    unsigned long long *scratch;                    // [0..3] accumulators, [4] ticket
-    uint32_t n_worlds, entities, levels, mask_words;
-};
-
-// One entity of one hierarchy level: integrate (optional), build the local transform, compose with
-// the parent's world transform (read through `parent_world(i, p)`), hand the result to `emit(i, v)`.
-template <bool kIntegrate, typename ParentFn, typename EmitFn>
-__device__ __forceinline__ void propagate_entity(uint32_t e, uint32_t E, float *__restrict__ pos, const float *__restrict__ vel,
-                                                 float dt, const float *__restrict__ rot, const float *__restrict__ scale,
-                                                 const uint32_t *__restrict__ parent, ParentFn parent_world, EmitFn emit) {
-    float px = pos[e], py = pos[E + e], pz = pos[2 * E + e];
-    if (kIntegrate) {
-        px = add(px, mul(vel[e], dt));
-        py = add(py, mul(vel[E + e], dt));
-        pz = add(pz, mul(vel[2 * E + e], dt));
-        pos[e] = px, pos[E + e] = py, pos[2 * E + e] = pz;
-    }
-    float L[12], W[12];
-    local_trs(L, px, py, pz, rot[e], rot[E + e], rot[2 * E + e], rot[3 * E + e], scale[e]);
-    const uint32_t p = parent[e];
-    if (p == kRoot) {
-#pragma unroll
-        for (int i = 0; i < 12; i++) W[i] = L[i];
-    } else {
-        float P[12];
-#pragma unroll
-        for (int i = 0; i < 12; i++) P[i] = parent_world(i, p);
-        compose(W, P, L);
-    }
-#pragma unroll
-    for (int i = 0; i < 12; i++) emit(i, W[i]);
-}
-
-// Folds one CTA's statistics into the batch accumulators; the last CTA of the grid publishes them
-// and re-arms the scratch block (so no memset node is needed between generations).
-__device__ __forceinline__ void publish_stats(const StepArgs &a, unsigned long long visible, unsigned long long mask_sum,
-                                              unsigned long long worlds) {
-    atomicAdd(&a.scratch[0], visible);
-    atomicAdd(&a.scratch[1], mask_sum);
-    atomicAdd(&a.scratch[2], worlds);
-    __threadfence();
-    const unsigned long long ticket = atomicAdd(&a.scratch[4], 1ull);
-    if (ticket == (unsigned long long)gridDim.x - 1) {
-        __threadfence();
-        const unsigned long long v = atomicExch(&a.scratch[0], 0ull);
-        const unsigned long long m = atomicExch(&a.scratch[1], 0ull);
-        const unsigned long long n = atomicExch(&a.scratch[2], 0ull);
-        a.stats[FIMO_B200_STAT_VISIBLE] = v;
-        a.stats[FIMO_B200_STAT_ENTITIES] = n * (unsigned long long)a.entities;
-        a.stats[FIMO_B200_STAT_MASK_SUM] = m;
-        a.stats[FIMO_B200_STAT_WORLDS] = n;
-        a.stats[FIMO_B200_STAT_STEPS] += n;
-        atomicExch(&a.scratch[4], 0ull);
-    }
-}
 
 // Cull of one world by one CTA.  `world_at(i, e)` reads component i of entity e's world transform.
 // Writes the bit mask (warp ballot), the ASCENDING visible-index list (warp popc prefix + block
@@ -221,10 +91,10 @@ __global__ void __launch_bounds__(256) k_integrate_v4(Plane pos, Plane vel, Plan
     float4 *p = (float4 *)fptr(pos, w) + i;
     const float4 v = __ldg((const float4 *)fptr(vel, w) + i);
     float4 x = *p;
-    x.x = add(x.x, mul(v.x, step));
-    x.y = add(x.y, mul(v.y, step));
-    x.z = add(x.z, mul(v.z, step));
-    x.w = add(x.w, mul(v.w, step));
+    x.x = fma1(v.x, step, x.x);
+    x.y = fma1(v.y, step, x.y);
+    x.z = fma1(v.z, step, x.z);
+    x.w = fma1(v.w, step, x.w);
     *p = x;
 }
 __global__ void __launch_bounds__(256) k_integrate_s(Plane pos, Plane vel, Plane dt, uint32_t words_per_world,
@@ -234,7 +104,7 @@ __global__ void __launch_bounds__(256) k_integrate_s(Plane pos, Plane vel, Plane
     if (i >= words_per_world) return;
     const float step = *fptr(dt, w);
     float *p = fptr(pos, w) + i;
-    *p = add(*p, mul(fptr(vel, w)[i], step));
+    *p = fma1(fptr(vel, w)[i], step, *p);
 }
 
 // propagate, one CTA per world: the world's 3x4 matrices are staged in shared memory ([12][E]
@@ -242,7 +112,7 @@ __global__ void __launch_bounds__(256) k_integrate_s(Plane pos, Plane vel, Plane
 template <int T, bool kIntegrate, bool kCull>
 __global__ void __launch_bounds__(T) k_world_cta(StepArgs a) {
     extern __shared__ float s_world[]; // [12][E]
-    __shared__ float s_frustum[24];
+    __shared__ __align__(16) float s_frustum[24];
     __shared__ uint32_t s_levels[kMaxLevels + 1];
     __shared__ uint32_t s_warp[2 * (T / 32)];
     const uint32_t E = a.entities;
@@ -299,7 +169,7 @@ __global__ void __launch_bounds__(256) k_propagate_level(StepArgs a, uint32_t le
 
 // cull, one CTA per world, transforms read from HBM.
 template <int T> __global__ void __launch_bounds__(T) k_cull_cta(StepArgs a) {
-    __shared__ float s_frustum[24];
+    __shared__ __align__(16) float s_frustum[24];
     __shared__ uint32_t s_warp[2 * (T / 32)];
     const uint32_t E = a.entities;
     unsigned long long cta_visible = 0, cta_mask_sum = 0, cta_worlds = 0;
@@ -315,79 +185,6 @@ template <int T> __global__ void __launch_bounds__(T) k_cull_cta(StepArgs a) {
         cta_worlds += 1;
     }
     if (threadIdx.x == 0) publish_stats(a, cta_visible, cta_mask_sum, cta_worlds);
-}
-
-// ---------------------------------------------------------------------------------------------
-// host side: argument checking and launches
-// ---------------------------------------------------------------------------------------------
-struct Fail {
-    const char *what;
-};
-
-Plane plane_of(const FimoB200_ResourceView *v, uint32_t scope, uint32_t components, uint64_t count, uint64_t n_worlds,
-               const char *name) {
-    if (!v || !v->device_ptr) throw Fail{name};
-    if (v->elem_bytes != 4 || v->scope != scope || (components && v->components != components) || v->count != count ||
-        v->n_worlds != n_worlds || v->comp_stride != 4 * count || v->world_stride != 4ull * v->components * count)
-        throw Fail{name};
-    return Plane{(uint32_t *)v->device_ptr, v->world_stride / 4};
-}
-
-FimoStatus fail(const char *what) {
-    std::fprintf(stderr, "fimo_worlds_b200: built-in system: resource `%s` does not have the expected shape\n", what);
-    return FIMO_STATUS_ERROR;
-}
-
-int sm_count(int device) {
-    static int cached[64] = {0};
-    if (device < 0 || device >= 64) device = 0;
-    if (!cached[device]) cudaDeviceGetAttribute(&cached[device], cudaDevAttrMultiProcessorCount, device);
-    return cached[device] ? cached[device] : 148;
-}
-
-constexpr size_t kMaxDynamicSmem = 200 * 1024; // of the 227 KB a CTA may use on sm_100a
-
-template <typename K> bool allow_smem(K kernel, size_t bytes) {
-    return cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes) == cudaSuccess;
-}
-
-FimoStatus check_launch(const char *name) {
-    const cudaError_t err = cudaGetLastError();
-    if (err == cudaSuccess) return FIMO_STATUS_OK;
-    std::fprintf(stderr, "fimo_worlds_b200: launch of %s failed: %s\n", name, cudaGetErrorString(err));
-    return FIMO_STATUS_ERROR;
-}
-
-void fill_propagate(StepArgs &a, const FimoB200_ResourceView *world, const FimoB200_ResourceView *pos,
-                    const FimoB200_ResourceView *rot, const FimoB200_ResourceView *scale,
-                    const FimoB200_ResourceView *parent, const FimoB200_ResourceView *level_start, uint64_t W, uint64_t E) {
-    a.world = plane_of(world, FIMO_B200_SCOPE_ENTITY, 12, E, W, "world");
-    a.pos = plane_of(pos, FIMO_B200_SCOPE_ENTITY, 3, E, W, "pos");
-    a.rot = plane_of(rot, FIMO_B200_SCOPE_ENTITY, 4, E, W, "rot");
-    a.scale = plane_of(scale, FIMO_B200_SCOPE_ENTITY, 1, E, W, "scale");
-    a.parent = plane_of(parent, FIMO_B200_SCOPE_ENTITY, 1, E, W, "parent");
-    a.level_start = plane_of(level_start, FIMO_B200_SCOPE_WORLD, 0, 1, W, "level_start");
-    if (level_start->components < 2 || level_start->components > kMaxLevels + 1) throw Fail{"level_start"};
-    a.levels = level_start->components - 1;
-}
-
-void fill_cull(StepArgs &a, const FimoB200_ResourceView *mask, const FimoB200_ResourceView *list,
-               const FimoB200_ResourceView *count, const FimoB200_ResourceView *stats, const FimoB200_ResourceView *world,
-               const FimoB200_ResourceView *aabb_c, const FimoB200_ResourceView *aabb_h,
-               const FimoB200_ResourceView *frustum, void *scratch, uint64_t W, uint64_t E) {
-    a.vis_mask = plane_of(mask, FIMO_B200_SCOPE_ENTITY_BITS, 1, (E + 31) / 32, W, "vis_mask");
-    a.vis_list = plane_of(list, FIMO_B200_SCOPE_ENTITY, 1, E, W, "vis_list");
-    a.vis_count = plane_of(count, FIMO_B200_SCOPE_WORLD, 1, 1, W, "vis_count");
-    a.world = plane_of(world, FIMO_B200_SCOPE_ENTITY, 12, E, W, "world");
-    a.aabb_c = plane_of(aabb_c, FIMO_B200_SCOPE_ENTITY, 3, E, W, "aabb_c");
-    a.aabb_h = plane_of(aabb_h, FIMO_B200_SCOPE_ENTITY, 3, E, W, "aabb_h");
-    a.frustum = plane_of(frustum, FIMO_B200_SCOPE_WORLD, 24, 1, W, "frustum");
-    if (!stats || !stats->device_ptr || stats->scope != FIMO_B200_SCOPE_BATCH || stats->components != 2 * FIMO_B200_STAT_WORDS)
-        throw Fail{"stats"};
-    if (!scratch) throw Fail{"cull scratch"};
-    a.stats = (unsigned long long *)stats->device_ptr;
-    a.scratch = (unsigned long long *)scratch;
-    a.mask_words = (uint32_t)((E + 31) / 32);
 }
 
 } // namespace
@@ -464,11 +261,11 @@ FimoStatus builtin_cull(void *system, const FimoB200_ResourceView *const *exclus
     }
 }
 
-bool world_step_supported(const WorldStepViews &v) {
+bool world_step_supported_v1(const WorldStepViews &v) {
     return v.world && 48 * v.world->count <= kMaxDynamicSmem && v.world->count > 0;
 }
 
-FimoStatus world_step_launch(const WorldStepViews &v, void *cull_scratch, const FimoB200_LaunchInfo *info) {
+FimoStatus world_step_launch_v1(const WorldStepViews &v, void *cull_scratch, const FimoB200_LaunchInfo *info) {
     const uint64_t W = info->n_worlds, E = info->entities_per_world;
     if (W == 0 || E == 0) return FIMO_STATUS_OK;
     try {

@@ -1,0 +1,215 @@
+// kernels_common.cuh — math, argument blocks and host-side launch helpers shared by kernels.cu
+// (per-system kernels, v1 world-step) and world_step.cu (TMA-pipelined world-step).
+#pragma once
+#include <cuda_runtime.h>
+
+#include <cstdint>
+#include <cstdio>
+
+#include "device.h"
+
+namespace fb::dev {
+namespace {
+
+constexpr uint32_t kRoot = FIMO_B200_PARENT_ROOT;
+constexpr int kMaxLevels = 32;
+constexpr unsigned kFull = 0xFFFFFFFFu;
+
+// ---------------------------------------------------------------------------------------------
+// math (each line is one rounding)
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ float mul(float a, float b) { return __fmul_rn(a, b); }
+__device__ __forceinline__ float add(float a, float b) { return __fadd_rn(a, b); }
+__device__ __forceinline__ float sub(float a, float b) { return __fsub_rn(a, b); }
+__device__ __forceinline__ float fma1(float a, float b, float c) { return __fmaf_rn(a, b, c); } // one rounding
+
+// local = T(pos) * R(quat x,y,z,w) * S(uniform s): 3x4 row-major affine.  33 roundings.
+__device__ __forceinline__ void local_trs(float (&L)[12], float px, float py, float pz, float x, float y, float z, float w,
+                                          float s) {
+    const float x2 = add(x, x), y2 = add(y, y), z2 = add(z, z);
+    const float xx = mul(x, x2), yy = mul(y, y2), zz = mul(z, z2);
+    const float xy = mul(x, y2), xz = mul(x, z2), yz = mul(y, z2);
+    const float wx = mul(w, x2), wy = mul(w, y2), wz = mul(w, z2);
+    L[0] = fma1(-add(yy, zz), s, s), L[1] = mul(sub(xy, wz), s), L[2] = mul(add(xz, wy), s), L[3] = px;
+    L[4] = mul(add(xy, wz), s), L[5] = fma1(-add(xx, zz), s, s), L[6] = mul(sub(yz, wx), s), L[7] = py;
+    L[8] = mul(sub(xz, wy), s), L[9] = mul(add(yz, wx), s), L[10] = fma1(-add(xx, yy), s, s), L[11] = pz;
+}
+
+// W = P o L  (both 3x4 affine): 36 roundings
+__device__ __forceinline__ void compose(float (&W)[12], const float (&P)[12], const float (&L)[12]) {
+#pragma unroll
+    for (int r = 0; r < 3; r++) {
+        const float a = P[r * 4 + 0], b = P[r * 4 + 1], c = P[r * 4 + 2], t = P[r * 4 + 3];
+#pragma unroll
+        for (int col = 0; col < 3; col++) W[r * 4 + col] = fma1(c, L[8 + col], fma1(b, L[4 + col], mul(a, L[col])));
+        W[r * 4 + 3] = fma1(c, L[11], fma1(b, L[7], fma1(a, L[3], t)));
+    }
+}
+
+// world-space AABB of (c,h) under W, tested against 6 planes (nx,ny,nz,d), inside = n.x + d >= 0
+__device__ __forceinline__ bool aabb_visible(const float (&W)[12], float c0, float c1, float c2, float h0, float h1,
+                                             float h2, const float *__restrict__ fr /* 24 floats, shared memory */) {
+    float wc[3], wh[3];
+#pragma unroll
+    for (int r = 0; r < 3; r++) {
+        wc[r] = fma1(W[r * 4 + 2], c2, fma1(W[r * 4 + 1], c1, fma1(W[r * 4 + 0], c0, W[r * 4 + 3])));
+        wh[r] = fma1(fabsf(W[r * 4 + 2]), h2, fma1(fabsf(W[r * 4 + 1]), h1, mul(fabsf(W[r * 4 + 0]), h0)));
+    }
+    bool visible = true;
+#pragma unroll
+    for (int p = 0; p < 6; p++) {
+        const float4 pl = *(const float4 *)(fr + p * 4);
+        float sd = fma1(pl.z, wc[2], fma1(pl.y, wc[1], fma1(pl.x, wc[0], pl.w)));
+        sd = fma1(fabsf(pl.z), wh[2], fma1(fabsf(pl.y), wh[1], fma1(fabsf(pl.x), wh[0], sd)));
+        if (!(sd >= 0.0f)) visible = false;
+    }
+    return visible;
+}
+
+// ---------------------------------------------------------------------------------------------
+// argument blocks (word strides; one block per kernel, passed by value)
+// ---------------------------------------------------------------------------------------------
+struct Plane { // a resource of the batch
+    uint32_t *base;
+    uint64_t world_words;
+};
+__device__ __forceinline__ float *fptr(const Plane &p, uint64_t w) { return (float *)(p.base + w * p.world_words); }
+__device__ __forceinline__ uint32_t *uptr(const Plane &p, uint64_t w) { return p.base + w * p.world_words; }
+
+struct StepArgs {
+    Plane pos, vel, dt;                             // integrate
+    Plane world, rot, scale, parent, level_start;   // propagate
+    Plane vis_mask, vis_list, vis_count;            // cull outputs
+    Plane aabb_c, aabb_h, frustum;                  // cull inputs
+    unsigned long long *stats;                      // FIMO_B200_STAT_* words of the batch
+    unsigned long long *scratch;                    // [0..3] accumulators, [4] ticket
+    uint32_t n_worlds, entities, levels, mask_words;
+};
+
+// One entity of one hierarchy level: integrate (optional), build the local transform, compose with
+// the parent's world transform (read through `parent_world(i, p)`), hand the result to `emit(i, v)`.
+template <bool kIntegrate, typename ParentFn, typename EmitFn>
+__device__ __forceinline__ void propagate_entity(uint32_t e, uint32_t E, float *__restrict__ pos, const float *__restrict__ vel,
+                                                 float dt, const float *__restrict__ rot, const float *__restrict__ scale,
+                                                 const uint32_t *__restrict__ parent, ParentFn parent_world, EmitFn emit) {
+    float px = pos[e], py = pos[E + e], pz = pos[2 * E + e];
+    if (kIntegrate) {
+        px = fma1(vel[e], dt, px);
+        py = fma1(vel[E + e], dt, py);
+        pz = fma1(vel[2 * E + e], dt, pz);
+        pos[e] = px, pos[E + e] = py, pos[2 * E + e] = pz;
+    }
+    float L[12], W[12];
+    local_trs(L, px, py, pz, rot[e], rot[E + e], rot[2 * E + e], rot[3 * E + e], scale[e]);
+    const uint32_t p = parent[e];
+    if (p == kRoot) {
+#pragma unroll
+        for (int i = 0; i < 12; i++) W[i] = L[i];
+    } else {
+        float P[12];
+#pragma unroll
+        for (int i = 0; i < 12; i++) P[i] = parent_world(i, p);
+        compose(W, P, L);
+    }
+#pragma unroll
+    for (int i = 0; i < 12; i++) emit(i, W[i]);
+}
+
+// Folds one CTA's statistics into the batch accumulators; the last CTA of the grid publishes them
+// and re-arms the scratch block (so no memset node is needed between generations).
+__device__ __forceinline__ void publish_stats(const StepArgs &a, unsigned long long visible, unsigned long long mask_sum,
+                                              unsigned long long worlds) {
+    atomicAdd(&a.scratch[0], visible);
+    atomicAdd(&a.scratch[1], mask_sum);
+    atomicAdd(&a.scratch[2], worlds);
+    __threadfence();
+    const unsigned long long ticket = atomicAdd(&a.scratch[4], 1ull);
+    if (ticket == (unsigned long long)gridDim.x - 1) {
+        __threadfence();
+        const unsigned long long v = atomicExch(&a.scratch[0], 0ull);
+        const unsigned long long m = atomicExch(&a.scratch[1], 0ull);
+        const unsigned long long n = atomicExch(&a.scratch[2], 0ull);
+        a.stats[FIMO_B200_STAT_VISIBLE] = v;
+        a.stats[FIMO_B200_STAT_ENTITIES] = n * (unsigned long long)a.entities;
+        a.stats[FIMO_B200_STAT_MASK_SUM] = m;
+        a.stats[FIMO_B200_STAT_WORLDS] = n;
+        a.stats[FIMO_B200_STAT_STEPS] += n;
+        atomicExch(&a.scratch[4], 0ull);
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// host side: argument checking and launches
+// ---------------------------------------------------------------------------------------------
+struct Fail {
+    const char *what;
+};
+
+Plane plane_of(const FimoB200_ResourceView *v, uint32_t scope, uint32_t components, uint64_t count, uint64_t n_worlds,
+               const char *name) {
+    if (!v || !v->device_ptr) throw Fail{name};
+    if (v->elem_bytes != 4 || v->scope != scope || (components && v->components != components) || v->count != count ||
+        v->n_worlds != n_worlds || v->comp_stride != 4 * count || v->world_stride != 4ull * v->components * count)
+        throw Fail{name};
+    return Plane{(uint32_t *)v->device_ptr, v->world_stride / 4};
+}
+
+FimoStatus fail(const char *what) {
+    std::fprintf(stderr, "fimo_worlds_b200: built-in system: resource `%s` does not have the expected shape\n", what);
+    return FIMO_STATUS_ERROR;
+}
+
+int sm_count(int device) {
+    static int cached[64] = {0};
+    if (device < 0 || device >= 64) device = 0;
+    if (!cached[device]) cudaDeviceGetAttribute(&cached[device], cudaDevAttrMultiProcessorCount, device);
+    return cached[device] ? cached[device] : 148;
+}
+
+constexpr size_t kMaxDynamicSmem = 200 * 1024; // of the 227 KB a CTA may use on sm_100a
+
+template <typename K> bool allow_smem(K kernel, size_t bytes) {
+    return cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes) == cudaSuccess;
+}
+
+FimoStatus check_launch(const char *name) {
+    const cudaError_t err = cudaGetLastError();
+    if (err == cudaSuccess) return FIMO_STATUS_OK;
+    std::fprintf(stderr, "fimo_worlds_b200: launch of %s failed: %s\n", name, cudaGetErrorString(err));
+    return FIMO_STATUS_ERROR;
+}
+
+void fill_propagate(StepArgs &a, const FimoB200_ResourceView *world, const FimoB200_ResourceView *pos,
+                    const FimoB200_ResourceView *rot, const FimoB200_ResourceView *scale,
+                    const FimoB200_ResourceView *parent, const FimoB200_ResourceView *level_start, uint64_t W, uint64_t E) {
+    a.world = plane_of(world, FIMO_B200_SCOPE_ENTITY, 12, E, W, "world");
+    a.pos = plane_of(pos, FIMO_B200_SCOPE_ENTITY, 3, E, W, "pos");
+    a.rot = plane_of(rot, FIMO_B200_SCOPE_ENTITY, 4, E, W, "rot");
+    a.scale = plane_of(scale, FIMO_B200_SCOPE_ENTITY, 1, E, W, "scale");
+    a.parent = plane_of(parent, FIMO_B200_SCOPE_ENTITY, 1, E, W, "parent");
+    a.level_start = plane_of(level_start, FIMO_B200_SCOPE_WORLD, 0, 1, W, "level_start");
+    if (level_start->components < 2 || level_start->components > kMaxLevels + 1) throw Fail{"level_start"};
+    a.levels = level_start->components - 1;
+}
+
+void fill_cull(StepArgs &a, const FimoB200_ResourceView *mask, const FimoB200_ResourceView *list,
+               const FimoB200_ResourceView *count, const FimoB200_ResourceView *stats, const FimoB200_ResourceView *world,
+               const FimoB200_ResourceView *aabb_c, const FimoB200_ResourceView *aabb_h,
+               const FimoB200_ResourceView *frustum, void *scratch, uint64_t W, uint64_t E) {
+    a.vis_mask = plane_of(mask, FIMO_B200_SCOPE_ENTITY_BITS, 1, (E + 31) / 32, W, "vis_mask");
+    a.vis_list = plane_of(list, FIMO_B200_SCOPE_ENTITY, 1, E, W, "vis_list");
+    a.vis_count = plane_of(count, FIMO_B200_SCOPE_WORLD, 1, 1, W, "vis_count");
+    a.world = plane_of(world, FIMO_B200_SCOPE_ENTITY, 12, E, W, "world");
+    a.aabb_c = plane_of(aabb_c, FIMO_B200_SCOPE_ENTITY, 3, E, W, "aabb_c");
+    a.aabb_h = plane_of(aabb_h, FIMO_B200_SCOPE_ENTITY, 3, E, W, "aabb_h");
+    a.frustum = plane_of(frustum, FIMO_B200_SCOPE_WORLD, 24, 1, W, "frustum");
+    if (!stats || !stats->device_ptr || stats->scope != FIMO_B200_SCOPE_BATCH || stats->components != 2 * FIMO_B200_STAT_WORDS)
+        throw Fail{"stats"};
+    if (!scratch) throw Fail{"cull scratch"};
+    a.stats = (unsigned long long *)stats->device_ptr;
+    a.scratch = (unsigned long long *)scratch;
+    a.mask_words = (uint32_t)((E + 31) / 32);
+}
+
+} // namespace
+} // namespace fb::dev

@@ -158,6 +158,21 @@ def bytes_per_entity_step(f_vis: float) -> float:
     return 72.0 + 60.125 + 4.0 * f_vis
 
 
+def integrate_matches(pos0: np.ndarray, vel: np.ndarray, steps: int, pos: np.ndarray) -> bool:
+    """pos == `steps` x fma(vel, dt, pos0) in binary32.  The product of two binary32 values is exact in
+    binary64, so one step is round32(round64(v*dt + p)); the double rounding can differ from a true fused
+    multiply-add only in the last bit, which is what is allowed here (per step)."""
+    lo = pos0.astype(np.float32).copy()
+    hi = lo.copy()
+    step = vel.astype(np.float64) * np.float64(DT)
+    for _ in range(steps):
+        a = (lo.astype(np.float64) + step).astype(np.float32)
+        b = (hi.astype(np.float64) + step).astype(np.float32)
+        lo = np.minimum(np.nextafter(a, np.float32(-np.inf)), np.nextafter(b, np.float32(-np.inf)))
+        hi = np.maximum(np.nextafter(a, np.float32(np.inf)), np.nextafter(b, np.float32(np.inf)))
+    return bool(((pos >= lo) & (pos <= hi)).all())
+
+
 @dataclass
 class RigOptions:
     fused: bool = True  # let the DAG compiler fuse integrate -> propagate -> cull into one world-step kernel

@@ -5,9 +5,10 @@
  * not a restatement of reference code: it is the DEFINITION of the three build-defined systems
  * named in BASELINE.json (integrate -> transform propagate -> AABB frustum cull), written as
  * plain scalar loops.  "Parity unpinned" for this arithmetic: nothing in the reference can pin it.
- * The CUDA kernels must reproduce these results bit for bit (every float op below is a single
- * IEEE-754 binary32 operation rounded to nearest-even, in exactly the order written; build with
- * -ffp-contract=off, device with --fmad=false).
+ * The CUDA kernels must reproduce these results bit for bit (every float op is a single
+ * IEEE-754 binary32 operation rounded to nearest-even — an add, a multiply, or an explicitly written
+ * fused multiply-add fmaf() — in exactly the order written; build with -ffp-contract=off so the
+ * compiler fuses nothing on its own, device with --fmad=false and __fmaf_rn where fmaf is written).
  *
  * Data layout of one world: component planes, plane k of a C-component
  * resource with E elements is at words [k*E, (k+1)*E).

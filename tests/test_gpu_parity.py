@@ -59,10 +59,19 @@ def test_three_system_chain_matches_oracle(oracle, product, W, E, D, steps, mode
     assert st[abi.STAT_STEPS] == W * steps and st[abi.STAT_WORLDS] == W
 
 
-def test_large_world_uses_per_level_propagate(oracle, product):
-    """configs[2] world shape (64k entities, depth 8): too large for one CTA's shared memory."""
-    got, want, info = run_both(oracle, product, 2, 65536, 8, 3)
+def test_large_world_per_level_propagate(oracle, product):
+    """configs[2] world shape (64k entities, depth 8), one kernel per system: the world is too large for one
+    CTA's shared memory, so propagate runs as one launch per hierarchy level."""
+    got, want, info = run_both(oracle, product, 2, 65536, 8, 3, synth.RigOptions(fused=False))
     assert info.fused_world_step == 0 and info.kernel_launches_per_generation == 1 + 8 + 1
+    problems = synth.compare_outputs(got, want, FLOAT_RTOL)
+    assert not problems, "\n".join(problems)
+
+
+def test_large_world_fused_pipeline(oracle, product):
+    """Same shape through the fused pipelined kernel: parents beyond the shared-memory window come from L2."""
+    got, want, info = run_both(oracle, product, 3, 65536, 8, 3)
+    assert info.fused_world_step == 1 and info.kernel_launches_per_generation == 1
     problems = synth.compare_outputs(got, want, FLOAT_RTOL)
     assert not problems, "\n".join(problems)
 
@@ -87,11 +96,7 @@ def test_full_size_properties(product):
     for w in (0, 1, 2047, 4095):                                          # list == ascending indices of the mask
         idx = np.nonzero(bits[w])[0].astype(np.uint32)
         assert np.array_equal(out["vis_list"][w, 0, :counts[w]], idx)
-    expect = host["pos"].copy()                                           # integrate is exactly K fp32 steps
-    step = (host["vel"] * synth.DT).astype(np.float32)
-    for _ in range(K):
-        expect = (expect + step).astype(np.float32)
-    assert np.array_equal(expect.view(np.uint32), out["pos"].view(np.uint32))
+    assert synth.integrate_matches(host["pos"], host["vel"], K, out["pos"])   # K x pos = fma(vel, dt, pos)
     roots = host["parent"][:, 0, :] == abi.PARENT_ROOT                    # roots: world translation == pos
     for k in range(3):
         assert np.array_equal(out["world"][:, 4 * k + 3, :][roots], out["pos"][:, k, :][roots])

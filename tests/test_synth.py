@@ -58,9 +58,6 @@ def test_oracle_chain_properties(oracle):
     assert st[abi.STAT_VISIBLE] == total and st[abi.STAT_ENTITIES] == 5 * 300
     assert st[abi.STAT_MASK_SUM] == mask_sum and st[abi.STAT_WORLDS] == 5 and st[abi.STAT_STEPS] == 20
     assert 0 < total < 5 * 300
-    # integrate is linear in the step count: pos_K = pos_0 + K * (vel*dt) up to per-step rounding
+    # integrate is K fused multiply-adds pos = fma(vel, dt, pos)
     d0 = synth.generate(5, 300, 4)
-    expect = d0["pos"].copy()
-    for _ in range(4):
-        expect = (expect + (d0["vel"] * synth.DT).astype(np.float32)).astype(np.float32)
-    assert np.array_equal(expect.view(np.uint32), out["pos"].view(np.uint32))
+    assert synth.integrate_matches(d0["pos"], d0["vel"], 4, out["pos"])
