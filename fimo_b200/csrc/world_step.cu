@@ -59,6 +59,22 @@ __device__ __forceinline__ void bulk_load(void *dst, const void *src, uint32_t b
                  : "memory");
 }
 
+// 1-D bulk async copy shared -> global (TMA engine), tracked by the issuing thread's bulk async-group.
+__device__ __forceinline__ void bulk_store(void *dst, const void *src, uint32_t bytes) {
+    asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst), "r"(smem_addr(src)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait_read_all() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+__device__ __forceinline__ void mbar_arrive(uint64_t *bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_addr(bar)) : "memory");
+}
+// generic-proxy writes to shared memory become visible to the async proxy (the TMA store reads them)
+__device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+template <int kThreads> __device__ __forceinline__ void consumer_sync() { // the T compute threads only (barrier 1)
+    asm volatile("bar.sync 1, %0;" ::"n"(kThreads) : "memory");
+}
+
 struct PipeArgs {
     StepArgs a;
     uint32_t stages;   // ring depth (chunks)
@@ -77,47 +93,87 @@ __device__ __forceinline__ const uint32_t *plane_src(const StepArgs &a, int p, u
     return uptr(a.aabb_h, w) + (uint64_t)(p - 15) * E;
 }
 
+// Warp-specialised: warps [0, T/32) compute (one entity of the chunk per thread), the last warp drives the
+// TMA engine — it loads chunk inputs into the ring and stores the finished chunk's outputs, which the
+// compute threads leave in the same ring stage (world matrices over planes 0-11, new positions over 12-14).
 template <int T, int kMinBlocks>
-__global__ void __launch_bounds__(T, kMinBlocks) k_world_step_pipe(const PipeArgs pa) {
+__global__ void __launch_bounds__(T + 32, kMinBlocks) k_world_step_pipe(const PipeArgs pa) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     const StepArgs &a = pa.a;
     const uint32_t E = a.entities, N = pa.stages, cap = pa.lvl_cap, nc = pa.chunks;
-    float *ring = (float *)smem_raw;                             // [N][kPlanes][T]
-    float *s_lvl = ring + (size_t)N * kPlanes * T;               // [12][cap]
-    uint64_t *full = (uint64_t *)(s_lvl + (size_t)12 * cap);      // [N]   (cap is even => 8-byte aligned)
+    float *ring = (float *)smem_raw;                        // [N][kPlanes][T]
+    float *s_lvl = ring + (size_t)N * kPlanes * T;          // [12][cap]
+    uint64_t *full = (uint64_t *)(s_lvl + (size_t)12 * cap); // [N] inputs have landed     (cap is even => 8-byte aligned)
+    uint64_t *done = full + N;                               // [N] outputs are in the stage
     __shared__ __align__(16) float s_frustum[24];
     __shared__ uint32_t s_ls[kMaxLevels + 1];
     __shared__ float s_dt;
-    __shared__ uint32_t s_cnt[T / 32];
+    __shared__ __align__(16) uint32_t s_cnt[2][T / 32];
+    __shared__ unsigned long long s_sum;
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     constexpr int kWarps = T / 32;
     const uint32_t levels = a.levels;
-
-    // worlds of this CTA: blockIdx.x, blockIdx.x + gridDim.x, ...
     const uint32_t my_worlds = a.n_worlds > blockIdx.x ? (a.n_worlds - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
     const uint32_t total = my_worlds * nc; // chunk iterations of this CTA
 
-    // producer: warp 0 issues the 18 plane copies of chunk iteration `it` into ring stage it % N
-    auto produce = [&](uint32_t it) {
-        const uint32_t k = it / nc, c = it - k * nc;
-        const uint64_t w = blockIdx.x + (uint64_t)k * gridDim.x;
-        const uint32_t first = c * T;
-        const uint32_t n = min((uint32_t)T, E - first); // multiple of 4 (E % 4 == 0)
-        const uint32_t s = it % N;
-        if (lane == 0) mbar_expect_tx(&full[s], n * 4u * kPlanes);
-        __syncwarp();
-        if (lane < kPlanes) bulk_load(ring + ((size_t)s * kPlanes + lane) * T, plane_src(a, lane, w, E) + first, n * 4u, &full[s]);
-    };
-
     if (tid == 0) {
-        for (uint32_t s = 0; s < N; s++) mbar_init(&full[s], 1);
+        for (uint32_t s = 0; s < N; s++) {
+            mbar_init(&full[s], 1);
+            mbar_init(&done[s], kWarps);
+        }
+        s_sum = 0;
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncthreads();
-    if (warp == 0)
-        for (uint32_t it = 0; it < N && it < total; it++) produce(it);
 
+    if (warp == kWarps) {
+        // ------------------------------- TMA warp -------------------------------------------------
+        if (lane != 0) return;
+        uint32_t k = 0, c = 0, s = 0, round = 0;       // position of the chunk being loaded
+        uint32_t sk = 0, sc = 0;                        // position of the chunk being stored (N behind)
+        auto store_chunk = [&](uint32_t stage, uint32_t wk, uint32_t wc) {
+            const uint64_t w = blockIdx.x + (uint64_t)wk * gridDim.x;
+            const uint32_t first = wc * T, bytes = min((uint32_t)T, E - first) * 4u;
+            const float *st = ring + (size_t)stage * kPlanes * T;
+            float *world = fptr(a.world, w) + first;
+            float *pos = fptr(a.pos, w) + first;
+#pragma unroll
+            for (int i = 0; i < 12; i++) bulk_store(world + (uint64_t)i * E, st + i * T, bytes);
+#pragma unroll
+            for (int i = 0; i < 3; i++) bulk_store(pos + (uint64_t)i * E, st + (12 + i) * T, bytes);
+            bulk_commit();
+        };
+        for (uint32_t it = 0; it < total; it++) {
+            if (it >= N) { // the stage still holds chunk it-N: wait for its outputs, drain them, then reuse it
+                mbar_wait(&done[s], (round - 1) & 1u);
+                store_chunk(s, sk, sc);
+                if (++sc == nc) sc = 0, sk++;
+                bulk_wait_read_all();
+            }
+            const uint64_t w = blockIdx.x + (uint64_t)k * gridDim.x;
+            const uint32_t first = c * T, bytes = min((uint32_t)T, E - first) * 4u; // multiple of 16 (E % 4 == 0)
+            float *st = ring + (size_t)s * kPlanes * T;
+            mbar_expect_tx(&full[s], bytes * kPlanes);
+#pragma unroll
+            for (int p = 0; p < kPlanes; p++) bulk_load(st + p * T, plane_src(a, p, w, E) + first, bytes, &full[s]);
+            if (++c == nc) c = 0, k++;
+            if (++s == N) s = 0, round++;
+        }
+        // drain the last min(N, total) chunks
+        const uint32_t tail = total < N ? total : N;
+        uint32_t ds = total < N ? 0 : s, dround = total < N ? 0 : round - 1;
+        for (uint32_t j = 0; j < tail; j++) {
+            mbar_wait(&done[ds], dround & 1u);
+            store_chunk(ds, sk, sc);
+            if (++sc == nc) sc = 0, sk++;
+            if (++ds == N) ds = 0, dround++;
+        }
+        bulk_wait_all();
+        return;
+    }
+
+    // ----------------------------------- compute warps ------------------------------------------------
     // per-world constants travel one world ahead in a register: frustum (24), dt (1), level_start (levels+1)
     auto const_word = [&](uint64_t w) -> uint32_t {
         if (tid < 24) return uptr(a.frustum, w)[tid];
@@ -126,21 +182,24 @@ __global__ void __launch_bounds__(T, kMinBlocks) k_world_step_pipe(const PipeArg
         return 0u;
     };
     uint32_t next_const = my_worlds ? const_word(blockIdx.x) : 0u;
-
-    unsigned long long cta_visible = 0, cta_mask_sum = 0; // thread 0 / lane 0 of each warp
-    uint32_t running = 0;                                  // visible entities of the current world so far
+    unsigned long long cta_visible = 0, warp_mask_sum = 0; // thread 0 / lane 0 of each warp
+    uint32_t running = 0;                                   // visible entities of the current world so far
+    uint32_t k = 0, c = 0, s = 0, parity = 0;
+    uint64_t w = blockIdx.x;
+    uint32_t *mask_out = nullptr, *list_out = nullptr;
+    float *world_out = nullptr;
 
     for (uint32_t it = 0; it < total; it++) {
-        const uint32_t k = it / nc, c = it - k * nc;
-        const uint64_t w = blockIdx.x + (uint64_t)k * gridDim.x;
-        const uint32_t s = it % N;
         if (c == 0) { // a new world begins: publish its constants, fetch the next world's
             if (tid < 24) s_frustum[tid] = __uint_as_float(next_const);
             if (tid == 24) s_dt = __uint_as_float(next_const);
             if (tid >= 32 && tid <= 32 + (int)levels) s_ls[tid - 32] = next_const;
             if (k + 1 < my_worlds) next_const = const_word(w + gridDim.x);
             running = 0;
-            __syncthreads();
+            mask_out = uptr(a.vis_mask, w);
+            list_out = uptr(a.vis_list, w);
+            world_out = fptr(a.world, w);
+            consumer_sync<T>();
         }
         const uint32_t first = c * T;
         const uint32_t e = first + tid;
@@ -155,23 +214,18 @@ __global__ void __launch_bounds__(T, kMinBlocks) k_world_step_pipe(const PipeArg
             l_me += (e >= start);
         }
 
-        mbar_wait(&full[s], (it / N) & 1u);
-        const float *st = ring + (size_t)s * kPlanes * T + tid;
+        mbar_wait(&full[s], parity);
+        float *st = ring + (size_t)s * kPlanes * T + tid;
         bool vis = false;
         for (uint32_t l = l_lo; l <= l_hi; l++) {
             if (valid && l_me == l) {
-                // integrate
                 const float dt = s_dt;
-                const float px = fma1(st[3 * T], dt, st[0 * T]);
+                const float px = fma1(st[3 * T], dt, st[0 * T]); // integrate
                 const float py = fma1(st[4 * T], dt, st[1 * T]);
                 const float pz = fma1(st[5 * T], dt, st[2 * T]);
-                float *pos = fptr(a.pos, w);
-                pos[e] = px, pos[E + e] = py, pos[2 * E + e] = pz;
-                // propagate
                 float L[12], Wm[12];
                 local_trs(L, px, py, pz, st[6 * T], st[7 * T], st[8 * T], st[9 * T], st[10 * T]);
                 const uint32_t p = __float_as_uint(st[11 * T]);
-                float *world = fptr(a.world, w);
                 if (p == kRoot) {
 #pragma unroll
                     for (int i = 0; i < 12; i++) Wm[i] = L[i];
@@ -180,57 +234,62 @@ __global__ void __launch_bounds__(T, kMinBlocks) k_world_step_pipe(const PipeArg
                     if (p < cap) {
 #pragma unroll
                         for (int i = 0; i < 12; i++) P[i] = s_lvl[i * cap + p];
-                    } else { // the parent did not fit the shared-memory window: this CTA wrote it to HBM earlier
+                    } else { // beyond the shared-memory window: written to HBM by this CTA below, read back through L2
 #pragma unroll
-                        for (int i = 0; i < 12; i++) P[i] = __ldcg(world + (uint64_t)i * E + p);
+                        for (int i = 0; i < 12; i++) P[i] = __ldcg(world_out + (uint64_t)i * E + p);
                     }
                     compose(Wm, P, L);
                 }
-#pragma unroll
-                for (int i = 0; i < 12; i++) world[(uint64_t)i * E + e] = Wm[i];
-                if (e < cap && l + 1 < levels) {
-#pragma unroll
-                    for (int i = 0; i < 12; i++) s_lvl[i * cap + e] = Wm[i];
-                }
-                // cull
                 vis = aabb_visible(Wm, st[12 * T], st[13 * T], st[14 * T], st[15 * T], st[16 * T], st[17 * T], s_frustum);
+                if (l + 1 < levels) { // may be somebody's parent
+                    if (e < cap) {
+#pragma unroll
+                        for (int i = 0; i < 12; i++) s_lvl[i * cap + e] = Wm[i];
+                    } else {
+#pragma unroll
+                        for (int i = 0; i < 12; i++) world_out[(uint64_t)i * E + e] = Wm[i];
+                    }
+                }
+                // outputs replace this thread's own (now dead) column of the stage; the TMA warp stores them
+#pragma unroll
+                for (int i = 0; i < 12; i++) st[i * T] = Wm[i];
+                st[12 * T] = px, st[13 * T] = py, st[14 * T] = pz;
             }
-            if (l < l_hi) __syncthreads(); // the next level of this chunk reads what this one wrote
+            if (l < l_hi) consumer_sync<T>(); // the next level of this chunk reads what this one wrote
         }
+        fence_async_smem();
         // mask word + ordered compaction
         const unsigned ballot = __ballot_sync(kFull, vis);
+        uint32_t *cnt = s_cnt[it & 1];
         if (lane == 0) {
-            if ((e >> 5) < a.mask_words) uptr(a.vis_mask, w)[e >> 5] = ballot;
-            cta_mask_sum += ballot;
-            s_cnt[warp] = __popc(ballot);
+            mbar_arrive(&done[s]); // this warp's outputs are in the stage
+            if ((e >> 5) < a.mask_words) mask_out[e >> 5] = ballot;
+            warp_mask_sum += ballot;
+            cnt[warp] = __popc(ballot);
         }
-        __syncthreads();
+        consumer_sync<T>();
         uint32_t before = 0, chunk_total = 0;
 #pragma unroll
         for (int i = 0; i < kWarps; i++) {
-            const uint32_t n = s_cnt[i];
+            const uint32_t n = cnt[i];
             before += (i < warp) ? n : 0u;
             chunk_total += n;
         }
-        if (vis) uptr(a.vis_list, w)[running + before + __popc(ballot & ((1u << lane) - 1u))] = e;
+        if (vis) list_out[running + before + __popc(ballot & ((1u << lane) - 1u))] = e;
         running += chunk_total;
-        if (c + 1 == nc && tid == 0) {
-            uptr(a.vis_count, w)[0] = running;
-            cta_visible += running;
+        if (++c == nc) {
+            if (tid == 0) {
+                uptr(a.vis_count, w)[0] = running;
+                cta_visible += running;
+            }
+            c = 0, k++, w += gridDim.x;
         }
-        __syncthreads(); // everyone is done with ring stage s, s_cnt and (for the next chunk) s_lvl is complete
-        if (warp == 0 && it + N < total) produce(it + N);
+        if (++s == N) s = 0, parity ^= 1u;
     }
 
     // fold the per-warp mask sums, publish the batch statistics
-    if (lane == 0) {
-        s_cnt[warp] = 0;
-    }
-    __shared__ unsigned long long s_sum;
-    if (tid == 0) s_sum = 0;
-    __syncthreads();
-    if (lane == 0) atomicAdd(&s_sum, cta_mask_sum);
-    __syncthreads();
+    if (lane == 0) atomicAdd(&s_sum, warp_mask_sum);
+    consumer_sync<T>();
     if (tid == 0) publish_stats(a, cta_visible, s_sum, my_worlds);
 }
 
@@ -264,13 +323,13 @@ PipeConfig pipe_config(const WorldStepViews &v) {
     const size_t kBudgetTwo = 110 * 1024, kBudgetOne = 220 * 1024; // per CTA, of the 227 KB / SM
     auto fit = [&](int T, size_t budget, uint32_t stages) {
         PipeConfig c;
-        const size_t ring = (size_t)stages * kPlanes * T * 4 + stages * 8 + 512 /* static */;
+        const size_t ring = (size_t)stages * kPlanes * T * 4 + stages * 16 + 1024 /* static + reserve */;
         if (ring >= budget) return c;
         uint64_t cap = (budget - ring) / 48;
         if (cap > E) cap = E;
         cap &= ~1ull;
         c.threads = T, c.stages = stages, c.lvl_cap = (uint32_t)cap;
-        c.smem = (size_t)stages * kPlanes * T * 4 + (size_t)cap * 48 + stages * 8;
+        c.smem = (size_t)stages * kPlanes * T * 4 + (size_t)cap * 48 + stages * 16;
         return c;
     };
     if (E <= 2048) return fit(256, kBudgetTwo, 4);
@@ -310,12 +369,12 @@ FimoStatus world_step_launch(const WorldStepViews &v, void *cull_scratch, const 
             auto kernel = k_world_step_pipe<256, 2>;
             if (!allow_smem(kernel, cfg.smem)) return check_launch("world_step (shared memory opt-in)");
             const unsigned grid = (unsigned)(W < 2ull * sms ? W : 2ull * sms);
-            kernel<<<grid, 256, cfg.smem, stream>>>(pa);
+            kernel<<<grid, 256 + 32, cfg.smem, stream>>>(pa);
         } else {
             auto kernel = k_world_step_pipe<512, 1>;
             if (!allow_smem(kernel, cfg.smem)) return check_launch("world_step (shared memory opt-in)");
             const unsigned grid = (unsigned)(W < (uint64_t)sms ? W : (uint64_t)sms);
-            kernel<<<grid, 512, cfg.smem, stream>>>(pa);
+            kernel<<<grid, 512 + 32, cfg.smem, stream>>>(pa);
         }
         return check_launch("world_step");
     } catch (const Fail &f) {
