@@ -70,9 +70,20 @@ struct WorldStepViews {
     const FimoB200_ResourceView *vis_mask, *vis_list, *vis_count, *stats;    // cull (exclusive)
     const FimoB200_ResourceView *aabb_c, *aabb_h, *frustum;                  // cull (shared)
 };
-bool world_step_supported(const WorldStepViews &v);
-FimoStatus world_step_launch(const WorldStepViews &v, void *cull_scratch, const FimoB200_LaunchInfo *info);
-const char *world_step_kernel_name(const WorldStepViews &v); // which kernel world_step_launch picks
+// How the fused kernel is launched for a given batch; made once when the executor is compiled (it reads
+// level_start from HBM to size the shared-memory parent window), then reused by every launch.
+struct WorldStepPlan {
+    int threads = 0;            // entities per chunk = compute threads per CTA (128/256/512); 0 = v1 kernel
+    uint32_t blocks_per_sm = 0; // resident CTAs per SM the plan is sized for
+    uint32_t stages = 0;        // ring depth in chunks
+    uint32_t lvl_cap = 0;       // parent matrices kept in shared memory: entities [0, lvl_cap)
+    uint32_t max_parents = 0;   // max over worlds of level_start[levels-1]
+    size_t smem = 0;            // dynamic shared memory per CTA
+};
+bool world_step_plan(const WorldStepViews &v, int device, WorldStepPlan &plan); // false: not fusable
+FimoStatus world_step_launch(const WorldStepViews &v, const WorldStepPlan &plan, void *cull_scratch,
+                             const FimoB200_LaunchInfo *info);
+const char *world_step_kernel_name(const WorldStepPlan &plan); // which kernel world_step_launch picks
 // v1: one CTA per world, whole world's matrices in shared memory, loads through registers (kernels.cu)
 bool world_step_supported_v1(const WorldStepViews &v);
 FimoStatus world_step_launch_v1(const WorldStepViews &v, void *cull_scratch, const FimoB200_LaunchInfo *info);

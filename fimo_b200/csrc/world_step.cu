@@ -20,6 +20,10 @@
 //   * cull compaction: __ballot_sync gives the 32-entity mask word, __popc prefix inside the warp and a
 //     scan over the warps' counts give each visible entity its slot in the ASCENDING index list;
 //   * outputs go straight from registers to HBM as coalesced 128-byte rows per plane.
+#include <algorithm>
+#include <cstdlib>
+#include <vector>
+
 #include "kernels_common.cuh"
 
 namespace fb::dev {
@@ -35,16 +39,18 @@ __device__ __forceinline__ void mbar_init(uint64_t *bar, uint32_t count) {
 __device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, uint32_t bytes) {
     asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_addr(bar)), "r"(bytes) : "memory");
 }
+// try_wait with a suspend-time hint: the thread sleeps in hardware until the phase completes (or the hint
+// expires) instead of spinning through issue slots the compute warps need.
 __device__ __forceinline__ bool mbar_try_wait(uint64_t *bar, uint32_t parity) {
     uint32_t done;
     asm volatile(
             "{\n"
             ".reg .pred p;\n"
-            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n"
             "selp.u32 %0, 1, 0, p;\n"
             "}\n"
             : "=r"(done)
-            : "r"(smem_addr(bar)), "r"(parity)
+            : "r"(smem_addr(bar)), "r"(parity), "r"(0x989680u)
             : "memory");
     return done != 0;
 }
@@ -75,12 +81,24 @@ template <int kThreads> __device__ __forceinline__ void consumer_sync() { // the
     asm volatile("bar.sync 1, %0;" ::"n"(kThreads) : "memory");
 }
 
+
 struct PipeArgs {
     StepArgs a;
     uint32_t stages;   // ring depth (chunks)
     uint32_t lvl_cap;  // parent matrices kept in shared memory: entities [0, lvl_cap) of a world
     uint32_t chunks;   // chunks per world = ceil(E / T)
 };
+
+// Per-world constants, double-buffered in shared memory (world k uses buffer k & 1): the compute threads
+// fetch world k+1's words into a register while world k is being stepped and publish them before the last
+// barrier of world k, so a world boundary costs no extra barrier and no exposed HBM latency.
+struct WorldConst {
+    float frustum[24];              // 6 planes (nx, ny, nz, d); 16-byte aligned for LDS.128
+    uint32_t ls[kMaxLevels + 1];    // level_start
+    float dt;
+    uint32_t pad[2];
+};
+static_assert(sizeof(WorldConst) % 16 == 0, "WorldConst");
 
 // Source plane p of world w (floats / u32), see kPlanes.
 __device__ __forceinline__ const uint32_t *plane_src(const StepArgs &a, int p, uint64_t w, uint32_t E) {
@@ -93,26 +111,72 @@ __device__ __forceinline__ const uint32_t *plane_src(const StepArgs &a, int p, u
     return uptr(a.aabb_h, w) + (uint64_t)(p - 15) * E;
 }
 
-// Warp-specialised: warps [0, T/32) compute (one entity of the chunk per thread), the last warp drives the
-// TMA engine — it loads chunk inputs into the ring and stores the finished chunk's outputs, which the
-// compute threads leave in the same ring stage (world matrices over planes 0-11, new positions over 12-14).
+// The TMA warp (one elected thread): loads chunk inputs into the ring and stores the finished chunk's
+// outputs, which the compute threads leave in the same ring stage (world matrices over planes 0-11, new
+// positions over 12-14).
+template <int T>
+__device__ __forceinline__ void tma_warp(const PipeArgs &pa, float *ring, uint64_t *full, uint64_t *done, uint32_t total) {
+    const StepArgs &a = pa.a;
+    const uint32_t E = a.entities, N = pa.stages, nc = pa.chunks;
+    uint32_t k = 0, c = 0, s = 0, round = 0; // position of the chunk being loaded
+    uint32_t sk = 0, sc = 0;                  // position of the chunk being stored (N behind)
+    auto store_chunk = [&](uint32_t stage, uint32_t wk, uint32_t wc) {
+        const uint64_t w = blockIdx.x + (uint64_t)wk * gridDim.x;
+        const uint32_t first = wc * T, bytes = min((uint32_t)T, E - first) * 4u;
+        const float *st = ring + (size_t)stage * kPlanes * T;
+        float *world = fptr(a.world, w) + first;
+        float *pos = fptr(a.pos, w) + first;
+#pragma unroll
+        for (int i = 0; i < 12; i++) bulk_store(world + (uint64_t)i * E, st + i * T, bytes);
+#pragma unroll
+        for (int i = 0; i < 3; i++) bulk_store(pos + (uint64_t)i * E, st + (12 + i) * T, bytes);
+        bulk_commit();
+    };
+    for (uint32_t it = 0; it < total; it++) {
+        if (it >= N) { // the stage still holds chunk it-N: wait for its outputs, drain them, then reuse it
+            mbar_wait(&done[s], (round - 1) & 1u);
+            store_chunk(s, sk, sc);
+            if (++sc == nc) sc = 0, sk++;
+            bulk_wait_read_all();
+        }
+        const uint64_t w = blockIdx.x + (uint64_t)k * gridDim.x;
+        const uint32_t first = c * T, bytes = min((uint32_t)T, E - first) * 4u; // multiple of 16 (E % 4 == 0)
+        float *st = ring + (size_t)s * kPlanes * T;
+        mbar_expect_tx(&full[s], bytes * kPlanes);
+#pragma unroll
+        for (int p = 0; p < kPlanes; p++) bulk_load(st + p * T, plane_src(a, p, w, E) + first, bytes, &full[s]);
+        if (++c == nc) c = 0, k++;
+        if (++s == N) s = 0, round++;
+    }
+    // drain the last min(N, total) chunks
+    const uint32_t tail = total < N ? total : N;
+    uint32_t ds = total < N ? 0 : s, dround = total < N ? 0 : round - 1;
+    for (uint32_t j = 0; j < tail; j++) {
+        mbar_wait(&done[ds], dround & 1u);
+        store_chunk(ds, sk, sc);
+        if (++sc == nc) sc = 0, sk++;
+        if (++ds == N) ds = 0, dround++;
+    }
+    bulk_wait_all();
+}
+
+// Warp-specialised: warps [0, T/32) compute (one entity of the chunk per thread), the last warp is the TMA warp.
 template <int T, int kMinBlocks>
 __global__ void __launch_bounds__(T + 32, kMinBlocks) k_world_step_pipe(const PipeArgs pa) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     const StepArgs &a = pa.a;
     const uint32_t E = a.entities, N = pa.stages, cap = pa.lvl_cap, nc = pa.chunks;
-    float *ring = (float *)smem_raw;                        // [N][kPlanes][T]
-    float *s_lvl = ring + (size_t)N * kPlanes * T;          // [12][cap]
-    uint64_t *full = (uint64_t *)(s_lvl + (size_t)12 * cap); // [N] inputs have landed     (cap is even => 8-byte aligned)
-    uint64_t *done = full + N;                               // [N] outputs are in the stage
-    __shared__ __align__(16) float s_frustum[24];
-    __shared__ uint32_t s_ls[kMaxLevels + 1];
-    __shared__ float s_dt;
-    __shared__ __align__(16) uint32_t s_cnt[2][T / 32];
+    float *ring = (float *)smem_raw;                              // [N][kPlanes][T] planes
+    float4 *s_win = (float4 *)(ring + (size_t)N * kPlanes * T);   // [cap][3]: parent window, one 48-byte matrix per entity
+    uint64_t *full = (uint64_t *)(s_win + (size_t)3 * cap);       // [N] inputs have landed
+    uint64_t *done = full + N;                                    // [N] outputs are in the stage
+    __shared__ __align__(16) WorldConst s_c[2];
+    __shared__ __align__(16) uint32_t s_cnt[2][4]; // per-warp visible counts of a chunk, one byte per warp
     __shared__ unsigned long long s_sum;
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     constexpr int kWarps = T / 32;
+    static_assert(kWarps <= 16, "one count byte per warp in s_cnt");
     const uint32_t levels = a.levels;
     const uint32_t my_worlds = a.n_worlds > blockIdx.x ? (a.n_worlds - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
     const uint32_t total = my_worlds * nc; // chunk iterations of this CTA
@@ -128,98 +192,61 @@ __global__ void __launch_bounds__(T + 32, kMinBlocks) k_world_step_pipe(const Pi
     __syncthreads();
 
     if (warp == kWarps) {
-        // ------------------------------- TMA warp -------------------------------------------------
-        if (lane != 0) return;
-        uint32_t k = 0, c = 0, s = 0, round = 0;       // position of the chunk being loaded
-        uint32_t sk = 0, sc = 0;                        // position of the chunk being stored (N behind)
-        auto store_chunk = [&](uint32_t stage, uint32_t wk, uint32_t wc) {
-            const uint64_t w = blockIdx.x + (uint64_t)wk * gridDim.x;
-            const uint32_t first = wc * T, bytes = min((uint32_t)T, E - first) * 4u;
-            const float *st = ring + (size_t)stage * kPlanes * T;
-            float *world = fptr(a.world, w) + first;
-            float *pos = fptr(a.pos, w) + first;
-#pragma unroll
-            for (int i = 0; i < 12; i++) bulk_store(world + (uint64_t)i * E, st + i * T, bytes);
-#pragma unroll
-            for (int i = 0; i < 3; i++) bulk_store(pos + (uint64_t)i * E, st + (12 + i) * T, bytes);
-            bulk_commit();
-        };
-        for (uint32_t it = 0; it < total; it++) {
-            if (it >= N) { // the stage still holds chunk it-N: wait for its outputs, drain them, then reuse it
-                mbar_wait(&done[s], (round - 1) & 1u);
-                store_chunk(s, sk, sc);
-                if (++sc == nc) sc = 0, sk++;
-                bulk_wait_read_all();
-            }
-            const uint64_t w = blockIdx.x + (uint64_t)k * gridDim.x;
-            const uint32_t first = c * T, bytes = min((uint32_t)T, E - first) * 4u; // multiple of 16 (E % 4 == 0)
-            float *st = ring + (size_t)s * kPlanes * T;
-            mbar_expect_tx(&full[s], bytes * kPlanes);
-#pragma unroll
-            for (int p = 0; p < kPlanes; p++) bulk_load(st + p * T, plane_src(a, p, w, E) + first, bytes, &full[s]);
-            if (++c == nc) c = 0, k++;
-            if (++s == N) s = 0, round++;
-        }
-        // drain the last min(N, total) chunks
-        const uint32_t tail = total < N ? total : N;
-        uint32_t ds = total < N ? 0 : s, dround = total < N ? 0 : round - 1;
-        for (uint32_t j = 0; j < tail; j++) {
-            mbar_wait(&done[ds], dround & 1u);
-            store_chunk(ds, sk, sc);
-            if (++sc == nc) sc = 0, sk++;
-            if (++ds == N) ds = 0, dround++;
-        }
-        bulk_wait_all();
+        if (lane == 0) tma_warp<T>(pa, ring, full, done, total);
         return;
     }
 
     // ----------------------------------- compute warps ------------------------------------------------
-    // per-world constants travel one world ahead in a register: frustum (24), dt (1), level_start (levels+1)
+    // which word of a world's constants this thread carries: frustum (24), dt (1), level_start (levels+1)
     auto const_word = [&](uint64_t w) -> uint32_t {
         if (tid < 24) return uptr(a.frustum, w)[tid];
         if (tid == 24) return uptr(a.dt, w)[0];
         if (tid >= 32 && tid <= 32 + (int)levels) return uptr(a.level_start, w)[tid - 32];
         return 0u;
     };
-    uint32_t next_const = my_worlds ? const_word(blockIdx.x) : 0u;
+    auto publish_const = [&](WorldConst &c, uint32_t v) {
+        if (tid < 24) c.frustum[tid] = __uint_as_float(v);
+        if (tid == 24) c.dt = __uint_as_float(v);
+        if (tid >= 32 && tid <= 32 + (int)levels) c.ls[tid - 32] = v;
+    };
+    if (my_worlds) publish_const(s_c[0], const_word(blockIdx.x));
+    consumer_sync<T>();
+
+    uint32_t next_const = 0;
     unsigned long long cta_visible = 0, warp_mask_sum = 0; // thread 0 / lane 0 of each warp
     uint32_t running = 0;                                   // visible entities of the current world so far
-    uint32_t k = 0, c = 0, s = 0, parity = 0;
+    uint32_t k = 0, c = 0, s = 0, parity = 0, l_lo = 0;
     uint64_t w = blockIdx.x;
     uint32_t *mask_out = nullptr, *list_out = nullptr;
     float *world_out = nullptr;
 
     for (uint32_t it = 0; it < total; it++) {
-        if (c == 0) { // a new world begins: publish its constants, fetch the next world's
-            if (tid < 24) s_frustum[tid] = __uint_as_float(next_const);
-            if (tid == 24) s_dt = __uint_as_float(next_const);
-            if (tid >= 32 && tid <= 32 + (int)levels) s_ls[tid - 32] = next_const;
+        const WorldConst &wc = s_c[k & 1];
+        if (c == 0) { // a new world begins
             if (k + 1 < my_worlds) next_const = const_word(w + gridDim.x);
-            running = 0;
+            running = 0, l_lo = 0;
             mask_out = uptr(a.vis_mask, w);
             list_out = uptr(a.vis_list, w);
             world_out = fptr(a.world, w);
-            consumer_sync<T>();
         }
         const uint32_t first = c * T;
         const uint32_t e = first + tid;
         const bool valid = e < E;
         const uint32_t last = min(E, first + T) - 1;
-        // hierarchy levels present in this chunk, and the level of this thread's entity
-        uint32_t l_lo = 0, l_hi = 0, l_me = 0;
-        for (uint32_t l = 1; l < levels; l++) {
-            const uint32_t start = s_ls[l];
-            l_lo += (first >= start);
-            l_hi += (last >= start);
-            l_me += (e >= start);
-        }
+        // hierarchy levels present in this chunk (uniform), and the level of this thread's entity
+        while (l_lo + 1 < levels && first >= wc.ls[l_lo + 1]) l_lo++;
+        uint32_t l_hi = l_lo;
+        while (l_hi + 1 < levels && last >= wc.ls[l_hi + 1]) l_hi++;
+        uint32_t l_me = l_lo;
+        while (l_me < l_hi && e >= wc.ls[l_me + 1]) l_me++;
+        const bool may_be_parent = l_me + 1 < levels;
 
         mbar_wait(&full[s], parity);
         float *st = ring + (size_t)s * kPlanes * T + tid;
         bool vis = false;
         for (uint32_t l = l_lo; l <= l_hi; l++) {
             if (valid && l_me == l) {
-                const float dt = s_dt;
+                const float dt = wc.dt;
                 const float px = fma1(st[3 * T], dt, st[0 * T]); // integrate
                 const float py = fma1(st[4 * T], dt, st[1 * T]);
                 const float pz = fma1(st[5 * T], dt, st[2 * T]);
@@ -232,19 +259,22 @@ __global__ void __launch_bounds__(T + 32, kMinBlocks) k_world_step_pipe(const Pi
                 } else {
                     float P[12];
                     if (p < cap) {
-#pragma unroll
-                        for (int i = 0; i < 12; i++) P[i] = s_lvl[i * cap + p];
+                        const float4 r0 = s_win[3 * p], r1 = s_win[3 * p + 1], r2 = s_win[3 * p + 2];
+                        P[0] = r0.x, P[1] = r0.y, P[2] = r0.z, P[3] = r0.w;
+                        P[4] = r1.x, P[5] = r1.y, P[6] = r1.z, P[7] = r1.w;
+                        P[8] = r2.x, P[9] = r2.y, P[10] = r2.z, P[11] = r2.w;
                     } else { // beyond the shared-memory window: written to HBM by this CTA below, read back through L2
 #pragma unroll
                         for (int i = 0; i < 12; i++) P[i] = __ldcg(world_out + (uint64_t)i * E + p);
                     }
                     compose(Wm, P, L);
                 }
-                vis = aabb_visible(Wm, st[12 * T], st[13 * T], st[14 * T], st[15 * T], st[16 * T], st[17 * T], s_frustum);
-                if (l + 1 < levels) { // may be somebody's parent
-                    if (e < cap) {
-#pragma unroll
-                        for (int i = 0; i < 12; i++) s_lvl[i * cap + e] = Wm[i];
+                vis = aabb_visible(Wm, st[12 * T], st[13 * T], st[14 * T], st[15 * T], st[16 * T], st[17 * T], wc.frustum);
+                if (may_be_parent) {
+                    if (e < cap) { // 48-byte rows: three conflict-free 128-bit stores
+                        s_win[3 * e] = make_float4(Wm[0], Wm[1], Wm[2], Wm[3]);
+                        s_win[3 * e + 1] = make_float4(Wm[4], Wm[5], Wm[6], Wm[7]);
+                        s_win[3 * e + 2] = make_float4(Wm[8], Wm[9], Wm[10], Wm[11]);
                     } else {
 #pragma unroll
                         for (int i = 0; i < 12; i++) world_out[(uint64_t)i * E + e] = Wm[i];
@@ -265,15 +295,19 @@ __global__ void __launch_bounds__(T + 32, kMinBlocks) k_world_step_pipe(const Pi
             mbar_arrive(&done[s]); // this warp's outputs are in the stage
             if ((e >> 5) < a.mask_words) mask_out[e >> 5] = ballot;
             warp_mask_sum += ballot;
-            cnt[warp] = __popc(ballot);
+            ((uint8_t *)cnt)[warp] = (uint8_t)__popc(ballot);
         }
+        if (c + 1 == nc && k + 1 < my_worlds) publish_const(s_c[(k + 1) & 1], next_const);
         consumer_sync<T>();
+        // the warps' counts are bytes: sums over "warps before me" and "all warps" are two dp4a per word
         uint32_t before = 0, chunk_total = 0;
 #pragma unroll
-        for (int i = 0; i < kWarps; i++) {
-            const uint32_t n = cnt[i];
-            before += (i < warp) ? n : 0u;
-            chunk_total += n;
+        for (int j = 0; j < (kWarps + 3) / 4; j++) {
+            const uint32_t word = cnt[j];
+            const int nb = warp - 4 * j; // bytes of this word that belong to earlier warps
+            const uint32_t below = nb >= 4 ? 0xFFFFFFFFu : (nb <= 0 ? 0u : (1u << (8 * nb)) - 1u);
+            before = __dp4a(word & below, 0x01010101u, before);
+            chunk_total = __dp4a(word, 0x01010101u, chunk_total);
         }
         if (vis) list_out[running + before + __popc(ballot & ((1u << lane) - 1u))] = e;
         running += chunk_total;
@@ -300,56 +334,98 @@ __global__ void __launch_bounds__(T + 32, kMinBlocks) k_world_step_pipe(const Pi
 // ---------------------------------------------------------------------------------------------
 namespace {
 
-struct PipeConfig {
-    int threads = 0;      // 256 (2 CTAs / SM) or 512 (1 CTA / SM); 0 = not applicable
-    uint32_t stages = 0;
-    uint32_t lvl_cap = 0;
-    size_t smem = 0;
-};
-
 bool aligned16(const FimoB200_ResourceView *v) { return v && ((uintptr_t)v->device_ptr % 16) == 0; }
 
-// The pipelined kernel needs 16-byte aligned plane rows (bulk copies): E % 4 == 0 and aligned bases.
-PipeConfig pipe_config(const WorldStepViews &v) {
-    PipeConfig cfg;
-    if (!v.world || !v.level_start) return cfg;
+constexpr size_t kSmemPerSm = 227 * 1024;  // usable by CTAs on sm_100a
+constexpr size_t kSmemPerCtaReserve = 1024; // the hardware reserves 1 KB per resident CTA
+constexpr size_t kStaticSmem = 768;         // WorldConst x2, counts, sum (see -Xptxas -v)
+
+size_t ring_bytes(int T, uint32_t stages) { return (size_t)stages * kPlanes * T * 4; }
+
+// Largest index of an entity that can be a parent, over all worlds: max level_start[levels-1].  Read once
+// from HBM when the executor is compiled (cold path).  If the host later uploads a different hierarchy the
+// kernel stays correct — parents outside the window are read back through L2 — only the sizing is stale.
+uint64_t max_parents(const WorldStepViews &v, int device) {
+    const FimoB200_ResourceView *ls = v.level_start;
     const uint64_t E = v.world->count;
-    if (E == 0 || E % 4 != 0 || E > 0x7FFFFFFFull) return cfg;
-    for (const FimoB200_ResourceView *r : {v.pos, v.vel, v.rot, v.scale, v.parent, v.aabb_c, v.aabb_h})
-        if (!aligned16(r)) return cfg;
-    // Entities that can be parents are [0, level_start[last]); the host does not read level_start (it
-    // lives in HBM), so the window is sized for the worst case the budget allows and the kernel falls
-    // back to L2 reads beyond it.
-    const size_t kBudgetTwo = 110 * 1024, kBudgetOne = 220 * 1024; // per CTA, of the 227 KB / SM
-    auto fit = [&](int T, size_t budget, uint32_t stages) {
-        PipeConfig c;
-        const size_t ring = (size_t)stages * kPlanes * T * 4 + stages * 16 + 1024 /* static + reserve */;
-        if (ring >= budget) return c;
-        uint64_t cap = (budget - ring) / 48;
-        if (cap > E) cap = E;
-        cap &= ~1ull;
-        c.threads = T, c.stages = stages, c.lvl_cap = (uint32_t)cap;
-        c.smem = (size_t)stages * kPlanes * T * 4 + (size_t)cap * 48 + stages * 16;
-        return c;
-    };
-    if (E <= 2048) return fit(256, kBudgetTwo, 4);
-    return fit(512, kBudgetOne, 4);
+    if (!ls || !ls->device_ptr || ls->components < 2) return E;
+    const size_t words = (size_t)ls->n_worlds * ls->components;
+    std::vector<uint32_t> host(words);
+    if (!hbm_download(device, host.data(), ls->device_ptr, words * 4)) return E;
+    uint64_t m = 0;
+    for (uint64_t w = 0; w < ls->n_worlds; w++) m = std::max<uint64_t>(m, host[w * ls->components + ls->components - 2]);
+    return std::min(m, E);
+}
+
+bool make_plan(WorldStepPlan &p, int T, uint32_t blocks, uint32_t stages, uint64_t want_cap, uint64_t E) {
+    const size_t budget = kSmemPerSm / blocks - kSmemPerCtaReserve - kStaticSmem;
+    const size_t fixed = ring_bytes(T, stages) + (size_t)stages * 16;
+    if (fixed + 48 * 2 > budget) return false;
+    uint64_t cap = std::min<uint64_t>({want_cap, E, (budget - fixed) / 48});
+    p.threads = T, p.blocks_per_sm = blocks, p.stages = stages, p.lvl_cap = (uint32_t)cap;
+    p.smem = ring_bytes(T, stages) + (size_t)cap * 48 + (size_t)stages * 16;
+    return true;
 }
 
 } // namespace
 
-bool world_step_supported(const WorldStepViews &v) { return pipe_config(v).threads != 0 || world_step_supported_v1(v); }
-
-const char *world_step_kernel_name(const WorldStepViews &v) {
-    const PipeConfig cfg = pipe_config(v);
-    if (cfg.threads == 256) return "k_world_step_pipe<256,2> (TMA-fed persistent world-step)";
-    if (cfg.threads == 512) return "k_world_step_pipe<512,1> (TMA-fed persistent world-step)";
-    return "k_world_cta<256,true,true> (one CTA per world)";
+bool world_step_plan(const WorldStepViews &v, int device, WorldStepPlan &plan) {
+    plan = WorldStepPlan{};
+    if (!v.world || !v.level_start) return false;
+    const uint64_t E = v.world->count;
+    if (E == 0 || E > 0x7FFFFFFFull) return false;
+    bool pipe = E % 4 == 0; // the pipelined kernel needs 16-byte aligned plane rows (bulk copies)
+    for (const FimoB200_ResourceView *r : {v.pos, v.vel, v.rot, v.scale, v.parent, v.aabb_c, v.aabb_h, v.world})
+        if (!aligned16(r)) pipe = false;
+    if (!pipe) { // ragged worlds: v1 (one CTA per world, loads through registers)
+        if (!world_step_supported_v1(v)) return false;
+        plan.threads = 0;
+        return true;
+    }
+    const uint64_t parents = max_parents(v, device);
+    plan.max_parents = (uint32_t)parents;
+    // FIMO_B200_PIPE=T,blocks,stages[,cap] overrides the heuristic (tuning sweeps; any value is correct)
+    if (const char *env = std::getenv("FIMO_B200_PIPE")) {
+        int T = 0;
+        unsigned blocks = 0, stages = 0;
+        unsigned long long cap = parents;
+        if (std::sscanf(env, "%d,%u,%u,%llu", &T, &blocks, &stages, &cap) >= 3 && (T == 128 || T == 256 || T == 512) &&
+            blocks >= 1 && blocks <= 6 && stages >= 2 && stages <= 16 && make_plan(plan, T, blocks, stages, cap, E))
+            return true;
+        std::fprintf(stderr, "fimo_worlds_b200: ignoring FIMO_B200_PIPE=%s\n", env);
+    }
+    // Heuristic (measured on B200, profiles/r1f_sweep.txt): many small CTAs hide the level barriers best —
+    // 4 CTAs x 128 entities with a 4-deep ring — as long as the whole parent window fits beside the ring.
+    if (make_plan(plan, 128, 4, 4, parents, E) && plan.lvl_cap >= parents) return true;
+    if (make_plan(plan, 256, 3, 3, parents, E) && plan.lvl_cap >= parents) return true;
+    if (make_plan(plan, 256, 2, 4, parents, E) && plan.lvl_cap >= parents) return true;
+    if (make_plan(plan, 256, 2, 3, parents, E) && plan.lvl_cap >= parents) return true;
+    return make_plan(plan, 256, 2, 4, parents, E); // partial window; the rest of the parents come from L2
 }
 
-FimoStatus world_step_launch(const WorldStepViews &v, void *cull_scratch, const FimoB200_LaunchInfo *info) {
-    const PipeConfig cfg = pipe_config(v);
-    if (cfg.threads == 0) return world_step_launch_v1(v, cull_scratch, info);
+const char *world_step_kernel_name(const WorldStepPlan &plan) {
+    if (plan.threads == 0) return "k_world_cta<256,true,true> (one CTA per world)";
+    return "k_world_step_pipe (TMA-fed persistent world-step)";
+}
+
+namespace {
+template <int T, int kBlocks>
+FimoStatus launch_pipe(const PipeArgs &pa, const WorldStepPlan &plan, uint64_t W, const FimoB200_LaunchInfo *info) {
+    auto kernel = k_world_step_pipe<T, kBlocks>;
+    if (!allow_smem(kernel, plan.smem)) return check_launch("world_step (shared memory opt-in)");
+    // Persistent grid with an even share of worlds per CTA: a ragged tail costs more than idle CTA slots
+    // on an HBM-bound kernel.
+    const uint64_t slots = (uint64_t)plan.blocks_per_sm * sm_count(info->device);
+    const uint64_t per_cta = (W + slots - 1) / slots;
+    const unsigned grid = (unsigned)((W + per_cta - 1) / per_cta);
+    kernel<<<grid, T + 32, plan.smem, (cudaStream_t)info->stream>>>(pa);
+    return check_launch("world_step");
+}
+} // namespace
+
+FimoStatus world_step_launch(const WorldStepViews &v, const WorldStepPlan &plan, void *cull_scratch,
+                             const FimoB200_LaunchInfo *info) {
+    if (plan.threads == 0) return world_step_launch_v1(v, cull_scratch, info);
     const uint64_t W = info->n_worlds, E = info->entities_per_world;
     if (W == 0 || E == 0) return FIMO_STATUS_OK;
     try {
@@ -360,23 +436,19 @@ FimoStatus world_step_launch(const WorldStepViews &v, void *cull_scratch, const 
         fill_cull(a, v.vis_mask, v.vis_list, v.vis_count, v.stats, v.world, v.aabb_c, v.aabb_h, v.frustum, cull_scratch, W, E);
         a.vel = plane_of(v.vel, FIMO_B200_SCOPE_ENTITY, 3, E, W, "vel");
         a.dt = plane_of(v.dt, FIMO_B200_SCOPE_WORLD, 1, 1, W, "dt");
-        pa.stages = cfg.stages;
-        pa.lvl_cap = cfg.lvl_cap;
-        pa.chunks = (uint32_t)((E + cfg.threads - 1) / cfg.threads);
-        cudaStream_t stream = (cudaStream_t)info->stream;
-        const int sms = sm_count(info->device);
-        if (cfg.threads == 256) {
-            auto kernel = k_world_step_pipe<256, 2>;
-            if (!allow_smem(kernel, cfg.smem)) return check_launch("world_step (shared memory opt-in)");
-            const unsigned grid = (unsigned)(W < 2ull * sms ? W : 2ull * sms);
-            kernel<<<grid, 256 + 32, cfg.smem, stream>>>(pa);
-        } else {
-            auto kernel = k_world_step_pipe<512, 1>;
-            if (!allow_smem(kernel, cfg.smem)) return check_launch("world_step (shared memory opt-in)");
-            const unsigned grid = (unsigned)(W < (uint64_t)sms ? W : (uint64_t)sms);
-            kernel<<<grid, 512 + 32, cfg.smem, stream>>>(pa);
+        pa.stages = plan.stages;
+        pa.lvl_cap = plan.lvl_cap;
+        pa.chunks = (uint32_t)((E + plan.threads - 1) / plan.threads);
+        const int key = plan.threads * 10 + (int)plan.blocks_per_sm;
+        switch (key) {
+        case 1284: case 1283: case 1282: case 1281: return launch_pipe<128, 4>(pa, plan, W, info);
+        case 1285: return launch_pipe<128, 5>(pa, plan, W, info);
+        case 1286: return launch_pipe<128, 6>(pa, plan, W, info);
+        case 2561: case 2562: return launch_pipe<256, 2>(pa, plan, W, info);
+        case 2563: return launch_pipe<256, 3>(pa, plan, W, info);
+        case 5121: return launch_pipe<512, 1>(pa, plan, W, info);
+        default: return fail("world_step plan");
         }
-        return check_launch("world_step");
     } catch (const Fail &f) {
         return fail(f.what);
     }

@@ -842,6 +842,7 @@ bool build_device_executor(Group *g, const char **err) {
                 mp->type->shared[0] == mi->type->exclusive[0] && mc->type->shared[0] == mp->type->exclusive[0] &&
                 mi->order < mp->order && mp->order < mc->order;
     dev::WorldStepViews views{};
+    dev::WorldStepPlan plan{};
     if (fuse) {
         views.pos = view_of(g, mi->type->exclusive[0]);
         views.vel = view_of(g, mi->type->shared[0]);
@@ -858,14 +859,14 @@ bool build_device_executor(Group *g, const char **err) {
         views.aabb_c = view_of(g, mc->type->shared[1]);
         views.aabb_h = view_of(g, mc->type->shared[2]);
         views.frustum = view_of(g, mc->type->shared[3]);
-        fuse = dev::world_step_supported(views);
+        fuse = dev::world_step_plan(views, g->world->device, plan);
     }
 
     std::vector<dev::Node> nodes;
     if (fuse) {
         dev::Node node;
         void *scratch = ((dev::BuiltinState *)mc->state)->scratch;
-        node.launch = [views, scratch](const FimoB200_LaunchInfo *info) { return dev::world_step_launch(views, scratch, info); };
+        node.launch = [views, plan, scratch](const FimoB200_LaunchInfo *info) { return dev::world_step_launch(views, plan, scratch, info); };
         node.kernels = 1;
         nodes.push_back(std::move(node));
         edges = 0;
