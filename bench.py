@@ -320,7 +320,22 @@ def run_e2e(rig, torch, np, abi, W, K, distributed, dist, world_size) -> dict:
         keep.append(t)
         outs[name] = v
 
+    from fimo_b200.worlds import Fence
+    landed = Fence(rig.lib)
+
     def step_headline():
+        # stream-ordered: H2D inputs -> one generation -> D2H result, all queued on the group's stream through
+        # fimo_b200_group_transfer / system_group_schedule; ONE host wait per step, on the last copy's fence
+        for name, v in ins.items():
+            rig.upload_async(name, v)
+        rig.schedule(1, signal_last=False)
+        rig.download_async("stats", outs["stats"])
+        landed.reset()
+        rig.download_async("vis_count", outs["vis_count"], landed)
+        landed.wait()
+
+    def step_locked():
+        # the reference's host-access protocol: world_lock_resources -> blocking copy -> unlock, per resource
         for name, v in ins.items():
             rig.upload(name, v)
         rig.step(1)
@@ -348,7 +363,12 @@ def run_e2e(rig, torch, np, abi, W, K, distributed, dist, world_size) -> dict:
             "h2d_bytes_per_step": int(sum(v.nbytes for v in ins.values())),
             "d2h_bytes_per_step": int(sum(v.nbytes for v in outs.values())), "steps": steps,
             "ms_per_step": 1e3 * dt_head / steps,
-            "inputs": "frustum + dt of every world from pinned host memory", "result": "stats + per-world visible counts"}
+            "inputs": "frustum + dt of every world from pinned host memory", "result": "stats + per-world visible counts",
+            "api": "fimo_b200_group_transfer (stream-ordered H2D) + system_group_schedule + fimo_b200_group_transfer (D2H) + "
+                   "fence wait; every step waits for its own result"}
+    dt_lock = timed(step_locked, steps)
+    head["locked_value"] = world_size * W * steps / dt_lock
+    head["locked_api"] = "world_lock_resources + blocking fimo_b200_resource_upload/download + schedule + fence wait"
 
     from fimo_b200 import synth
     fins, fouts = {}, {}

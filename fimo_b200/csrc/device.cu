@@ -53,6 +53,7 @@ struct Completion {
     Executor *ex;
     void (*done)(void *);
     void *user;
+    bool generation = true; // false: a stream-ordered transfer (not part of the per-generation timers)
 };
 
 struct Completer {
@@ -129,8 +130,8 @@ void Completer::run() {
         cudaSetDevice(c.ex->device);
         ok(cudaEventSynchronize(c.end), "cudaEventSynchronize");
         float ms = 0.0f;
-        const bool timed = cudaEventElapsedTime(&ms, c.start, c.end) == cudaSuccess;
-        if (!timed) (void)cudaGetLastError();
+        const bool timed = c.generation && cudaEventElapsedTime(&ms, c.start, c.end) == cudaSuccess;
+        if (c.generation && !timed) (void)cudaGetLastError();
         if (c.done) c.done(c.user);
         Executor *ex = c.ex;
         std::lock_guard<std::mutex> g(ex->m);
@@ -138,11 +139,15 @@ void Completer::run() {
             ex->ms_sum += ms;
             ex->ms_count++;
         }
-        if (!ex->span_anchor) ex->span_anchor = c.start;
-        else ex->free_events.push_back(c.start);
-        float span = 0.0f;
-        if (cudaEventElapsedTime(&span, ex->span_anchor, c.end) == cudaSuccess) ex->span_ms = span;
-        else (void)cudaGetLastError();
+        if (c.generation) {
+            if (!ex->span_anchor) ex->span_anchor = c.start;
+            else ex->free_events.push_back(c.start);
+            float span = 0.0f;
+            if (cudaEventElapsedTime(&span, ex->span_anchor, c.end) == cudaSuccess) ex->span_ms = span;
+            else (void)cudaGetLastError();
+        } else if (c.start) {
+            ex->free_events.push_back(c.start);
+        }
         ex->free_events.push_back(c.end);
         if (--ex->in_flight == 0) ex->idle_cv.notify_all();
     }
@@ -347,6 +352,31 @@ bool executor_launch(Executor *ex, void (*done)(void *), void *user) {
     if (!launched) c.done = nullptr; // the caller reports the failure itself
     completer().post(c);
     return launched;
+}
+
+bool executor_transfer(Executor *ex, void *dst, const void *src, size_t bytes, bool to_device, void (*done)(void *), void *user) {
+    DeviceGuard guard(ex->device);
+    Completion c{nullptr, ex->take_event(), ex, done, user, false};
+    if (!c.end) return false;
+    {
+        std::lock_guard<std::mutex> g(ex->m);
+        ex->in_flight++;
+    }
+    bool queued = ok(cudaMemcpyAsync(dst, src, bytes, to_device ? cudaMemcpyHostToDevice : cudaMemcpyDeviceToHost, ex->stream),
+                     "cudaMemcpyAsync");
+    queued = ok(cudaEventRecord(c.end, ex->stream), "cudaEventRecord") && queued;
+    if (!queued) c.done = nullptr;
+    completer().post(c);
+    return queued;
+}
+
+void *host_alloc_pinned(size_t bytes) {
+    void *p = nullptr;
+    if (!ok(cudaHostAlloc(&p, bytes ? bytes : 1, cudaHostAllocDefault), "cudaHostAlloc")) return nullptr;
+    return p;
+}
+void host_free_pinned(void *p) {
+    if (p) ok(cudaFreeHost(p), "cudaFreeHost");
 }
 
 void *executor_stream(Executor *ex) { return ex->stream; }

@@ -39,6 +39,10 @@ bool executor_compile(Executor *ex, std::vector<Node> nodes, const FimoB200_Laun
 // Enqueue one generation.  `done(user)` runs on the completion thread once the device finished it
 // (never inside a CUDA callback, so it may take locks and wake futex waiters).
 bool executor_launch(Executor *ex, void (*done)(void *), void *user);
+// Enqueue a stream-ordered copy between host memory and HBM behind everything launched so far.
+bool executor_transfer(Executor *ex, void *dst, const void *src, size_t bytes, bool to_device, void (*done)(void *), void *user);
+void *host_alloc_pinned(size_t bytes);
+void host_free_pinned(void *p);
 void executor_wait_idle(Executor *ex);
 void *executor_stream(Executor *ex);
 bool executor_uses_graph(Executor *ex);

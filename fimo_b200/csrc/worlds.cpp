@@ -600,6 +600,11 @@ struct Job { // one scheduled generation (Job.zig:216-264 wraps SystemGroup.run 
     size_t generation;
     std::vector<FimoWorldsMeta_Fence *> wait_on;
     FimoWorldsMeta_Fence *signal;
+    // A stream-ordered transfer of one group resource instead of a generation (fimo_b200_group_transfer):
+    // queued and ordered exactly like a generation, but it does not consume a generation number.
+    ResourceType *xfer_resource = nullptr;
+    void *xfer_host = nullptr;
+    bool xfer_to_device = false;
 };
 
 struct Group {
@@ -1060,6 +1065,16 @@ void device_generation_done(void *user) {
     if (signal) fence_signal(signal); // the group may be destroyed by the waiter from here on
 }
 
+void device_transfer_done(void *user) {
+    std::unique_ptr<DeviceDone> done((DeviceDone *)user);
+    Group *g = done->group;
+    {
+        std::lock_guard<std::mutex> lock(g->m);
+        if (--g->in_flight == 0) unlock_group_resources(g);
+    }
+    if (done->signal) fence_signal(done->signal);
+}
+
 // Enqueues one device generation.  g->m held.  `blocking`: may wait for the resource locks.
 // Returns 0 = started, 1 = would block, -1 = failed (*err set).
 int start_device_generation(Group *g, Job *job, bool blocking, const char **err) {
@@ -1073,6 +1088,26 @@ int start_device_generation(Group *g, Job *job, bool blocking, const char **err)
         std::vector<void *> blobs(g->resources.size());
         if (blocking) world_lock_resources(g->world, g->resources.data(), g->resources.size(), nullptr, 0, blobs.data());
         else if (!world_try_lock_resources(g->world, g->resources.data(), g->resources.size(), blobs.data())) return 1;
+    }
+    if (job->xfer_resource) {
+        const FimoB200_ResourceView *view = view_of(g, job->xfer_resource);
+        if (!view || !view->device_ptr) {
+            if (g->in_flight == 0) unlock_group_resources(g);
+            *err = "NotFound";
+            return -1;
+        }
+        g->in_flight++;
+        DeviceDone *done = new DeviceDone{g, job->signal};
+        const size_t bytes = view->world_stride * view->n_worlds;
+        void *dst = job->xfer_to_device ? view->device_ptr : job->xfer_host;
+        const void *src = job->xfer_to_device ? job->xfer_host : view->device_ptr;
+        if (!dev::executor_transfer(g->executor_dev, dst, src, bytes, job->xfer_to_device, &device_transfer_done, done)) {
+            delete done;
+            if (--g->in_flight == 0) unlock_group_resources(g);
+            *err = "DeviceError";
+            return -1;
+        }
+        return 0;
     }
     g->in_flight++;
     DeviceDone *done = new DeviceDone{g, job->signal};
@@ -1155,6 +1190,8 @@ void dispatcher_main(Group *g) {
         if (device) {
             std::lock_guard<std::mutex> relock(g->m);
             if (start_device_generation(g, job, true, &err) != 0) panic("device generation failed to start");
+        } else if (job->xfer_resource) {
+            panic("transfer queued on a group without device systems");
         } else {
             FimoWorldsMeta_timeline_semaphore_wait(&g->schedule_semaphore, (uint64_t)job->generation, g_futex_wait);
             run_host_generation(g, job);
@@ -1167,11 +1204,20 @@ void dispatcher_main(Group *g) {
     g->dispatcher_running = false;
 }
 
-const char *group_schedule(Group *g, FimoWorldsMeta_Fence *const *wait_on, size_t n, FimoWorldsMeta_Fence *signal) {
+struct Transfer {
+    ResourceType *resource;
+    void *host;
+    bool to_device;
+};
+
+const char *group_schedule(Group *g, FimoWorldsMeta_Fence *const *wait_on, size_t n, FimoWorldsMeta_Fence *signal,
+                           const Transfer *xfer = nullptr) {
     // SystemGroup.zig:430-452
     std::unique_lock<std::mutex> lock(g->m);
     Job *job = new Job{g, g->next_generation, std::vector<FimoWorldsMeta_Fence *>(wait_on, wait_on + n), signal};
-    g->next_generation += 1;
+    const size_t consumed = xfer ? 0 : 1; // a transfer rides between generations, it is not one
+    if (xfer) job->xfer_resource = xfer->resource, job->xfer_host = xfer->host, job->xfer_to_device = xfer->to_device;
+    g->next_generation += consumed;
     const char *err = nullptr;
     // fast path: a device group with nothing queued ahead starts the generation right here
     if (g->backlog.empty() && !g->dispatcher_busy && fences_signaled(job)) {
@@ -1181,7 +1227,7 @@ const char *group_schedule(Group *g, FimoWorldsMeta_Fence *const *wait_on, size_
             for (auto &p : g->members) any_device |= p.second->type->device_entry != nullptr;
             if (any_device) {
                 if (!compile(g, &err)) {
-                    g->next_generation -= 1;
+                    g->next_generation -= consumed;
                     delete job;
                     return err;
                 }
@@ -1195,7 +1241,7 @@ const char *group_schedule(Group *g, FimoWorldsMeta_Fence *const *wait_on, size_
                 return nullptr;
             }
             if (rc < 0) {
-                g->next_generation -= 1;
+                g->next_generation -= consumed;
                 delete job;
                 return err;
             }
@@ -1527,6 +1573,25 @@ FimoStatus fimo_b200_resource_download(const FimoB200_ResourceView *view, void *
                    ? FIMO_STATUS_OK
                    : report("DeviceError");
 }
+
+FimoStatus fimo_b200_group_transfer(FimoWorldsMeta_SystemGroup *group, FimoWorldsMeta_ResourceHandle handle, void *host,
+                                    uint32_t direction, FimoWorldsMeta_Fence *signal) {
+    Group *g = (Group *)group;
+    if (!g || !handle || !host || direction > FIMO_B200_TRANSFER_DEVICE_TO_HOST) return report("InvalidArgument");
+    {
+        std::lock_guard<std::mutex> lock(g->m);
+        const char *err = nullptr;
+        if (g->dirty && g->in_flight == 0 && g->backlog.empty() && !g->dispatcher_busy && !compile(g, &err)) return report(err);
+        if (!g->has_device_systems) return report("NoDevice");
+        if (std::find(g->resources.begin(), g->resources.end(), (ResourceType *)handle) == g->resources.end())
+            return report("NotFound"); // only resources the group's systems use ride on its stream
+    }
+    const Transfer xfer{(ResourceType *)handle, host, direction == FIMO_B200_TRANSFER_HOST_TO_DEVICE};
+    if (const char *err = group_schedule(g, nullptr, 0, signal, &xfer)) return report(err);
+    return FIMO_STATUS_OK;
+}
+void *fimo_b200_host_alloc(FimoUSize bytes) { return dev::host_alloc_pinned(bytes); }
+void fimo_b200_host_free(void *ptr) { dev::host_free_pinned(ptr); }
 
 FimoStatus fimo_b200_group_executor_info(FimoWorldsMeta_SystemGroup *group, FimoB200_ExecutorInfo *info) {
     Group *g = (Group *)group;

@@ -321,6 +321,21 @@ class WorldStepRig:
         finally:
             self.resources[name].unlock_in_world(self.world, True)
 
+    # ---- stream-ordered transfers (product only): queued like generations, no host lock dance ---------
+    def upload_async(self, name: str, arr: np.ndarray) -> None:
+        """H2D copy of a whole resource, ordered before every generation scheduled afterwards; `arr` (pinned
+        for a truly asynchronous copy) must stay untouched until a later fence has been waited on."""
+        assert arr.dtype.itemsize == 4 and arr.flags["C_CONTIGUOUS"] and arr.shape == self.host[name].shape
+        self.lib.check(self.lib.fimo_b200_group_transfer(self.group.handle, self.resources[name].handle, arr.ctypes.data,
+                                                         abi.TRANSFER_HOST_TO_DEVICE, None))
+
+    def download_async(self, name: str, arr: np.ndarray, signal: Fence | None = None) -> None:
+        """D2H copy of a whole resource, ordered after every generation scheduled before; `signal` fires when
+        the data has landed in `arr`."""
+        assert arr.dtype.itemsize == 4 and arr.flags["C_CONTIGUOUS"] and arr.shape == self.host[name].shape
+        self.lib.check(self.lib.fimo_b200_group_transfer(self.group.handle, self.resources[name].handle, arr.ctypes.data,
+                                                         abi.TRANSFER_DEVICE_TO_HOST, signal.ptr() if signal else None))
+
     def stats(self) -> np.ndarray:
         return self.download(("stats",))["stats"].reshape(-1).view(np.uint64)
 

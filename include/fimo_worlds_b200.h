@@ -681,6 +681,20 @@ FIMO_B200_EXPORT FimoStatus fimo_b200_builtin_system(uint32_t builtin_id, FimoWo
 FIMO_B200_EXPORT FimoStatus fimo_b200_resource_upload(const FimoB200_ResourceView *view, const void *host_src);
 FIMO_B200_EXPORT FimoStatus fimo_b200_resource_download(const FimoB200_ResourceView *view, void *host_dst);
 
+/* Stream-ordered transfer of one resource used by the group's systems between HBM and host memory, queued
+ * like a generation (system_group_schedule, symbols.zig:150-166): it runs after every generation / transfer
+ * queued before it and before everything queued after it, on the group's stream, without the host taking
+ * the resource lock (the group holds its resources while work is in flight, SystemGroup.zig:340-351).  It
+ * does not consume a generation number.  `host` holds the whole resource ([n_worlds][components][count]
+ * words) and must stay valid until `signal` (nullable) is signaled; use pinned memory
+ * (fimo_b200_host_alloc, or any cudaHostRegister'ed / torch-pinned buffer) for a truly asynchronous copy. */
+enum { FIMO_B200_TRANSFER_HOST_TO_DEVICE = 0, FIMO_B200_TRANSFER_DEVICE_TO_HOST = 1 };
+FIMO_B200_EXPORT FimoStatus fimo_b200_group_transfer(FimoWorldsMeta_SystemGroup *group,
+                                                     FimoWorldsMeta_ResourceHandle handle, void *host,
+                                                     uint32_t direction, FimoWorldsMeta_Fence *signal);
+FIMO_B200_EXPORT void *fimo_b200_host_alloc(FimoUSize bytes); /* page-locked host memory; NULL on failure */
+FIMO_B200_EXPORT void fimo_b200_host_free(void *ptr);
+
 /* What the DAG compiler produced for the group's current system set. */
 typedef struct FimoB200_ExecutorInfo {
     uint32_t systems;          /* member systems */

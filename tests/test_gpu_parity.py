@@ -147,3 +147,36 @@ def test_reference_goldens_on_gpu_box(product, case_name):
     import reference_goldens as G
 
     getattr(G, case_name)(product)
+
+
+def test_stream_ordered_transfers_match_locked_host_access(oracle, product):
+    """fimo_b200_group_transfer: uploads / downloads queued between generations give the same result as the
+    lock-copy-unlock protocol on the oracle, and do not consume generation numbers."""
+    from fimo_b200.worlds import Fence
+
+    W, E, D = 8, 512, 4
+    data = synth.generate(W, E, D)
+    other = synth.generate(W, E, D, world0=1000)["frustum"]
+    ref = synth.WorldStepRig(oracle, W, E, D, data={k: v.copy() for k, v in data.items()})
+    try:
+        ref.step(2)
+        ref.upload("frustum", other)
+        ref.step(3)
+        want = ref.download()
+    finally:
+        ref.close()
+    rig = synth.WorldStepRig(product, W, E, D, data={k: v.copy() for k, v in data.items()})
+    try:
+        got = {name: np.empty_like(rig.host[name]) for name in synth.OUTPUTS}
+        rig.schedule(2, signal_last=False)
+        rig.upload_async("frustum", other)          # ordered after generation 2, before generation 3
+        rig.schedule(3, signal_last=False)
+        fence = Fence(product)
+        for i, name in enumerate(synth.OUTPUTS):
+            rig.download_async(name, got[name], fence if i == len(synth.OUTPUTS) - 1 else None)
+        fence.wait()
+        assert rig.stats()[abi.STAT_STEPS] == W * 5
+    finally:
+        rig.close()
+    problems = synth.compare_outputs(got, want, FLOAT_RTOL)
+    assert not problems, "\n".join(problems)
