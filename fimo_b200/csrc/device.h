@@ -5,6 +5,7 @@
 #include <cstddef>
 #include <cstdint>
 #include <functional>
+#include <memory>
 #include <vector>
 
 #include "fimo_worlds_b200.h"
@@ -81,8 +82,13 @@ struct WorldStepPlan {
     uint32_t blocks_per_sm = 0; // resident CTAs per SM the plan is sized for
     uint32_t stages = 0;        // ring depth in chunks
     uint32_t lvl_cap = 0;       // parent matrices kept in shared memory: entities [0, lvl_cap)
-    uint32_t max_parents = 0;   // max over worlds of level_start[levels-1]
+    uint32_t max_parents = 0;   // max over worlds of level_start[levels-1] when the plan was made
+    uint32_t team = 1;          // CTAs that step one world together (> 1: large worlds / few worlds)
+    uint32_t teams = 0;         // worlds in flight = grid / team
+    uint32_t kernels = 1;       // launches per generation (team mode adds the list-compaction kernel)
     size_t smem = 0;            // dynamic shared memory per CTA
+    std::shared_ptr<void> rows;     // HBM: [n_worlds][E] 48-byte parent rows (parents outside the window)
+    std::shared_ptr<void> lvl_done; // HBM: [n_worlds][32] level-completion counters (team mode)
 };
 bool world_step_plan(const WorldStepViews &v, int device, WorldStepPlan &plan); // false: not fusable
 FimoStatus world_step_launch(const WorldStepViews &v, const WorldStepPlan &plan, void *cull_scratch,

@@ -118,13 +118,13 @@ __device__ __forceinline__ void propagate_entity(uint32_t e, uint32_t E, float *
 // Folds one CTA's statistics into the batch accumulators; the last CTA of the grid publishes them
 // and re-arms the scratch block (so no memset node is needed between generations).
 __device__ __forceinline__ void publish_stats(const StepArgs &a, unsigned long long visible, unsigned long long mask_sum,
-                                              unsigned long long worlds) {
+                                              unsigned long long worlds, unsigned long long n_ctas) {
     atomicAdd(&a.scratch[0], visible);
     atomicAdd(&a.scratch[1], mask_sum);
     atomicAdd(&a.scratch[2], worlds);
     __threadfence();
     const unsigned long long ticket = atomicAdd(&a.scratch[4], 1ull);
-    if (ticket == (unsigned long long)gridDim.x - 1) {
+    if (ticket == n_ctas - 1) {
         __threadfence();
         const unsigned long long v = atomicExch(&a.scratch[0], 0ull);
         const unsigned long long m = atomicExch(&a.scratch[1], 0ull);
@@ -136,6 +136,10 @@ __device__ __forceinline__ void publish_stats(const StepArgs &a, unsigned long l
         a.stats[FIMO_B200_STAT_STEPS] += n;
         atomicExch(&a.scratch[4], 0ull);
     }
+}
+__device__ __forceinline__ void publish_stats(const StepArgs &a, unsigned long long visible, unsigned long long mask_sum,
+                                              unsigned long long worlds) {
+    publish_stats(a, visible, mask_sum, worlds, (unsigned long long)gridDim.x);
 }
 
 // ---------------------------------------------------------------------------------------------

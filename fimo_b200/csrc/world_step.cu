@@ -87,7 +87,20 @@ struct PipeArgs {
     uint32_t stages;   // ring depth (chunks)
     uint32_t lvl_cap;  // parent matrices kept in shared memory: entities [0, lvl_cap) of a world
     uint32_t chunks;   // chunks per world = ceil(E / T)
+    uint32_t team;     // CTAs that step one world together (1 = a world belongs to one CTA)
+    uint32_t teams;    // gridDim.x / team
+    // Parent matrices that do not fit the shared-memory window: [n_worlds][E] rows of 48 bytes in HBM, written
+    // by whoever computes the parent and read back through L2 with three 128-bit loads.  nullptr if unused.
+    float4 *rows;
+    uint32_t flags; // kPipe*
+    // Team mode: entities of (world, level) whose matrices are visible in `rows` — the dataflow counters the
+    // CTAs of a team synchronise on ([n_worlds][kMaxLevels], zeroed by the compaction kernel).
+    uint32_t *lvl_done;
 };
+
+constexpr uint32_t kPipePublishPerChunk = 2u; // FIMO_B200_PUBLISH=chunk: announce level progress after every chunk
+constexpr uint32_t kPipePrefetchBlocking = 4u; // FIMO_B200_PREFETCH=2: wait for the next chunk's inputs before this chunk's math
+constexpr uint32_t kPipeNoPrefetch = 1u; // FIMO_B200_PREFETCH=0: parent rows are loaded where they are used
 
 // Per-world constants, double-buffered in shared memory (world k uses buffer k & 1): the compute threads
 // fetch world k+1's words into a register while world k is being stepped and publish them before the last
@@ -111,17 +124,29 @@ __device__ __forceinline__ const uint32_t *plane_src(const StepArgs &a, int p, u
     return uptr(a.aabb_h, w) + (uint64_t)(p - 15) * E;
 }
 
+// Work of one CTA: worlds team_id, team_id + teams, ... and of each world the chunks rank, rank + team, ...
+struct Walk {
+    uint32_t team_id, rank, my_worlds, my_chunks, total;
+    __device__ __forceinline__ Walk(const PipeArgs &pa) {
+        team_id = blockIdx.x / pa.team;
+        rank = blockIdx.x % pa.team;
+        my_worlds = pa.a.n_worlds > team_id ? (pa.a.n_worlds - team_id + pa.teams - 1) / pa.teams : 0;
+        my_chunks = pa.chunks > rank ? (pa.chunks - rank + pa.team - 1) / pa.team : 0;
+        total = my_worlds * my_chunks;
+    }
+};
+
 // The TMA warp (one elected thread): loads chunk inputs into the ring and stores the finished chunk's
 // outputs, which the compute threads leave in the same ring stage (world matrices over planes 0-11, new
 // positions over 12-14).
 template <int T>
-__device__ __forceinline__ void tma_warp(const PipeArgs &pa, float *ring, uint64_t *full, uint64_t *done, uint32_t total) {
+__device__ __forceinline__ void tma_warp(const PipeArgs &pa, const Walk &wk, float *ring, uint64_t *full, uint64_t *done) {
     const StepArgs &a = pa.a;
-    const uint32_t E = a.entities, N = pa.stages, nc = pa.chunks;
-    uint32_t k = 0, c = 0, s = 0, round = 0; // position of the chunk being loaded
-    uint32_t sk = 0, sc = 0;                  // position of the chunk being stored (N behind)
-    auto store_chunk = [&](uint32_t stage, uint32_t wk, uint32_t wc) {
-        const uint64_t w = blockIdx.x + (uint64_t)wk * gridDim.x;
+    const uint32_t E = a.entities, N = pa.stages, nc = pa.chunks, G = pa.team, total = wk.total;
+    uint32_t k = 0, c = wk.rank, s = 0, round = 0; // position of the chunk being loaded
+    uint32_t sk = 0, sc = wk.rank;                  // position of the chunk being stored (N behind)
+    auto store_chunk = [&](uint32_t stage, uint32_t wk_, uint32_t wc) {
+        const uint64_t w = wk.team_id + (uint64_t)wk_ * pa.teams;
         const uint32_t first = wc * T, bytes = min((uint32_t)T, E - first) * 4u;
         const float *st = ring + (size_t)stage * kPlanes * T;
         float *world = fptr(a.world, w) + first;
@@ -136,16 +161,16 @@ __device__ __forceinline__ void tma_warp(const PipeArgs &pa, float *ring, uint64
         if (it >= N) { // the stage still holds chunk it-N: wait for its outputs, drain them, then reuse it
             mbar_wait(&done[s], (round - 1) & 1u);
             store_chunk(s, sk, sc);
-            if (++sc == nc) sc = 0, sk++;
+            if ((sc += G) >= nc) sc = wk.rank, sk++;
             bulk_wait_read_all();
         }
-        const uint64_t w = blockIdx.x + (uint64_t)k * gridDim.x;
+        const uint64_t w = wk.team_id + (uint64_t)k * pa.teams;
         const uint32_t first = c * T, bytes = min((uint32_t)T, E - first) * 4u; // multiple of 16 (E % 4 == 0)
         float *st = ring + (size_t)s * kPlanes * T;
         mbar_expect_tx(&full[s], bytes * kPlanes);
 #pragma unroll
         for (int p = 0; p < kPlanes; p++) bulk_load(st + p * T, plane_src(a, p, w, E) + first, bytes, &full[s]);
-        if (++c == nc) c = 0, k++;
+        if ((c += G) >= nc) c = wk.rank, k++;
         if (++s == N) s = 0, round++;
     }
     // drain the last min(N, total) chunks
@@ -154,22 +179,58 @@ __device__ __forceinline__ void tma_warp(const PipeArgs &pa, float *ring, uint64
     for (uint32_t j = 0; j < tail; j++) {
         mbar_wait(&done[ds], dround & 1u);
         store_chunk(ds, sk, sc);
-        if (++sc == nc) sc = 0, sk++;
+        if ((sc += G) >= nc) sc = wk.rank, sk++;
         if (++ds == N) ds = 0, dround++;
     }
     bulk_wait_all();
 }
 
+// non-blocking probe of an mbarrier phase
+__device__ __forceinline__ bool mbar_test(uint64_t *bar, uint32_t parity) {
+    uint32_t done;
+    asm volatile(
+            "{\n"
+            ".reg .pred p;\n"
+            "mbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+            "selp.u32 %0, 1, 0, p;\n"
+            "}\n"
+            : "=r"(done)
+            : "r"(smem_addr(bar)), "r"(parity)
+            : "memory");
+    return done != 0;
+}
+// 16-byte asynchronous copy global (L2) -> shared, no registers in between (LDGSTS)
+__device__ __forceinline__ void cp_async16(void *dst, const void *src) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_addr(dst)), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void cp_async_wait_all_but_latest() { asm volatile("cp.async.wait_group 1;" ::: "memory"); }
+
+__device__ __forceinline__ uint32_t ld_acquire_gpu(const uint32_t *p) {
+    uint32_t v;
+    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void red_release_gpu_add(uint32_t *p, uint32_t v) {
+    asm volatile("red.release.gpu.global.add.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+
 // Warp-specialised: warps [0, T/32) compute (one entity of the chunk per thread), the last warp is the TMA warp.
-template <int T, int kMinBlocks>
+// kTeam = false: a world belongs to one CTA; mask, ordered list, count and statistics leave this kernel.
+// kTeam = true : `team` CTAs step one world together (large worlds, few worlds); chunks are dealt round-robin,
+//                parents travel through `rows` in L2, and a CTA starts level l of a chunk once the (world, l-1)
+//                counter says every entity of level l-1 is visible — dataflow, no team-wide barrier.  Only the
+//                mask leaves this kernel; k_compact_lists derives list, count and statistics from it.
+template <int T, int kMinBlocks, bool kTeam>
 __global__ void __launch_bounds__(T + 32, kMinBlocks) k_world_step_pipe(const PipeArgs pa) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     const StepArgs &a = pa.a;
-    const uint32_t E = a.entities, N = pa.stages, cap = pa.lvl_cap, nc = pa.chunks;
+    const uint32_t E = a.entities, N = pa.stages, cap = pa.lvl_cap, nc = pa.chunks, G = pa.team;
     float *ring = (float *)smem_raw;                              // [N][kPlanes][T] planes
     float4 *s_win = (float4 *)(ring + (size_t)N * kPlanes * T);   // [cap][3]: parent window, one 48-byte matrix per entity
     uint64_t *full = (uint64_t *)(s_win + (size_t)3 * cap);       // [N] inputs have landed
     uint64_t *done = full + N;                                    // [N] outputs are in the stage
+    float4 *s_pre = (float4 *)(done + N);                         // team mode: [2][T][3] parent rows prefetched from L2
     __shared__ __align__(16) WorldConst s_c[2];
     __shared__ __align__(16) uint32_t s_cnt[2][4]; // per-warp visible counts of a chunk, one byte per warp
     __shared__ unsigned long long s_sum;
@@ -178,8 +239,8 @@ __global__ void __launch_bounds__(T + 32, kMinBlocks) k_world_step_pipe(const Pi
     constexpr int kWarps = T / 32;
     static_assert(kWarps <= 16, "one count byte per warp in s_cnt");
     const uint32_t levels = a.levels;
-    const uint32_t my_worlds = a.n_worlds > blockIdx.x ? (a.n_worlds - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
-    const uint32_t total = my_worlds * nc; // chunk iterations of this CTA
+    const Walk wk(pa);
+    const uint32_t my_worlds = wk.my_worlds, total = wk.total;
 
     if (tid == 0) {
         for (uint32_t s = 0; s < N; s++) {
@@ -192,7 +253,7 @@ __global__ void __launch_bounds__(T + 32, kMinBlocks) k_world_step_pipe(const Pi
     __syncthreads();
 
     if (warp == kWarps) {
-        if (lane == 0) tma_warp<T>(pa, ring, full, done, total);
+        if (lane == 0) tma_warp<T>(pa, wk, ring, full, done);
         return;
     }
 
@@ -209,25 +270,40 @@ __global__ void __launch_bounds__(T + 32, kMinBlocks) k_world_step_pipe(const Pi
         if (tid == 24) c.dt = __uint_as_float(v);
         if (tid >= 32 && tid <= 32 + (int)levels) c.ls[tid - 32] = v;
     };
-    if (my_worlds) publish_const(s_c[0], const_word(blockIdx.x));
+    if (total) publish_const(s_c[0], const_word(wk.team_id));
     consumer_sync<T>();
 
     uint32_t next_const = 0;
     unsigned long long cta_visible = 0, warp_mask_sum = 0; // thread 0 / lane 0 of each warp
     uint32_t running = 0;                                   // visible entities of the current world so far
-    uint32_t k = 0, c = 0, s = 0, parity = 0, l_lo = 0;
-    uint64_t w = blockIdx.x;
+    uint32_t k = 0, c = wk.rank, s = 0, parity = 0, l_lo = 0;
+    // team mode: entities of level pend_level this CTA has finished but not yet announced.  Dependants only
+    // care about a level being COMPLETE, so a CTA announces its share once, when it moves past the level.
+    int pend_level = -1;
+    uint32_t pend_count = 0;
+    auto flush_pending = [&](uint32_t *counters) {
+        if (pend_level < 0) return;
+        consumer_sync<T>(); // every thread's rows of that level are written
+        if (tid == 0) red_release_gpu_add(counters + pend_level, pend_count);
+        pend_level = -1, pend_count = 0;
+    };
+    bool pre_have = false; // team mode: this thread's parent row of the current chunk is (being) prefetched into s_pre
+    int ready_upto = -1; // team mode: levels [0, ready_upto] of the current world are known to be complete
+    uint64_t w = wk.team_id;
     uint32_t *mask_out = nullptr, *list_out = nullptr;
-    float *world_out = nullptr;
+    float4 *rows = nullptr;
+    uint32_t *lvl_done = nullptr;
 
     for (uint32_t it = 0; it < total; it++) {
         const WorldConst &wc = s_c[k & 1];
-        if (c == 0) { // a new world begins
-            if (k + 1 < my_worlds) next_const = const_word(w + gridDim.x);
-            running = 0, l_lo = 0;
+        if (c == wk.rank) { // a new world begins
+            if (kTeam && it != 0) consumer_sync<T>(); // its constants were published during the previous world
+            if (k + 1 < my_worlds) next_const = const_word(w + pa.teams);
+            running = 0, l_lo = 0, ready_upto = -1;
             mask_out = uptr(a.vis_mask, w);
             list_out = uptr(a.vis_list, w);
-            world_out = fptr(a.world, w);
+            rows = pa.rows ? pa.rows + w * (uint64_t)E * 3 : nullptr;
+            if (kTeam) lvl_done = pa.lvl_done + w * kMaxLevels;
         }
         const uint32_t first = c * T;
         const uint32_t e = first + tid;
@@ -240,11 +316,47 @@ __global__ void __launch_bounds__(T + 32, kMinBlocks) k_world_step_pipe(const Pi
         uint32_t l_me = l_lo;
         while (l_me < l_hi && e >= wc.ls[l_me + 1]) l_me++;
         const bool may_be_parent = l_me + 1 < levels;
+        if (kTeam && pend_level >= 0 && (int)l_lo > pend_level) flush_pending(lvl_done); // moved past that level
 
         mbar_wait(&full[s], parity);
         float *st = ring + (size_t)s * kPlanes * T + tid;
         bool vis = false;
+        bool pre_next = false;
+        if (kTeam) {
+            // Parent rows come from L2 (~1 us under load): fetch the NEXT chunk's rows now, asynchronously and
+            // without registers (cp.async), so that this chunk's arithmetic covers the latency.  Safe when this
+            // chunk and the next lie inside one level nl whose parent level is already known to be complete.
+            if (c + G < nc && !(pa.flags & kPipeNoPrefetch)) {
+                const uint32_t nfirst = (c + G) * T, nlast = min(E, nfirst + T) - 1;
+                uint32_t nl = l_hi;
+                while (nl + 1 < levels && nfirst >= wc.ls[nl + 1]) nl++;
+                const bool single = !(nl + 1 < levels && nlast >= wc.ls[nl + 1]);
+                const uint32_t ns = s + 1 == N ? 0 : s + 1;
+                const uint32_t npar = ns == 0 ? parity ^ 1u : parity;
+                if (single && nl >= 1 && l_lo == nl && ready_upto >= (int)nl - 1 &&
+                    ((pa.flags & kPipePrefetchBlocking) ? (mbar_wait(&full[ns], npar), true) : mbar_test(&full[ns], npar))) {
+                    const uint32_t np = __float_as_uint(ring[(size_t)ns * kPlanes * T + 11 * T + tid]);
+                    if (nfirst + tid < E && np != kRoot) {
+                        const float4 *src = rows + (uint64_t)np * 3;
+                        float4 *dst = s_pre + ((size_t)((it + 1) & 1) * T + tid) * 3;
+                        cp_async16(dst, src), cp_async16(dst + 1, src + 1), cp_async16(dst + 2, src + 2);
+                    }
+                    pre_next = true;
+                }
+            }
+            cp_async_commit(); // one group per iteration, possibly empty
+        }
         for (uint32_t l = l_lo; l <= l_hi; l++) {
+            if (kTeam && l >= 1 && ready_upto < (int)l - 1) {
+                flush_pending(lvl_done); // our own share of level l-1 (same chunk) counts too
+                // every entity of level l-1 — in whichever CTA's chunk — must be visible in `rows`
+                if (tid == 0) {
+                    const uint32_t need = wc.ls[l] - wc.ls[l - 1];
+                    while (ld_acquire_gpu(lvl_done + (l - 1)) < need) __nanosleep(64);
+                }
+                consumer_sync<T>();
+                ready_upto = (int)l - 1;
+            }
             if (valid && l_me == l) {
                 const float dt = wc.dt;
                 const float px = fma1(st[3 * T], dt, st[0 * T]); // integrate
@@ -257,74 +369,151 @@ __global__ void __launch_bounds__(T + 32, kMinBlocks) k_world_step_pipe(const Pi
 #pragma unroll
                     for (int i = 0; i < 12; i++) Wm[i] = L[i];
                 } else {
-                    float P[12];
-                    if (p < cap) {
-                        const float4 r0 = s_win[3 * p], r1 = s_win[3 * p + 1], r2 = s_win[3 * p + 2];
-                        P[0] = r0.x, P[1] = r0.y, P[2] = r0.z, P[3] = r0.w;
-                        P[4] = r1.x, P[5] = r1.y, P[6] = r1.z, P[7] = r1.w;
-                        P[8] = r2.x, P[9] = r2.y, P[10] = r2.z, P[11] = r2.w;
-                    } else { // beyond the shared-memory window: written to HBM by this CTA below, read back through L2
-#pragma unroll
-                        for (int i = 0; i < 12; i++) P[i] = __ldcg(world_out + (uint64_t)i * E + p);
+                    float4 r0, r1, r2;
+                    if (!kTeam && p < cap) {
+                        r0 = s_win[3 * p], r1 = s_win[3 * p + 1], r2 = s_win[3 * p + 2];
+                    } else if (kTeam && pre_have) {
+                        cp_async_wait_all_but_latest(); // the group committed one iteration ago
+                        const float4 *row = s_pre + ((size_t)(it & 1) * T + tid) * 3;
+                        r0 = row[0], r1 = row[1], r2 = row[2];
+                    } else { // beyond the shared-memory window: the parent's row comes back through L2
+                        const float4 *row = rows + (uint64_t)p * 3;
+                        r0 = __ldcg(row), r1 = __ldcg(row + 1), r2 = __ldcg(row + 2);
                     }
+                    const float P[12] = {r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, r1.w, r2.x, r2.y, r2.z, r2.w};
                     compose(Wm, P, L);
                 }
                 vis = aabb_visible(Wm, st[12 * T], st[13 * T], st[14 * T], st[15 * T], st[16 * T], st[17 * T], wc.frustum);
-                if (may_be_parent) {
-                    if (e < cap) { // 48-byte rows: three conflict-free 128-bit stores
-                        s_win[3 * e] = make_float4(Wm[0], Wm[1], Wm[2], Wm[3]);
-                        s_win[3 * e + 1] = make_float4(Wm[4], Wm[5], Wm[6], Wm[7]);
-                        s_win[3 * e + 2] = make_float4(Wm[8], Wm[9], Wm[10], Wm[11]);
-                    } else {
-#pragma unroll
-                        for (int i = 0; i < 12; i++) world_out[(uint64_t)i * E + e] = Wm[i];
-                    }
+                if (may_be_parent) { // 48-byte rows: three 128-bit stores, conflict-free in shared memory
+                    float4 *row = (!kTeam && e < cap) ? s_win + 3 * e : rows + (uint64_t)e * 3;
+                    row[0] = make_float4(Wm[0], Wm[1], Wm[2], Wm[3]);
+                    row[1] = make_float4(Wm[4], Wm[5], Wm[6], Wm[7]);
+                    row[2] = make_float4(Wm[8], Wm[9], Wm[10], Wm[11]);
                 }
                 // outputs replace this thread's own (now dead) column of the stage; the TMA warp stores them
 #pragma unroll
                 for (int i = 0; i < 12; i++) st[i * T] = Wm[i];
                 st[12 * T] = px, st[13 * T] = py, st[14 * T] = pz;
             }
-            if (l < l_hi) consumer_sync<T>(); // the next level of this chunk reads what this one wrote
+            if (kTeam) {
+                if (l + 1 < levels) { // this chunk's share of level l is (being) written to `rows`
+                    if (pend_level != (int)l) flush_pending(lvl_done);
+                    pend_level = (int)l;
+                    pend_count += min(last, wc.ls[l + 1] - 1) - max(first, wc.ls[l]) + 1;
+                    if (pa.flags & kPipePublishPerChunk) flush_pending(lvl_done);
+                }
+            } else if (l < l_hi) {
+                consumer_sync<T>(); // the next level of this chunk reads what this one wrote
+            }
         }
         fence_async_smem();
-        // mask word + ordered compaction
         const unsigned ballot = __ballot_sync(kFull, vis);
-        uint32_t *cnt = s_cnt[it & 1];
-        if (lane == 0) {
-            mbar_arrive(&done[s]); // this warp's outputs are in the stage
-            if ((e >> 5) < a.mask_words) mask_out[e >> 5] = ballot;
-            warp_mask_sum += ballot;
-            ((uint8_t *)cnt)[warp] = (uint8_t)__popc(ballot);
-        }
-        if (c + 1 == nc && k + 1 < my_worlds) publish_const(s_c[(k + 1) & 1], next_const);
-        consumer_sync<T>();
-        // the warps' counts are bytes: sums over "warps before me" and "all warps" are two dp4a per word
-        uint32_t before = 0, chunk_total = 0;
+        const bool world_ends = c + G >= nc;
+        if (kTeam) {
+            if (lane == 0) {
+                mbar_arrive(&done[s]); // this warp's outputs are in the stage
+                if ((e >> 5) < a.mask_words) mask_out[e >> 5] = ballot;
+            }
+            if (world_ends) flush_pending(lvl_done);
+            if (world_ends && k + 1 < my_worlds) publish_const(s_c[(k + 1) & 1], next_const);
+        } else {
+            // mask word + ordered compaction
+            uint32_t *cnt = s_cnt[it & 1];
+            if (lane == 0) {
+                mbar_arrive(&done[s]);
+                if ((e >> 5) < a.mask_words) mask_out[e >> 5] = ballot;
+                warp_mask_sum += ballot;
+                ((uint8_t *)cnt)[warp] = (uint8_t)__popc(ballot);
+            }
+            if (world_ends && k + 1 < my_worlds) publish_const(s_c[(k + 1) & 1], next_const);
+            consumer_sync<T>();
+            // the warps' counts are bytes: sums over "warps before me" and "all warps" are two dp4a per word
+            uint32_t before = 0, chunk_total = 0;
 #pragma unroll
-        for (int j = 0; j < (kWarps + 3) / 4; j++) {
-            const uint32_t word = cnt[j];
-            const int nb = warp - 4 * j; // bytes of this word that belong to earlier warps
-            const uint32_t below = nb >= 4 ? 0xFFFFFFFFu : (nb <= 0 ? 0u : (1u << (8 * nb)) - 1u);
-            before = __dp4a(word & below, 0x01010101u, before);
-            chunk_total = __dp4a(word, 0x01010101u, chunk_total);
+            for (int j = 0; j < (kWarps + 3) / 4; j++) {
+                const uint32_t word = cnt[j];
+                const int nb = warp - 4 * j; // bytes of this word that belong to earlier warps
+                const uint32_t below = nb >= 4 ? 0xFFFFFFFFu : (nb <= 0 ? 0u : (1u << (8 * nb)) - 1u);
+                before = __dp4a(word & below, 0x01010101u, before);
+                chunk_total = __dp4a(word, 0x01010101u, chunk_total);
+            }
+            if (vis) list_out[running + before + __popc(ballot & ((1u << lane) - 1u))] = e;
+            running += chunk_total;
         }
-        if (vis) list_out[running + before + __popc(ballot & ((1u << lane) - 1u))] = e;
-        running += chunk_total;
-        if (++c == nc) {
-            if (tid == 0) {
+        if (world_ends) {
+            if (!kTeam && tid == 0) {
                 uptr(a.vis_count, w)[0] = running;
                 cta_visible += running;
             }
-            c = 0, k++, w += gridDim.x;
+            c = wk.rank, k++, w += pa.teams;
+        } else {
+            c += G;
         }
         if (++s == N) s = 0, parity ^= 1u;
+        pre_have = pre_next;
     }
 
-    // fold the per-warp mask sums, publish the batch statistics
-    if (lane == 0) atomicAdd(&s_sum, warp_mask_sum);
-    consumer_sync<T>();
-    if (tid == 0) publish_stats(a, cta_visible, s_sum, my_worlds);
+    if (!kTeam) { // fold the per-warp mask sums, publish the batch statistics
+        if (lane == 0) atomicAdd(&s_sum, warp_mask_sum);
+        consumer_sync<T>();
+        if (tid == 0) publish_stats(a, cta_visible, s_sum, my_worlds);
+    }
+}
+
+// Team mode, second kernel: the ordered visible list, the per-world count and the batch statistics, derived
+// from the mask alone (1 bit per entity in, 4 f_vis bytes per entity out — < 1 % of the step's traffic).
+// One CTA per (segment of 256 mask words = 8192 entities, world); a segment's base offset is the popcount of
+// the world's mask words before it (re-read through L2).  Segment 0 also re-arms the world's level counters.
+constexpr int kCompactThreads = 256;
+__global__ void __launch_bounds__(kCompactThreads) k_compact_lists(const StepArgs a, uint32_t *lvl_done_all) {
+    __shared__ uint32_t s_warp[2][kCompactThreads / 32];
+    __shared__ unsigned long long s_mask_sum;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const uint32_t seg = blockIdx.x;
+    const uint64_t w = blockIdx.y;
+    const uint32_t *__restrict__ mask = uptr(a.vis_mask, w);
+    uint32_t *__restrict__ list = uptr(a.vis_list, w);
+    if (tid == 0) s_mask_sum = 0;
+    if (seg == 0 && tid < kMaxLevels && lvl_done_all) lvl_done_all[w * kMaxLevels + tid] = 0;
+
+    uint32_t before = 0; // visible entities of this world in earlier segments (this thread's share)
+    for (uint32_t i = tid; i < seg * kCompactThreads; i += kCompactThreads) before += __popc(__ldcg(mask + i));
+    const uint32_t wi = seg * kCompactThreads + tid;
+    uint32_t word = wi < a.mask_words ? __ldcg(mask + wi) : 0u;
+    const uint32_t mine = __popc(word);
+    // warp-inclusive scan of `mine`, warp sum of `before`
+    uint32_t incl = mine;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        const uint32_t v = __shfl_up_sync(kFull, incl, d);
+        if (lane >= d) incl += v;
+    }
+    const uint32_t before_warp = __reduce_add_sync(kFull, before);
+    if (lane == 31) s_warp[0][warp] = incl;
+    if (lane == 0) s_warp[1][warp] = before_warp;
+    __syncthreads();
+    uint32_t all_before = 0, earlier = 0, seg_total = 0;
+#pragma unroll
+    for (int i = 0; i < kCompactThreads / 32; i++) {
+        all_before += s_warp[1][i];
+        earlier += i < warp ? s_warp[0][i] : 0u;
+        seg_total += s_warp[0][i];
+    }
+    uint32_t off = all_before + earlier + incl - mine;
+    const unsigned long long word64 = word;
+    while (word) {
+        const uint32_t b = __ffs(word) - 1;
+        list[off++] = wi * 32u + b;
+        word &= word - 1;
+    }
+    const unsigned long long warp_sum = __reduce_add_sync(kFull, (uint32_t)(word64 & 0xFFFFu)) +
+                                        ((unsigned long long)__reduce_add_sync(kFull, (uint32_t)(word64 >> 16)) << 16);
+    if (lane == 0) atomicAdd(&s_mask_sum, warp_sum);
+    __syncthreads();
+    if (tid == 0) {
+        if (seg == gridDim.x - 1) uptr(a.vis_count, w)[0] = all_before + seg_total;
+        publish_stats(a, seg_total, s_mask_sum, seg == 0 ? 1ull : 0ull, (unsigned long long)gridDim.x * gridDim.y);
+    }
 }
 
 } // namespace
@@ -343,8 +532,9 @@ constexpr size_t kStaticSmem = 768;         // WorldConst x2, counts, sum (see -
 size_t ring_bytes(int T, uint32_t stages) { return (size_t)stages * kPlanes * T * 4; }
 
 // Largest index of an entity that can be a parent, over all worlds: max level_start[levels-1].  Read once
-// from HBM when the executor is compiled (cold path).  If the host later uploads a different hierarchy the
-// kernel stays correct — parents outside the window are read back through L2 — only the sizing is stale.
+// from HBM when the executor is compiled (cold path) to size the shared-memory window.  If the host later
+// uploads a different hierarchy the kernel stays correct — parents outside the window travel through the
+// `rows` buffer, which always covers every entity — only the sizing is stale.
 uint64_t max_parents(const WorldStepViews &v, int device) {
     const FimoB200_ResourceView *ls = v.level_start;
     const uint64_t E = v.world->count;
@@ -360,11 +550,34 @@ uint64_t max_parents(const WorldStepViews &v, int device) {
 bool make_plan(WorldStepPlan &p, int T, uint32_t blocks, uint32_t stages, uint64_t want_cap, uint64_t E) {
     const size_t budget = kSmemPerSm / blocks - kSmemPerCtaReserve - kStaticSmem;
     const size_t fixed = ring_bytes(T, stages) + (size_t)stages * 16;
-    if (fixed + 48 * 2 > budget) return false;
+    if (fixed > budget) return false;
     uint64_t cap = std::min<uint64_t>({want_cap, E, (budget - fixed) / 48});
     p.threads = T, p.blocks_per_sm = blocks, p.stages = stages, p.lvl_cap = (uint32_t)cap;
     p.smem = ring_bytes(T, stages) + (size_t)cap * 48 + (size_t)stages * 16;
     return true;
+}
+
+// How many CTAs step one world together.  Few worlds (W below the CTA slots of the GPU) leave slots idle and
+// serialise each world inside one CTA, so the slots are dealt out as `teams` x `team`: the split that keeps
+// the most slots busy with an even number of worlds per team, ties to the smaller team.
+void choose_team(WorldStepPlan &p, uint64_t W, uint64_t chunks, uint64_t slots) {
+    p.team = 1, p.teams = 0;
+    if (chunks < 2 || W * 2 > slots) return;
+    double best = 0.0;
+    for (uint64_t per = 1; per <= 8 && per <= W; per++) {
+        const uint64_t teams = (W + per - 1) / per;
+        const uint64_t team = std::min<uint64_t>(slots / teams, chunks);
+        if (team < 1) continue;
+        const double used = (double)(teams * team) / (double)slots * ((double)W / (double)(teams * per));
+        if (used > best + 1e-9) best = used, p.team = (uint32_t)team, p.teams = (uint32_t)teams;
+    }
+    if (p.team <= 1) p.team = 1, p.teams = 0;
+}
+
+std::shared_ptr<void> hbm_shared(int device, size_t bytes) {
+    void *ptr = hbm_alloc(device, bytes);
+    if (!ptr) return nullptr;
+    return std::shared_ptr<void>(ptr, [device](void *q) { hbm_free(device, q); });
 }
 
 } // namespace
@@ -372,7 +585,7 @@ bool make_plan(WorldStepPlan &p, int T, uint32_t blocks, uint32_t stages, uint64
 bool world_step_plan(const WorldStepViews &v, int device, WorldStepPlan &plan) {
     plan = WorldStepPlan{};
     if (!v.world || !v.level_start) return false;
-    const uint64_t E = v.world->count;
+    const uint64_t E = v.world->count, W = v.world->n_worlds;
     if (E == 0 || E > 0x7FFFFFFFull) return false;
     bool pipe = E % 4 == 0; // the pipelined kernel needs 16-byte aligned plane rows (bulk copies)
     for (const FimoB200_ResourceView *r : {v.pos, v.vel, v.rot, v.scale, v.parent, v.aabb_c, v.aabb_h, v.world})
@@ -384,6 +597,7 @@ bool world_step_plan(const WorldStepViews &v, int device, WorldStepPlan &plan) {
     }
     const uint64_t parents = max_parents(v, device);
     plan.max_parents = (uint32_t)parents;
+    bool planned = false;
     // FIMO_B200_PIPE=T,blocks,stages[,cap] overrides the heuristic (tuning sweeps; any value is correct)
     if (const char *env = std::getenv("FIMO_B200_PIPE")) {
         int T = 0;
@@ -391,34 +605,80 @@ bool world_step_plan(const WorldStepViews &v, int device, WorldStepPlan &plan) {
         unsigned long long cap = parents;
         if (std::sscanf(env, "%d,%u,%u,%llu", &T, &blocks, &stages, &cap) >= 3 && (T == 128 || T == 256 || T == 512) &&
             blocks >= 1 && blocks <= 6 && stages >= 2 && stages <= 16 && make_plan(plan, T, blocks, stages, cap, E))
-            return true;
-        std::fprintf(stderr, "fimo_worlds_b200: ignoring FIMO_B200_PIPE=%s\n", env);
+            planned = true;
+        else
+            std::fprintf(stderr, "fimo_worlds_b200: ignoring FIMO_B200_PIPE=%s\n", env);
     }
-    // Heuristic (measured on B200, profiles/r1f_sweep.txt): many small CTAs hide the level barriers best —
-    // 4 CTAs x 128 entities with a 4-deep ring — as long as the whole parent window fits beside the ring.
-    if (make_plan(plan, 128, 4, 4, parents, E) && plan.lvl_cap >= parents) return true;
-    if (make_plan(plan, 256, 3, 3, parents, E) && plan.lvl_cap >= parents) return true;
-    if (make_plan(plan, 256, 2, 4, parents, E) && plan.lvl_cap >= parents) return true;
-    if (make_plan(plan, 256, 2, 3, parents, E) && plan.lvl_cap >= parents) return true;
-    return make_plan(plan, 256, 2, 4, parents, E); // partial window; the rest of the parents come from L2
+    // Heuristic (measured on B200, profiles/r1h_sweep.txt): parent matrices gathered from shared memory are what
+    // keeps the kernel on the HBM roofline, so the plan that holds the largest share of the parents in its window
+    // wins; among equals, more and smaller CTAs (they hide the level barriers best).  A 3-deep ring beats deeper
+    // ones on every shape measured.  Parents outside the window travel through `rows`.
+    if (!planned) {
+        static const struct { int T; uint32_t blocks, stages; } kCandidates[] = {{128, 4, 3}, {256, 3, 3}, {256, 2, 3}, {512, 1, 3}};
+        double best = -1.0;
+        for (const auto &cand : kCandidates) {
+            WorldStepPlan trial = plan;
+            if (!make_plan(trial, cand.T, cand.blocks, cand.stages, parents, E)) continue;
+            const double coverage = parents ? std::min(1.0, (double)trial.lvl_cap / (double)parents) : 1.0;
+            if (coverage > best + 1e-9) best = coverage, plan = trial;
+        }
+        if (best < 0.0) return false;
+    }
+    // Few worlds (or a forced team size): CTA teams, with the geometry that suits them (no window needed).
+    const char *team_env = std::getenv("FIMO_B200_TEAM"); // force the team size (1 = one CTA per world)
+    const uint64_t forced = team_env ? std::strtoull(team_env, nullptr, 10) : 0;
+    if (!planned && (!team_env || forced > 1)) {
+        WorldStepPlan trial = plan;
+        make_plan(trial, 128, 4, 3, 0, E);
+        choose_team(trial, W, (E + 127) / 128, 4ull * sm_count(device));
+        if (trial.team > 1 || forced > 1) plan = trial;
+    }
+    const uint64_t chunks = (E + plan.threads - 1) / plan.threads;
+    const uint64_t slots = (uint64_t)plan.blocks_per_sm * sm_count(device);
+    if (!team_env) choose_team(plan, W, chunks, slots);
+    else if (forced <= 1) plan.team = 1, plan.teams = 0;
+    else plan.team = (uint32_t)std::min<uint64_t>({forced, chunks, slots}), plan.teams = (uint32_t)std::min<uint64_t>(W, slots / plan.team);
+    if (plan.team <= 1) plan.team = 1, plan.teams = 0;
+    if (plan.team > 1) { // no window: every parent row goes through L2
+        plan.lvl_cap = 0;
+        plan.smem = ring_bytes(plan.threads, plan.stages) + (size_t)plan.stages * 16 + (size_t)2 * plan.threads * 48;
+        plan.kernels = 2;
+        plan.lvl_done = hbm_shared(device, (size_t)W * kMaxLevels * 4);
+        if (!plan.lvl_done) return false;
+    }
+    plan.rows = hbm_shared(device, (size_t)W * E * 48);
+    return plan.rows != nullptr;
 }
 
 const char *world_step_kernel_name(const WorldStepPlan &plan) {
     if (plan.threads == 0) return "k_world_cta<256,true,true> (one CTA per world)";
+    if (plan.team > 1) return "k_world_step_pipe<team> + k_compact_lists (TMA-fed persistent world-step, CTA teams per world)";
     return "k_world_step_pipe (TMA-fed persistent world-step)";
 }
 
 namespace {
 template <int T, int kBlocks>
-FimoStatus launch_pipe(const PipeArgs &pa, const WorldStepPlan &plan, uint64_t W, const FimoB200_LaunchInfo *info) {
-    auto kernel = k_world_step_pipe<T, kBlocks>;
+FimoStatus launch_pipe(PipeArgs &pa, const WorldStepPlan &plan, uint64_t W, const FimoB200_LaunchInfo *info) {
+    cudaStream_t stream = (cudaStream_t)info->stream;
+    if (plan.team > 1) {
+        auto kernel = k_world_step_pipe<T, kBlocks, true>;
+        if (!allow_smem(kernel, plan.smem)) return check_launch("world_step (shared memory opt-in)");
+        pa.team = plan.team, pa.teams = plan.teams;
+        kernel<<<plan.team * plan.teams, T + 32, plan.smem, stream>>>(pa);
+        if (check_launch("world_step") != FIMO_STATUS_OK) return FIMO_STATUS_ERROR;
+        const unsigned segments = (pa.a.mask_words + kCompactThreads - 1) / kCompactThreads;
+        k_compact_lists<<<dim3(segments, (unsigned)W), kCompactThreads, 0, stream>>>(pa.a, pa.lvl_done);
+        return check_launch("compact_lists");
+    }
+    auto kernel = k_world_step_pipe<T, kBlocks, false>;
     if (!allow_smem(kernel, plan.smem)) return check_launch("world_step (shared memory opt-in)");
     // Persistent grid with an even share of worlds per CTA: a ragged tail costs more than idle CTA slots
     // on an HBM-bound kernel.
     const uint64_t slots = (uint64_t)plan.blocks_per_sm * sm_count(info->device);
     const uint64_t per_cta = (W + slots - 1) / slots;
     const unsigned grid = (unsigned)((W + per_cta - 1) / per_cta);
-    kernel<<<grid, T + 32, plan.smem, (cudaStream_t)info->stream>>>(pa);
+    pa.team = 1, pa.teams = grid;
+    kernel<<<grid, T + 32, plan.smem, stream>>>(pa);
     return check_launch("world_step");
 }
 } // namespace
@@ -439,6 +699,13 @@ FimoStatus world_step_launch(const WorldStepViews &v, const WorldStepPlan &plan,
         pa.stages = plan.stages;
         pa.lvl_cap = plan.lvl_cap;
         pa.chunks = (uint32_t)((E + plan.threads - 1) / plan.threads);
+        pa.rows = (float4 *)plan.rows.get();
+        pa.lvl_done = (uint32_t *)plan.lvl_done.get();
+        pa.flags = kPipePrefetchBlocking; // FIMO_B200_PREFETCH=0 / 1 (only if already landed) / 2 (default)
+        if (const char *env = std::getenv("FIMO_B200_PREFETCH"))
+            pa.flags = (pa.flags & ~kPipePrefetchBlocking) | (env[0] == '0' ? kPipeNoPrefetch : (env[0] == '2' ? kPipePrefetchBlocking : 0u));
+        if (const char *env = std::getenv("FIMO_B200_PUBLISH"))
+            if (env[0] == 'c') pa.flags |= kPipePublishPerChunk;
         const int key = plan.threads * 10 + (int)plan.blocks_per_sm;
         switch (key) {
         case 1284: case 1283: case 1282: case 1281: return launch_pipe<128, 4>(pa, plan, W, info);

@@ -872,7 +872,7 @@ bool build_device_executor(Group *g, const char **err) {
         dev::Node node;
         void *scratch = ((dev::BuiltinState *)mc->state)->scratch;
         node.launch = [views, plan, scratch](const FimoB200_LaunchInfo *info) { return dev::world_step_launch(views, plan, scratch, info); };
-        node.kernels = 1;
+        node.kernels = plan.kernels;
         nodes.push_back(std::move(node));
         edges = 0;
     } else {

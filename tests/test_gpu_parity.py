@@ -43,13 +43,17 @@ CASES = [
 
 
 @pytest.mark.parametrize("W,E,D,steps", CASES)
-@pytest.mark.parametrize("mode", ["fused", "unfused-graph", "unfused-streams"])
-def test_three_system_chain_matches_oracle(oracle, product, W, E, D, steps, mode):
-    options = synth.RigOptions(fused=(mode == "fused"), graph=(mode != "unfused-streams"))
+@pytest.mark.parametrize("mode", ["fused", "fused-one-cta-per-world", "unfused-graph", "unfused-streams"])
+def test_three_system_chain_matches_oracle(oracle, product, monkeypatch, W, E, D, steps, mode):
+    if mode == "fused-one-cta-per-world":
+        monkeypatch.setenv("FIMO_B200_TEAM", "1")  # small batches default to CTA teams; pin the other kernel too
+    options = synth.RigOptions(fused=mode.startswith("fused"), graph=(mode != "unfused-streams"))
     got, want, info = run_both(oracle, product, W, E, D, steps, options)
     assert info.systems == 3 and info.device_systems == 3
-    if mode == "fused":
-        assert info.fused_world_step == 1 and info.nodes == 1 and info.kernel_launches_per_generation == 1
+    if mode.startswith("fused"):
+        assert info.fused_world_step == 1 and info.nodes == 1
+        assert info.kernel_launches_per_generation == (1 if mode == "fused-one-cta-per-world" else info.kernel_launches_per_generation)
+        assert info.kernel_launches_per_generation in (1, 2)  # 2 = team kernel + list compaction
     else:
         assert info.fused_world_step == 0 and info.nodes == 3
     assert info.uses_cuda_graph == (0 if mode == "unfused-streams" else 1)
@@ -57,6 +61,31 @@ def test_three_system_chain_matches_oracle(oracle, product, W, E, D, steps, mode
     assert not problems, "\n".join(problems)
     st = got["stats"].reshape(-1).view(np.uint64)
     assert st[abi.STAT_STEPS] == W * steps and st[abi.STAT_WORLDS] == W
+
+
+TEAM_CASES = [
+    # (worlds, entities, depth, steps, forced team size or None = heuristic)
+    (3, 65536, 8, 3, None),    # configs[2] world shape: a world is stepped by ~197 CTAs
+    (16, 1024, 4, 4, None),    # more CTAs than chunks per world
+    (5, 4096, 4, 3, 3),        # team size that does not divide the chunk count
+    (2, 8192, 8, 2, 37),
+    (40, 2048, 8, 3, 2),
+    (9, 640, 5, 4, 4),         # last chunk ragged, 5 levels
+]
+
+
+@pytest.mark.parametrize("W,E,D,steps,team", TEAM_CASES)
+def test_cta_teams_match_oracle(oracle, product, monkeypatch, W, E, D, steps, team):
+    """Large worlds / few worlds: several CTAs step one world together (dataflow level counters through L2,
+    list compaction in a second kernel).  Same bit-exact bar."""
+    if team is not None:
+        monkeypatch.setenv("FIMO_B200_TEAM", str(team))
+    got, want, info = run_both(oracle, product, W, E, D, steps)
+    assert info.fused_world_step == 1 and info.kernel_launches_per_generation == 2
+    problems = synth.compare_outputs(got, want, FLOAT_RTOL)
+    assert not problems, "\n".join(problems)
+    st = got["stats"].reshape(-1).view(np.uint64)
+    assert st[abi.STAT_STEPS] == W * steps and st[abi.STAT_WORLDS] == W and st[abi.STAT_ENTITIES] == W * E
 
 
 def test_large_world_per_level_propagate(oracle, product):
@@ -68,8 +97,9 @@ def test_large_world_per_level_propagate(oracle, product):
     assert not problems, "\n".join(problems)
 
 
-def test_large_world_fused_pipeline(oracle, product):
-    """Same shape through the fused pipelined kernel: parents beyond the shared-memory window come from L2."""
+def test_large_world_fused_pipeline(oracle, product, monkeypatch):
+    """Same shape through the fused pipelined kernel: parents beyond the shared-memory window travel through the 48-byte row buffer in L2."""
+    monkeypatch.setenv("FIMO_B200_TEAM", "1")
     got, want, info = run_both(oracle, product, 3, 65536, 8, 3)
     assert info.fused_world_step == 1 and info.kernel_launches_per_generation == 1
     problems = synth.compare_outputs(got, want, FLOAT_RTOL)
