@@ -21,6 +21,9 @@ STYPE_GROUP_DEVICE = 0xB2000004
 
 SCOPE_ENTITY, SCOPE_WORLD, SCOPE_ENTITY_BITS, SCOPE_BATCH = 0, 1, 2, 3
 BUILTIN_NONE, BUILTIN_INTEGRATE, BUILTIN_PROPAGATE, BUILTIN_CULL = 0, 1, 2, 3
+(BUILTIN_FORCES, BUILTIN_INTEGRATE_ANG, BUILTIN_WORLD_AABB, BUILTIN_CULL_WAABB, BUILTIN_BOUNDS_REDUCE, BUILTIN_GROUP_STATS,
+ BUILTIN_PREV_COPY, BUILTIN_LOD, BUILTIN_VEL_CLAMP, BUILTIN_SLEEP_FLAGS, BUILTIN_ANGVEL_DAMP, BUILTIN_VIS_BOUNDS) = range(4, 16)
+GSTAT_VISIBLE_LO, GSTAT_WORLDS_LO, GSTAT_BOUNDS, GSTAT_WORDS = 0, 2, 4, 16
 STAT_VISIBLE, STAT_ENTITIES, STAT_MASK_SUM, STAT_WORLDS, STAT_STEPS, STAT_WORDS = 0, 1, 2, 3, 4, 8
 PARENT_ROOT = 0xFFFFFFFF
 DEP_WEAK, DEP_IGNORE_DEFERRED = 1, 2

@@ -59,6 +59,23 @@ FimoStatus builtin_propagate(void *system, const FimoB200_ResourceView *const *e
                              const FimoB200_ResourceView *const *shared, const FimoB200_LaunchInfo *info);
 FimoStatus builtin_cull(void *system, const FimoB200_ResourceView *const *exclusive,
                         const FimoB200_ResourceView *const *shared, const FimoB200_LaunchInfo *info);
+#define FB_DECLARE_ENTRY(fn)                                                                                       \
+    FimoStatus fn(void *system, const FimoB200_ResourceView *const *exclusive, const FimoB200_ResourceView *const *shared, \
+                  const FimoB200_LaunchInfo *info)
+// systems_extra.cu: the systems of the 8- and 16-system DAGs
+FB_DECLARE_ENTRY(builtin_forces);
+FB_DECLARE_ENTRY(builtin_vel_clamp);
+FB_DECLARE_ENTRY(builtin_angvel_damp);
+FB_DECLARE_ENTRY(builtin_integrate_ang);
+FB_DECLARE_ENTRY(builtin_world_aabb);
+FB_DECLARE_ENTRY(builtin_prev_copy);
+FB_DECLARE_ENTRY(builtin_lod);
+FB_DECLARE_ENTRY(builtin_sleep_flags);
+FB_DECLARE_ENTRY(builtin_cull_waabb);
+FB_DECLARE_ENTRY(builtin_bounds_reduce);
+FB_DECLARE_ENTRY(builtin_vis_bounds);
+FB_DECLARE_ENTRY(builtin_group_stats);
+#undef FB_DECLARE_ENTRY
 uint32_t builtin_propagate_kernels(const FimoB200_ResourceView *world, const FimoB200_ResourceView *level_start);
 
 // State of a built-in system instance (what `system_create` builds into the system blob).

@@ -776,7 +776,10 @@ uint64_t algorithmic_bytes(Group *g) {
         for (ResourceType *r : m->type->shared)
             if (!written.count(r)) read.insert(r);
         for (ResourceType *r : m->type->exclusive) {
-            if (m->type->builtin_id == FIMO_B200_BUILTIN_INTEGRATE && !written.count(r)) read.insert(r);
+            const uint32_t id = m->type->builtin_id; // built-ins that update their exclusive resource in place
+            const bool in_place = id == FIMO_B200_BUILTIN_INTEGRATE || id == FIMO_B200_BUILTIN_FORCES || id == FIMO_B200_BUILTIN_VEL_CLAMP ||
+                                  id == FIMO_B200_BUILTIN_ANGVEL_DAMP || id == FIMO_B200_BUILTIN_INTEGRATE_ANG;
+            if (in_place && !written.count(r)) read.insert(r);
             written.insert(r);
         }
     }
@@ -1332,7 +1335,7 @@ bool builtin_create(const void *factory, FimoWorldsMeta_SystemContext *context, 
     state->device = m->group->world->device;
     state->scratch = nullptr;
     if (state->device < 0) return false; // built-in systems exist on the device only
-    if (m->type->builtin_id == FIMO_B200_BUILTIN_CULL) {
+    if (m->type->builtin_id == FIMO_B200_BUILTIN_CULL || m->type->builtin_id == FIMO_B200_BUILTIN_CULL_WAABB) {
         state->scratch = dev::hbm_alloc(state->device, 64);
         if (!state->scratch) return false;
     }
@@ -1544,6 +1547,18 @@ FimoStatus fimo_b200_builtin_system(uint32_t builtin_id, FimoWorldsMeta_SystemDe
         case FIMO_B200_BUILTIN_INTEGRATE: entry = &dev::builtin_integrate; break;
         case FIMO_B200_BUILTIN_PROPAGATE: entry = &dev::builtin_propagate; break;
         case FIMO_B200_BUILTIN_CULL: entry = &dev::builtin_cull; break;
+        case FIMO_B200_BUILTIN_FORCES: entry = &dev::builtin_forces; break;
+        case FIMO_B200_BUILTIN_INTEGRATE_ANG: entry = &dev::builtin_integrate_ang; break;
+        case FIMO_B200_BUILTIN_WORLD_AABB: entry = &dev::builtin_world_aabb; break;
+        case FIMO_B200_BUILTIN_CULL_WAABB: entry = &dev::builtin_cull_waabb; break;
+        case FIMO_B200_BUILTIN_BOUNDS_REDUCE: entry = &dev::builtin_bounds_reduce; break;
+        case FIMO_B200_BUILTIN_GROUP_STATS: entry = &dev::builtin_group_stats; break;
+        case FIMO_B200_BUILTIN_PREV_COPY: entry = &dev::builtin_prev_copy; break;
+        case FIMO_B200_BUILTIN_LOD: entry = &dev::builtin_lod; break;
+        case FIMO_B200_BUILTIN_VEL_CLAMP: entry = &dev::builtin_vel_clamp; break;
+        case FIMO_B200_BUILTIN_SLEEP_FLAGS: entry = &dev::builtin_sleep_flags; break;
+        case FIMO_B200_BUILTIN_ANGVEL_DAMP: entry = &dev::builtin_angvel_damp; break;
+        case FIMO_B200_BUILTIN_VIS_BOUNDS: entry = &dev::builtin_vis_bounds; break;
         default: return report("NotFound");
     }
     *ext = FimoB200_SystemDeviceExt{};

@@ -39,12 +39,59 @@ LAYOUT = {
     "vis_count": (abi.SCOPE_WORLD, 1, np.uint32),
     "stats": (abi.SCOPE_BATCH, 2 * abi.STAT_WORDS, np.uint32),
 }
+# resources the 8-system DAG adds (BASELINE.json configs[2]) ...
+LAYOUT_DAG8 = {
+    "gravity": (abi.SCOPE_WORLD, 3, np.float32),
+    "angvel": (abi.SCOPE_ENTITY, 3, np.float32),
+    "waabb": (abi.SCOPE_ENTITY, 6, np.float32),
+    "wbounds": (abi.SCOPE_WORLD, 6, np.float32),
+    "gstats": (abi.SCOPE_BATCH, abi.GSTAT_WORDS, np.uint32),
+}
+# ... and the 16-system DAG (configs[4])
+LAYOUT_DAG16 = {
+    "frustum2": (abi.SCOPE_WORLD, 24, np.float32),
+    "vis_mask2": (abi.SCOPE_ENTITY_BITS, 1, np.uint32),
+    "vis_list2": (abi.SCOPE_ENTITY, 1, np.uint32),
+    "vis_count2": (abi.SCOPE_WORLD, 1, np.uint32),
+    "stats2": (abi.SCOPE_BATCH, 2 * abi.STAT_WORDS, np.uint32),
+    "prev_world": (abi.SCOPE_ENTITY, 12, np.float32),
+    "lod": (abi.SCOPE_ENTITY, 1, np.uint32),
+    "campos": (abi.SCOPE_WORLD, 3, np.float32),
+    "lod_dist2": (abi.SCOPE_WORLD, 3, np.float32),
+    "vmax": (abi.SCOPE_WORLD, 1, np.float32),
+    "sleep": (abi.SCOPE_ENTITY_BITS, 1, np.uint32),
+    "sleep_eps": (abi.SCOPE_WORLD, 1, np.float32),
+    "damp": (abi.SCOPE_WORLD, 1, np.float32),
+    "vbounds": (abi.SCOPE_WORLD, 6, np.float32),
+    "gstats2": (abi.SCOPE_BATCH, abi.GSTAT_WORDS, np.uint32),
+}
+DAGS = ("chain3", "dag8", "dag16")
+
+
+def layout_for(dag: str) -> dict:
+    out = dict(LAYOUT)
+    if dag in ("dag8", "dag16"):
+        out.update(LAYOUT_DAG8)
+    if dag == "dag16":
+        out.update(LAYOUT_DAG16)
+    return out
+
+
+def outputs_for(dag: str) -> tuple:
+    """Every resource some system of the DAG writes."""
+    out = OUTPUTS
+    if dag in ("dag8", "dag16"):
+        out = out + ("vel", "rot", "waabb", "wbounds", "gstats")
+    if dag == "dag16":
+        out = out + ("angvel", "vis_mask2", "vis_list2", "vis_count2", "stats2", "prev_world", "lod", "sleep", "vbounds", "gstats2")
+    return out
 LIVE_IN = ("pos", "vel", "rot", "scale", "parent", "aabb_c", "aabb_h")  # 72 B / entity
 LIVE_OUT = ("pos", "world", "vis_mask", "vis_list")  # 60.125 + 4 f_vis B / entity
 OUTPUTS = ("pos", "world", "vis_mask", "vis_list", "vis_count", "stats")
 
 _F = {  # field ids of the generator
-    "pos": 0, "vel": 3, "rot": 6, "scale": 10, "aabb_c": 11, "aabb_h": 14, "parent": 17, "yaw": 18, "rot_retry": 32,
+    "pos": 0, "vel": 3, "rot": 6, "scale": 10, "aabb_c": 11, "aabb_h": 14, "parent": 17, "yaw": 18, "angvel": 19, "yaw2": 22,
+    "campos": 23, "rot_retry": 32,
 }
 
 
@@ -84,7 +131,7 @@ def level_starts(entities: int, depth: int) -> np.ndarray:
     return starts
 
 
-def generate(n_worlds: int, entities: int, depth: int, world0: int = 0, seed: int = SEED) -> dict[str, np.ndarray]:
+def generate(n_worlds: int, entities: int, depth: int, world0: int = 0, seed: int = SEED, dag: str = "chain3") -> dict[str, np.ndarray]:
     """All resources of `n_worlds` worlds starting at global world index `world0`, each laid out
     [n_worlds][components][count] (4-byte words), outputs zero-filled."""
     W, E = n_worlds, entities
@@ -137,19 +184,51 @@ def generate(n_worlds: int, entities: int, depth: int, world0: int = 0, seed: in
     def unit(v):
         return v / np.linalg.norm(v, axis=1, keepdims=True)
 
-    planes[:, 0, :3], planes[:, 0, 3] = f, -0.1  # near
-    planes[:, 1, :3], planes[:, 1, 3] = -f, 400.0  # far
-    planes[:, 2, :3] = unit(f + r)  # left
-    planes[:, 3, :3] = unit(f - r)  # right
-    planes[:, 4, :3] = unit(f + up)  # bottom
-    planes[:, 5, :3] = unit(f - up)  # top
-    out["frustum"] = planes.reshape(W, 24, 1).astype(np.float32)
+    def frustum_planes(f, r):
+        planes[:, 0, :3], planes[:, 0, 3] = f, -0.1  # near
+        planes[:, 1, :3], planes[:, 1, 3] = -f, 400.0  # far
+        planes[:, 2, :3] = unit(f + r)  # left
+        planes[:, 3, :3] = unit(f - r)  # right
+        planes[:, 4, :3] = unit(f + up)  # bottom
+        planes[:, 5, :3] = unit(f - up)  # top
+        return planes.reshape(W, 24, 1).astype(np.float32)
+
+    out["frustum"] = frustum_planes(f, r)
 
     out["world"] = np.zeros((W, 12, E), dtype=np.float32)
     out["vis_mask"] = np.zeros((W, 1, (E + 31) // 32), dtype=np.uint32)
     out["vis_list"] = np.zeros((W, 1, E), dtype=np.uint32)
     out["vis_count"] = np.zeros((W, 1, 1), dtype=np.uint32)
     out["stats"] = np.zeros((1, 2 * abi.STAT_WORDS, 1), dtype=np.uint32)
+
+    if dag in ("dag8", "dag16"):
+        out["gravity"] = np.broadcast_to(np.array([0.0, -9.81, 0.0], dtype=np.float32)[None, :, None], (W, 3, 1)).copy()
+        out["angvel"] = field3("angvel", -2.0, 2.0)
+        out["waabb"] = np.zeros((W, 6, E), dtype=np.float32)
+        out["wbounds"] = np.zeros((W, 6, 1), dtype=np.float32)
+        out["gstats"] = np.zeros((1, abi.GSTAT_WORDS, 1), dtype=np.uint32)
+    if dag == "dag16":
+        u2 = (pcg_hash(_key(seed, wi[:, 0], np.zeros(W, np.uint32), _F["yaw2"])) >> np.uint32(8)).astype(np.float64) / (1 << 24)
+        yaw2 = 2.0 * math.pi * u2
+        out["frustum2"] = frustum_planes(np.stack([np.sin(yaw2), np.zeros(W), np.cos(yaw2)], axis=1),
+                                         np.stack([np.cos(yaw2), np.zeros(W), -np.sin(yaw2)], axis=1))
+        out["vis_mask2"] = np.zeros((W, 1, (E + 31) // 32), dtype=np.uint32)
+        out["vis_list2"] = np.zeros((W, 1, E), dtype=np.uint32)
+        out["vis_count2"] = np.zeros((W, 1, 1), dtype=np.uint32)
+        out["stats2"] = np.zeros((1, 2 * abi.STAT_WORDS, 1), dtype=np.uint32)
+        out["prev_world"] = np.zeros((W, 12, E), dtype=np.float32)
+        out["lod"] = np.zeros((W, 1, E), dtype=np.uint32)
+        cam = np.empty((W, 3, 1), dtype=np.float32)
+        for k in range(3):
+            cam[:, k, 0] = _uniform(seed, wi[:, 0], np.zeros(W, np.uint32), _F["campos"] + 8 * k, -20.0, 20.0)
+        out["campos"] = cam
+        out["lod_dist2"] = np.broadcast_to(np.array([50.0 ** 2, 100.0 ** 2, 150.0 ** 2], dtype=np.float32)[None, :, None], (W, 3, 1)).copy()
+        out["vmax"] = np.full((W, 1, 1), 0.9, dtype=np.float32)
+        out["sleep"] = np.zeros((W, 1, (E + 31) // 32), dtype=np.uint32)
+        out["sleep_eps"] = np.full((W, 1, 1), 0.75, dtype=np.float32)
+        out["damp"] = np.full((W, 1, 1), 0.99, dtype=np.float32)
+        out["vbounds"] = np.zeros((W, 6, 1), dtype=np.float32)
+        out["gstats2"] = np.zeros((1, abi.GSTAT_WORDS, 1), dtype=np.uint32)
     return {k: np.ascontiguousarray(v) for k, v in out.items()}
 
 
@@ -192,12 +271,14 @@ class WorldStepRig:
 
     def __init__(self, lib: abi.WorldsLib, n_worlds: int, entities: int, depth: int, world0: int = 0,
                  options: RigOptions | None = None, data: dict[str, np.ndarray] | None = None, pool: abi.Pool | None = None,
-                 post_step=None):
-        self.lib, self.W, self.E, self.depth = lib, n_worlds, entities, depth
+                 post_step=None, dag: str = "chain3"):
+        assert dag in DAGS
+        self.lib, self.W, self.E, self.depth, self.dag = lib, n_worlds, entities, depth, dag
         self.opt = options or RigOptions()
         self.on_device = lib.is_product
-        self.host = data if data is not None else generate(n_worlds, entities, depth, world0)
+        self.host = data if data is not None else generate(n_worlds, entities, depth, world0, dag=dag)
         self._keep: list = []
+        self._registered: list = []
         self.resources: dict[str, Resource] = {}
         self.views: dict[str, abi.ResourceView] = {}
 
@@ -205,7 +286,7 @@ class WorldStepRig:
         if self.on_device:
             batch = abi.WorldBatchExt(abi.ExtHeader(abi.STYPE_WORLD_BATCH, 0, None), n_worlds, entities, self.opt.device, 0)
         self.world = World.init(lib, "synthetic-batch", pool=pool, batch=batch)
-        for name, (scope, comps, _dtype) in LAYOUT.items():
+        for name, (scope, comps, _dtype) in layout_for(dag).items():
             if name == "level_start":
                 comps = depth + 1
             arr = self.host[name]
@@ -227,14 +308,49 @@ class WorldStepRig:
         self.group = self.world.add_system_group("world-step", pool=pool, ext=gext)
 
         R = self.resources
-        self.sys_integrate = self._system("integrate", abi.BUILTIN_INTEGRATE, [R["pos"]], [R["vel"], R["dt"]])
-        self.sys_propagate = self._system("propagate", abi.BUILTIN_PROPAGATE, [R["world"]],
-                                          [R["pos"], R["rot"], R["scale"], R["parent"], R["level_start"]],
-                                          before=[self.sys_integrate])
-        self.sys_cull = self._system("cull", abi.BUILTIN_CULL,
-                                     [R["vis_mask"], R["vis_list"], R["vis_count"], R["stats"]],
-                                     [R["world"], R["aabb_c"], R["aabb_h"], R["frustum"]], before=[self.sys_propagate])
-        self.systems = [self.sys_integrate, self.sys_propagate, self.sys_cull]
+        sysdef = self._system
+        if dag == "chain3":
+            integrate = sysdef("integrate", abi.BUILTIN_INTEGRATE, [R["pos"]], [R["vel"], R["dt"]])
+            propagate = sysdef("propagate", abi.BUILTIN_PROPAGATE, [R["world"]],
+                               [R["pos"], R["rot"], R["scale"], R["parent"], R["level_start"]], before=[integrate])
+            cull = sysdef("cull", abi.BUILTIN_CULL, [R["vis_mask"], R["vis_list"], R["vis_count"], R["stats"]],
+                          [R["world"], R["aabb_c"], R["aabb_h"], R["frustum"]], before=[propagate])
+            self.systems = [integrate, propagate, cull]
+        else:
+            # 8-system fan-out / fan-in DAG: forces -> integrate_lin || integrate_ang -> propagate ->
+            # world_aabb -> { cull || bounds_reduce } -> group_stats
+            forces = sysdef("forces", abi.BUILTIN_FORCES, [R["vel"]], [R["gravity"], R["dt"]])
+            integrate = sysdef("integrate_lin", abi.BUILTIN_INTEGRATE, [R["pos"]], [R["vel"], R["dt"]], before=[forces])
+            integrate_ang = sysdef("integrate_ang", abi.BUILTIN_INTEGRATE_ANG, [R["rot"]], [R["angvel"], R["dt"]])
+            propagate = sysdef("propagate", abi.BUILTIN_PROPAGATE, [R["world"]],
+                               [R["pos"], R["rot"], R["scale"], R["parent"], R["level_start"]], before=[integrate, integrate_ang])
+            world_aabb = sysdef("world_aabb", abi.BUILTIN_WORLD_AABB, [R["waabb"]], [R["world"], R["aabb_c"], R["aabb_h"]],
+                                before=[propagate])
+            cull = sysdef("cull", abi.BUILTIN_CULL_WAABB, [R["vis_mask"], R["vis_list"], R["vis_count"], R["stats"]],
+                          [R["waabb"], R["frustum"]], before=[world_aabb])
+            bounds = sysdef("bounds_reduce", abi.BUILTIN_BOUNDS_REDUCE, [R["wbounds"]], [R["waabb"]], before=[world_aabb])
+            gstats = sysdef("group_stats", abi.BUILTIN_GROUP_STATS, [R["gstats"]], [R["vis_count"], R["wbounds"]],
+                            before=[cull, bounds])
+            self.systems = [forces, integrate, integrate_ang, propagate, world_aabb, cull, bounds, gstats]
+            if dag == "dag16":
+                # 8 more systems; where no `before` is given the order follows from resource conflicts alone
+                # (W/W, R/W, W/R in rank-then-add order, SystemGroup.zig:264-336):
+                #   vel_clamp   W/W with forces on vel (after it: same rank, added later), read by integrate_lin
+                #   angvel_damp writes angvel, read by integrate_ang
+                #   prev_copy   reads world before propagate overwrites it (R/W)
+                #   sleep_flags reads the clamped vel
+                vel_clamp = sysdef("vel_clamp", abi.BUILTIN_VEL_CLAMP, [R["vel"]], [R["vmax"]])
+                angvel_damp = sysdef("angvel_damp", abi.BUILTIN_ANGVEL_DAMP, [R["angvel"]], [R["damp"]])
+                prev_copy = sysdef("prev_copy", abi.BUILTIN_PREV_COPY, [R["prev_world"]], [R["world"]])
+                sleep = sysdef("sleep_flags", abi.BUILTIN_SLEEP_FLAGS, [R["sleep"]], [R["vel"], R["sleep_eps"]])
+                cull2 = sysdef("cull2", abi.BUILTIN_CULL_WAABB, [R["vis_mask2"], R["vis_list2"], R["vis_count2"], R["stats2"]],
+                               [R["waabb"], R["frustum2"]], before=[world_aabb])
+                lod = sysdef("lod", abi.BUILTIN_LOD, [R["lod"]], [R["waabb"], R["campos"], R["lod_dist2"]], before=[world_aabb])
+                vis_bounds = sysdef("vis_bounds", abi.BUILTIN_VIS_BOUNDS, [R["vbounds"]], [R["waabb"], R["vis_mask"]], before=[cull])
+                gstats2 = sysdef("group_stats2", abi.BUILTIN_GROUP_STATS, [R["gstats2"]], [R["vis_count2"], R["vbounds"]],
+                                 before=[cull2, vis_bounds])
+                self.systems = [forces, vel_clamp, integrate, angvel_damp, integrate_ang, prev_copy, propagate, world_aabb, cull,
+                                cull2, bounds, vis_bounds, lod, sleep, gstats, gstats2]
         self.group.add_systems(self.systems)
         self._fence = Fence(lib)
         self.closed = False
@@ -248,7 +364,9 @@ class WorldStepRig:
             keep.append(ext)
         else:
             self.lib.check(self.lib.fimo_oracle_builtin_system(builtin, C.byref(desc)))
-        return System.register(self.lib, label, exclusive=exclusive, shared=shared, before=before, descriptor=desc, keep=keep)
+        system = System.register(self.lib, label, exclusive=exclusive, shared=shared, before=before, descriptor=desc, keep=keep)
+        self._registered.append(system)
+        return system
 
     # ---- stepping -----------------------------------------------------------------------------------
     def schedule(self, steps: int = 1, signal_last: bool = True) -> None:
@@ -282,8 +400,9 @@ class WorldStepRig:
         ptr = self.resources[name].lock_in_world(self.world, exclusive)
         return C.cast(ptr, C.POINTER(abi.ResourceView)).contents
 
-    def download(self, names=OUTPUTS) -> dict[str, np.ndarray]:
+    def download(self, names=None) -> dict[str, np.ndarray]:
         """world_lock_resources (shared) -> copy out -> unlock, per resource."""
+        names = outputs_for(self.dag) if names is None else names
         out = {}
         for name in names:
             view = self._locked_view(name, exclusive=False)
@@ -345,7 +464,7 @@ class WorldStepRig:
         self.closed = True
         for s in self.systems:
             self.group.remove_system(s)
-        for s in reversed(self.systems):
+        for s in reversed(self._registered):  # dependants first
             s.unregister()
         self.group.deinit()
         for name, res in self.resources.items():

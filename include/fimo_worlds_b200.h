@@ -508,6 +508,20 @@ enum {
     FIMO_B200_BUILTIN_INTEGRATE = 1, /* X: pos            S: vel, dt */
     FIMO_B200_BUILTIN_PROPAGATE = 2, /* X: world          S: pos, rot, scale, parent, level_start */
     FIMO_B200_BUILTIN_CULL = 3,      /* X: vis_mask, vis_list, vis_count, stats   S: world, aabb_c, aabb_h, frustum */
+    /* the 8-system fan-out / fan-in DAG (BASELINE.json configs[2]) adds: */
+    FIMO_B200_BUILTIN_FORCES = 4,        /* X: vel            S: gravity (world,3), dt          vel += gravity*dt */
+    FIMO_B200_BUILTIN_INTEGRATE_ANG = 5, /* X: rot            S: angvel (entity,3), dt          q += dt/2 * (w (x) q), renormalised */
+    FIMO_B200_BUILTIN_WORLD_AABB = 6,    /* X: waabb (entity,6: centre, half extent)   S: world, aabb_c, aabb_h */
+    FIMO_B200_BUILTIN_CULL_WAABB = 7,    /* X: vis_mask, vis_list, vis_count, stats   S: waabb, frustum */
+    FIMO_B200_BUILTIN_BOUNDS_REDUCE = 8, /* X: wbounds (world,6: min xyz, max xyz)    S: waabb */
+    FIMO_B200_BUILTIN_GROUP_STATS = 9,   /* X: gstats (batch,16 words)               S: vis_count, wbounds */
+    /* the 16-system DAG with mixed read/write conflicts (configs[4]) adds: */
+    FIMO_B200_BUILTIN_PREV_COPY = 10,    /* X: prev_world     S: world                         last step's transforms */
+    FIMO_B200_BUILTIN_LOD = 11,          /* X: lod (entity,1 u32)   S: waabb, campos (world,3), lod_dist2 (world,3) */
+    FIMO_B200_BUILTIN_VEL_CLAMP = 12,    /* X: vel            S: vmax (world,1) */
+    FIMO_B200_BUILTIN_SLEEP_FLAGS = 13,  /* X: sleep (entity bits)  S: vel, sleep_eps (world,1) */
+    FIMO_B200_BUILTIN_ANGVEL_DAMP = 14,  /* X: angvel         S: damp (world,1) */
+    FIMO_B200_BUILTIN_VIS_BOUNDS = 15,   /* X: vbounds (world,6)    S: waabb, vis_mask           bounds of the visible entities */
     FIMO_B200_BUILTIN_COUNT_
 };
 
@@ -543,6 +557,14 @@ enum {
     FIMO_B200_STAT_STEPS = 4,    /* world-steps accumulated since the resource was added (+1 per world per step) */
     FIMO_B200_STAT_WORDS = 8
 };
+/* Words written by BUILTIN_GROUP_STATS into `gstats` (16 x u32 per batch). */
+enum {
+    FIMO_B200_GSTAT_VISIBLE_LO = 0, /* u64: sum over worlds of vis_count */
+    FIMO_B200_GSTAT_WORLDS_LO = 2,  /* u64: worlds reduced */
+    FIMO_B200_GSTAT_BOUNDS = 4,     /* 6 x f32: min xyz, max xyz over all worlds' wbounds */
+    FIMO_B200_GSTAT_WORDS = 16
+};
+#define FIMO_B200_BOUNDS_EMPTY_MIN 3.402823466e+38f   /* bounds of nothing: min = +FLT_MAX, max = -FLT_MAX */
 #define FIMO_B200_PARENT_ROOT 0xFFFFFFFFu
 
 /* ------------------------------------------------------------------------- */

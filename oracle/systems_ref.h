@@ -35,6 +35,29 @@ int fimo_ref_propagate(float *world, const float *pos, const float *rot, const f
 void fimo_ref_cull(uint32_t *vis_mask, uint32_t *vis_list, uint32_t *vis_count, uint64_t *stats, const float *world,
                    const float *aabb_c, const float *aabb_h, const float *frustum, size_t n);
 
+/* ---- the 8- and 16-system DAGs (BASELINE.json configs[2], configs[4]); same rules: one rounding per written
+ * operation, fmaf exactly where written, sqrtf and / are the IEEE correctly rounded ones ---- */
+
+/* forces   X: vel[3][E]   S: gravity[3], dt        vel = fmaf(g, dt, vel) */
+void fimo_ref_forces(float *vel, const float *gravity, float dt, size_t n);
+/* vel_clamp   X: vel   S: vmax                     v = fminf(fmaxf(v, -vmax), vmax) */
+void fimo_ref_vel_clamp(float *vel, float vmax, size_t n);
+/* angvel_damp   X: angvel[3][E]   S: damp          w = w * damp */
+void fimo_ref_angvel_damp(float *angvel, float damp, size_t n);
+/* integrate_ang   X: rot[4][E] (x,y,z,w)   S: angvel, dt      q += (dt/2) (omega (x) q); q /= |q| */
+void fimo_ref_integrate_ang(float *rot, const float *angvel, float dt, size_t n);
+/* world_aabb   X: waabb[6][E] (centre xyz, half extent xyz)   S: world, aabb_c, aabb_h */
+void fimo_ref_world_aabb(float *waabb, const float *world, const float *aabb_c, const float *aabb_h, size_t n);
+/* cull_waabb   X: vis_mask, vis_list, vis_count, stats   S: waabb, frustum   (the plane test of fimo_ref_cull) */
+void fimo_ref_cull_waabb(uint32_t *vis_mask, uint32_t *vis_list, uint32_t *vis_count, uint64_t *stats, const float *waabb,
+                         const float *frustum, size_t n);
+/* bounds_reduce   X: wbounds[6] (min xyz, max xyz)   S: waabb; vis_mask == NULL: every entity, else the visible ones */
+void fimo_ref_bounds(float *bounds, const float *waabb, const uint32_t *vis_mask, size_t n);
+/* lod   X: lod[E] u32   S: waabb, campos[3], lod_dist2[3]     lod = #{i : |c' - cam|^2 >= lod_dist2[i]} */
+void fimo_ref_lod(uint32_t *lod, const float *waabb, const float *campos, const float *lod_dist2, size_t n);
+/* sleep_flags   X: sleep[ceil(E/32)]   S: vel, sleep_eps      bit = |vx| + |vy| + |vz| < eps */
+void fimo_ref_sleep_flags(uint32_t *sleep, const float *vel, float eps, size_t n);
+
 #ifdef __cplusplus
 }
 #endif

@@ -12,15 +12,15 @@ pytestmark = pytest.mark.gpu
 FLOAT_RTOL = 0.0  # bit-exact; north_star tolerance is 1e-5 relative
 
 
-def run_both(oracle, product, W, E, D, steps, options=None, world0=0):
-    data = synth.generate(W, E, D, world0=world0)
-    ref = synth.WorldStepRig(oracle, W, E, D, data={k: v.copy() for k, v in data.items()})
+def run_both(oracle, product, W, E, D, steps, options=None, world0=0, dag="chain3"):
+    data = synth.generate(W, E, D, world0=world0, dag=dag)
+    ref = synth.WorldStepRig(oracle, W, E, D, data={k: v.copy() for k, v in data.items()}, dag=dag)
     try:
         ref.step(steps)
         want = ref.download()
     finally:
         ref.close()
-    dev = synth.WorldStepRig(product, W, E, D, data={k: v.copy() for k, v in data.items()}, options=options)
+    dev = synth.WorldStepRig(product, W, E, D, data={k: v.copy() for k, v in data.items()}, options=options, dag=dag)
     try:
         info = dev.executor_info()
         dev.step(steps)
@@ -210,3 +210,29 @@ def test_stream_ordered_transfers_match_locked_host_access(oracle, product):
         rig.close()
     problems = synth.compare_outputs(got, want, FLOAT_RTOL)
     assert not problems, "\n".join(problems)
+
+
+DAG_CASES = [
+    # (dag, worlds, entities, depth, steps)
+    ("dag8", 1, 1024, 4, 8),
+    ("dag8", 3, 65536, 8, 2),     # BASELINE configs[2] world shape
+    ("dag8", 37, 1000, 8, 4),     # ragged
+    ("dag16", 4, 4096, 4, 4),
+    ("dag16", 61, 260, 5, 6),
+    ("dag16", 2, 33, 3, 3),
+]
+
+
+@pytest.mark.parametrize("dag,W,E,D,steps", DAG_CASES)
+@pytest.mark.parametrize("graph", [True, False])
+def test_system_dags_match_oracle(oracle, product, dag, W, E, D, steps, graph):
+    """The 8-system fan-out/fan-in DAG and the 16-system DAG with conflict-only orderings, one kernel per system
+    in a CUDA graph (or plain streams with fork/join events): every resource any system writes is bit-exact."""
+    got, want, info = run_both(oracle, product, W, E, D, steps, synth.RigOptions(graph=graph), dag=dag)
+    n = 8 if dag == "dag8" else 16
+    assert info.systems == n and info.device_systems == n and info.nodes == n and info.fused_world_step == 0
+    assert info.uses_cuda_graph == (1 if graph else 0) and info.edges >= n - 1
+    problems = synth.compare_outputs(got, want, FLOAT_RTOL)
+    assert not problems, "\n".join(problems)
+    st = got["stats"].reshape(-1).view(np.uint64)
+    assert st[abi.STAT_STEPS] == W * steps
