@@ -40,6 +40,9 @@ def parse_args():
     p.add_argument("--worlds", type=int, default=WORLDS_PER_GPU, help="worlds per GPU")
     p.add_argument("--entities", type=int, default=ENTITIES)
     p.add_argument("--depth", type=int, default=DEPTH)
+    p.add_argument("--dag", default="chain3", choices=["chain3", "dag8", "dag16"],
+                   help="system set: the 3-system chain (configs[1]), the 8-system fan-out/fan-in DAG (configs[2]) or the "
+                        "16-system DAG with mixed read/write conflicts (configs[4])")
     p.add_argument("--no-fusion", action="store_true", help="one kernel per system (CUDA graph of the DAG)")
     p.add_argument("--no-cpu-baseline", action="store_true")
     p.add_argument("--no-e2e", action="store_true")
@@ -59,7 +62,12 @@ def measured_peaks() -> tuple[float, str]:
 # CPU arm: the reference's own structure — one World + one SystemGroup per world, every group scheduled
 # each step on ONE shared pool with all host threads, systems as system_run callbacks.
 # ------------------------------------------------------------------------------------------------
-def cpu_arm(worlds: int, entities: int, depth: int, steps: int, warmup: int) -> dict:
+DAG_TEXT = {"chain3": "3-system chain (integrate -> propagate -> AABB frustum cull)",
+            "dag8": "8-system fan-out/fan-in DAG (forces -> integrate_lin || integrate_ang -> propagate -> world_aabb -> cull || bounds -> stats)",
+            "dag16": "16-system DAG with mixed read/write resource conflicts"}
+
+
+def cpu_arm(worlds: int, entities: int, depth: int, steps: int, warmup: int, dag: str = "chain3") -> dict:
     from fimo_b200 import synth
     from fimo_b200.worlds import create_pool
     from oracle import loader
@@ -67,11 +75,11 @@ def cpu_arm(worlds: int, entities: int, depth: int, steps: int, warmup: int) -> 
     lib = loader.load()
     cores = int(lib.fimo_oracle_hardware_threads()) or (os.cpu_count() or 1)
     pool = create_pool(lib, "cpu-baseline", cores)
-    data = synth.generate(worlds, entities, depth)
+    data = synth.generate(worlds, entities, depth, dag=dag)
     rigs = []
     for w in range(worlds):
-        one = {k: (v if k == "stats" else v[w:w + 1]).copy() for k, v in data.items()}
-        rigs.append(synth.WorldStepRig(lib, 1, entities, depth, data=one, pool=pool))
+        one = {k: (v if v.shape[0] != worlds else v[w:w + 1]).copy() for k, v in data.items()}
+        rigs.append(synth.WorldStepRig(lib, 1, entities, depth, data=one, pool=pool, dag=dag))
     groups = (C.c_void_p * worlds)(*[r.group.handle for r in rigs])
     if steps <= 0:  # size the run for ~15 s of CPU work
         t = lib.fimo_oracle_step_groups(groups, worlds, 2)
@@ -83,7 +91,7 @@ def cpu_arm(worlds: int, entities: int, depth: int, steps: int, warmup: int) -> 
     pool.unref()
     return {
         "value": worlds * steps / seconds, "unit": UNIT, "cores": cores, "kind": "port",
-        "sample": f"{worlds} worlds x {entities} entities, depth {depth}, 3-system chain, {steps} steps, one World+SystemGroup "
+        "sample": f"{worlds} worlds x {entities} entities, depth {depth}, {dag}, {steps} steps, one World+SystemGroup "
                   f"per world on one shared {cores}-thread pool (oracle restatement of fimo_worlds/fimo_tasks; the reference "
                   f"itself needs zig + boost.context and cannot be built here)",
         "seconds": seconds, "steps": steps, "ms_per_step": 1e3 * seconds / steps,
@@ -95,13 +103,14 @@ def run_reference(args) -> None:
     if rank != 0:
         return
     steps = args.steps if args.steps != 200 else 0
-    base = cpu_arm(CPU_SAMPLE_WORLDS, args.entities, args.depth, min(steps, 400), min(args.warmup, 3))
+    sample_worlds = max(1, min(CPU_SAMPLE_WORLDS, args.worlds, (CPU_SAMPLE_WORLDS * 1024) // max(args.entities, 1)))
+    base = cpu_arm(sample_worlds, args.entities, args.depth, min(steps, 400), min(args.warmup, 3), args.dag)
     line = {
         "impl": "reference", "metric": METRIC, "value": base["value"], "unit": UNIT, "n_gpus": args.gpus,
         "steps": base["steps"], "warmup": min(args.warmup, 3), "ms_per_step": base["ms_per_step"], "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": f"{args.worlds} worlds x {args.entities} entities, depth {args.depth}, 3-system chain "
-                               f"(integrate -> propagate -> cull); CPU arm steps a {CPU_SAMPLE_WORLDS}-world sample per step"},
+        "config": {"workload": f"{args.worlds} worlds x {args.entities} entities, depth {args.depth}, {DAG_TEXT[args.dag]}; "
+                               f"CPU arm steps a {sample_worlds}-world sample per step"},
         "cpu_baseline": {k: base[k] for k in ("value", "unit", "cores", "kind", "sample")},
         "e2e": {"value": base["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
@@ -164,7 +173,7 @@ def run_b200(args) -> None:
     lib = library.load()
     W, E, D = args.worlds, args.entities, args.depth
     K, WU = args.steps, max(args.warmup, 3)
-    data = synth.generate(W, E, D, world0=rank * W)  # shard = contiguous block of global world indices
+    data = synth.generate(W, E, D, world0=rank * W, dag=args.dag)  # shard = contiguous block of global world indices
 
     # End-of-step statistics all-reduce (the path's only collective): after every generation a 64-byte
     # snapshot is taken in stream order, then reduced over NCCL on a side stream so that it overlaps the
@@ -188,7 +197,7 @@ def run_b200(args) -> None:
 
     options = synth.RigOptions(fused=not args.no_fusion, device=local_rank)
     rig = synth.WorldStepRig(lib, W, E, D, data=data, options=options,
-                             post_step=post_step if distributed else None)
+                             post_step=post_step if distributed else None, dag=args.dag)
     if distributed:
         # a torch view over the stats resource in HBM (locked once to fetch the device pointer)
         view = rig._locked_view("stats", exclusive=False)
@@ -234,7 +243,11 @@ def run_b200(args) -> None:
 
     # ---- roofline of the dominant kernel ---------------------------------------------------------------
     peak, peak_src = measured_peaks()
-    b3 = synth.bytes_per_entity_step(f_vis)
+    f_vis2 = 0.0
+    if args.dag == "dag16":
+        st2 = rig.download(("stats2",))["stats2"].reshape(-1).view(np.uint64)
+        f_vis2 = float(st2[abi.STAT_VISIBLE]) / float(st2[abi.STAT_ENTITIES])
+    b3 = synth.dag_bytes_per_entity_step(args.dag, f_vis, f_vis2)
     alg_bytes = b3 * W * E
     achieved = alg_bytes / (kernel_ms * 1e-3) / 1e9 if kernel_ms > 0 else 0.0
     traffic = None
@@ -243,7 +256,10 @@ def run_b200(args) -> None:
     except Exception:
         pass
     roofline = {"bound": "hbm", "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s", "frac": round(achieved / peak, 4),
-                "traffic": traffic, "kernel": ("k_world_step_pipe (TMA-fed persistent fused world-step)" if E % 4 == 0 else "k_world_cta (fused, one CTA per world)") if info.fused_world_step else "per-system kernels",
+                "traffic": traffic, "kernel": (("k_world_step_pipe (TMA-fed persistent fused world-step)" if info.kernel_launches_per_generation == 1 else
+                            "k_world_step_pipe<team> + k_compact_lists (CTA teams per world)") if E % 4 == 0 else
+                           "k_world_cta (fused, one CTA per world)") if info.fused_world_step else
+                          f"CUDA graph of {info.nodes} per-system kernels (whole generation)",
                 "algorithmic_bytes_per_launch": int(alg_bytes), "bytes_per_entity_step": round(b3, 3), "f_vis": round(f_vis, 4),
                 "kernel_ms": round(kernel_ms, 5), "peak_source": peak_src, "traffic_source": "profiles/traffic.json (ncu --set full)"}
 
@@ -256,8 +272,9 @@ def run_b200(args) -> None:
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world_size, "steps": K, "warmup": WU,
         "ms_per_step": t_ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
         "data": "synthetic",
-        "config": {"workload": f"{W} worlds x {E} entities per GPU, depth-{D} transform hierarchy, 3-system chain "
-                               f"(integrate -> propagate -> AABB frustum cull), BASELINE.json configs[1]",
+        "config": {"workload": f"{W} worlds x {E} entities per GPU, depth-{D} transform hierarchy, {DAG_TEXT[args.dag]}"
+                               + (", BASELINE.json configs[1]" if (W, E, D, args.dag) == (4096, 1024, 4, "chain3") else ""),
+                   "dag": args.dag,
                    "worlds_per_gpu": W, "entities_per_world": E, "depth": D, "executor": "fused world-step kernel in a CUDA graph"
                    if info.fused_world_step else "CUDA graph of per-system kernels",
                    "l2": "inputs larger than L2 (state touched per step = %.0f MB > 126 MB)" % (alg_bytes / 1e6),
@@ -274,7 +291,7 @@ def run_b200(args) -> None:
                                 "worlds": int(global_stats[abi.STAT_WORLDS])}
     rig.close()
     if rank == 0 and not args.no_cpu_baseline and world_size == 1:
-        base = cpu_arm(CPU_SAMPLE_WORLDS, E, D, args.cpu_steps, 2)
+        base = cpu_arm(max(1, min(CPU_SAMPLE_WORLDS, W, (CPU_SAMPLE_WORLDS * 1024) // max(E, 1))), E, D, args.cpu_steps, 2, args.dag)
         line["cpu_baseline"] = {k: base[k] for k in ("value", "unit", "cores", "kind", "sample")}
     if rank == 0:
         print(json.dumps(line), flush=True)

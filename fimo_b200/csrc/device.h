@@ -91,6 +91,12 @@ struct WorldStepViews {
     const FimoB200_ResourceView *world, *rot, *scale, *parent, *level_start; // propagate
     const FimoB200_ResourceView *vis_mask, *vis_list, *vis_count, *stats;    // cull (exclusive)
     const FimoB200_ResourceView *aabb_c, *aabb_h, *frustum;                  // cull (shared)
+    // set 1 — the fused 8-system DAG (forces, [vel_clamp], integrate_lin, integrate_ang, propagate, world_aabb,
+    // cull on waabb, bounds_reduce, group_stats) — additionally uses:
+    uint32_t set = 0;        // 0: 3-system chain; 1: 8-system DAG
+    bool vel_clamp = false;  // vel_clamp of the 16-system DAG sits between forces and integrate_lin
+    const FimoB200_ResourceView *gravity = nullptr, *angvel = nullptr, *vmax = nullptr, *waabb = nullptr, *wbounds = nullptr,
+                                *gstats = nullptr;
 };
 // How the fused kernel is launched for a given batch; made once when the executor is compiled (it reads
 // level_start from HBM to size the shared-memory parent window), then reused by every launch.
@@ -106,6 +112,8 @@ struct WorldStepPlan {
     size_t smem = 0;            // dynamic shared memory per CTA
     std::shared_ptr<void> rows;     // HBM: [n_worlds][E] 48-byte parent rows (parents outside the window)
     std::shared_ptr<void> lvl_done; // HBM: [n_worlds][32] level-completion counters (team mode)
+    std::shared_ptr<void> bounds;   // HBM: [6 + 6 n_worlds] bounds accumulators as float keys (set 1)
+    uint32_t set = 0;               // copied from the views
 };
 bool world_step_plan(const WorldStepViews &v, int device, WorldStepPlan &plan); // false: not fusable
 FimoStatus world_step_launch(const WorldStepViews &v, const WorldStepPlan &plan, void *cull_scratch,

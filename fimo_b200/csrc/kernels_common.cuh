@@ -46,15 +46,19 @@ __device__ __forceinline__ void compose(float (&W)[12], const float (&P)[12], co
     }
 }
 
-// world-space AABB of (c,h) under W, tested against 6 planes (nx,ny,nz,d), inside = n.x + d >= 0
-__device__ __forceinline__ bool aabb_visible(const float (&W)[12], float c0, float c1, float c2, float h0, float h1,
-                                             float h2, const float *__restrict__ fr /* 24 floats, shared memory */) {
-    float wc[3], wh[3];
+// world-space AABB of (c,h) under W: centre wc = W c + t, half extent wh = |W| h.  18 roundings.
+__device__ __forceinline__ void world_aabb_of(float (&wc)[3], float (&wh)[3], const float (&W)[12], float c0, float c1, float c2,
+                                              float h0, float h1, float h2) {
 #pragma unroll
     for (int r = 0; r < 3; r++) {
         wc[r] = fma1(W[r * 4 + 2], c2, fma1(W[r * 4 + 1], c1, fma1(W[r * 4 + 0], c0, W[r * 4 + 3])));
         wh[r] = fma1(fabsf(W[r * 4 + 2]), h2, fma1(fabsf(W[r * 4 + 1]), h1, mul(fabsf(W[r * 4 + 0]), h0)));
     }
+}
+
+// AABB (wc, wh) against 6 planes (nx,ny,nz,d), inside = n.x + d >= 0.  36 roundings.
+__device__ __forceinline__ bool planes_visible(const float (&wc)[3], const float (&wh)[3],
+                                               const float *__restrict__ fr /* 24 floats, shared memory, 16-byte aligned */) {
     bool visible = true;
 #pragma unroll
     for (int p = 0; p < 6; p++) {
@@ -65,6 +69,31 @@ __device__ __forceinline__ bool aabb_visible(const float (&W)[12], float c0, flo
     }
     return visible;
 }
+
+__device__ __forceinline__ bool aabb_visible(const float (&W)[12], float c0, float c1, float c2, float h0, float h1,
+                                             float h2, const float *__restrict__ fr) {
+    float wc[3], wh[3];
+    world_aabb_of(wc, wh, W, c0, c1, c2, h0, h1, h2);
+    return planes_visible(wc, wh, fr);
+}
+
+// q += (dt/2) (omega (x) q); q /= |q|   (IEEE sqrt and division).  h = 0.5 * dt, already rounded.
+__device__ __forceinline__ void integrate_quat(float &x, float &y, float &z, float &w, float ax, float ay, float az, float h) {
+    const float dx = fma1(ay, z, fma1(-az, y, mul(ax, w)));
+    const float dy = fma1(az, x, fma1(-ax, z, mul(ay, w)));
+    const float dz = fma1(ax, y, fma1(-ay, x, mul(az, w)));
+    const float dw = -fma1(az, z, fma1(ay, y, mul(ax, x)));
+    x = fma1(dx, h, x), y = fma1(dy, h, y), z = fma1(dz, h, z), w = fma1(dw, h, w);
+    const float len = __fsqrt_rn(fma1(w, w, fma1(z, z, fma1(y, y, mul(x, x)))));
+    x = __fdiv_rn(x, len), y = __fdiv_rn(y, len), z = __fdiv_rn(z, len), w = __fdiv_rn(w, len);
+}
+
+// order-preserving int encoding of a finite float (for atomicMin / atomicMax on bounds)
+__device__ __forceinline__ int float_key(float f) {
+    const int b = __float_as_int(f);
+    return b >= 0 ? b : b ^ 0x7FFFFFFF;
+}
+__device__ __forceinline__ float key_float(int k) { return __int_as_float(k >= 0 ? k : k ^ 0x7FFFFFFF); }
 
 // ---------------------------------------------------------------------------------------------
 // argument blocks (word strides; one block per kernel, passed by value)
@@ -83,6 +112,10 @@ struct StepArgs {
     Plane aabb_c, aabb_h, frustum;                  // cull inputs
     unsigned long long *stats;                      // FIMO_B200_STAT_* words of the batch
     unsigned long long *scratch;                    // [0..3] accumulators, [4] ticket
+    // the fused 8-system DAG (world_step.cu, kSet = 1) additionally uses:
+    Plane angvel, gravity, vmax, waabb, wbounds;
+    uint32_t *gstats;     // FIMO_B200_GSTAT_* words of the batch
+    int *bounds_keys;     // [0..5] batch bounds as float_key accumulators, then [n_worlds][6] per-world ones (team mode)
     uint32_t n_worlds, entities, levels, mask_words;
 };
 
@@ -117,29 +150,43 @@ __device__ __forceinline__ void propagate_entity(uint32_t e, uint32_t E, float *
 
 // Folds one CTA's statistics into the batch accumulators; the last CTA of the grid publishes them
 // and re-arms the scratch block (so no memset node is needed between generations).
-__device__ __forceinline__ void publish_stats(const StepArgs &a, unsigned long long visible, unsigned long long mask_sum,
+// Returns true on the last CTA (the one that published).  kGroupStats: the fused 8-system DAG also publishes
+// BUILTIN_GROUP_STATS' words — total visible, worlds, and the batch bounds every CTA merged into
+// a.bounds_keys[0..5] (float keys) before calling — and re-arms those keys.
+template <bool kGroupStats = false>
+__device__ __forceinline__ bool publish_stats(const StepArgs &a, unsigned long long visible, unsigned long long mask_sum,
                                               unsigned long long worlds, unsigned long long n_ctas) {
     atomicAdd(&a.scratch[0], visible);
     atomicAdd(&a.scratch[1], mask_sum);
     atomicAdd(&a.scratch[2], worlds);
     __threadfence();
     const unsigned long long ticket = atomicAdd(&a.scratch[4], 1ull);
-    if (ticket == n_ctas - 1) {
-        __threadfence();
-        const unsigned long long v = atomicExch(&a.scratch[0], 0ull);
-        const unsigned long long m = atomicExch(&a.scratch[1], 0ull);
-        const unsigned long long n = atomicExch(&a.scratch[2], 0ull);
-        a.stats[FIMO_B200_STAT_VISIBLE] = v;
-        a.stats[FIMO_B200_STAT_ENTITIES] = n * (unsigned long long)a.entities;
-        a.stats[FIMO_B200_STAT_MASK_SUM] = m;
-        a.stats[FIMO_B200_STAT_WORLDS] = n;
-        a.stats[FIMO_B200_STAT_STEPS] += n;
-        atomicExch(&a.scratch[4], 0ull);
+    if (ticket != n_ctas - 1) return false;
+    __threadfence();
+    const unsigned long long v = atomicExch(&a.scratch[0], 0ull);
+    const unsigned long long m = atomicExch(&a.scratch[1], 0ull);
+    const unsigned long long n = atomicExch(&a.scratch[2], 0ull);
+    a.stats[FIMO_B200_STAT_VISIBLE] = v;
+    a.stats[FIMO_B200_STAT_ENTITIES] = n * (unsigned long long)a.entities;
+    a.stats[FIMO_B200_STAT_MASK_SUM] = m;
+    a.stats[FIMO_B200_STAT_WORLDS] = n;
+    a.stats[FIMO_B200_STAT_STEPS] += n;
+    if (kGroupStats) {
+        uint32_t *g = a.gstats;
+        for (int i = 0; i < FIMO_B200_GSTAT_WORDS; i++) g[i] = 0u;
+        g[FIMO_B200_GSTAT_VISIBLE_LO] = (uint32_t)(v & 0xFFFFFFFFull), g[FIMO_B200_GSTAT_VISIBLE_LO + 1] = (uint32_t)(v >> 32);
+        g[FIMO_B200_GSTAT_WORLDS_LO] = (uint32_t)(n & 0xFFFFFFFFull), g[FIMO_B200_GSTAT_WORLDS_LO + 1] = (uint32_t)(n >> 32);
+        for (int i = 0; i < 6; i++) {
+            const int empty = i < 3 ? float_key(FIMO_B200_BOUNDS_EMPTY_MIN) : float_key(-FIMO_B200_BOUNDS_EMPTY_MIN);
+            g[FIMO_B200_GSTAT_BOUNDS + i] = __float_as_uint(key_float(atomicExch(a.bounds_keys + i, empty)));
+        }
     }
+    atomicExch(&a.scratch[4], 0ull);
+    return true;
 }
-__device__ __forceinline__ void publish_stats(const StepArgs &a, unsigned long long visible, unsigned long long mask_sum,
+__device__ __forceinline__ bool publish_stats(const StepArgs &a, unsigned long long visible, unsigned long long mask_sum,
                                               unsigned long long worlds) {
-    publish_stats(a, visible, mask_sum, worlds, (unsigned long long)gridDim.x);
+    return publish_stats<false>(a, visible, mask_sum, worlds, (unsigned long long)gridDim.x);
 }
 
 // ---------------------------------------------------------------------------------------------

@@ -65,14 +65,8 @@ __global__ void __launch_bounds__(kT) k_integrate_ang(Plane rot, Plane angvel, P
     const float *a = fptr(angvel, t.w);
     const float h = mul(0.5f, *fptr(dt, t.w));
     float x = q[e], y = q[E + e], z = q[2 * E + e], w = q[3 * E + e];
-    const float ax = a[e], ay = a[E + e], az = a[2 * E + e];
-    const float dx = fma1(ay, z, fma1(-az, y, mul(ax, w)));
-    const float dy = fma1(az, x, fma1(-ax, z, mul(ay, w)));
-    const float dz = fma1(ax, y, fma1(-ay, x, mul(az, w)));
-    const float dw = -fma1(az, z, fma1(ay, y, mul(ax, x)));
-    x = fma1(dx, h, x), y = fma1(dy, h, y), z = fma1(dz, h, z), w = fma1(dw, h, w);
-    const float len = __fsqrt_rn(fma1(w, w, fma1(z, z, fma1(y, y, mul(x, x)))));
-    q[e] = __fdiv_rn(x, len), q[E + e] = __fdiv_rn(y, len), q[2 * E + e] = __fdiv_rn(z, len), q[3 * E + e] = __fdiv_rn(w, len);
+    integrate_quat(x, y, z, w, a[e], a[E + e], a[2 * E + e], h);
+    q[e] = x, q[E + e] = y, q[2 * E + e] = z, q[3 * E + e] = w;
 }
 
 // world_aabb: c' = W c + t, h' = |W| h
@@ -120,18 +114,6 @@ __global__ void __launch_bounds__(kT) k_sleep_flags(Plane sleep, Plane vel, Plan
 
 // Cull on precomputed world AABBs, one CTA per world (persistent): same mask / ordered list / count / stats
 // contract as k_cull_cta in kernels.cu.
-__device__ __forceinline__ bool planes_visible(const float (&wc)[3], const float (&wh)[3], const float *fr) {
-    bool visible = true;
-#pragma unroll
-    for (int p = 0; p < 6; p++) {
-        const float4 pl = *(const float4 *)(fr + p * 4);
-        float sd = fma1(pl.z, wc[2], fma1(pl.y, wc[1], fma1(pl.x, wc[0], pl.w)));
-        sd = fma1(fabsf(pl.z), wh[2], fma1(fabsf(pl.y), wh[1], fma1(fabsf(pl.x), wh[0], sd)));
-        if (!(sd >= 0.0f)) visible = false;
-    }
-    return visible;
-}
-
 template <int T> __global__ void __launch_bounds__(T) k_cull_waabb(StepArgs a, Plane waabb) {
     __shared__ __align__(16) float s_frustum[24];
     __shared__ uint32_t s_warp[2 * (T / 32)];

@@ -29,7 +29,18 @@
 namespace fb::dev {
 namespace {
 
-constexpr int kPlanes = 18; // pos 0-2, vel 3-5, rot 6-9, scale 10, parent 11, aabb_c 12-14, aabb_h 15-17
+// System sets this kernel fuses.  kSet 0: integrate -> propagate -> cull (3-system chain).
+// kSet 1: the 8-system DAG forces -> [vel_clamp] -> integrate_lin || integrate_ang -> propagate -> world_aabb ->
+//         cull || bounds_reduce -> group_stats (vel_clamp of the 16-system DAG is a runtime option).
+// Input planes of a chunk: pos 0-2, vel 3-5, rot 6-9, scale 10, parent 11, aabb_c 12-14, aabb_h 15-17, [angvel 18-20].
+// Output planes left in the same stage: world 0-11, pos 12-14, [vel 15-17, rot 18-21].
+template <int kSet> struct SetTraits;
+template <> struct SetTraits<0> {
+    static constexpr int kIn = 18, kOut = 15, kStage = 18;
+};
+template <> struct SetTraits<1> {
+    static constexpr int kIn = 21, kOut = 22, kStage = 22;
+};
 
 __device__ __forceinline__ uint32_t smem_addr(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
@@ -98,6 +109,7 @@ struct PipeArgs {
     uint32_t *lvl_done;
 };
 
+constexpr uint32_t kPipeVelClamp = 8u;         // kSet 1: vel_clamp sits between forces and integrate_lin
 constexpr uint32_t kPipePublishPerChunk = 2u; // FIMO_B200_PUBLISH=chunk: announce level progress after every chunk
 constexpr uint32_t kPipePrefetchBlocking = 4u; // FIMO_B200_PREFETCH=2: wait for the next chunk's inputs before this chunk's math
 constexpr uint32_t kPipeNoPrefetch = 1u; // FIMO_B200_PREFETCH=0: parent rows are loaded where they are used
@@ -109,11 +121,12 @@ struct WorldConst {
     float frustum[24];              // 6 planes (nx, ny, nz, d); 16-byte aligned for LDS.128
     uint32_t ls[kMaxLevels + 1];    // level_start
     float dt;
+    float gravity[3], vmax;         // kSet 1
     uint32_t pad[2];
 };
 static_assert(sizeof(WorldConst) % 16 == 0, "WorldConst");
 
-// Source plane p of world w (floats / u32), see kPlanes.
+// Source plane p of world w (floats / u32), see SetTraits.
 __device__ __forceinline__ const uint32_t *plane_src(const StepArgs &a, int p, uint64_t w, uint32_t E) {
     if (p < 3) return uptr(a.pos, w) + (uint64_t)p * E;
     if (p < 6) return uptr(a.vel, w) + (uint64_t)(p - 3) * E;
@@ -121,7 +134,8 @@ __device__ __forceinline__ const uint32_t *plane_src(const StepArgs &a, int p, u
     if (p == 10) return uptr(a.scale, w);
     if (p == 11) return uptr(a.parent, w);
     if (p < 15) return uptr(a.aabb_c, w) + (uint64_t)(p - 12) * E;
-    return uptr(a.aabb_h, w) + (uint64_t)(p - 15) * E;
+    if (p < 18) return uptr(a.aabb_h, w) + (uint64_t)(p - 15) * E;
+    return uptr(a.angvel, w) + (uint64_t)(p - 18) * E;
 }
 
 // Work of one CTA: worlds team_id, team_id + teams, ... and of each world the chunks rank, rank + team, ...
@@ -139,8 +153,9 @@ struct Walk {
 // The TMA warp (one elected thread): loads chunk inputs into the ring and stores the finished chunk's
 // outputs, which the compute threads leave in the same ring stage (world matrices over planes 0-11, new
 // positions over 12-14).
-template <int T>
+template <int T, int kSet>
 __device__ __forceinline__ void tma_warp(const PipeArgs &pa, const Walk &wk, float *ring, uint64_t *full, uint64_t *done) {
+    constexpr int kIn = SetTraits<kSet>::kIn, kStage = SetTraits<kSet>::kStage;
     const StepArgs &a = pa.a;
     const uint32_t E = a.entities, N = pa.stages, nc = pa.chunks, G = pa.team, total = wk.total;
     uint32_t k = 0, c = wk.rank, s = 0, round = 0; // position of the chunk being loaded
@@ -148,13 +163,21 @@ __device__ __forceinline__ void tma_warp(const PipeArgs &pa, const Walk &wk, flo
     auto store_chunk = [&](uint32_t stage, uint32_t wk_, uint32_t wc) {
         const uint64_t w = wk.team_id + (uint64_t)wk_ * pa.teams;
         const uint32_t first = wc * T, bytes = min((uint32_t)T, E - first) * 4u;
-        const float *st = ring + (size_t)stage * kPlanes * T;
+        const float *st = ring + (size_t)stage * kStage * T;
         float *world = fptr(a.world, w) + first;
         float *pos = fptr(a.pos, w) + first;
 #pragma unroll
         for (int i = 0; i < 12; i++) bulk_store(world + (uint64_t)i * E, st + i * T, bytes);
 #pragma unroll
         for (int i = 0; i < 3; i++) bulk_store(pos + (uint64_t)i * E, st + (12 + i) * T, bytes);
+        if (kSet == 1) {
+            float *vel = fptr(a.vel, w) + first;
+            float *rot = fptr(a.rot, w) + first;
+#pragma unroll
+            for (int i = 0; i < 3; i++) bulk_store(vel + (uint64_t)i * E, st + (15 + i) * T, bytes);
+#pragma unroll
+            for (int i = 0; i < 4; i++) bulk_store(rot + (uint64_t)i * E, st + (18 + i) * T, bytes);
+        }
         bulk_commit();
     };
     for (uint32_t it = 0; it < total; it++) {
@@ -166,10 +189,10 @@ __device__ __forceinline__ void tma_warp(const PipeArgs &pa, const Walk &wk, flo
         }
         const uint64_t w = wk.team_id + (uint64_t)k * pa.teams;
         const uint32_t first = c * T, bytes = min((uint32_t)T, E - first) * 4u; // multiple of 16 (E % 4 == 0)
-        float *st = ring + (size_t)s * kPlanes * T;
-        mbar_expect_tx(&full[s], bytes * kPlanes);
+        float *st = ring + (size_t)s * kStage * T;
+        mbar_expect_tx(&full[s], bytes * kIn);
 #pragma unroll
-        for (int p = 0; p < kPlanes; p++) bulk_load(st + p * T, plane_src(a, p, w, E) + first, bytes, &full[s]);
+        for (int p = 0; p < kIn; p++) bulk_load(st + p * T, plane_src(a, p, w, E) + first, bytes, &full[s]);
         if ((c += G) >= nc) c = wk.rank, k++;
         if (++s == N) s = 0, round++;
     }
@@ -221,23 +244,28 @@ __device__ __forceinline__ void red_release_gpu_add(uint32_t *p, uint32_t v) {
 //                parents travel through `rows` in L2, and a CTA starts level l of a chunk once the (world, l-1)
 //                counter says every entity of level l-1 is visible — dataflow, no team-wide barrier.  Only the
 //                mask leaves this kernel; k_compact_lists derives list, count and statistics from it.
-template <int T, int kMinBlocks, bool kTeam>
+template <int T, int kMinBlocks, bool kTeam, int kSet>
 __global__ void __launch_bounds__(T + 32, kMinBlocks) k_world_step_pipe(const PipeArgs pa) {
+    constexpr int kStage = SetTraits<kSet>::kStage;
     extern __shared__ __align__(128) unsigned char smem_raw[];
     const StepArgs &a = pa.a;
     const uint32_t E = a.entities, N = pa.stages, cap = pa.lvl_cap, nc = pa.chunks, G = pa.team;
-    float *ring = (float *)smem_raw;                              // [N][kPlanes][T] planes
-    float4 *s_win = (float4 *)(ring + (size_t)N * kPlanes * T);   // [cap][3]: parent window, one 48-byte matrix per entity
+    float *ring = (float *)smem_raw;                              // [N][kStage][T] planes
+    float4 *s_win = (float4 *)(ring + (size_t)N * kStage * T);    // [cap][3]: parent window, one 48-byte matrix per entity
     uint64_t *full = (uint64_t *)(s_win + (size_t)3 * cap);       // [N] inputs have landed
     uint64_t *done = full + N;                                    // [N] outputs are in the stage
     float4 *s_pre = (float4 *)(done + N);                         // team mode: [2][T][3] parent rows prefetched from L2
     __shared__ __align__(16) WorldConst s_c[2];
     __shared__ __align__(16) uint32_t s_cnt[2][4]; // per-warp visible counts of a chunk, one byte per warp
     __shared__ unsigned long long s_sum;
+    __shared__ int s_bounds[2][6]; // kSet 1: bounds of the current world as float keys (min xyz, max xyz), by world parity
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     constexpr int kWarps = T / 32;
     static_assert(kWarps <= 16, "one count byte per warp in s_cnt");
+    const int kEmptyKey = tid % 6 < 3 ? float_key(FIMO_B200_BOUNDS_EMPTY_MIN) : float_key(-FIMO_B200_BOUNDS_EMPTY_MIN);
+    if (kSet == 1 && tid < 12) s_bounds[tid / 6][tid % 6] = kEmptyKey;
+    int cta_bounds_key = kEmptyKey; // threads 0-5: bounds over every world this CTA stepped (kTeam = false)
     const uint32_t levels = a.levels;
     const Walk wk(pa);
     const uint32_t my_worlds = wk.my_worlds, total = wk.total;
@@ -253,7 +281,7 @@ __global__ void __launch_bounds__(T + 32, kMinBlocks) k_world_step_pipe(const Pi
     __syncthreads();
 
     if (warp == kWarps) {
-        if (lane == 0) tma_warp<T>(pa, wk, ring, full, done);
+        if (lane == 0) tma_warp<T, kSet>(pa, wk, ring, full, done);
         return;
     }
 
@@ -262,12 +290,16 @@ __global__ void __launch_bounds__(T + 32, kMinBlocks) k_world_step_pipe(const Pi
     auto const_word = [&](uint64_t w) -> uint32_t {
         if (tid < 24) return uptr(a.frustum, w)[tid];
         if (tid == 24) return uptr(a.dt, w)[0];
+        if (kSet == 1 && tid >= 25 && tid < 28) return uptr(a.gravity, w)[tid - 25];
+        if (kSet == 1 && tid == 28 && (pa.flags & kPipeVelClamp)) return uptr(a.vmax, w)[0];
         if (tid >= 32 && tid <= 32 + (int)levels) return uptr(a.level_start, w)[tid - 32];
         return 0u;
     };
     auto publish_const = [&](WorldConst &c, uint32_t v) {
         if (tid < 24) c.frustum[tid] = __uint_as_float(v);
         if (tid == 24) c.dt = __uint_as_float(v);
+        if (kSet == 1 && tid >= 25 && tid < 28) c.gravity[tid - 25] = __uint_as_float(v);
+        if (kSet == 1 && tid == 28) c.vmax = __uint_as_float(v);
         if (tid >= 32 && tid <= 32 + (int)levels) c.ls[tid - 32] = v;
     };
     if (total) publish_const(s_c[0], const_word(wk.team_id));
@@ -293,6 +325,7 @@ __global__ void __launch_bounds__(T + 32, kMinBlocks) k_world_step_pipe(const Pi
     uint32_t *mask_out = nullptr, *list_out = nullptr;
     float4 *rows = nullptr;
     uint32_t *lvl_done = nullptr;
+    float *waabb_out = nullptr;
 
     for (uint32_t it = 0; it < total; it++) {
         const WorldConst &wc = s_c[k & 1];
@@ -304,6 +337,7 @@ __global__ void __launch_bounds__(T + 32, kMinBlocks) k_world_step_pipe(const Pi
             list_out = uptr(a.vis_list, w);
             rows = pa.rows ? pa.rows + w * (uint64_t)E * 3 : nullptr;
             if (kTeam) lvl_done = pa.lvl_done + w * kMaxLevels;
+            if (kSet == 1) waabb_out = fptr(a.waabb, w);
         }
         const uint32_t first = c * T;
         const uint32_t e = first + tid;
@@ -319,7 +353,9 @@ __global__ void __launch_bounds__(T + 32, kMinBlocks) k_world_step_pipe(const Pi
         if (kTeam && pend_level >= 0 && (int)l_lo > pend_level) flush_pending(lvl_done); // moved past that level
 
         mbar_wait(&full[s], parity);
-        float *st = ring + (size_t)s * kPlanes * T + tid;
+        float *st = ring + (size_t)s * kStage * T + tid;
+        float lo[3] = {FIMO_B200_BOUNDS_EMPTY_MIN, FIMO_B200_BOUNDS_EMPTY_MIN, FIMO_B200_BOUNDS_EMPTY_MIN};
+        float hi[3] = {-FIMO_B200_BOUNDS_EMPTY_MIN, -FIMO_B200_BOUNDS_EMPTY_MIN, -FIMO_B200_BOUNDS_EMPTY_MIN};
         bool vis = false;
         bool pre_next = false;
         if (kTeam) {
@@ -335,7 +371,7 @@ __global__ void __launch_bounds__(T + 32, kMinBlocks) k_world_step_pipe(const Pi
                 const uint32_t npar = ns == 0 ? parity ^ 1u : parity;
                 if (single && nl >= 1 && l_lo == nl && ready_upto >= (int)nl - 1 &&
                     ((pa.flags & kPipePrefetchBlocking) ? (mbar_wait(&full[ns], npar), true) : mbar_test(&full[ns], npar))) {
-                    const uint32_t np = __float_as_uint(ring[(size_t)ns * kPlanes * T + 11 * T + tid]);
+                    const uint32_t np = __float_as_uint(ring[(size_t)ns * kStage * T + 11 * T + tid]);
                     if (nfirst + tid < E && np != kRoot) {
                         const float4 *src = rows + (uint64_t)np * 3;
                         float4 *dst = s_pre + ((size_t)((it + 1) & 1) * T + tid) * 3;
@@ -359,11 +395,21 @@ __global__ void __launch_bounds__(T + 32, kMinBlocks) k_world_step_pipe(const Pi
             }
             if (valid && l_me == l) {
                 const float dt = wc.dt;
-                const float px = fma1(st[3 * T], dt, st[0 * T]); // integrate
-                const float py = fma1(st[4 * T], dt, st[1 * T]);
-                const float pz = fma1(st[5 * T], dt, st[2 * T]);
+                float vx = st[3 * T], vy = st[4 * T], vz = st[5 * T];
+                float rx = st[6 * T], ry = st[7 * T], rz = st[8 * T], rw = st[9 * T];
+                if (kSet == 1) {
+                    vx = fma1(wc.gravity[0], dt, vx), vy = fma1(wc.gravity[1], dt, vy), vz = fma1(wc.gravity[2], dt, vz); // forces
+                    if (pa.flags & kPipeVelClamp) {
+                        const float m = wc.vmax;
+                        vx = fminf(fmaxf(vx, -m), m), vy = fminf(fmaxf(vy, -m), m), vz = fminf(fmaxf(vz, -m), m);
+                    }
+                    integrate_quat(rx, ry, rz, rw, st[18 * T], st[19 * T], st[20 * T], mul(0.5f, dt)); // integrate_ang
+                }
+                const float px = fma1(vx, dt, st[0 * T]); // integrate (linear)
+                const float py = fma1(vy, dt, st[1 * T]);
+                const float pz = fma1(vz, dt, st[2 * T]);
                 float L[12], Wm[12];
-                local_trs(L, px, py, pz, st[6 * T], st[7 * T], st[8 * T], st[9 * T], st[10 * T]);
+                local_trs(L, px, py, pz, rx, ry, rz, rw, st[10 * T]);
                 const uint32_t p = __float_as_uint(st[11 * T]);
                 if (p == kRoot) {
 #pragma unroll
@@ -383,7 +429,17 @@ __global__ void __launch_bounds__(T + 32, kMinBlocks) k_world_step_pipe(const Pi
                     const float P[12] = {r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, r1.w, r2.x, r2.y, r2.z, r2.w};
                     compose(Wm, P, L);
                 }
-                vis = aabb_visible(Wm, st[12 * T], st[13 * T], st[14 * T], st[15 * T], st[16 * T], st[17 * T], wc.frustum);
+                float wcn[3], whn[3];
+                world_aabb_of(wcn, whn, Wm, st[12 * T], st[13 * T], st[14 * T], st[15 * T], st[16 * T], st[17 * T]);
+                vis = planes_visible(wcn, whn, wc.frustum);
+                if (kSet == 1) { // world_aabb leaves through plain coalesced stores; bounds_reduce folds it
+#pragma unroll
+                    for (int r = 0; r < 3; r++) {
+                        waabb_out[(uint64_t)r * E + e] = wcn[r];
+                        waabb_out[(uint64_t)(3 + r) * E + e] = whn[r];
+                        lo[r] = sub(wcn[r], whn[r]), hi[r] = add(wcn[r], whn[r]);
+                    }
+                }
                 if (may_be_parent) { // 48-byte rows: three 128-bit stores, conflict-free in shared memory
                     float4 *row = (!kTeam && e < cap) ? s_win + 3 * e : rows + (uint64_t)e * 3;
                     row[0] = make_float4(Wm[0], Wm[1], Wm[2], Wm[3]);
@@ -394,6 +450,10 @@ __global__ void __launch_bounds__(T + 32, kMinBlocks) k_world_step_pipe(const Pi
 #pragma unroll
                 for (int i = 0; i < 12; i++) st[i * T] = Wm[i];
                 st[12 * T] = px, st[13 * T] = py, st[14 * T] = pz;
+                if (kSet == 1) {
+                    st[15 * T] = vx, st[16 * T] = vy, st[17 * T] = vz;
+                    st[18 * T] = rx, st[19 * T] = ry, st[20 * T] = rz, st[21 * T] = rw;
+                }
             }
             if (kTeam) {
                 if (l + 1 < levels) { // this chunk's share of level l is (being) written to `rows`
@@ -409,6 +469,21 @@ __global__ void __launch_bounds__(T + 32, kMinBlocks) k_world_step_pipe(const Pi
         fence_async_smem();
         const unsigned ballot = __ballot_sync(kFull, vis);
         const bool world_ends = c + G >= nc;
+        if (kSet == 1) { // min / max are exact in any order: warp REDUX on order-preserving keys, then shared atomics
+            int key[6];
+#pragma unroll
+            for (int r = 0; r < 3; r++) {
+                key[r] = __reduce_min_sync(kFull, float_key(lo[r]));
+                key[3 + r] = __reduce_max_sync(kFull, float_key(hi[r]));
+            }
+            if (lane < 6) {
+                int mine = key[0];
+#pragma unroll
+                for (int r = 1; r < 6; r++) mine = lane == r ? key[r] : mine;
+                if (lane < 3) atomicMin(&s_bounds[k & 1][lane], mine);
+                else atomicMax(&s_bounds[k & 1][lane], mine);
+            }
+        }
         if (kTeam) {
             if (lane == 0) {
                 mbar_arrive(&done[s]); // this warp's outputs are in the stage
@@ -416,6 +491,15 @@ __global__ void __launch_bounds__(T + 32, kMinBlocks) k_world_step_pipe(const Pi
             }
             if (world_ends) flush_pending(lvl_done);
             if (world_ends && k + 1 < my_worlds) publish_const(s_c[(k + 1) & 1], next_const);
+            if (kSet == 1 && world_ends) { // this CTA's share of the world's bounds joins the team's
+                consumer_sync<T>();
+                if (tid < 6) {
+                    int *dst = a.bounds_keys + 6 + w * 6 + tid;
+                    if (tid < 3) atomicMin(dst, s_bounds[k & 1][tid]);
+                    else atomicMax(dst, s_bounds[k & 1][tid]);
+                    s_bounds[k & 1][tid] = kEmptyKey;
+                }
+            }
         } else {
             // mask word + ordered compaction
             uint32_t *cnt = s_cnt[it & 1];
@@ -445,6 +529,12 @@ __global__ void __launch_bounds__(T + 32, kMinBlocks) k_world_step_pipe(const Pi
                 uptr(a.vis_count, w)[0] = running;
                 cta_visible += running;
             }
+            if (kSet == 1 && !kTeam && tid < 6) { // after this chunk's barrier: every warp's keys are in
+                const int key = s_bounds[k & 1][tid];
+                fptr(a.wbounds, w)[tid] = key_float(key);
+                cta_bounds_key = tid < 3 ? min(cta_bounds_key, key) : max(cta_bounds_key, key);
+                s_bounds[k & 1][tid] = kEmptyKey;
+            }
             c = wk.rank, k++, w += pa.teams;
         } else {
             c += G;
@@ -455,8 +545,12 @@ __global__ void __launch_bounds__(T + 32, kMinBlocks) k_world_step_pipe(const Pi
 
     if (!kTeam) { // fold the per-warp mask sums, publish the batch statistics
         if (lane == 0) atomicAdd(&s_sum, warp_mask_sum);
+        if (kSet == 1 && tid < 6 && my_worlds) {
+            if (tid < 3) atomicMin(a.bounds_keys + tid, cta_bounds_key);
+            else atomicMax(a.bounds_keys + tid, cta_bounds_key);
+        }
         consumer_sync<T>();
-        if (tid == 0) publish_stats(a, cta_visible, s_sum, my_worlds);
+        if (tid == 0) publish_stats<kSet == 1>(a, cta_visible, s_sum, my_worlds, (unsigned long long)gridDim.x);
     }
 }
 
@@ -465,6 +559,7 @@ __global__ void __launch_bounds__(T + 32, kMinBlocks) k_world_step_pipe(const Pi
 // One CTA per (segment of 256 mask words = 8192 entities, world); a segment's base offset is the popcount of
 // the world's mask words before it (re-read through L2).  Segment 0 also re-arms the world's level counters.
 constexpr int kCompactThreads = 256;
+template <bool kGroupStats>
 __global__ void __launch_bounds__(kCompactThreads) k_compact_lists(const StepArgs a, uint32_t *lvl_done_all) {
     __shared__ uint32_t s_warp[2][kCompactThreads / 32];
     __shared__ unsigned long long s_mask_sum;
@@ -475,6 +570,13 @@ __global__ void __launch_bounds__(kCompactThreads) k_compact_lists(const StepArg
     uint32_t *__restrict__ list = uptr(a.vis_list, w);
     if (tid == 0) s_mask_sum = 0;
     if (seg == 0 && tid < kMaxLevels && lvl_done_all) lvl_done_all[w * kMaxLevels + tid] = 0;
+    if (kGroupStats && seg == 0 && tid < 6) { // the team's bounds of this world: publish, fold into the batch's, re-arm
+        const int empty = tid < 3 ? float_key(FIMO_B200_BOUNDS_EMPTY_MIN) : float_key(-FIMO_B200_BOUNDS_EMPTY_MIN);
+        const int key = atomicExch(a.bounds_keys + 6 + w * 6 + tid, empty);
+        fptr(a.wbounds, w)[tid] = key_float(key);
+        if (tid < 3) atomicMin(a.bounds_keys + tid, key);
+        else atomicMax(a.bounds_keys + tid, key);
+    }
 
     uint32_t before = 0; // visible entities of this world in earlier segments (this thread's share)
     for (uint32_t i = tid; i < seg * kCompactThreads; i += kCompactThreads) before += __popc(__ldcg(mask + i));
@@ -512,7 +614,7 @@ __global__ void __launch_bounds__(kCompactThreads) k_compact_lists(const StepArg
     __syncthreads();
     if (tid == 0) {
         if (seg == gridDim.x - 1) uptr(a.vis_count, w)[0] = all_before + seg_total;
-        publish_stats(a, seg_total, s_mask_sum, seg == 0 ? 1ull : 0ull, (unsigned long long)gridDim.x * gridDim.y);
+        publish_stats<kGroupStats>(a, seg_total, s_mask_sum, seg == 0 ? 1ull : 0ull, (unsigned long long)gridDim.x * gridDim.y);
     }
 }
 
@@ -529,7 +631,9 @@ constexpr size_t kSmemPerSm = 227 * 1024;  // usable by CTAs on sm_100a
 constexpr size_t kSmemPerCtaReserve = 1024; // the hardware reserves 1 KB per resident CTA
 constexpr size_t kStaticSmem = 768;         // WorldConst x2, counts, sum (see -Xptxas -v)
 
-size_t ring_bytes(int T, uint32_t stages) { return (size_t)stages * kPlanes * T * 4; }
+size_t ring_bytes(uint32_t set, int T, uint32_t stages) {
+    return (size_t)stages * (set == 1 ? SetTraits<1>::kStage : SetTraits<0>::kStage) * T * 4;
+}
 
 // Largest index of an entity that can be a parent, over all worlds: max level_start[levels-1].  Read once
 // from HBM when the executor is compiled (cold path) to size the shared-memory window.  If the host later
@@ -549,11 +653,11 @@ uint64_t max_parents(const WorldStepViews &v, int device) {
 
 bool make_plan(WorldStepPlan &p, int T, uint32_t blocks, uint32_t stages, uint64_t want_cap, uint64_t E) {
     const size_t budget = kSmemPerSm / blocks - kSmemPerCtaReserve - kStaticSmem;
-    const size_t fixed = ring_bytes(T, stages) + (size_t)stages * 16;
+    const size_t fixed = ring_bytes(p.set, T, stages) + (size_t)stages * 16;
     if (fixed > budget) return false;
     uint64_t cap = std::min<uint64_t>({want_cap, E, (budget - fixed) / 48});
     p.threads = T, p.blocks_per_sm = blocks, p.stages = stages, p.lvl_cap = (uint32_t)cap;
-    p.smem = ring_bytes(T, stages) + (size_t)cap * 48 + (size_t)stages * 16;
+    p.smem = ring_bytes(p.set, T, stages) + (size_t)cap * 48 + (size_t)stages * 16;
     return true;
 }
 
@@ -591,12 +695,22 @@ bool world_step_plan(const WorldStepViews &v, int device, WorldStepPlan &plan) {
     for (const FimoB200_ResourceView *r : {v.pos, v.vel, v.rot, v.scale, v.parent, v.aabb_c, v.aabb_h, v.world})
         if (!aligned16(r)) pipe = false;
     if (!pipe) { // ragged worlds: v1 (one CTA per world, loads through registers)
-        if (!world_step_supported_v1(v)) return false;
+        if (v.set != 0 || !world_step_supported_v1(v)) return false; // v1 knows the 3-system chain only
         plan.threads = 0;
         return true;
     }
     const uint64_t parents = max_parents(v, device);
     plan.max_parents = (uint32_t)parents;
+    plan.set = v.set;
+    if (v.set == 1) {
+        if (!v.gravity || !v.angvel || !v.waabb || !v.wbounds || !v.gstats || (v.vel_clamp && !v.vmax) || !aligned16(v.angvel)) return false;
+        // bounds accumulators: batch [0..5] then per world, armed "empty" (min slots +FLT_MAX, max slots -FLT_MAX as keys)
+        std::vector<int> keys(6 + 6 * W);
+        const int32_t kMinKey = 0x7F7FFFFF, kMaxKey = (int32_t)(0xFF7FFFFFu ^ 0x7FFFFFFFu);
+        for (size_t i = 0; i < keys.size(); i++) keys[i] = i % 6 < 3 ? kMinKey : kMaxKey;
+        plan.bounds = hbm_shared(device, keys.size() * 4);
+        if (!plan.bounds || !hbm_upload(device, plan.bounds.get(), keys.data(), keys.size() * 4)) return false;
+    }
     bool planned = false;
     // FIMO_B200_PIPE=T,blocks,stages[,cap] overrides the heuristic (tuning sweeps; any value is correct)
     if (const char *env = std::getenv("FIMO_B200_PIPE")) {
@@ -604,7 +718,8 @@ bool world_step_plan(const WorldStepViews &v, int device, WorldStepPlan &plan) {
         unsigned blocks = 0, stages = 0;
         unsigned long long cap = parents;
         if (std::sscanf(env, "%d,%u,%u,%llu", &T, &blocks, &stages, &cap) >= 3 && (T == 128 || T == 256 || T == 512) &&
-            blocks >= 1 && blocks <= 6 && stages >= 2 && stages <= 16 && make_plan(plan, T, blocks, stages, cap, E))
+            blocks >= 1 && blocks <= 6 && stages >= 2 && stages <= 16 && (v.set == 0 || blocks <= 4) &&
+            make_plan(plan, T, blocks, stages, cap, E))
             planned = true;
         else
             std::fprintf(stderr, "fimo_worlds_b200: ignoring FIMO_B200_PIPE=%s\n", env);
@@ -641,7 +756,7 @@ bool world_step_plan(const WorldStepViews &v, int device, WorldStepPlan &plan) {
     if (plan.team <= 1) plan.team = 1, plan.teams = 0;
     if (plan.team > 1) { // no window: every parent row goes through L2
         plan.lvl_cap = 0;
-        plan.smem = ring_bytes(plan.threads, plan.stages) + (size_t)plan.stages * 16 + (size_t)2 * plan.threads * 48;
+        plan.smem = ring_bytes(plan.set, plan.threads, plan.stages) + (size_t)plan.stages * 16 + (size_t)2 * plan.threads * 48;
         plan.kernels = 2;
         plan.lvl_done = hbm_shared(device, (size_t)W * kMaxLevels * 4);
         if (!plan.lvl_done) return false;
@@ -657,20 +772,20 @@ const char *world_step_kernel_name(const WorldStepPlan &plan) {
 }
 
 namespace {
-template <int T, int kBlocks>
+template <int T, int kBlocks, int kSet>
 FimoStatus launch_pipe(PipeArgs &pa, const WorldStepPlan &plan, uint64_t W, const FimoB200_LaunchInfo *info) {
     cudaStream_t stream = (cudaStream_t)info->stream;
     if (plan.team > 1) {
-        auto kernel = k_world_step_pipe<T, kBlocks, true>;
+        auto kernel = k_world_step_pipe<T, kBlocks, true, kSet>;
         if (!allow_smem(kernel, plan.smem)) return check_launch("world_step (shared memory opt-in)");
         pa.team = plan.team, pa.teams = plan.teams;
         kernel<<<plan.team * plan.teams, T + 32, plan.smem, stream>>>(pa);
         if (check_launch("world_step") != FIMO_STATUS_OK) return FIMO_STATUS_ERROR;
         const unsigned segments = (pa.a.mask_words + kCompactThreads - 1) / kCompactThreads;
-        k_compact_lists<<<dim3(segments, (unsigned)W), kCompactThreads, 0, stream>>>(pa.a, pa.lvl_done);
+        k_compact_lists<kSet == 1><<<dim3(segments, (unsigned)W), kCompactThreads, 0, stream>>>(pa.a, pa.lvl_done);
         return check_launch("compact_lists");
     }
-    auto kernel = k_world_step_pipe<T, kBlocks, false>;
+    auto kernel = k_world_step_pipe<T, kBlocks, false, kSet>;
     if (!allow_smem(kernel, plan.smem)) return check_launch("world_step (shared memory opt-in)");
     // Persistent grid with an even share of worlds per CTA: a ragged tail costs more than idle CTA slots
     // on an HBM-bound kernel.
@@ -706,14 +821,28 @@ FimoStatus world_step_launch(const WorldStepViews &v, const WorldStepPlan &plan,
             pa.flags = (pa.flags & ~kPipePrefetchBlocking) | (env[0] == '0' ? kPipeNoPrefetch : (env[0] == '2' ? kPipePrefetchBlocking : 0u));
         if (const char *env = std::getenv("FIMO_B200_PUBLISH"))
             if (env[0] == 'c') pa.flags |= kPipePublishPerChunk;
-        const int key = plan.threads * 10 + (int)plan.blocks_per_sm;
+        if (plan.set == 1) {
+            a.angvel = plane_of(v.angvel, FIMO_B200_SCOPE_ENTITY, 3, E, W, "angvel");
+            a.gravity = plane_of(v.gravity, FIMO_B200_SCOPE_WORLD, 3, 1, W, "gravity");
+            a.waabb = plane_of(v.waabb, FIMO_B200_SCOPE_ENTITY, 6, E, W, "waabb");
+            a.wbounds = plane_of(v.wbounds, FIMO_B200_SCOPE_WORLD, 6, 1, W, "wbounds");
+            if (v.vel_clamp) a.vmax = plane_of(v.vmax, FIMO_B200_SCOPE_WORLD, 1, 1, W, "vmax"), pa.flags |= kPipeVelClamp;
+            if (!v.gstats->device_ptr || v.gstats->scope != FIMO_B200_SCOPE_BATCH || v.gstats->components != FIMO_B200_GSTAT_WORDS) throw Fail{"gstats"};
+            a.gstats = (uint32_t *)v.gstats->device_ptr;
+            a.bounds_keys = (int *)plan.bounds.get();
+        }
+        const int key = plan.threads * 100 + (int)plan.blocks_per_sm * 10 + (int)plan.set;
         switch (key) {
-        case 1284: case 1283: case 1282: case 1281: return launch_pipe<128, 4>(pa, plan, W, info);
-        case 1285: return launch_pipe<128, 5>(pa, plan, W, info);
-        case 1286: return launch_pipe<128, 6>(pa, plan, W, info);
-        case 2561: case 2562: return launch_pipe<256, 2>(pa, plan, W, info);
-        case 2563: return launch_pipe<256, 3>(pa, plan, W, info);
-        case 5121: return launch_pipe<512, 1>(pa, plan, W, info);
+        case 12840: case 12830: case 12820: case 12810: return launch_pipe<128, 4, 0>(pa, plan, W, info);
+        case 12850: return launch_pipe<128, 5, 0>(pa, plan, W, info);
+        case 12860: return launch_pipe<128, 6, 0>(pa, plan, W, info);
+        case 25610: case 25620: return launch_pipe<256, 2, 0>(pa, plan, W, info);
+        case 25630: return launch_pipe<256, 3, 0>(pa, plan, W, info);
+        case 51210: return launch_pipe<512, 1, 0>(pa, plan, W, info);
+        case 12841: case 12831: case 12821: case 12811: return launch_pipe<128, 4, 1>(pa, plan, W, info);
+        case 25611: case 25621: return launch_pipe<256, 2, 1>(pa, plan, W, info);
+        case 25631: return launch_pipe<256, 3, 1>(pa, plan, W, info);
+        case 51211: return launch_pipe<512, 1, 1>(pa, plan, W, info);
         default: return fail("world_step plan");
         }
     } catch (const Fail &f) {

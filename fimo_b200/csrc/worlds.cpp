@@ -837,61 +837,139 @@ bool build_device_executor(Group *g, const char **err) {
         deps[j].swap(kept);
     }
 
-    // fusion: integrate -> propagate -> cull over the same pos/world collapses into one world-step kernel
-    Member *mi = nullptr, *mp = nullptr, *mc = nullptr;
-    for (Member *m : g->order) {
-        if (m->type->builtin_id == FIMO_B200_BUILTIN_INTEGRATE && !mi) mi = m;
-        if (m->type->builtin_id == FIMO_B200_BUILTIN_PROPAGATE && !mp) mp = m;
-        if (m->type->builtin_id == FIMO_B200_BUILTIN_CULL && !mc) mc = m;
-    }
-    bool fuse = !(g->ext_flags & FIMO_B200_GROUP_FLAG_NO_FUSION) && mi && mp && mc && n == 3 &&
-                mi->type->exclusive.size() == 1 && mi->type->shared.size() == 2 && mp->type->exclusive.size() == 1 &&
-                mp->type->shared.size() == 5 && mc->type->exclusive.size() == 4 && mc->type->shared.size() == 4 &&
-                mp->type->shared[0] == mi->type->exclusive[0] && mc->type->shared[0] == mp->type->exclusive[0] &&
-                mi->order < mp->order && mp->order < mc->order;
+    // Fusion.  Two patterns collapse into the world-step kernel (world_step.cu):
+    //   set 0: integrate -> propagate -> cull (the whole group);
+    //   set 1: forces -> [vel_clamp] -> integrate_lin || integrate_ang -> propagate -> world_aabb -> cull_waabb ||
+    //          bounds_reduce -> group_stats, wired through the same resources.  Other systems of the group stay
+    //          separate graph nodes around the fused one, provided the fused set is convex in the DAG (nothing
+    //          outside it sits between two of its members).
+    auto by_id = [&](uint32_t id, auto pred) -> Member * {
+        for (Member *m : g->order)
+            if (m->type->builtin_id == id && pred(m)) return m;
+        return nullptr;
+    };
+    auto any = [](Member *) { return true; };
+    auto arity = [](Member *m, size_t x, size_t s) { return m && m->type->exclusive.size() == x && m->type->shared.size() == s; };
+    std::vector<Member *> fused;
     dev::WorldStepViews views{};
     dev::WorldStepPlan plan{};
-    if (fuse) {
-        views.pos = view_of(g, mi->type->exclusive[0]);
-        views.vel = view_of(g, mi->type->shared[0]);
-        views.dt = view_of(g, mi->type->shared[1]);
-        views.world = view_of(g, mp->type->exclusive[0]);
-        views.rot = view_of(g, mp->type->shared[1]);
-        views.scale = view_of(g, mp->type->shared[2]);
-        views.parent = view_of(g, mp->type->shared[3]);
-        views.level_start = view_of(g, mp->type->shared[4]);
-        views.vis_mask = view_of(g, mc->type->exclusive[0]);
-        views.vis_list = view_of(g, mc->type->exclusive[1]);
-        views.vis_count = view_of(g, mc->type->exclusive[2]);
-        views.stats = view_of(g, mc->type->exclusive[3]);
-        views.aabb_c = view_of(g, mc->type->shared[1]);
-        views.aabb_h = view_of(g, mc->type->shared[2]);
-        views.frustum = view_of(g, mc->type->shared[3]);
-        fuse = dev::world_step_plan(views, g->world->device, plan);
+    Member *mc = nullptr; // the cull member: owner of the statistics scratch block
+    if (!(g->ext_flags & FIMO_B200_GROUP_FLAG_NO_FUSION)) {
+        Member *mi = by_id(FIMO_B200_BUILTIN_INTEGRATE, any), *mp = by_id(FIMO_B200_BUILTIN_PROPAGATE, any);
+        if (arity(mi, 1, 2) && arity(mp, 1, 5) && mp->type->shared[0] == mi->type->exclusive[0] && mi->order < mp->order) {
+            ResourceType *pos = mi->type->exclusive[0], *vel = mi->type->shared[0], *dt = mi->type->shared[1];
+            ResourceType *world = mp->type->exclusive[0], *rot = mp->type->shared[1];
+            views.pos = view_of(g, pos), views.vel = view_of(g, vel), views.dt = view_of(g, dt);
+            views.world = view_of(g, world), views.rot = view_of(g, rot);
+            views.scale = view_of(g, mp->type->shared[2]), views.parent = view_of(g, mp->type->shared[3]);
+            views.level_start = view_of(g, mp->type->shared[4]);
+            Member *c3 = by_id(FIMO_B200_BUILTIN_CULL, [&](Member *m) { return arity(m, 4, 4) && m->type->shared[0] == world; });
+            if (n == 3 && c3 && mp->order < c3->order) {
+                mc = c3;
+                views.aabb_c = view_of(g, mc->type->shared[1]), views.aabb_h = view_of(g, mc->type->shared[2]);
+                views.frustum = view_of(g, mc->type->shared[3]);
+                fused = {mi, mp, mc};
+            } else {
+                Member *mf = by_id(FIMO_B200_BUILTIN_FORCES, [&](Member *m) { return arity(m, 1, 2) && m->type->exclusive[0] == vel && m->type->shared[1] == dt; });
+                Member *ma = by_id(FIMO_B200_BUILTIN_INTEGRATE_ANG, [&](Member *m) { return arity(m, 1, 2) && m->type->exclusive[0] == rot && m->type->shared[1] == dt; });
+                Member *mw = by_id(FIMO_B200_BUILTIN_WORLD_AABB, [&](Member *m) { return arity(m, 1, 3) && m->type->shared[0] == world; });
+                ResourceType *waabb = mw ? mw->type->exclusive[0] : nullptr;
+                Member *mb = by_id(FIMO_B200_BUILTIN_BOUNDS_REDUCE, [&](Member *m) { return arity(m, 1, 1) && m->type->shared[0] == waabb; });
+                Member *ms = nullptr, *c8 = nullptr;
+                for (Member *cand : g->order) { // the cull whose count feeds a group_stats together with bounds_reduce's output
+                    if (cand->type->builtin_id != FIMO_B200_BUILTIN_CULL_WAABB || !arity(cand, 4, 2) || cand->type->shared[0] != waabb || !mb) continue;
+                    ms = by_id(FIMO_B200_BUILTIN_GROUP_STATS, [&](Member *m) {
+                        return arity(m, 1, 2) && m->type->shared[0] == cand->type->exclusive[2] && m->type->shared[1] == mb->type->exclusive[0];
+                    });
+                    if (ms) {
+                        c8 = cand;
+                        break;
+                    }
+                }
+                Member *mv = by_id(FIMO_B200_BUILTIN_VEL_CLAMP, [&](Member *m) { return arity(m, 1, 1) && m->type->exclusive[0] == vel; });
+                const bool ordered = mf && ma && mw && mb && ms && c8 && mf->order < mi->order && ma->order < mp->order &&
+                                     mp->order < mw->order && mw->order < c8->order && mw->order < mb->order && c8->order < ms->order &&
+                                     mb->order < ms->order && (!mv || (mf->order < mv->order && mv->order < mi->order));
+                if (ordered) {
+                    mc = c8;
+                    views.set = 1;
+                    views.gravity = view_of(g, mf->type->shared[0]);
+                    views.angvel = view_of(g, ma->type->shared[0]);
+                    views.waabb = view_of(g, waabb);
+                    views.aabb_c = view_of(g, mw->type->shared[1]), views.aabb_h = view_of(g, mw->type->shared[2]);
+                    views.frustum = view_of(g, mc->type->shared[1]);
+                    views.wbounds = view_of(g, mb->type->exclusive[0]);
+                    views.gstats = view_of(g, ms->type->exclusive[0]);
+                    if (mv) views.vel_clamp = true, views.vmax = view_of(g, mv->type->shared[0]);
+                    fused = {mf, mi, ma, mp, mw, mc, mb, ms};
+                    if (mv) fused.push_back(mv);
+                }
+            }
+            if (!fused.empty()) {
+                views.vis_mask = view_of(g, mc->type->exclusive[0]), views.vis_list = view_of(g, mc->type->exclusive[1]);
+                views.vis_count = view_of(g, mc->type->exclusive[2]), views.stats = view_of(g, mc->type->exclusive[3]);
+            }
+        }
     }
+    // convexity: an outside node may be before the fused set or after it, never both
+    std::vector<char> in_set(n, 0), pred(n, 0), succ(n, 0);
+    for (Member *m : fused) in_set[m->order] = 1;
+    if (!fused.empty())
+        for (size_t x = 0; x < n && !fused.empty(); x++) {
+            if (in_set[x]) continue;
+            for (size_t f = 0; f < n; f++) {
+                if (!in_set[f]) continue;
+                if (reach[f][x]) pred[x] = 1;
+                if (reach[x][f]) succ[x] = 1;
+            }
+            if (pred[x] && succ[x]) fused.clear();
+        }
+    bool fuse = !fused.empty() && dev::world_step_plan(views, g->world->device, plan);
 
     std::vector<dev::Node> nodes;
-    if (fuse) {
+    auto system_node = [&](Member *m) {
         dev::Node node;
-        void *scratch = ((dev::BuiltinState *)mc->state)->scratch;
-        node.launch = [views, plan, scratch](const FimoB200_LaunchInfo *info) { return dev::world_step_launch(views, plan, scratch, info); };
-        node.kernels = plan.kernels;
-        nodes.push_back(std::move(node));
+        const size_t n_ex = m->type->exclusive.size();
+        node.launch = [m, n_ex](const FimoB200_LaunchInfo *info) {
+            const FimoB200_ResourceView *const *blobs = (const FimoB200_ResourceView *const *)m->blobs.data();
+            return m->type->device_entry(m->state, blobs, blobs + n_ex, info);
+        };
+        node.kernels = 1;
+        if (m->type->builtin_id == FIMO_B200_BUILTIN_PROPAGATE)
+            node.kernels = dev::builtin_propagate_kernels(view_of(g, m->type->exclusive[0]), view_of(g, m->type->shared[4]));
+        return node;
+    };
+    for (Member *m : g->order)
+        if (!m->type->device_entry) return *err = "MixedGroup", false;
+    if (fuse) {
+        // new order: everything that is not after the fused set (original order), the fused node, the rest
+        std::vector<int> index(n, -1);
+        for (size_t x = 0; x < n; x++)
+            if (!in_set[x] && !succ[x]) index[x] = (int)nodes.size(), nodes.push_back(system_node(g->order[x]));
+        const int fused_index = (int)nodes.size();
+        {
+            dev::Node node;
+            void *scratch = ((dev::BuiltinState *)mc->state)->scratch;
+            node.launch = [views, plan, scratch](const FimoB200_LaunchInfo *info) { return dev::world_step_launch(views, plan, scratch, info); };
+            node.kernels = plan.kernels;
+            nodes.push_back(std::move(node));
+        }
+        for (size_t x = 0; x < n; x++) {
+            if (in_set[x]) index[x] = fused_index;
+            else if (succ[x]) index[x] = (int)nodes.size(), nodes.push_back(system_node(g->order[x]));
+        }
         edges = 0;
+        for (size_t x = 0; x < n; x++)
+            for (uint32_t d : deps[x]) {
+                const int from = index[d], to = index[x];
+                if (from == to) continue;
+                auto &list = nodes[(size_t)to].deps;
+                if (std::find(list.begin(), list.end(), (uint32_t)from) == list.end()) list.push_back((uint32_t)from), edges++;
+            }
     } else {
         for (size_t j = 0; j < n; j++) {
-            Member *m = g->order[j];
-            if (!m->type->device_entry) return *err = "MixedGroup", false;
-            dev::Node node;
+            dev::Node node = system_node(g->order[j]);
             node.deps = deps[j];
-            const size_t n_ex = m->type->exclusive.size();
-            node.launch = [m, n_ex](const FimoB200_LaunchInfo *info) {
-                const FimoB200_ResourceView *const *blobs = (const FimoB200_ResourceView *const *)m->blobs.data();
-                return m->type->device_entry(m->state, blobs, blobs + n_ex, info);
-            };
-            node.kernels = 1;
-            if (m->type->builtin_id == FIMO_B200_BUILTIN_PROPAGATE)
-                node.kernels = dev::builtin_propagate_kernels(view_of(g, m->type->exclusive[0]), view_of(g, m->type->shared[4]));
             nodes.push_back(std::move(node));
         }
     }

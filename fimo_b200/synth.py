@@ -237,6 +237,21 @@ def bytes_per_entity_step(f_vis: float) -> float:
     return 72.0 + 60.125 + 4.0 * f_vis
 
 
+def dag_bytes_per_entity_step(dag: str, f_vis: float, f_vis2: float = 0.0) -> float:
+    """Algorithmic bytes per entity-step of a DAG by the same rule: every live-in resource read
+    once, every live-out resource written once, per generation.
+    dag8 : reads vel 12, pos 12, rot 16, angvel 12, scale 4, parent 4, aabb 24 = 84;
+           writes vel 12, pos 12, rot 16, world 48, waabb 24, mask 0.125, list 4 f_vis.
+    dag16: also reads world 48 (prev_copy, before propagate overwrites it); also writes angvel 12, prev_world 48,
+           lod 4, sleep 0.125, mask2 0.125, list2 4 f_vis2."""
+    if dag == "chain3":
+        return bytes_per_entity_step(f_vis)
+    b = 84.0 + 112.125 + 4.0 * f_vis
+    if dag == "dag16":
+        b += 48.0 + 12.0 + 48.0 + 4.0 + 0.125 + 0.125 + 4.0 * f_vis2
+    return b
+
+
 def integrate_matches(pos0: np.ndarray, vel: np.ndarray, steps: int, pos: np.ndarray) -> bool:
     """pos == `steps` x fma(vel, dt, pos0) in binary32.  The product of two binary32 values is exact in
     binary64, so one step is round32(round64(v*dt + p)); the double rounding can differ from a true fused

@@ -220,18 +220,28 @@ DAG_CASES = [
     ("dag16", 4, 4096, 4, 4),
     ("dag16", 61, 260, 5, 6),
     ("dag16", 2, 33, 3, 3),
+    ("dag8", 700, 128, 4, 3),     # more worlds than CTA slots, one chunk per world
+    ("dag16", 5, 8192, 8, 2),
 ]
 
 
 @pytest.mark.parametrize("dag,W,E,D,steps", DAG_CASES)
-@pytest.mark.parametrize("graph", [True, False])
-def test_system_dags_match_oracle(oracle, product, dag, W, E, D, steps, graph):
-    """The 8-system fan-out/fan-in DAG and the 16-system DAG with conflict-only orderings, one kernel per system
-    in a CUDA graph (or plain streams with fork/join events): every resource any system writes is bit-exact."""
-    got, want, info = run_both(oracle, product, W, E, D, steps, synth.RigOptions(graph=graph), dag=dag)
+@pytest.mark.parametrize("mode", ["fused", "fused-one-cta-per-world", "graph", "streams"])
+def test_system_dags_match_oracle(oracle, product, monkeypatch, dag, W, E, D, steps, mode):
+    """The 8-system fan-out/fan-in DAG and the 16-system DAG with conflict-only orderings: every resource any
+    system writes is bit-exact.  fused: the 8-system core (plus vel_clamp) runs inside the world-step kernel and
+    the other systems stay graph nodes around it; graph / streams: one kernel per system."""
+    if mode == "fused-one-cta-per-world":
+        monkeypatch.setenv("FIMO_B200_TEAM", "1")
+    fused = mode.startswith("fused")
+    got, want, info = run_both(oracle, product, W, E, D, steps, synth.RigOptions(fused=fused, graph=(mode != "streams")), dag=dag)
     n = 8 if dag == "dag8" else 16
-    assert info.systems == n and info.device_systems == n and info.nodes == n and info.fused_world_step == 0
-    assert info.uses_cuda_graph == (1 if graph else 0) and info.edges >= n - 1
+    assert info.systems == n and info.device_systems == n
+    if fused and E % 4 == 0:
+        assert info.fused_world_step == 1 and info.nodes == (1 if dag == "dag8" else 8)
+    else:
+        assert info.fused_world_step == 0 and info.nodes == n and info.edges >= n - 1
+    assert info.uses_cuda_graph == (0 if mode == "streams" else 1)
     problems = synth.compare_outputs(got, want, FLOAT_RTOL)
     assert not problems, "\n".join(problems)
     st = got["stats"].reshape(-1).view(np.uint64)
