@@ -93,10 +93,15 @@ struct WorldStepViews {
     const FimoB200_ResourceView *aabb_c, *aabb_h, *frustum;                  // cull (shared)
     // set 1 — the fused 8-system DAG (forces, [vel_clamp], integrate_lin, integrate_ang, propagate, world_aabb,
     // cull on waabb, bounds_reduce, group_stats) — additionally uses:
-    uint32_t set = 0;        // 0: 3-system chain; 1: 8-system DAG
+    uint32_t set = 0;        // 0: 3-system chain; 1: 8-system DAG; 2: 15 systems of the 16-system DAG
     bool vel_clamp = false;  // vel_clamp of the 16-system DAG sits between forces and integrate_lin
     const FimoB200_ResourceView *gravity = nullptr, *angvel = nullptr, *vmax = nullptr, *waabb = nullptr, *wbounds = nullptr,
                                 *gstats = nullptr;
+    // set 2 — set 1 with vel_clamp, plus angvel_damp, sleep_flags, lod, cull2, vis_bounds, group_stats2 of the 16-system DAG:
+    const FimoB200_ResourceView *damp = nullptr, *sleep_eps = nullptr, *campos = nullptr, *lod_dist2 = nullptr, *frustum2 = nullptr,
+                                *sleep = nullptr, *lod = nullptr, *vis_mask2 = nullptr, *vis_list2 = nullptr, *vis_count2 = nullptr,
+                                *stats2 = nullptr, *vbounds = nullptr, *gstats2 = nullptr;
+    void *scratch2 = nullptr; // cull2's statistics accumulator block (its BuiltinState)
 };
 // How the fused kernel is launched for a given batch; made once when the executor is compiled (it reads
 // level_start from HBM to size the shared-memory parent window), then reused by every launch.
@@ -113,6 +118,7 @@ struct WorldStepPlan {
     std::shared_ptr<void> rows;     // HBM: [n_worlds][E] 48-byte parent rows (parents outside the window)
     std::shared_ptr<void> lvl_done; // HBM: [n_worlds][32] level-completion counters (team mode)
     std::shared_ptr<void> bounds;   // HBM: [6 + 6 n_worlds] bounds accumulators as float keys (set 1)
+    std::shared_ptr<void> bounds2;  // HBM: [6] batch bounds of the visible entities (set 2)
     uint32_t set = 0;               // copied from the views
 };
 bool world_step_plan(const WorldStepViews &v, int device, WorldStepPlan &plan); // false: not fusable

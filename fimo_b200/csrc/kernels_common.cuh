@@ -116,6 +116,12 @@ struct StepArgs {
     Plane angvel, gravity, vmax, waabb, wbounds;
     uint32_t *gstats;     // FIMO_B200_GSTAT_* words of the batch
     int *bounds_keys;     // [0..5] batch bounds as float_key accumulators, then [n_worlds][6] per-world ones (team mode)
+    // the fused 16-system DAG (kSet = 2) additionally uses:
+    Plane damp, sleep_eps, campos, lod_dist2, frustum2;     // per-world constants
+    Plane sleep, lod, vis_mask2, vis_list2, vis_count2, vbounds;
+    unsigned long long *stats2, *scratch2; // cull2's statistics and its accumulator block
+    uint32_t *gstats2;                     // group_stats2
+    int *bounds_keys2;                     // [0..5] batch bounds of the visible entities (float keys)
     uint32_t n_worlds, entities, levels, mask_words;
 };
 
@@ -153,9 +159,15 @@ __device__ __forceinline__ void propagate_entity(uint32_t e, uint32_t E, float *
 // Returns true on the last CTA (the one that published).  kGroupStats: the fused 8-system DAG also publishes
 // BUILTIN_GROUP_STATS' words — total visible, worlds, and the batch bounds every CTA merged into
 // a.bounds_keys[0..5] (float keys) before calling — and re-arms those keys.
-template <bool kGroupStats = false>
-__device__ __forceinline__ bool publish_stats(const StepArgs &a, unsigned long long visible, unsigned long long mask_sum,
-                                              unsigned long long worlds, unsigned long long n_ctas) {
+struct StatsSink { // where one cull's batch statistics go (the DAGs have up to two culls)
+    unsigned long long *stats, *scratch;
+    uint32_t *gstats; // group statistics fed by this cull (nullptr: none)
+    int *bounds_keys; // batch bounds accumulators that go with gstats
+    uint32_t entities;
+};
+template <bool kGroupStats>
+__device__ __forceinline__ bool publish_stats_to(const StatsSink &a, unsigned long long visible, unsigned long long mask_sum,
+                                                 unsigned long long worlds, unsigned long long n_ctas) {
     atomicAdd(&a.scratch[0], visible);
     atomicAdd(&a.scratch[1], mask_sum);
     atomicAdd(&a.scratch[2], worlds);
@@ -183,6 +195,11 @@ __device__ __forceinline__ bool publish_stats(const StepArgs &a, unsigned long l
     }
     atomicExch(&a.scratch[4], 0ull);
     return true;
+}
+template <bool kGroupStats = false>
+__device__ __forceinline__ bool publish_stats(const StepArgs &a, unsigned long long visible, unsigned long long mask_sum,
+                                              unsigned long long worlds, unsigned long long n_ctas) {
+    return publish_stats_to<kGroupStats>(StatsSink{a.stats, a.scratch, a.gstats, a.bounds_keys, a.entities}, visible, mask_sum, worlds, n_ctas);
 }
 __device__ __forceinline__ bool publish_stats(const StepArgs &a, unsigned long long visible, unsigned long long mask_sum,
                                               unsigned long long worlds) {

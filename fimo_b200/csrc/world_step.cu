@@ -41,6 +41,14 @@ template <> struct SetTraits<0> {
 template <> struct SetTraits<1> {
     static constexpr int kIn = 21, kOut = 22, kStage = 22;
 };
+// kSet 2: set 1 with vel_clamp plus six more systems of the 16-system DAG that only touch data the kernel already
+// holds: angvel_damp (angvel *= damp, written back: planes 22-24), sleep_flags (bit per entity from the clamped
+// velocity), lod (u32 per entity from the world AABB centre), cull2 (second frustum: mask2 / list2 / count2 /
+// stats2), vis_bounds (bounds over the VISIBLE entities of cull) and group_stats2.  prev_copy stays a separate
+// node in front of the kernel (it reads the world matrices this kernel overwrites).
+template <> struct SetTraits<2> {
+    static constexpr int kIn = 21, kOut = 25, kStage = 25;
+};
 
 __device__ __forceinline__ uint32_t smem_addr(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
@@ -123,6 +131,8 @@ struct WorldConst {
     float dt;
     float gravity[3], vmax;         // kSet 1
     uint32_t pad[2];
+    float frustum2[24];             // kSet 2 (16-byte aligned)
+    float damp, sleep_eps, campos[3], lod_dist2[3];
 };
 static_assert(sizeof(WorldConst) % 16 == 0, "WorldConst");
 
@@ -170,13 +180,18 @@ __device__ __forceinline__ void tma_warp(const PipeArgs &pa, const Walk &wk, flo
         for (int i = 0; i < 12; i++) bulk_store(world + (uint64_t)i * E, st + i * T, bytes);
 #pragma unroll
         for (int i = 0; i < 3; i++) bulk_store(pos + (uint64_t)i * E, st + (12 + i) * T, bytes);
-        if (kSet == 1) {
+        if (kSet >= 1) {
             float *vel = fptr(a.vel, w) + first;
             float *rot = fptr(a.rot, w) + first;
 #pragma unroll
             for (int i = 0; i < 3; i++) bulk_store(vel + (uint64_t)i * E, st + (15 + i) * T, bytes);
 #pragma unroll
             for (int i = 0; i < 4; i++) bulk_store(rot + (uint64_t)i * E, st + (18 + i) * T, bytes);
+        }
+        if (kSet == 2) {
+            float *angvel = fptr(a.angvel, w) + first;
+#pragma unroll
+            for (int i = 0; i < 3; i++) bulk_store(angvel + (uint64_t)i * E, st + (22 + i) * T, bytes);
         }
         bulk_commit();
     };
@@ -258,14 +273,20 @@ __global__ void __launch_bounds__(T + 32, kMinBlocks) k_world_step_pipe(const Pi
     __shared__ __align__(16) WorldConst s_c[2];
     __shared__ __align__(16) uint32_t s_cnt[2][4]; // per-warp visible counts of a chunk, one byte per warp
     __shared__ unsigned long long s_sum;
-    __shared__ int s_bounds[2][6]; // kSet 1: bounds of the current world as float keys (min xyz, max xyz), by world parity
+    __shared__ int s_bounds[2][6]; // kSet >= 1: bounds of the current world as float keys (min xyz, max xyz), by world parity
+    __shared__ int s_vbounds[2][6]; // kSet 2: the same over the entities `cull` found visible (vis_bounds)
+    __shared__ __align__(16) uint32_t s_cnt2[2][4]; // kSet 2: per-warp counts of cull2
+    __shared__ unsigned long long s_sum2;
+    static_assert(!(kTeam && kSet == 2), "the 16-system set is fused for one-CTA-per-world plans only");
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     constexpr int kWarps = T / 32;
     static_assert(kWarps <= 16, "one count byte per warp in s_cnt");
     const int kEmptyKey = tid % 6 < 3 ? float_key(FIMO_B200_BOUNDS_EMPTY_MIN) : float_key(-FIMO_B200_BOUNDS_EMPTY_MIN);
-    if (kSet == 1 && tid < 12) s_bounds[tid / 6][tid % 6] = kEmptyKey;
+    if (kSet >= 1 && tid < 12) s_bounds[tid / 6][tid % 6] = kEmptyKey;
+    if (kSet == 2 && tid < 12) s_vbounds[tid / 6][tid % 6] = kEmptyKey;
     int cta_bounds_key = kEmptyKey; // threads 0-5: bounds over every world this CTA stepped (kTeam = false)
+    int cta_vbounds_key = kEmptyKey;
     const uint32_t levels = a.levels;
     const Walk wk(pa);
     const uint32_t my_worlds = wk.my_worlds, total = wk.total;
@@ -276,6 +297,7 @@ __global__ void __launch_bounds__(T + 32, kMinBlocks) k_world_step_pipe(const Pi
             mbar_init(&done[s], kWarps);
         }
         s_sum = 0;
+        s_sum2 = 0;
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncthreads();
@@ -290,24 +312,40 @@ __global__ void __launch_bounds__(T + 32, kMinBlocks) k_world_step_pipe(const Pi
     auto const_word = [&](uint64_t w) -> uint32_t {
         if (tid < 24) return uptr(a.frustum, w)[tid];
         if (tid == 24) return uptr(a.dt, w)[0];
-        if (kSet == 1 && tid >= 25 && tid < 28) return uptr(a.gravity, w)[tid - 25];
-        if (kSet == 1 && tid == 28 && (pa.flags & kPipeVelClamp)) return uptr(a.vmax, w)[0];
+        if (kSet >= 1 && tid >= 25 && tid < 28) return uptr(a.gravity, w)[tid - 25];
+        if (kSet >= 1 && tid == 28 && (pa.flags & kPipeVelClamp)) return uptr(a.vmax, w)[0];
         if (tid >= 32 && tid <= 32 + (int)levels) return uptr(a.level_start, w)[tid - 32];
+        if (kSet == 2) { // threads 65..96 (T >= 128)
+            if (tid >= 65 && tid < 89) return uptr(a.frustum2, w)[tid - 65];
+            if (tid == 89) return uptr(a.damp, w)[0];
+            if (tid == 90) return uptr(a.sleep_eps, w)[0];
+            if (tid >= 91 && tid < 94) return uptr(a.campos, w)[tid - 91];
+            if (tid >= 94 && tid < 97) return uptr(a.lod_dist2, w)[tid - 94];
+        }
         return 0u;
     };
     auto publish_const = [&](WorldConst &c, uint32_t v) {
         if (tid < 24) c.frustum[tid] = __uint_as_float(v);
         if (tid == 24) c.dt = __uint_as_float(v);
-        if (kSet == 1 && tid >= 25 && tid < 28) c.gravity[tid - 25] = __uint_as_float(v);
-        if (kSet == 1 && tid == 28) c.vmax = __uint_as_float(v);
+        if (kSet >= 1 && tid >= 25 && tid < 28) c.gravity[tid - 25] = __uint_as_float(v);
+        if (kSet >= 1 && tid == 28) c.vmax = __uint_as_float(v);
         if (tid >= 32 && tid <= 32 + (int)levels) c.ls[tid - 32] = v;
+        if (kSet == 2) {
+            if (tid >= 65 && tid < 89) c.frustum2[tid - 65] = __uint_as_float(v);
+            if (tid == 89) c.damp = __uint_as_float(v);
+            if (tid == 90) c.sleep_eps = __uint_as_float(v);
+            if (tid >= 91 && tid < 94) c.campos[tid - 91] = __uint_as_float(v);
+            if (tid >= 94 && tid < 97) c.lod_dist2[tid - 94] = __uint_as_float(v);
+        }
     };
     if (total) publish_const(s_c[0], const_word(wk.team_id));
     consumer_sync<T>();
 
     uint32_t next_const = 0;
     unsigned long long cta_visible = 0, warp_mask_sum = 0; // thread 0 / lane 0 of each warp
+    unsigned long long cta_visible2 = 0, warp_mask_sum2 = 0; // kSet 2: cull2
     uint32_t running = 0;                                   // visible entities of the current world so far
+    uint32_t running2 = 0;
     uint32_t k = 0, c = wk.rank, s = 0, parity = 0, l_lo = 0;
     // team mode: entities of level pend_level this CTA has finished but not yet announced.  Dependants only
     // care about a level being COMPLETE, so a CTA announces its share once, when it moves past the level.
@@ -326,18 +364,23 @@ __global__ void __launch_bounds__(T + 32, kMinBlocks) k_world_step_pipe(const Pi
     float4 *rows = nullptr;
     uint32_t *lvl_done = nullptr;
     float *waabb_out = nullptr;
+    uint32_t *mask2_out = nullptr, *list2_out = nullptr, *sleep_out = nullptr, *lod_out = nullptr;
 
     for (uint32_t it = 0; it < total; it++) {
         const WorldConst &wc = s_c[k & 1];
         if (c == wk.rank) { // a new world begins
             if (kTeam && it != 0) consumer_sync<T>(); // its constants were published during the previous world
             if (k + 1 < my_worlds) next_const = const_word(w + pa.teams);
-            running = 0, l_lo = 0, ready_upto = -1;
+            running = 0, running2 = 0, l_lo = 0, ready_upto = -1;
             mask_out = uptr(a.vis_mask, w);
             list_out = uptr(a.vis_list, w);
             rows = pa.rows ? pa.rows + w * (uint64_t)E * 3 : nullptr;
             if (kTeam) lvl_done = pa.lvl_done + w * kMaxLevels;
-            if (kSet == 1) waabb_out = fptr(a.waabb, w);
+            if (kSet >= 1) waabb_out = fptr(a.waabb, w);
+            if (kSet == 2) {
+                mask2_out = uptr(a.vis_mask2, w), list2_out = uptr(a.vis_list2, w);
+                sleep_out = uptr(a.sleep, w), lod_out = uptr(a.lod, w);
+            }
         }
         const uint32_t first = c * T;
         const uint32_t e = first + tid;
@@ -356,7 +399,7 @@ __global__ void __launch_bounds__(T + 32, kMinBlocks) k_world_step_pipe(const Pi
         float *st = ring + (size_t)s * kStage * T + tid;
         float lo[3] = {FIMO_B200_BOUNDS_EMPTY_MIN, FIMO_B200_BOUNDS_EMPTY_MIN, FIMO_B200_BOUNDS_EMPTY_MIN};
         float hi[3] = {-FIMO_B200_BOUNDS_EMPTY_MIN, -FIMO_B200_BOUNDS_EMPTY_MIN, -FIMO_B200_BOUNDS_EMPTY_MIN};
-        bool vis = false;
+        bool vis = false, vis2 = false, asleep = false;
         bool pre_next = false;
         if (kTeam) {
             // Parent rows come from L2 (~1 us under load): fetch the NEXT chunk's rows now, asynchronously and
@@ -397,13 +440,19 @@ __global__ void __launch_bounds__(T + 32, kMinBlocks) k_world_step_pipe(const Pi
                 const float dt = wc.dt;
                 float vx = st[3 * T], vy = st[4 * T], vz = st[5 * T];
                 float rx = st[6 * T], ry = st[7 * T], rz = st[8 * T], rw = st[9 * T];
-                if (kSet == 1) {
+                if (kSet >= 1) {
                     vx = fma1(wc.gravity[0], dt, vx), vy = fma1(wc.gravity[1], dt, vy), vz = fma1(wc.gravity[2], dt, vz); // forces
-                    if (pa.flags & kPipeVelClamp) {
+                    if (kSet == 2 || (pa.flags & kPipeVelClamp)) {
                         const float m = wc.vmax;
                         vx = fminf(fmaxf(vx, -m), m), vy = fminf(fmaxf(vy, -m), m), vz = fminf(fmaxf(vz, -m), m);
                     }
-                    integrate_quat(rx, ry, rz, rw, st[18 * T], st[19 * T], st[20 * T], mul(0.5f, dt)); // integrate_ang
+                    float ax = st[18 * T], ay = st[19 * T], az = st[20 * T];
+                    if (kSet == 2) {
+                        ax = mul(ax, wc.damp), ay = mul(ay, wc.damp), az = mul(az, wc.damp); // angvel_damp
+                        st[22 * T] = ax, st[23 * T] = ay, st[24 * T] = az;
+                        asleep = add(add(fabsf(vx), fabsf(vy)), fabsf(vz)) < wc.sleep_eps;       // sleep_flags
+                    }
+                    integrate_quat(rx, ry, rz, rw, ax, ay, az, mul(0.5f, dt)); // integrate_ang
                 }
                 const float px = fma1(vx, dt, st[0 * T]); // integrate (linear)
                 const float py = fma1(vy, dt, st[1 * T]);
@@ -432,13 +481,19 @@ __global__ void __launch_bounds__(T + 32, kMinBlocks) k_world_step_pipe(const Pi
                 float wcn[3], whn[3];
                 world_aabb_of(wcn, whn, Wm, st[12 * T], st[13 * T], st[14 * T], st[15 * T], st[16 * T], st[17 * T]);
                 vis = planes_visible(wcn, whn, wc.frustum);
-                if (kSet == 1) { // world_aabb leaves through plain coalesced stores; bounds_reduce folds it
+                if (kSet >= 1) { // world_aabb leaves through plain coalesced stores; bounds_reduce folds it
 #pragma unroll
                     for (int r = 0; r < 3; r++) {
                         waabb_out[(uint64_t)r * E + e] = wcn[r];
                         waabb_out[(uint64_t)(3 + r) * E + e] = whn[r];
                         lo[r] = sub(wcn[r], whn[r]), hi[r] = add(wcn[r], whn[r]);
                     }
+                }
+                if (kSet == 2) {
+                    vis2 = planes_visible(wcn, whn, wc.frustum2); // cull2
+                    const float dx = sub(wcn[0], wc.campos[0]), dy = sub(wcn[1], wc.campos[1]), dz = sub(wcn[2], wc.campos[2]);
+                    const float d2 = fma1(dz, dz, fma1(dy, dy, mul(dx, dx)));
+                    lod_out[e] = (uint32_t)(d2 >= wc.lod_dist2[0]) + (uint32_t)(d2 >= wc.lod_dist2[1]) + (uint32_t)(d2 >= wc.lod_dist2[2]); // lod
                 }
                 if (may_be_parent) { // 48-byte rows: three 128-bit stores, conflict-free in shared memory
                     float4 *row = (!kTeam && e < cap) ? s_win + 3 * e : rows + (uint64_t)e * 3;
@@ -450,7 +505,7 @@ __global__ void __launch_bounds__(T + 32, kMinBlocks) k_world_step_pipe(const Pi
 #pragma unroll
                 for (int i = 0; i < 12; i++) st[i * T] = Wm[i];
                 st[12 * T] = px, st[13 * T] = py, st[14 * T] = pz;
-                if (kSet == 1) {
+                if (kSet >= 1) {
                     st[15 * T] = vx, st[16 * T] = vy, st[17 * T] = vz;
                     st[18 * T] = rx, st[19 * T] = ry, st[20 * T] = rz, st[21 * T] = rw;
                 }
@@ -469,21 +524,35 @@ __global__ void __launch_bounds__(T + 32, kMinBlocks) k_world_step_pipe(const Pi
         fence_async_smem();
         const unsigned ballot = __ballot_sync(kFull, vis);
         const bool world_ends = c + G >= nc;
-        if (kSet == 1) { // min / max are exact in any order: warp REDUX on order-preserving keys, then shared atomics
-            int key[6];
+        if (kSet >= 1) { // min / max are exact in any order: warp REDUX on order-preserving keys, then shared atomics
+            int key[6], vkey[6];
 #pragma unroll
             for (int r = 0; r < 3; r++) {
-                key[r] = __reduce_min_sync(kFull, float_key(lo[r]));
-                key[3 + r] = __reduce_max_sync(kFull, float_key(hi[r]));
+                const int klo = float_key(lo[r]), khi = float_key(hi[r]);
+                key[r] = __reduce_min_sync(kFull, klo);
+                key[3 + r] = __reduce_max_sync(kFull, khi);
+                if (kSet == 2) { // vis_bounds: the same over the entities cull found visible
+                    vkey[r] = __reduce_min_sync(kFull, vis ? klo : float_key(FIMO_B200_BOUNDS_EMPTY_MIN));
+                    vkey[3 + r] = __reduce_max_sync(kFull, vis ? khi : float_key(-FIMO_B200_BOUNDS_EMPTY_MIN));
+                }
             }
             if (lane < 6) {
-                int mine = key[0];
+                int mine = key[0], vmine = kSet == 2 ? vkey[0] : 0;
 #pragma unroll
-                for (int r = 1; r < 6; r++) mine = lane == r ? key[r] : mine;
+                for (int r = 1; r < 6; r++) {
+                    mine = lane == r ? key[r] : mine;
+                    if (kSet == 2) vmine = lane == r ? vkey[r] : vmine;
+                }
                 if (lane < 3) atomicMin(&s_bounds[k & 1][lane], mine);
                 else atomicMax(&s_bounds[k & 1][lane], mine);
+                if (kSet == 2) {
+                    if (lane < 3) atomicMin(&s_vbounds[k & 1][lane], vmine);
+                    else atomicMax(&s_vbounds[k & 1][lane], vmine);
+                }
             }
         }
+        unsigned ballot2 = 0, ballot_sleep = 0;
+        if (kSet == 2) ballot2 = __ballot_sync(kFull, vis2), ballot_sleep = __ballot_sync(kFull, asleep);
         if (kTeam) {
             if (lane == 0) {
                 mbar_arrive(&done[s]); // this warp's outputs are in the stage
@@ -491,7 +560,7 @@ __global__ void __launch_bounds__(T + 32, kMinBlocks) k_world_step_pipe(const Pi
             }
             if (world_ends) flush_pending(lvl_done);
             if (world_ends && k + 1 < my_worlds) publish_const(s_c[(k + 1) & 1], next_const);
-            if (kSet == 1 && world_ends) { // this CTA's share of the world's bounds joins the team's
+            if (kSet >= 1 && world_ends) { // this CTA's share of the world's bounds joins the team's
                 consumer_sync<T>();
                 if (tid < 6) {
                     int *dst = a.bounds_keys + 6 + w * 6 + tid;
@@ -508,6 +577,11 @@ __global__ void __launch_bounds__(T + 32, kMinBlocks) k_world_step_pipe(const Pi
                 if ((e >> 5) < a.mask_words) mask_out[e >> 5] = ballot;
                 warp_mask_sum += ballot;
                 ((uint8_t *)cnt)[warp] = (uint8_t)__popc(ballot);
+                if (kSet == 2) {
+                    if ((e >> 5) < a.mask_words) mask2_out[e >> 5] = ballot2, sleep_out[e >> 5] = ballot_sleep;
+                    warp_mask_sum2 += ballot2;
+                    ((uint8_t *)s_cnt2[it & 1])[warp] = (uint8_t)__popc(ballot2);
+                }
             }
             if (world_ends && k + 1 < my_worlds) publish_const(s_c[(k + 1) & 1], next_const);
             consumer_sync<T>();
@@ -523,17 +597,38 @@ __global__ void __launch_bounds__(T + 32, kMinBlocks) k_world_step_pipe(const Pi
             }
             if (vis) list_out[running + before + __popc(ballot & ((1u << lane) - 1u))] = e;
             running += chunk_total;
+            if (kSet == 2) { // cull2's ordered list, same scan on its own count bytes
+                const uint32_t *cnt2 = s_cnt2[it & 1];
+                uint32_t before2 = 0, chunk_total2 = 0;
+#pragma unroll
+                for (int j = 0; j < (kWarps + 3) / 4; j++) {
+                    const uint32_t word = cnt2[j];
+                    const int nb = warp - 4 * j;
+                    const uint32_t below = nb >= 4 ? 0xFFFFFFFFu : (nb <= 0 ? 0u : (1u << (8 * nb)) - 1u);
+                    before2 = __dp4a(word & below, 0x01010101u, before2);
+                    chunk_total2 = __dp4a(word, 0x01010101u, chunk_total2);
+                }
+                if (vis2) list2_out[running2 + before2 + __popc(ballot2 & ((1u << lane) - 1u))] = e;
+                running2 += chunk_total2;
+            }
         }
         if (world_ends) {
             if (!kTeam && tid == 0) {
                 uptr(a.vis_count, w)[0] = running;
                 cta_visible += running;
+                if (kSet == 2) uptr(a.vis_count2, w)[0] = running2, cta_visible2 += running2;
             }
-            if (kSet == 1 && !kTeam && tid < 6) { // after this chunk's barrier: every warp's keys are in
+            if (kSet >= 1 && !kTeam && tid < 6) { // after this chunk's barrier: every warp's keys are in
                 const int key = s_bounds[k & 1][tid];
                 fptr(a.wbounds, w)[tid] = key_float(key);
                 cta_bounds_key = tid < 3 ? min(cta_bounds_key, key) : max(cta_bounds_key, key);
                 s_bounds[k & 1][tid] = kEmptyKey;
+                if (kSet == 2) {
+                    const int vkey = s_vbounds[k & 1][tid];
+                    fptr(a.vbounds, w)[tid] = key_float(vkey);
+                    cta_vbounds_key = tid < 3 ? min(cta_vbounds_key, vkey) : max(cta_vbounds_key, vkey);
+                    s_vbounds[k & 1][tid] = kEmptyKey;
+                }
             }
             c = wk.rank, k++, w += pa.teams;
         } else {
@@ -545,12 +640,22 @@ __global__ void __launch_bounds__(T + 32, kMinBlocks) k_world_step_pipe(const Pi
 
     if (!kTeam) { // fold the per-warp mask sums, publish the batch statistics
         if (lane == 0) atomicAdd(&s_sum, warp_mask_sum);
-        if (kSet == 1 && tid < 6 && my_worlds) {
+        if (kSet == 2 && lane == 0) atomicAdd(&s_sum2, warp_mask_sum2);
+        if (kSet >= 1 && tid < 6 && my_worlds) {
             if (tid < 3) atomicMin(a.bounds_keys + tid, cta_bounds_key);
             else atomicMax(a.bounds_keys + tid, cta_bounds_key);
+            if (kSet == 2) {
+                if (tid < 3) atomicMin(a.bounds_keys2 + tid, cta_vbounds_key);
+                else atomicMax(a.bounds_keys2 + tid, cta_vbounds_key);
+            }
         }
         consumer_sync<T>();
-        if (tid == 0) publish_stats<kSet == 1>(a, cta_visible, s_sum, my_worlds, (unsigned long long)gridDim.x);
+        if (tid == 0) {
+            publish_stats<kSet >= 1>(a, cta_visible, s_sum, my_worlds, (unsigned long long)gridDim.x);
+            if (kSet == 2)
+                publish_stats_to<true>(StatsSink{a.stats2, a.scratch2, a.gstats2, a.bounds_keys2, a.entities}, cta_visible2, s_sum2,
+                                       my_worlds, (unsigned long long)gridDim.x);
+        }
     }
 }
 
@@ -629,10 +734,10 @@ bool aligned16(const FimoB200_ResourceView *v) { return v && ((uintptr_t)v->devi
 
 constexpr size_t kSmemPerSm = 227 * 1024;  // usable by CTAs on sm_100a
 constexpr size_t kSmemPerCtaReserve = 1024; // the hardware reserves 1 KB per resident CTA
-constexpr size_t kStaticSmem = 768;         // WorldConst x2, counts, sum (see -Xptxas -v)
+constexpr size_t static_smem(uint32_t set) { return set == 2 ? 1024 : 896; } // WorldConst x2, counts, sums, bounds keys (see -Xptxas -v)
 
 size_t ring_bytes(uint32_t set, int T, uint32_t stages) {
-    return (size_t)stages * (set == 1 ? SetTraits<1>::kStage : SetTraits<0>::kStage) * T * 4;
+    return (size_t)stages * (set == 2 ? SetTraits<2>::kStage : set == 1 ? SetTraits<1>::kStage : SetTraits<0>::kStage) * T * 4;
 }
 
 // Largest index of an entity that can be a parent, over all worlds: max level_start[levels-1].  Read once
@@ -652,7 +757,7 @@ uint64_t max_parents(const WorldStepViews &v, int device) {
 }
 
 bool make_plan(WorldStepPlan &p, int T, uint32_t blocks, uint32_t stages, uint64_t want_cap, uint64_t E) {
-    const size_t budget = kSmemPerSm / blocks - kSmemPerCtaReserve - kStaticSmem;
+    const size_t budget = kSmemPerSm / blocks - kSmemPerCtaReserve - static_smem(p.set);
     const size_t fixed = ring_bytes(p.set, T, stages) + (size_t)stages * 16;
     if (fixed > budget) return false;
     uint64_t cap = std::min<uint64_t>({want_cap, E, (budget - fixed) / 48});
@@ -702,7 +807,10 @@ bool world_step_plan(const WorldStepViews &v, int device, WorldStepPlan &plan) {
     const uint64_t parents = max_parents(v, device);
     plan.max_parents = (uint32_t)parents;
     plan.set = v.set;
-    if (v.set == 1) {
+    if (v.set == 2 && (!v.vel_clamp || !v.damp || !v.sleep_eps || !v.campos || !v.lod_dist2 || !v.frustum2 || !v.sleep || !v.lod ||
+                       !v.vis_mask2 || !v.vis_list2 || !v.vis_count2 || !v.stats2 || !v.vbounds || !v.gstats2 || !v.scratch2))
+        return false;
+    if (v.set >= 1) {
         if (!v.gravity || !v.angvel || !v.waabb || !v.wbounds || !v.gstats || (v.vel_clamp && !v.vmax) || !aligned16(v.angvel)) return false;
         // bounds accumulators: batch [0..5] then per world, armed "empty" (min slots +FLT_MAX, max slots -FLT_MAX as keys)
         std::vector<int> keys(6 + 6 * W);
@@ -710,6 +818,10 @@ bool world_step_plan(const WorldStepViews &v, int device, WorldStepPlan &plan) {
         for (size_t i = 0; i < keys.size(); i++) keys[i] = i % 6 < 3 ? kMinKey : kMaxKey;
         plan.bounds = hbm_shared(device, keys.size() * 4);
         if (!plan.bounds || !hbm_upload(device, plan.bounds.get(), keys.data(), keys.size() * 4)) return false;
+        if (v.set == 2) {
+            plan.bounds2 = hbm_shared(device, 6 * 4);
+            if (!plan.bounds2 || !hbm_upload(device, plan.bounds2.get(), keys.data(), 6 * 4)) return false;
+        }
     }
     bool planned = false;
     // FIMO_B200_PIPE=T,blocks,stages[,cap] overrides the heuristic (tuning sweeps; any value is correct)
@@ -742,7 +854,7 @@ bool world_step_plan(const WorldStepViews &v, int device, WorldStepPlan &plan) {
     // Few worlds (or a forced team size): CTA teams, with the geometry that suits them (no window needed).
     const char *team_env = std::getenv("FIMO_B200_TEAM"); // force the team size (1 = one CTA per world)
     const uint64_t forced = team_env ? std::strtoull(team_env, nullptr, 10) : 0;
-    if (!planned && (!team_env || forced > 1)) {
+    if (!planned && v.set != 2 && (!team_env || forced > 1)) {
         WorldStepPlan trial = plan;
         make_plan(trial, 128, 4, 3, 0, E);
         choose_team(trial, W, (E + 127) / 128, 4ull * sm_count(device));
@@ -750,7 +862,12 @@ bool world_step_plan(const WorldStepViews &v, int device, WorldStepPlan &plan) {
     }
     const uint64_t chunks = (E + plan.threads - 1) / plan.threads;
     const uint64_t slots = (uint64_t)plan.blocks_per_sm * sm_count(device);
-    if (!team_env) choose_team(plan, W, chunks, slots);
+    if (v.set == 2) { // the 16-system set runs one CTA per world only; few large worlds fall back to set 1 + teams
+        if (!team_env) choose_team(plan, W, chunks, slots);
+        else plan.team = (uint32_t)std::max<uint64_t>(forced, 1);
+        if (plan.team > 1) return false;
+        plan.team = 1, plan.teams = 0;
+    } else if (!team_env) choose_team(plan, W, chunks, slots);
     else if (forced <= 1) plan.team = 1, plan.teams = 0;
     else plan.team = (uint32_t)std::min<uint64_t>({forced, chunks, slots}), plan.teams = (uint32_t)std::min<uint64_t>(W, slots / plan.team);
     if (plan.team <= 1) plan.team = 1, plan.teams = 0;
@@ -776,6 +893,8 @@ template <int T, int kBlocks, int kSet>
 FimoStatus launch_pipe(PipeArgs &pa, const WorldStepPlan &plan, uint64_t W, const FimoB200_LaunchInfo *info) {
     cudaStream_t stream = (cudaStream_t)info->stream;
     if (plan.team > 1) {
+        if constexpr (kSet == 2) return fail("world_step plan (teams cannot run the 16-system set)");
+        else {
         auto kernel = k_world_step_pipe<T, kBlocks, true, kSet>;
         if (!allow_smem(kernel, plan.smem)) return check_launch("world_step (shared memory opt-in)");
         pa.team = plan.team, pa.teams = plan.teams;
@@ -784,6 +903,7 @@ FimoStatus launch_pipe(PipeArgs &pa, const WorldStepPlan &plan, uint64_t W, cons
         const unsigned segments = (pa.a.mask_words + kCompactThreads - 1) / kCompactThreads;
         k_compact_lists<kSet == 1><<<dim3(segments, (unsigned)W), kCompactThreads, 0, stream>>>(pa.a, pa.lvl_done);
         return check_launch("compact_lists");
+        }
     }
     auto kernel = k_world_step_pipe<T, kBlocks, false, kSet>;
     if (!allow_smem(kernel, plan.smem)) return check_launch("world_step (shared memory opt-in)");
@@ -821,7 +941,7 @@ FimoStatus world_step_launch(const WorldStepViews &v, const WorldStepPlan &plan,
             pa.flags = (pa.flags & ~kPipePrefetchBlocking) | (env[0] == '0' ? kPipeNoPrefetch : (env[0] == '2' ? kPipePrefetchBlocking : 0u));
         if (const char *env = std::getenv("FIMO_B200_PUBLISH"))
             if (env[0] == 'c') pa.flags |= kPipePublishPerChunk;
-        if (plan.set == 1) {
+        if (plan.set >= 1) {
             a.angvel = plane_of(v.angvel, FIMO_B200_SCOPE_ENTITY, 3, E, W, "angvel");
             a.gravity = plane_of(v.gravity, FIMO_B200_SCOPE_WORLD, 3, 1, W, "gravity");
             a.waabb = plane_of(v.waabb, FIMO_B200_SCOPE_ENTITY, 6, E, W, "waabb");
@@ -830,6 +950,26 @@ FimoStatus world_step_launch(const WorldStepViews &v, const WorldStepPlan &plan,
             if (!v.gstats->device_ptr || v.gstats->scope != FIMO_B200_SCOPE_BATCH || v.gstats->components != FIMO_B200_GSTAT_WORDS) throw Fail{"gstats"};
             a.gstats = (uint32_t *)v.gstats->device_ptr;
             a.bounds_keys = (int *)plan.bounds.get();
+        }
+        if (plan.set == 2) {
+            const uint64_t words = (E + 31) / 32;
+            a.damp = plane_of(v.damp, FIMO_B200_SCOPE_WORLD, 1, 1, W, "damp");
+            a.sleep_eps = plane_of(v.sleep_eps, FIMO_B200_SCOPE_WORLD, 1, 1, W, "sleep_eps");
+            a.campos = plane_of(v.campos, FIMO_B200_SCOPE_WORLD, 3, 1, W, "campos");
+            a.lod_dist2 = plane_of(v.lod_dist2, FIMO_B200_SCOPE_WORLD, 3, 1, W, "lod_dist2");
+            a.frustum2 = plane_of(v.frustum2, FIMO_B200_SCOPE_WORLD, 24, 1, W, "frustum2");
+            a.sleep = plane_of(v.sleep, FIMO_B200_SCOPE_ENTITY_BITS, 1, words, W, "sleep");
+            a.lod = plane_of(v.lod, FIMO_B200_SCOPE_ENTITY, 1, E, W, "lod");
+            a.vis_mask2 = plane_of(v.vis_mask2, FIMO_B200_SCOPE_ENTITY_BITS, 1, words, W, "vis_mask2");
+            a.vis_list2 = plane_of(v.vis_list2, FIMO_B200_SCOPE_ENTITY, 1, E, W, "vis_list2");
+            a.vis_count2 = plane_of(v.vis_count2, FIMO_B200_SCOPE_WORLD, 1, 1, W, "vis_count2");
+            a.vbounds = plane_of(v.vbounds, FIMO_B200_SCOPE_WORLD, 6, 1, W, "vbounds");
+            if (!v.stats2->device_ptr || v.stats2->scope != FIMO_B200_SCOPE_BATCH || v.stats2->components != 2 * FIMO_B200_STAT_WORDS) throw Fail{"stats2"};
+            if (!v.gstats2->device_ptr || v.gstats2->scope != FIMO_B200_SCOPE_BATCH || v.gstats2->components != FIMO_B200_GSTAT_WORDS) throw Fail{"gstats2"};
+            a.stats2 = (unsigned long long *)v.stats2->device_ptr;
+            a.scratch2 = (unsigned long long *)v.scratch2;
+            a.gstats2 = (uint32_t *)v.gstats2->device_ptr;
+            a.bounds_keys2 = (int *)plan.bounds2.get();
         }
         const int key = plan.threads * 100 + (int)plan.blocks_per_sm * 10 + (int)plan.set;
         switch (key) {
@@ -843,6 +983,10 @@ FimoStatus world_step_launch(const WorldStepViews &v, const WorldStepPlan &plan,
         case 25611: case 25621: return launch_pipe<256, 2, 1>(pa, plan, W, info);
         case 25631: return launch_pipe<256, 3, 1>(pa, plan, W, info);
         case 51211: return launch_pipe<512, 1, 1>(pa, plan, W, info);
+        case 12842: case 12832: case 12822: case 12812: return launch_pipe<128, 4, 2>(pa, plan, W, info);
+        case 25612: case 25622: return launch_pipe<256, 2, 2>(pa, plan, W, info);
+        case 25632: return launch_pipe<256, 3, 2>(pa, plan, W, info);
+        case 51212: return launch_pipe<512, 1, 2>(pa, plan, W, info);
         default: return fail("world_step plan");
         }
     } catch (const Fail &f) {

@@ -18,6 +18,7 @@
 //     enqueue, the completion thread performs the end-of-generation protocol;
 //   * host systems still run on the pool through a command buffer, exactly as in the reference.
 #include <algorithm>
+#include <cstdlib>
 #include <cstring>
 #include <deque>
 #include <memory>
@@ -850,8 +851,8 @@ bool build_device_executor(Group *g, const char **err) {
     };
     auto any = [](Member *) { return true; };
     auto arity = [](Member *m, size_t x, size_t s) { return m && m->type->exclusive.size() == x && m->type->shared.size() == s; };
-    std::vector<Member *> fused;
-    dev::WorldStepViews views{};
+    std::vector<Member *> fused, fused16; // fused16: the larger set (set 2), tried first
+    dev::WorldStepViews views{}, views16{};
     dev::WorldStepPlan plan{};
     Member *mc = nullptr; // the cull member: owner of the statistics scratch block
     if (!(g->ext_flags & FIMO_B200_GROUP_FLAG_NO_FUSION)) {
@@ -903,28 +904,64 @@ bool build_device_executor(Group *g, const char **err) {
                     if (mv) views.vel_clamp = true, views.vmax = view_of(g, mv->type->shared[0]);
                     fused = {mf, mi, ma, mp, mw, mc, mb, ms};
                     if (mv) fused.push_back(mv);
+                    // set 2: six more systems of the 16-system DAG that only touch data the kernel already holds
+                    ResourceType *angvel = ma->type->shared[0], *mask = mc->type->exclusive[0];
+                    Member *md = by_id(FIMO_B200_BUILTIN_ANGVEL_DAMP, [&](Member *m) { return arity(m, 1, 1) && m->type->exclusive[0] == angvel; });
+                    Member *msl = by_id(FIMO_B200_BUILTIN_SLEEP_FLAGS, [&](Member *m) { return arity(m, 1, 2) && m->type->shared[0] == vel; });
+                    Member *ml = by_id(FIMO_B200_BUILTIN_LOD, [&](Member *m) { return arity(m, 1, 3) && m->type->shared[0] == waabb; });
+                    Member *c2 = by_id(FIMO_B200_BUILTIN_CULL_WAABB, [&](Member *m) { return m != c8 && arity(m, 4, 2) && m->type->shared[0] == waabb; });
+                    Member *mvb = by_id(FIMO_B200_BUILTIN_VIS_BOUNDS, [&](Member *m) {
+                        return arity(m, 1, 2) && m->type->shared[0] == waabb && m->type->shared[1] == mask;
+                    });
+                    Member *ms2 = (c2 && mvb) ? by_id(FIMO_B200_BUILTIN_GROUP_STATS, [&](Member *m) {
+                        return m != ms && arity(m, 1, 2) && m->type->shared[0] == c2->type->exclusive[2] && m->type->shared[1] == mvb->type->exclusive[0];
+                    }) : nullptr;
+                    if (mv && md && msl && ml && c2 && mvb && ms2 && md->order < ma->order && mv->order < msl->order && mw->order < ml->order &&
+                        mw->order < c2->order && c8->order < mvb->order && c2->order < ms2->order && mvb->order < ms2->order) {
+                        views16 = views;
+                        views16.set = 2;
+                        views16.damp = view_of(g, md->type->shared[0]);
+                        views16.sleep = view_of(g, msl->type->exclusive[0]), views16.sleep_eps = view_of(g, msl->type->shared[1]);
+                        views16.lod = view_of(g, ml->type->exclusive[0]);
+                        views16.campos = view_of(g, ml->type->shared[1]), views16.lod_dist2 = view_of(g, ml->type->shared[2]);
+                        views16.vis_mask2 = view_of(g, c2->type->exclusive[0]), views16.vis_list2 = view_of(g, c2->type->exclusive[1]);
+                        views16.vis_count2 = view_of(g, c2->type->exclusive[2]), views16.stats2 = view_of(g, c2->type->exclusive[3]);
+                        views16.frustum2 = view_of(g, c2->type->shared[1]);
+                        views16.vbounds = view_of(g, mvb->type->exclusive[0]);
+                        views16.gstats2 = view_of(g, ms2->type->exclusive[0]);
+                        views16.scratch2 = ((dev::BuiltinState *)c2->state)->scratch;
+                        fused16 = fused;
+                        for (Member *m : {md, msl, ml, c2, mvb, ms2}) fused16.push_back(m);
+                    }
                 }
             }
             if (!fused.empty()) {
                 views.vis_mask = view_of(g, mc->type->exclusive[0]), views.vis_list = view_of(g, mc->type->exclusive[1]);
                 views.vis_count = view_of(g, mc->type->exclusive[2]), views.stats = view_of(g, mc->type->exclusive[3]);
+                views16.vis_mask = views.vis_mask, views16.vis_list = views.vis_list, views16.vis_count = views.vis_count, views16.stats = views.stats;
             }
         }
     }
     // convexity: an outside node may be before the fused set or after it, never both
-    std::vector<char> in_set(n, 0), pred(n, 0), succ(n, 0);
-    for (Member *m : fused) in_set[m->order] = 1;
-    if (!fused.empty())
-        for (size_t x = 0; x < n && !fused.empty(); x++) {
+    std::vector<char> in_set, pred, succ;
+    auto convex = [&](std::vector<Member *> &set) {
+        in_set.assign(n, 0), pred.assign(n, 0), succ.assign(n, 0);
+        for (Member *m : set) in_set[m->order] = 1;
+        for (size_t x = 0; x < n && !set.empty(); x++) {
             if (in_set[x]) continue;
             for (size_t f = 0; f < n; f++) {
                 if (!in_set[f]) continue;
                 if (reach[f][x]) pred[x] = 1;
                 if (reach[x][f]) succ[x] = 1;
             }
-            if (pred[x] && succ[x]) fused.clear();
+            if (pred[x] && succ[x]) set.clear();
         }
-    bool fuse = !fused.empty() && dev::world_step_plan(views, g->world->device, plan);
+        return !set.empty();
+    };
+    bool fuse = false;
+    if (!fused16.empty() && !std::getenv("FIMO_B200_NO_SET2") && convex(fused16) && dev::world_step_plan(views16, g->world->device, plan))
+        fuse = true, fused = fused16, views = views16;
+    if (!fuse) fuse = convex(fused) && dev::world_step_plan(views, g->world->device, plan);
 
     std::vector<dev::Node> nodes;
     auto system_node = [&](Member *m) {
