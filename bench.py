@@ -392,6 +392,7 @@ def run_e2e(rig, torch, np, abi, W, K, distributed, dist, world_size) -> dict:
             keep.append(t)
             so[name] = v
         pin_slots.append(si), pout_slots.append(so), fences.append(Fence(rig.lib))
+    io_slots = [(rig.io_list(pin_slots[i]), rig.io_list(pout_slots[i])) for i in range(DEPTH)]
     pipe = {"i": 0, "pending": [False] * DEPTH}
 
     def step_pipelined():
@@ -399,13 +400,14 @@ def run_e2e(rig, torch, np, abi, W, K, distributed, dist, world_size) -> dict:
         pipe["i"] += 1
         if pipe["pending"][slot]:
             fences[slot].wait()  # the result of the step that used this slot DEPTH steps ago has landed
-        for name, v in pin_slots[slot].items():
-            rig.upload_async(name, v)
-        rig.schedule(1, signal_last=False)
-        rig.download_async("stats", pout_slots[slot]["stats"])
         fences[slot].reset()
-        rig.download_async("vis_count", pout_slots[slot]["vis_count"], fences[slot])
+        rig.schedule_io(io_slots[slot][0], io_slots[slot][1], fences[slot])  # H2D inputs -> generation -> D2H result
         pipe["pending"][slot] = True
+
+    def step_io_sync():
+        fences[0].reset()
+        rig.schedule_io(io_slots[0][0], io_slots[0][1], fences[0])
+        fences[0].wait()
 
     def drain_pipeline():
         for slot in range(DEPTH):
@@ -433,18 +435,22 @@ def run_e2e(rig, torch, np, abi, W, K, distributed, dist, world_size) -> dict:
 
     psteps = max(steps, min(K, 200))
     dt_pipe = timed_pipelined(psteps)
-    dt_head = timed(step_headline, steps)
+    dt_head = timed(step_io_sync, steps)
+    dt_xfer = timed(step_headline, steps)
     head = {"value": world_size * W * psteps / dt_pipe, "unit": UNIT,
             "h2d_bytes_per_step": int(sum(v.nbytes for v in ins.values())),
             "d2h_bytes_per_step": int(sum(v.nbytes for v in outs.values())), "steps": psteps,
             "ms_per_step": 1e3 * dt_pipe / psteps,
             "inputs": "frustum + dt of every world from pinned host memory", "result": "stats + per-world visible counts",
-            "api": "fimo_b200_group_transfer (stream-ordered H2D) + system_group_schedule + fimo_b200_group_transfer (D2H) "
-                   f"with a completion fence per step; up to {DEPTH} steps in flight (each with its own pinned input/result "
-                   "slot), every result waited for inside the timed region",
+            "api": "fimo_b200_group_schedule_io: one C-ABI call per step = stream-ordered H2D of the step's inputs + one "
+                   f"generation + D2H of its result + completion fence; up to {DEPTH} steps in flight (each with its own pinned "
+                   "input/result slot), every result waited for inside the timed region",
             "in_flight": DEPTH,
             "sync_value": world_size * W * steps / dt_head, "sync_ms_per_step": 1e3 * dt_head / steps,
-            "sync_api": "same calls, one step in flight: the host waits for each step's result before it queues the next"}
+            "sync_api": "same call, one step in flight: the host waits for each step's result before it queues the next",
+            "transfer_value": world_size * W * steps / dt_xfer,
+            "transfer_api": "fimo_b200_group_transfer x2 (H2D) + system_group_schedule + fimo_b200_group_transfer x2 (D2H) + fence "
+                            "wait, one step in flight"}
     dt_lock = timed(step_locked, steps)
     head["locked_value"] = world_size * W * steps / dt_lock
     head["locked_api"] = "world_lock_resources + blocking fimo_b200_resource_upload/download + schedule + fence wait"

@@ -371,10 +371,15 @@ PRODUCT_SYMBOLS = [
     ("fimo_b200_group_device_ms", c_double, [c_void_p, POINTER(c_uint64)]),
     ("fimo_b200_group_span_ms", c_double, [c_void_p]),
     ("fimo_b200_group_transfer", FimoStatus, [c_void_p, c_void_p, c_void_p, c_uint32, POINTER(Fence)]),
+    ("fimo_b200_group_schedule_io", FimoStatus, [c_void_p, c_void_p, c_size_t, c_void_p, c_size_t, c_void_p, c_size_t, POINTER(Fence)]),
     ("fimo_b200_host_alloc", c_void_p, [c_size_t]),
     ("fimo_b200_host_free", None, [c_void_p]),
 ]
 TRANSFER_HOST_TO_DEVICE, TRANSFER_DEVICE_TO_HOST = 0, 1
+
+
+class StepTransfer(C.Structure):  # FimoB200_StepTransfer
+    _fields_ = [("resource", c_void_p), ("host", c_void_p)]
 
 # CPU-oracle-only helpers (tests / bench cpu_baseline only)
 ORACLE_SYMBOLS = [

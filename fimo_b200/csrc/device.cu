@@ -54,6 +54,7 @@ struct Completion {
     void (*done)(void *);
     void *user;
     bool generation = true; // false: a stream-ordered transfer (not part of the per-generation timers)
+    cudaEvent_t landed = nullptr; // a generation with result copies behind it: completes when they have landed
 };
 
 struct Completer {
@@ -128,7 +129,7 @@ void Completer::run() {
             pending.pop_front();
         }
         cudaSetDevice(c.ex->device);
-        ok(cudaEventSynchronize(c.end), "cudaEventSynchronize");
+        ok(cudaEventSynchronize(c.landed ? c.landed : c.end), "cudaEventSynchronize");
         float ms = 0.0f;
         const bool timed = c.generation && cudaEventElapsedTime(&ms, c.start, c.end) == cudaSuccess;
         if (c.generation && !timed) (void)cudaGetLastError();
@@ -149,6 +150,7 @@ void Completer::run() {
             ex->free_events.push_back(c.start);
         }
         ex->free_events.push_back(c.end);
+        if (c.landed) ex->free_events.push_back(c.landed);
         if (--ex->in_flight == 0) ex->idle_cv.notify_all();
     }
 }
@@ -335,20 +337,28 @@ bool executor_compile(Executor *ex, std::vector<Node> nodes, const FimoB200_Laun
     return true;
 }
 
-bool executor_launch(Executor *ex, void (*done)(void *), void *user) {
+bool executor_launch(Executor *ex, void (*done)(void *), void *user, const Copy *uploads, size_t n_up, const Copy *downloads,
+                     size_t n_down) {
     DeviceGuard guard(ex->device);
     Completion c{ex->take_event(), ex->take_event(), ex, done, user};
     if (!c.start || !c.end) return false;
+    if (n_down && !(c.landed = ex->take_event())) return false;
     {
         std::lock_guard<std::mutex> g(ex->m);
         ex->in_flight++;
     }
-    bool launched = ok(cudaEventRecord(c.start, ex->stream), "cudaEventRecord");
+    bool launched = true;
+    for (size_t i = 0; i < n_up && launched; i++) // this generation's inputs, in stream order in front of it
+        launched = ok(cudaMemcpyAsync(uploads[i].dst, uploads[i].src, uploads[i].bytes, cudaMemcpyHostToDevice, ex->stream), "cudaMemcpyAsync H2D");
+    launched = ok(cudaEventRecord(c.start, ex->stream), "cudaEventRecord") && launched;
     if (launched) {
         if (ex->use_graph) launched = ok(cudaGraphLaunch(ex->graph_exec, ex->stream), "cudaGraphLaunch");
         else launched = replay(ex, false);
     }
     launched = ok(cudaEventRecord(c.end, ex->stream), "cudaEventRecord") && launched;
+    for (size_t i = 0; i < n_down && launched; i++) // its results, behind it
+        launched = ok(cudaMemcpyAsync(downloads[i].dst, downloads[i].src, downloads[i].bytes, cudaMemcpyDeviceToHost, ex->stream), "cudaMemcpyAsync D2H");
+    if (c.landed) launched = ok(cudaEventRecord(c.landed, ex->stream), "cudaEventRecord") && launched;
     if (!launched) c.done = nullptr; // the caller reports the failure itself
     completer().post(c);
     return launched;

@@ -39,7 +39,15 @@ void executor_destroy(Executor *ex); // waits until idle
 bool executor_compile(Executor *ex, std::vector<Node> nodes, const FimoB200_LaunchInfo &info, bool use_graph);
 // Enqueue one generation.  `done(user)` runs on the completion thread once the device finished it
 // (never inside a CUDA callback, so it may take locks and wake futex waiters).
-bool executor_launch(Executor *ex, void (*done)(void *), void *user);
+// `uploads` are copied host -> HBM in front of the generation and `downloads` HBM -> host behind it, all in stream
+// order; with downloads, `done` runs once they have landed.
+struct Copy {
+    void *dst;
+    const void *src;
+    size_t bytes;
+};
+bool executor_launch(Executor *ex, void (*done)(void *), void *user, const Copy *uploads = nullptr, size_t n_up = 0,
+                     const Copy *downloads = nullptr, size_t n_down = 0);
 // Enqueue a stream-ordered copy between host memory and HBM behind everything launched so far.
 bool executor_transfer(Executor *ex, void *dst, const void *src, size_t bytes, bool to_device, void (*done)(void *), void *user);
 void *host_alloc_pinned(size_t bytes);

@@ -606,6 +606,8 @@ struct Job { // one scheduled generation (Job.zig:216-264 wraps SystemGroup.run 
     ResourceType *xfer_resource = nullptr;
     void *xfer_host = nullptr;
     bool xfer_to_device = false;
+    // fimo_b200_group_schedule_io: a generation with its own input copies in front and result copies behind
+    std::vector<std::pair<ResourceType *, void *>> io_up, io_down;
 };
 
 struct Group {
@@ -1227,9 +1229,22 @@ int start_device_generation(Group *g, Job *job, bool blocking, const char **err)
         }
         return 0;
     }
+    std::vector<dev::Copy> ups, downs;
+    for (int dir = 0; dir < 2; dir++)
+        for (auto &io : dir == 0 ? job->io_up : job->io_down) {
+            const FimoB200_ResourceView *view = view_of(g, io.first);
+            if (!view || !view->device_ptr) {
+                if (g->in_flight == 0) unlock_group_resources(g);
+                *err = "NotFound";
+                return -1;
+            }
+            const size_t bytes = view->world_stride * view->n_worlds;
+            if (dir == 0) ups.push_back(dev::Copy{view->device_ptr, io.second, bytes});
+            else downs.push_back(dev::Copy{io.second, view->device_ptr, bytes});
+        }
     g->in_flight++;
     DeviceDone *done = new DeviceDone{g, job->signal};
-    if (!dev::executor_launch(g->executor_dev, &device_generation_done, done)) {
+    if (!dev::executor_launch(g->executor_dev, &device_generation_done, done, ups.data(), ups.size(), downs.data(), downs.size())) {
         // The completion entry still drains through the completion thread (without `done`); undo here.
         delete done;
         if (--g->in_flight == 0) unlock_group_resources(g);
@@ -1328,11 +1343,22 @@ struct Transfer {
     bool to_device;
 };
 
+struct StepIo {
+    const FimoB200_StepTransfer *uploads;
+    size_t n_up;
+    const FimoB200_StepTransfer *downloads;
+    size_t n_down;
+};
+
 const char *group_schedule(Group *g, FimoWorldsMeta_Fence *const *wait_on, size_t n, FimoWorldsMeta_Fence *signal,
-                           const Transfer *xfer = nullptr) {
+                           const Transfer *xfer = nullptr, const StepIo *io = nullptr) {
     // SystemGroup.zig:430-452
     std::unique_lock<std::mutex> lock(g->m);
     Job *job = new Job{g, g->next_generation, std::vector<FimoWorldsMeta_Fence *>(wait_on, wait_on + n), signal};
+    if (io) {
+        for (size_t i = 0; i < io->n_up; i++) job->io_up.emplace_back((ResourceType *)io->uploads[i].resource, io->uploads[i].host);
+        for (size_t i = 0; i < io->n_down; i++) job->io_down.emplace_back((ResourceType *)io->downloads[i].resource, io->downloads[i].host);
+    }
     const size_t consumed = xfer ? 0 : 1; // a transfer rides between generations, it is not one
     if (xfer) job->xfer_resource = xfer->resource, job->xfer_host = xfer->host, job->xfer_to_device = xfer->to_device;
     g->next_generation += consumed;
@@ -1718,6 +1744,32 @@ FimoStatus fimo_b200_group_transfer(FimoWorldsMeta_SystemGroup *group, FimoWorld
     }
     const Transfer xfer{(ResourceType *)handle, host, direction == FIMO_B200_TRANSFER_HOST_TO_DEVICE};
     if (const char *err = group_schedule(g, nullptr, 0, signal, &xfer)) return report(err);
+    return FIMO_STATUS_OK;
+}
+FimoStatus fimo_b200_group_schedule_io(FimoWorldsMeta_SystemGroup *group, const FimoB200_StepTransfer *uploads, FimoUSize n_uploads,
+                                       const FimoB200_StepTransfer *downloads, FimoUSize n_downloads,
+                                       FimoWorldsMeta_Fence *const *wait_on, FimoUSize n_wait, FimoWorldsMeta_Fence *signal) {
+    Group *g = (Group *)group;
+    if ((n_uploads && !uploads) || (n_downloads && !downloads)) return report("InvalidArgument");
+    for (size_t i = 0; i < n_uploads; i++)
+        if (!uploads[i].resource || !uploads[i].host) return report("InvalidArgument");
+    for (size_t i = 0; i < n_downloads; i++)
+        if (!downloads[i].resource || !downloads[i].host) return report("InvalidArgument");
+    {
+        std::lock_guard<std::mutex> lock(g->m);
+        const char *err = nullptr;
+        if (g->dirty && g->in_flight == 0 && !compile(g, &err)) return report(err);
+        if (!g->has_device_systems) return report("NoDevice");
+        auto used = [&](FimoWorldsMeta_ResourceHandle h) {
+            return std::find(g->resources.begin(), g->resources.end(), (ResourceType *)h) != g->resources.end();
+        };
+        for (size_t i = 0; i < n_uploads; i++)
+            if (!used(uploads[i].resource)) return report("NotFound");
+        for (size_t i = 0; i < n_downloads; i++)
+            if (!used(downloads[i].resource)) return report("NotFound");
+    }
+    const StepIo io{uploads, n_uploads, downloads, n_downloads};
+    if (const char *err = group_schedule(g, wait_on, n_wait, signal, nullptr, &io)) return report(err);
     return FIMO_STATUS_OK;
 }
 void *fimo_b200_host_alloc(FimoUSize bytes) { return dev::host_alloc_pinned(bytes); }

@@ -470,6 +470,21 @@ class WorldStepRig:
         self.lib.check(self.lib.fimo_b200_group_transfer(self.group.handle, self.resources[name].handle, arr.ctypes.data,
                                                          abi.TRANSFER_DEVICE_TO_HOST, signal.ptr() if signal else None))
 
+    def io_list(self, arrays: dict[str, np.ndarray]):
+        """A FimoB200_StepTransfer array over whole-resource host buffers (build once, reuse every step)."""
+        items = (abi.StepTransfer * max(1, len(arrays)))()
+        for i, (name, arr) in enumerate(arrays.items()):
+            assert arr.dtype.itemsize == 4 and arr.flags["C_CONTIGUOUS"] and arr.shape == self.host[name].shape
+            items[i].resource = self.resources[name].handle
+            items[i].host = arr.ctypes.data
+        return items, len(arrays)
+
+    def schedule_io(self, uploads, downloads, signal: Fence | None = None) -> None:
+        """fimo_b200_group_schedule_io: one generation with its input copies in front and its result copies behind,
+        one call, one completion; `uploads` / `downloads` come from io_list()."""
+        self.lib.check(self.lib.fimo_b200_group_schedule_io(self.group.handle, uploads[0], uploads[1], downloads[0], downloads[1],
+                                                            None, 0, signal.ptr() if signal else None))
+
     def stats(self) -> np.ndarray:
         return self.download(("stats",))["stats"].reshape(-1).view(np.uint64)
 

@@ -661,6 +661,60 @@ typedef struct FimoB200_Export {
 } FimoB200_Export;
 FIMO_B200_EXPORT const FimoB200_Export *fimo_worlds_b200_exports(FimoUSize *count);
 
+/* The module record the fimo loader looks for.  The reference's loader `dlopen`s `module.fimo_module` and calls
+ * `fimo_impl_module_export_iterator` (pkgs/fimo_std/include/fimo_std/impl/module.h:40,61-62; Zig side
+ * pkgs/fimo_std/src/modules/exports.zig:2016-2044), which walks the pointers stored in the ELF section
+ * `fimo_module` (`__start_fimo_module` .. `__stop_fimo_module`, NULL entries skipped) and hands each
+ * `FimoModulesExport` (modules.h:942-1002) to the inspector.  This library embeds ONE such record: module
+ * "fimo_worlds", namespace import "fimo-tasks", symbol imports `futex_wait` / `futex_wake`
+ * (pkgs/fimo_tasks_meta/src/symbols.zig:132-160), and the 32 "fimo-worlds" symbols as static exports
+ * (the function pointers of the table above), versioned with the context version the build was given
+ * (-DFIMO_B200_CONTEXT_VERSION_{MAJOR,MINOR,PATCH}; default 0.2.0 = build.zig.zon of the reference).
+ * The structs below mirror modules.h / version.h byte for byte. */
+typedef struct FimoB200_Version { /* FimoVersion, version.h:14-22 */
+    FimoUSize major, minor, patch;
+    const char *pre;
+    FimoUSize pre_len;
+    const char *build;
+    FimoUSize build_len;
+} FimoB200_Version;
+typedef struct FimoB200_ModulesNamespaceImport { /* modules.h: FimoModulesNamespaceImport */
+    const char *name;
+} FimoB200_ModulesNamespaceImport;
+typedef struct FimoB200_ModulesSymbolImport { /* FimoModulesSymbolImport */
+    FimoB200_Version version;
+    const char *name;
+    const char *ns;
+} FimoB200_ModulesSymbolImport;
+typedef struct FimoB200_ModulesSymbolExport { /* FimoModulesSymbolExport */
+    const void *symbol;
+    int32_t linkage; /* FIMO_MODULES_SYMBOL_LINKAGE_GLOBAL = 0 */
+    FimoB200_Version version;
+    const char *name;
+    const char *ns;
+} FimoB200_ModulesSymbolExport;
+typedef struct FimoB200_ModulesExport { /* struct FimoModulesExport, modules.h:942-1002 */
+    const void *next;
+    FimoB200_Version version;
+    const char *name, *description, *author, *license;
+    const void *parameters;
+    FimoUSize parameters_count;
+    const void *resources;
+    FimoUSize resources_count;
+    const FimoB200_ModulesNamespaceImport *namespace_imports;
+    FimoUSize namespace_imports_count;
+    const FimoB200_ModulesSymbolImport *symbol_imports;
+    FimoUSize symbol_imports_count;
+    const FimoB200_ModulesSymbolExport *symbol_exports;
+    FimoUSize symbol_exports_count;
+    const void *dynamic_symbol_exports;
+    FimoUSize dynamic_symbol_exports_count;
+    const void *modifiers;
+    FimoUSize modifiers_count;
+} FimoB200_ModulesExport;
+typedef bool (*FimoB200_ModuleInspector)(const FimoB200_ModulesExport *module, void *data);
+FIMO_B200_EXPORT void fimo_impl_module_export_iterator(FimoB200_ModuleInspector inspector, void *data);
+
 /* Name of the error behind the last FIMO_STATUS_ERROR on this thread
  * ("NotFound", "Deadlock", "Duplicate", "InUse", "InitError", "OutOfMemory", ...).
  * Stand-in for the thread-local context result (pkgs/fimo_std/src/ctx.zig:184-186). */
@@ -714,6 +768,22 @@ enum { FIMO_B200_TRANSFER_HOST_TO_DEVICE = 0, FIMO_B200_TRANSFER_DEVICE_TO_HOST 
 FIMO_B200_EXPORT FimoStatus fimo_b200_group_transfer(FimoWorldsMeta_SystemGroup *group,
                                                      FimoWorldsMeta_ResourceHandle handle, void *host,
                                                      uint32_t direction, FimoWorldsMeta_Fence *signal);
+/* One generation with its own host inputs and host results — system_group_schedule (symbols.zig:150-166,
+ * SystemGroup.zig:430-452) bracketed by stream-ordered copies: `uploads` are copied host -> HBM in front of the
+ * generation, `downloads` HBM -> host behind it, all on the group's stream in this order and ordered with every
+ * other generation / transfer of the group.  It consumes one generation number; `signal` (nullable) fires once
+ * the generation has completed AND the downloads have landed.  Buffers follow fimo_b200_group_transfer's rules
+ * (whole resource, valid until `signal`; pinned memory for asynchronous copies).  Several such steps may be in
+ * flight; each needs its own host buffers. */
+typedef struct FimoB200_StepTransfer {
+    FimoWorldsMeta_ResourceHandle resource;
+    void *host;
+} FimoB200_StepTransfer;
+FIMO_B200_EXPORT FimoStatus fimo_b200_group_schedule_io(FimoWorldsMeta_SystemGroup *group,
+                                                        const FimoB200_StepTransfer *uploads, FimoUSize n_uploads,
+                                                        const FimoB200_StepTransfer *downloads, FimoUSize n_downloads,
+                                                        FimoWorldsMeta_Fence *const *wait_on, FimoUSize n_wait,
+                                                        FimoWorldsMeta_Fence *signal);
 FIMO_B200_EXPORT void *fimo_b200_host_alloc(FimoUSize bytes); /* page-locked host memory; NULL on failure */
 FIMO_B200_EXPORT void fimo_b200_host_free(void *ptr);
 

@@ -212,6 +212,46 @@ def test_stream_ordered_transfers_match_locked_host_access(oracle, product):
     assert not problems, "\n".join(problems)
 
 
+def test_schedule_io_steps_in_flight_match_oracle(oracle, product):
+    """fimo_b200_group_schedule_io: generations with their own input uploads and result downloads, several in
+    flight, each with its own host buffers: every step's downloaded result equals the oracle's after the same
+    uploads, and generation numbers advance by one per call."""
+    from fimo_b200.worlds import Fence
+
+    W, E, D, K = 8, 512, 4, 6
+    data = synth.generate(W, E, D)
+    frusta = [synth.generate(W, E, D, world0=100 * (i + 1))["frustum"] for i in range(K)]
+    ref = synth.WorldStepRig(oracle, W, E, D, data={k: v.copy() for k, v in data.items()})
+    want = []
+    try:
+        for i in range(K):
+            ref.upload("frustum", frusta[i])
+            ref.step(1)
+            want.append(ref.download(("vis_count", "stats", "vis_mask")))
+    finally:
+        ref.close()
+    rig = synth.WorldStepRig(product, W, E, D, data={k: v.copy() for k, v in data.items()})
+    try:
+        gen0 = rig.group.generation() if hasattr(rig.group, "generation") else None
+        fences = [Fence(product) for _ in range(K)]
+        got = [{n: np.empty_like(rig.host[n]) for n in ("vis_count", "stats", "vis_mask")} for _ in range(K)]
+        lists = []
+        for i in range(K):  # all K steps queued before any is waited for
+            up, down = rig.io_list({"frustum": frusta[i]}), rig.io_list(got[i])
+            lists.append((up, down))
+            rig.schedule_io(up, down, fences[i])
+        for f in fences:
+            f.wait()
+        for i in range(K):
+            problems = synth.compare_outputs(got[i], want[i], 0.0)
+            assert not problems, f"step {i}:\n" + "\n".join(problems)
+        assert rig.stats()[abi.STAT_STEPS] == W * K
+        if gen0 is not None:
+            assert rig.group.generation() == gen0 + K
+    finally:
+        rig.close()
+
+
 DAG_CASES = [
     # (dag, worlds, entities, depth, steps)
     ("dag8", 1, 1024, 4, 8),

@@ -34,6 +34,73 @@ def test_export_table_lists_the_32_fimo_worlds_symbols_in_order(lib):
         assert fn == C.cast(getattr(lib.dll, "fimo_worlds_" + name), C.c_void_p).value
 
 
+class _Version(C.Structure):  # FimoVersion, version.h:14-22
+    _fields_ = [("major", C.c_size_t), ("minor", C.c_size_t), ("patch", C.c_size_t), ("pre", C.c_char_p), ("pre_len", C.c_size_t),
+                ("build", C.c_char_p), ("build_len", C.c_size_t)]
+
+
+class _SymbolImport(C.Structure):  # FimoModulesSymbolImport
+    _fields_ = [("version", _Version), ("name", C.c_char_p), ("ns", C.c_char_p)]
+
+
+class _SymbolExport(C.Structure):  # FimoModulesSymbolExport
+    _fields_ = [("symbol", C.c_void_p), ("linkage", C.c_int32), ("version", _Version), ("name", C.c_char_p), ("ns", C.c_char_p)]
+
+
+class _NamespaceImport(C.Structure):
+    _fields_ = [("name", C.c_char_p)]
+
+
+class _ModuleExport(C.Structure):  # struct FimoModulesExport, modules.h:942-1002
+    _fields_ = [("next", C.c_void_p), ("version", _Version), ("name", C.c_char_p), ("description", C.c_char_p), ("author", C.c_char_p),
+                ("license", C.c_char_p), ("parameters", C.c_void_p), ("parameters_count", C.c_size_t), ("resources", C.c_void_p),
+                ("resources_count", C.c_size_t), ("namespace_imports", C.POINTER(_NamespaceImport)), ("namespace_imports_count", C.c_size_t),
+                ("symbol_imports", C.POINTER(_SymbolImport)), ("symbol_imports_count", C.c_size_t),
+                ("symbol_exports", C.POINTER(_SymbolExport)), ("symbol_exports_count", C.c_size_t),
+                ("dynamic_symbol_exports", C.c_void_p), ("dynamic_symbol_exports_count", C.c_size_t), ("modifiers", C.c_void_p),
+                ("modifiers_count", C.c_size_t)]
+
+
+def test_module_record_in_the_fimo_module_section(lib):
+    """What the fimo loader does with `module.fimo_module` (impl/module.h:40,61-62; exports.zig:2016-2044): iterate the
+    `fimo_module` section; exactly one record, exporting the 32 fimo-worlds symbols and importing the futex symbols."""
+    import subprocess
+
+    path = os.path.join(ROOT, "fimo_b200", "libfimo_worlds_b200.so")
+    sections = subprocess.run(["readelf", "-S", "-W", path], capture_output=True, text=True).stdout
+    assert re.search(r"\bfimo_module\s+PROGBITS", sections), "no fimo_module ELF section"
+    inspector_t = C.CFUNCTYPE(C.c_bool, C.POINTER(_ModuleExport), C.c_void_p)
+    seen = []
+
+    def inspect(module, _data):
+        m = module.contents
+        seen.append({
+            "name": m.name.decode(), "version": (m.version.major, m.version.minor, m.version.patch), "next": m.next,
+            "namespaces": [m.namespace_imports[i].name.decode() for i in range(m.namespace_imports_count)],
+            "imports": [(m.symbol_imports[i].name.decode(), m.symbol_imports[i].ns.decode()) for i in range(m.symbol_imports_count)],
+            "exports": [(m.symbol_exports[i].name.decode(), m.symbol_exports[i].ns.decode(), m.symbol_exports[i].symbol,
+                         m.symbol_exports[i].linkage) for i in range(m.symbol_exports_count)],
+            "dynamic": m.dynamic_symbol_exports_count, "modifiers": m.modifiers_count,
+        })
+        return True
+
+    fn = lib.dll.fimo_impl_module_export_iterator
+    fn.restype, fn.argtypes = None, [inspector_t, C.c_void_p]
+    fn(inspector_t(inspect), None)
+    assert len(seen) == 1  # the NULL entry of the section is skipped
+    m = seen[0]
+    assert m["name"] == "fimo_worlds" and m["next"] is None and m["dynamic"] == 0 and m["modifiers"] == 0
+    assert m["namespaces"] == ["fimo-tasks"]
+    assert m["imports"] == [("futex_wait", "fimo-tasks"), ("futex_wake", "fimo-tasks")]  # fimo_tasks_meta symbols.zig:132-160
+    assert [e[0] for e in m["exports"]] == [name for name, _, _ in abi.WORLDS_SYMBOLS]
+    assert all(e[1] == "fimo-worlds" and e[3] == 0 for e in m["exports"])
+    table = {name: fn for name, _, fn in lib.exports()}
+    assert all(e[2] == table[e[0]] for e in m["exports"])
+    stopped = []
+    fn(inspector_t(lambda module, _d: bool(stopped.append(1))), None)  # returning false stops the iteration
+    assert stopped == [1]
+
+
 def test_no_cpu_fallback_for_batch_worlds(lib):
     """Without a CUDA device a batch world must fail loudly, not degrade to a CPU path."""
     import torch
