@@ -178,22 +178,28 @@ def run_b200(args) -> None:
     # End-of-step statistics all-reduce (the path's only collective): after every generation a 64-byte
     # snapshot is taken in stream order, then reduced over NCCL on a side stream so that it overlaps the
     # next generation.  Buffers rotate; the group's stream never waits for the collective.
-    snaps = [torch.zeros(abi.STAT_WORDS, dtype=torch.int64, device="cuda") for _ in range(4)]
+    snaps = [torch.zeros(abi.STAT_WORDS, dtype=torch.int64, device="cuda") for _ in range(8)]
     side = torch.cuda.Stream()
+    copied = [torch.cuda.Event() for _ in snaps]   # snapshot i has been taken (group stream)
+    reduced = [torch.cuda.Event() for _ in snaps]  # snapshot i has been all-reduced (side stream)
     state = {"ext": None, "n": 0, "stats_ptr": None}
 
     def post_step(_user, stream, generation):
         if state["ext"] is None:
             state["ext"] = torch.cuda.ExternalStream(stream, device=torch.device("cuda", local_rank))
-        buf = snaps[state["n"] % len(snaps)]
+        ext = state["ext"]
+        i = state["n"] % len(snaps)
+        buf = snaps[i]
+        if state["n"] >= len(snaps):
+            ext.wait_event(reduced[i])  # the buffer is reused: its previous all-reduce must have finished
         state["n"] += 1
-        with torch.cuda.stream(state["ext"]):
+        with torch.cuda.stream(ext):
             buf.copy_(state["stats"], non_blocking=True)
-            ev = torch.cuda.Event()
-            ev.record()
-        side.wait_event(ev)
+        copied[i].record(ext)
+        side.wait_event(copied[i])
         with torch.cuda.stream(side):
             dist.all_reduce(buf)
+        reduced[i].record(side)
 
     options = synth.RigOptions(fused=not args.no_fusion, device=local_rank)
     rig = synth.WorldStepRig(lib, W, E, D, data=data, options=options,
