@@ -380,6 +380,16 @@ bool executor_transfer(Executor *ex, void *dst, const void *src, size_t bytes, b
     return queued;
 }
 
+bool enqueue_host_node(void *stream, const Copy *d2h, size_t n_d2h, void (*fn)(void *), void *user, const Copy *h2d, size_t n_h2d) {
+    cudaStream_t s = (cudaStream_t)stream;
+    for (size_t i = 0; i < n_d2h; i++)
+        if (!ok(cudaMemcpyAsync(d2h[i].dst, d2h[i].src, d2h[i].bytes, cudaMemcpyDeviceToHost, s), "cudaMemcpyAsync D2H (mirror)")) return false;
+    if (!ok(cudaLaunchHostFunc(s, fn, user), "cudaLaunchHostFunc")) return false;
+    for (size_t i = 0; i < n_h2d; i++)
+        if (!ok(cudaMemcpyAsync(h2d[i].dst, h2d[i].src, h2d[i].bytes, cudaMemcpyHostToDevice, s), "cudaMemcpyAsync H2D (mirror)")) return false;
+    return true;
+}
+
 void *host_alloc_pinned(size_t bytes) {
     void *p = nullptr;
     if (!ok(cudaHostAlloc(&p, bytes ? bytes : 1, cudaHostAllocDefault), "cudaHostAlloc")) return nullptr;

@@ -50,6 +50,10 @@ bool executor_launch(Executor *ex, void (*done)(void *), void *user, const Copy 
                      const Copy *downloads = nullptr, size_t n_down = 0);
 // Enqueue a stream-ordered copy between host memory and HBM behind everything launched so far.
 bool executor_transfer(Executor *ex, void *dst, const void *src, size_t bytes, bool to_device, void (*done)(void *), void *user);
+// A host system inside a device group: `d2h` copies (HBM -> pinned mirrors) in front, `fn(user)` as a host node
+// (cudaLaunchHostFunc — also under stream capture, where it becomes a host node of the CUDA graph), `h2d` copies
+// (mirrors -> HBM) behind, all in stream order on `stream`.  `fn` must not call the CUDA API.
+bool enqueue_host_node(void *stream, const Copy *d2h, size_t n_d2h, void (*fn)(void *), void *user, const Copy *h2d, size_t n_h2d);
 void *host_alloc_pinned(size_t bytes);
 void host_free_pinned(void *p);
 void executor_wait_idle(Executor *ex);

@@ -316,6 +316,7 @@ struct Instance { // World.zig:28-32
     void *blob = nullptr; // host blob; for a device resource: the FimoB200_ResourceView
     std::atomic<size_t> references{0};
     size_t hbm_bytes = 0;
+    void *mirror = nullptr; // pinned host copy of a device resource, made when a host system of a device group uses it
 };
 
 struct World {
@@ -455,6 +456,7 @@ const char *world_remove_resource(World *w, ResourceType *type, void *value) {
         if (host_dst && inst->hbm_bytes && !dev::hbm_download(w->device, host_dst, view->device_ptr, inst->hbm_bytes))
             err = "DeviceError";
         if (!(view->flags & FIMO_B200_VIEW_FLAG_EXTERNAL)) dev::hbm_free(w->device, view->device_ptr);
+        if (inst->mirror) dev::host_free_pinned(inst->mirror);
         view->host_ptr = host_dst;
     }
     std::memcpy(value, inst->blob, type->size);
@@ -797,6 +799,68 @@ uint64_t algorithmic_bytes(Group *g) {
     return total;
 }
 
+// A host system inside a device group.  It runs where the reference runs every system — as a task on
+// the group's pool (SystemContext.run, SystemContext.zig:91-100) — started from a host node of the generation's CUDA
+// graph, so it is ordered with the device systems by the same DAG edges.  Device resources it uses appear to it as
+// `FimoB200_ResourceView::host_ptr`: a pinned mirror, refreshed (HBM -> host) in front of the system and, for the
+// resources it holds exclusively, written back (host -> HBM) behind it.
+void member_run_from_stream(void *user) {
+    Member *m = (Member *)user;
+    Group *g = m->group;
+    FimoTasksMeta_CommandBufferEntry entry{};
+    entry.type = FIMO_TASKS_META_COMMAND_BUFFER_ENTRY_TYPE_ENQUEUE_TASK;
+    entry.payload.enqueue_task = &m->task;
+    FimoTasksMeta_CommandBuffer buffer{};
+    buffer.label = m->type->label.data();
+    buffer.label_len = m->type->label.size();
+    buffer.entries = &entry;
+    buffer.entries_len = 1;
+    FimoTasksMeta_CommandBufferHandle handle{};
+    if (g->executor.vtable->enqueue_buffer(g->executor.data, &buffer, &handle) != FIMO_STATUS_OK)
+        panic("enqueue of a host system of a device group failed");
+    handle.vtable->wait_on(handle.data);
+    handle.vtable->release(handle.data);
+}
+
+void *ensure_mirror(World *w, ResourceType *type) {
+    w->lock.lock_read();
+    auto it = w->resources.find(type);
+    Instance *inst = it == w->resources.end() ? nullptr : it->second;
+    w->lock.unlock_read();
+    if (!inst || !type->on_device) return nullptr;
+    FimoB200_ResourceView *view = (FimoB200_ResourceView *)inst->blob;
+    if (!inst->mirror) {
+        inst->mirror = dev::host_alloc_pinned(inst->hbm_bytes);
+        view->host_ptr = inst->mirror; // the group holds the resource exclusively whenever a system looks at the view
+    }
+    return inst->mirror;
+}
+
+bool host_node(Group *g, Member *m, dev::Node &node, const char **err) {
+    std::vector<dev::Copy> in, out;
+    auto add = [&](ResourceType *r, bool exclusive) {
+        if (!r->on_device) return true;
+        const FimoB200_ResourceView *view = view_of(g, r);
+        void *mirror = ensure_mirror(g->world, r);
+        if (!view || !view->device_ptr || !mirror) return false;
+        const size_t bytes = view->world_stride * view->n_worlds;
+        in.push_back(dev::Copy{mirror, view->device_ptr, bytes});
+        if (exclusive) out.push_back(dev::Copy{view->device_ptr, mirror, bytes});
+        return true;
+    };
+    for (ResourceType *r : m->type->exclusive)
+        if (!add(r, true)) return *err = "OutOfMemory", false;
+    for (ResourceType *r : m->type->shared)
+        if (!add(r, false)) return *err = "OutOfMemory", false;
+    node.launch = [m, in, out](const FimoB200_LaunchInfo *info) {
+        return dev::enqueue_host_node(info->stream, in.data(), in.size(), &member_run_from_stream, m, out.data(), out.size())
+                       ? FIMO_STATUS_OK
+                       : FIMO_STATUS_ERROR;
+    };
+    node.kernels = 0;
+    return true;
+}
+
 bool build_device_executor(Group *g, const char **err) {
     // Emits the true DAG: node j depends on node i (i earlier in rank order) if j names i as an
     // explicit predecessor or they conflict on a resource (W/W, R/W, W/R) — the same ordering
@@ -867,7 +931,7 @@ bool build_device_executor(Group *g, const char **err) {
             views.scale = view_of(g, mp->type->shared[2]), views.parent = view_of(g, mp->type->shared[3]);
             views.level_start = view_of(g, mp->type->shared[4]);
             Member *c3 = by_id(FIMO_B200_BUILTIN_CULL, [&](Member *m) { return arity(m, 4, 4) && m->type->shared[0] == world; });
-            if (n == 3 && c3 && mp->order < c3->order) {
+            if (c3 && mp->order < c3->order) {
                 mc = c3;
                 views.aabb_c = view_of(g, mc->type->shared[1]), views.aabb_h = view_of(g, mc->type->shared[2]);
                 views.frustum = view_of(g, mc->type->shared[3]);
@@ -966,8 +1030,13 @@ bool build_device_executor(Group *g, const char **err) {
     if (!fuse) fuse = convex(fused) && dev::world_step_plan(views, g->world->device, plan);
 
     std::vector<dev::Node> nodes;
+    bool nodes_ok = true;
     auto system_node = [&](Member *m) {
         dev::Node node;
+        if (!m->type->device_entry) { // a host system of this device group
+            if (!host_node(g, m, node, err)) nodes_ok = false;
+            return node;
+        }
         const size_t n_ex = m->type->exclusive.size();
         node.launch = [m, n_ex](const FimoB200_LaunchInfo *info) {
             const FimoB200_ResourceView *const *blobs = (const FimoB200_ResourceView *const *)m->blobs.data();
@@ -978,8 +1047,6 @@ bool build_device_executor(Group *g, const char **err) {
             node.kernels = dev::builtin_propagate_kernels(view_of(g, m->type->exclusive[0]), view_of(g, m->type->shared[4]));
         return node;
     };
-    for (Member *m : g->order)
-        if (!m->type->device_entry) return *err = "MixedGroup", false;
     if (fuse) {
         // new order: everything that is not after the fused set (original order), the fused node, the rest
         std::vector<int> index(n, -1);
@@ -1012,11 +1079,13 @@ bool build_device_executor(Group *g, const char **err) {
             nodes.push_back(std::move(node));
         }
     }
+    if (!nodes_ok) return false;
     if (!g->executor_dev) g->executor_dev = dev::executor_create(g->world->device);
     if (!g->executor_dev) return *err = "DeviceError", false;
     g->info = FimoB200_ExecutorInfo{};
     g->info.systems = (uint32_t)n;
-    g->info.device_systems = (uint32_t)n;
+    g->info.device_systems = 0;
+    for (Member *m : g->order) g->info.device_systems += m->type->device_entry ? 1u : 0u;
     g->info.nodes = (uint32_t)nodes.size();
     g->info.fused_world_step = fuse ? 1u : 0u;
     g->info.edges = edges;
@@ -1076,7 +1145,9 @@ bool compile(Group *g, const char **err) {
         m->deferred_deps.clear(); // :184-191
         for (auto &e : m->type->before)
             if (!e.second.ignore_deferred)
-                if (Member *dep = g->find(e.first)) m->deferred_deps.push_back(dep);
+                if (Member *dep = g->find(e.first))
+                    if (!(m->type->device_entry || dep->type->device_entry)) // device work is ordered by the stream, not by fences
+                        m->deferred_deps.push_back(dep);
         m->type->links_lock.unlock_read();
         m->blobs.assign(m->type->exclusive.size() + m->type->shared.size(), nullptr);
         m->order = (size_t)-1;
@@ -1141,7 +1212,6 @@ bool compile(Group *g, const char **err) {
     g->info = FimoB200_ExecutorInfo{};
     g->info.systems = (uint32_t)g->order.size();
     if (g->has_device_systems) {
-        if (g->has_host_systems) return *err = "MixedGroup", false; // host + device systems in one group: not yet
         if (g->world->device < 0) return *err = "NoDevice", false;
         g->compiled_epoch = g->world->resource_epoch.load(std::memory_order_acquire);
         if (!snapshot_blobs(g)) return *err = "NotFound", false;

@@ -286,8 +286,8 @@ class WorldStepRig:
 
     def __init__(self, lib: abi.WorldsLib, n_worlds: int, entities: int, depth: int, world0: int = 0,
                  options: RigOptions | None = None, data: dict[str, np.ndarray] | None = None, pool: abi.Pool | None = None,
-                 post_step=None, dag: str = "chain3"):
-        assert dag in DAGS
+                 post_step=None, dag: str = "chain3", host_systems: bool = False):
+        assert dag in DAGS and not (host_systems and dag != "chain3")
         self.lib, self.W, self.E, self.depth, self.dag = lib, n_worlds, entities, depth, dag
         self.opt = options or RigOptions()
         self.on_device = lib.is_product
@@ -331,6 +331,8 @@ class WorldStepRig:
             cull = sysdef("cull", abi.BUILTIN_CULL, [R["vis_mask"], R["vis_list"], R["vis_count"], R["stats"]],
                           [R["world"], R["aabb_c"], R["aabb_h"], R["frustum"]], before=[propagate])
             self.systems = [integrate, propagate, cull]
+            if host_systems:
+                self.systems += self._host_systems(cull)
         else:
             # 8-system fan-out / fan-in DAG: forces -> integrate_lin || integrate_ang -> propagate ->
             # world_aabb -> { cull || bounds_reduce } -> group_stats
@@ -369,6 +371,59 @@ class WorldStepRig:
         self.group.add_systems(self.systems)
         self._fence = Fence(lib)
         self.closed = False
+
+    def _host_systems(self, cull):
+        """Two ordinary host systems (`system_run` callbacks on the pool) in the same group as the device systems
+        (SURVEY.md §8 f2): `host_camera` writes the frusta every generation (X: frustum — ordered before `cull` by the
+        W/R conflict alone), `host_census` reads the per-world visible counts after `cull` (S: vis_count, explicit
+        dependency) into a plain host resource.  Both see device resources as `ResourceView.host_ptr`: the data
+        itself on the CPU oracle, a coherent pinned mirror on the product."""
+        class Census(C.Structure):
+            _fields_ = [("visible", C.c_uint64), ("generations", C.c_uint64), ("last", C.c_uint64)]
+
+        self.Census = Census
+        census = Resource.register(self.lib, "census", C.sizeof(Census), 8)
+        census.add_to_world(self.world, Census(0, 0, 0))
+        self.resources["census"] = census
+        self.host_errors: list = []
+
+        def words(blob_ptr, dtype):
+            view = C.cast(blob_ptr, C.POINTER(abi.ResourceView)).contents
+            n = view.n_worlds * view.components * view.count
+            return np.ctypeslib.as_array(C.cast(view.host_ptr, C.POINTER(C.c_uint32)), shape=(n,)).view(dtype).reshape(
+                view.n_worlds, view.components, view.count)
+
+        def run_camera(_ctx, ex, _sh, _fence):
+            try:
+                fr = words(ex[0], np.float32)
+                fr[...] = np.roll(fr, 1, axis=0)  # every world takes its neighbour's camera
+            except Exception as e:  # noqa: BLE001 - reported by the test, never swallowed
+                self.host_errors.append(e)
+
+        def run_census(_ctx, ex, sh, _fence):
+            try:
+                c = C.cast(ex[0], C.POINTER(Census)).contents
+                last = int(words(sh[0], np.uint32).sum())
+                c.visible += last
+                c.generations += 1
+                c.last = last
+            except Exception as e:  # noqa: BLE001
+                self.host_errors.append(e)
+
+        R = self.resources
+        camera = System.register(self.lib, "host_camera", run=run_camera, exclusive=[R["frustum"]])
+        counted = System.register(self.lib, "host_census", run=run_census, exclusive=[census], shared=[R["vis_count"]], before=[cull])
+        self._registered += [camera, counted]
+        return [camera, counted]
+
+    def census(self):
+        """The host resource `host_census` writes (locked shared, copied out)."""
+        ptr = self.resources["census"].lock_in_world(self.world, False)
+        try:
+            c = C.cast(ptr, C.POINTER(self.Census)).contents
+            return int(c.visible), int(c.generations), int(c.last)
+        finally:
+            self.resources["census"].unlock_in_world(self.world, False)
 
     def _system(self, label, builtin, exclusive, shared, before=()):
         desc = abi.SystemDescriptor()

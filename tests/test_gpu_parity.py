@@ -252,6 +252,41 @@ def test_schedule_io_steps_in_flight_match_oracle(oracle, product):
         rig.close()
 
 
+@pytest.mark.parametrize("mode", ["fused", "graph", "streams"])
+@pytest.mark.parametrize("W,E,D,steps", [(16, 1024, 4, 6), (40, 260, 5, 4), (3, 8192, 8, 3)])
+def test_mixed_host_and_device_systems_match_oracle(oracle, product, W, E, D, steps, mode):
+    """host systems (plain `system_run` callbacks on the pool) and device systems in ONE group.
+    `host_camera` rewrites every world's frustum before `cull` (ordered by the W/R resource conflict only) and
+    `host_census` sums the per-world visible counts after `cull` into a host resource.  On the product the host
+    systems run from host nodes of the generation's CUDA graph and see pinned mirrors of the device resources;
+    every output, the rewritten frusta and the census equal the CPU oracle's."""
+    data = synth.generate(W, E, D)
+    names = synth.OUTPUTS + ("frustum",)
+    ref = synth.WorldStepRig(oracle, W, E, D, data={k: v.copy() for k, v in data.items()}, host_systems=True)
+    try:
+        ref.step(steps)
+        want, want_census = ref.download(names), ref.census()
+        assert not ref.host_errors, ref.host_errors
+    finally:
+        ref.close()
+    opts = synth.RigOptions(fused=(mode == "fused"), graph=(mode != "streams"))
+    dev = synth.WorldStepRig(product, W, E, D, data={k: v.copy() for k, v in data.items()}, options=opts, host_systems=True)
+    try:
+        info = dev.executor_info()
+        dev.step(steps)
+        got, got_census = dev.download(names), dev.census()
+        assert not dev.host_errors, dev.host_errors
+    finally:
+        dev.close()
+    assert info.systems == 5 and info.device_systems == 3
+    assert info.nodes == (3 if mode == "fused" and E % 4 == 0 else 5)  # camera -> fused world-step -> census
+    assert info.fused_world_step == (1 if mode == "fused" else 0)
+    problems = synth.compare_outputs(got, want, FLOAT_RTOL)
+    assert not problems, "\n".join(problems)
+    assert got_census == want_census and got_census[1] == steps
+    assert got_census[2] == int(got["vis_count"].sum())
+
+
 DAG_CASES = [
     # (dag, worlds, entities, depth, steps)
     ("dag8", 1, 1024, 4, 8),

@@ -61,3 +61,20 @@ def test_oracle_chain_properties(oracle):
     # integrate is K fused multiply-adds pos = fma(vel, dt, pos)
     d0 = synth.generate(5, 300, 4)
     assert synth.integrate_matches(d0["pos"], d0["vel"], 4, out["pos"])
+
+
+def test_host_systems_in_the_chain_on_the_oracle(oracle):
+    """The mixed-group rig on the CPU oracle: host_camera rolls the frusta once per generation, host_census runs
+    after cull and sums exactly the counts cull just wrote."""
+    W, E, D, K = 6, 256, 4, 3
+    data = synth.generate(W, E, D)
+    rig = synth.WorldStepRig(oracle, W, E, D, data={k: v.copy() for k, v in data.items()}, host_systems=True)
+    try:
+        rig.step(K)
+        out = rig.download(("frustum", "vis_count"))
+        visible, generations, last = rig.census()
+        assert not rig.host_errors, rig.host_errors
+    finally:
+        rig.close()
+    assert generations == K and last == int(out["vis_count"].sum()) and visible >= last
+    assert np.array_equal(out["frustum"], np.roll(data["frustum"], K, axis=0))
