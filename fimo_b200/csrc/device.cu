@@ -9,8 +9,10 @@
 // does it with a timeline semaphore).
 #include <cuda_runtime.h>
 
+#include <algorithm>
 #include <atomic>
 #include <condition_variable>
+#include <cstdlib>
 #include <deque>
 #include <mutex>
 #include <string>
@@ -337,6 +339,70 @@ bool executor_compile(Executor *ex, std::vector<Node> nodes, const FimoB200_Laun
     return true;
 }
 
+// ---- small host <-> HBM copies as ONE kernel --------------------------------------------------------------------
+// A copy-engine transfer costs ~8-10 us of stream time whatever its size; the per-step inputs / results of
+// fimo_b200_group_schedule_io are a handful of small resources (frusta, dt, counts, statistics).  When every host
+// buffer is page-locked (so the GPU can address it, UVA) the whole batch is moved by one kernel launch that
+// reads / writes host memory over PCIe directly: 128-bit accesses, all requests in flight at once.
+namespace {
+constexpr int kIoMaxCopies = 8;
+constexpr size_t kIoMaxBytes = 8u << 20; // beyond this the copy engine wins
+struct IoBatch {
+    void *dst[kIoMaxCopies];
+    const void *src[kIoMaxCopies];
+    unsigned long long bytes[kIoMaxCopies];
+};
+__global__ void __launch_bounds__(256) k_io_copy(const IoBatch b) {
+    const int c = blockIdx.y;
+    const unsigned long long bytes = b.bytes[c];
+    const size_t stride = (size_t)gridDim.x * blockDim.x, first = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if ((((uintptr_t)b.dst[c] | (uintptr_t)b.src[c] | bytes) & 15u) == 0) {
+        uint4 *dst = (uint4 *)b.dst[c];
+        const uint4 *src = (const uint4 *)b.src[c];
+        for (size_t i = first; i < bytes / 16; i += stride) dst[i] = src[i];
+    } else {
+        uint32_t *dst = (uint32_t *)b.dst[c];
+        const uint32_t *src = (const uint32_t *)b.src[c];
+        for (size_t i = first; i < bytes / 4; i += stride) dst[i] = src[i];
+    }
+}
+
+// device-visible alias of a page-locked host pointer, or nullptr (pageable memory: the copy engine must stage it)
+void *device_alias(const void *host) {
+    cudaPointerAttributes attr{};
+    if (cudaPointerGetAttributes(&attr, host) != cudaSuccess) {
+        (void)cudaGetLastError();
+        return nullptr;
+    }
+    return attr.type == cudaMemoryTypeHost ? attr.devicePointer : nullptr;
+}
+
+bool enqueue_copies(cudaStream_t stream, const Copy *copies, size_t n, bool to_device) {
+    if (n == 0) return true;
+    bool by_kernel = n <= (size_t)kIoMaxCopies && !std::getenv("FIMO_B200_IO_MEMCPY");
+    IoBatch batch{};
+    size_t total = 0, largest = 0;
+    for (size_t i = 0; i < n && by_kernel; i++) {
+        void *alias = device_alias(to_device ? copies[i].src : copies[i].dst);
+        if (!alias || copies[i].bytes % 4) by_kernel = false;
+        batch.dst[i] = to_device ? copies[i].dst : alias;
+        batch.src[i] = to_device ? alias : copies[i].src;
+        batch.bytes[i] = copies[i].bytes;
+        total += copies[i].bytes, largest = std::max(largest, copies[i].bytes);
+    }
+    if (by_kernel && total <= kIoMaxBytes) {
+        const unsigned blocks = (unsigned)std::min<size_t>(std::max<size_t>((largest / 16 + 255) / 256, 1), 148);
+        k_io_copy<<<dim3(blocks, (unsigned)n), 256, 0, stream>>>(batch);
+        return ok(cudaGetLastError(), "k_io_copy");
+    }
+    for (size_t i = 0; i < n; i++)
+        if (!ok(cudaMemcpyAsync(copies[i].dst, copies[i].src, copies[i].bytes, to_device ? cudaMemcpyHostToDevice : cudaMemcpyDeviceToHost, stream),
+                to_device ? "cudaMemcpyAsync H2D" : "cudaMemcpyAsync D2H"))
+            return false;
+    return true;
+}
+} // namespace
+
 bool executor_launch(Executor *ex, void (*done)(void *), void *user, const Copy *uploads, size_t n_up, const Copy *downloads,
                      size_t n_down) {
     DeviceGuard guard(ex->device);
@@ -347,17 +413,14 @@ bool executor_launch(Executor *ex, void (*done)(void *), void *user, const Copy 
         std::lock_guard<std::mutex> g(ex->m);
         ex->in_flight++;
     }
-    bool launched = true;
-    for (size_t i = 0; i < n_up && launched; i++) // this generation's inputs, in stream order in front of it
-        launched = ok(cudaMemcpyAsync(uploads[i].dst, uploads[i].src, uploads[i].bytes, cudaMemcpyHostToDevice, ex->stream), "cudaMemcpyAsync H2D");
+    bool launched = enqueue_copies(ex->stream, uploads, n_up, true); // this generation's inputs, in stream order in front of it
     launched = ok(cudaEventRecord(c.start, ex->stream), "cudaEventRecord") && launched;
     if (launched) {
         if (ex->use_graph) launched = ok(cudaGraphLaunch(ex->graph_exec, ex->stream), "cudaGraphLaunch");
         else launched = replay(ex, false);
     }
     launched = ok(cudaEventRecord(c.end, ex->stream), "cudaEventRecord") && launched;
-    for (size_t i = 0; i < n_down && launched; i++) // its results, behind it
-        launched = ok(cudaMemcpyAsync(downloads[i].dst, downloads[i].src, downloads[i].bytes, cudaMemcpyDeviceToHost, ex->stream), "cudaMemcpyAsync D2H");
+    if (launched) launched = enqueue_copies(ex->stream, downloads, n_down, false); // its results, behind it
     if (c.landed) launched = ok(cudaEventRecord(c.landed, ex->stream), "cudaEventRecord") && launched;
     if (!launched) c.done = nullptr; // the caller reports the failure itself
     completer().post(c);

@@ -212,15 +212,28 @@ def test_stream_ordered_transfers_match_locked_host_access(oracle, product):
     assert not problems, "\n".join(problems)
 
 
-def test_schedule_io_steps_in_flight_match_oracle(oracle, product):
+@pytest.mark.parametrize("pinned", [False, True])
+def test_schedule_io_steps_in_flight_match_oracle(oracle, product, pinned):
     """fimo_b200_group_schedule_io: generations with their own input uploads and result downloads, several in
     flight, each with its own host buffers: every step's downloaded result equals the oracle's after the same
-    uploads, and generation numbers advance by one per call."""
+    uploads, and generation numbers advance by one per call.  pinned: page-locked buffers (fimo_b200_host_alloc) —
+    the whole batch of small copies is one kernel that addresses host memory directly; pageable: the copy engine."""
     from fimo_b200.worlds import Fence
 
     W, E, D, K = 8, 512, 4, 6
     data = synth.generate(W, E, D)
     frusta = [synth.generate(W, E, D, world0=100 * (i + 1))["frustum"] for i in range(K)]
+    locked = []
+
+    def buffer_like(a):
+        if not pinned:
+            return np.empty_like(a)
+        ptr = product.fimo_b200_host_alloc(a.nbytes)
+        assert ptr
+        locked.append(ptr)
+        import ctypes as C
+        return np.ctypeslib.as_array(C.cast(ptr, C.POINTER(C.c_uint32)), shape=(a.size,)).view(a.dtype).reshape(a.shape)
+
     ref = synth.WorldStepRig(oracle, W, E, D, data={k: v.copy() for k, v in data.items()})
     want = []
     try:
@@ -234,10 +247,12 @@ def test_schedule_io_steps_in_flight_match_oracle(oracle, product):
     try:
         gen0 = rig.group.generation() if hasattr(rig.group, "generation") else None
         fences = [Fence(product) for _ in range(K)]
-        got = [{n: np.empty_like(rig.host[n]) for n in ("vis_count", "stats", "vis_mask")} for _ in range(K)]
+        got = [{n: buffer_like(rig.host[n]) for n in ("vis_count", "stats", "vis_mask")} for _ in range(K)]
         lists = []
         for i in range(K):  # all K steps queued before any is waited for
-            up, down = rig.io_list({"frustum": frusta[i]}), rig.io_list(got[i])
+            src = buffer_like(frusta[i])
+            src[...] = frusta[i]
+            up, down = rig.io_list({"frustum": src}), rig.io_list(got[i])
             lists.append((up, down))
             rig.schedule_io(up, down, fences[i])
         for f in fences:
@@ -248,8 +263,11 @@ def test_schedule_io_steps_in_flight_match_oracle(oracle, product):
         assert rig.stats()[abi.STAT_STEPS] == W * K
         if gen0 is not None:
             assert rig.group.generation() == gen0 + K
+        got = [{n: v.copy() for n, v in g.items()} for g in got]
     finally:
         rig.close()
+        for ptr in locked:
+            product.fimo_b200_host_free(ptr)
 
 
 @pytest.mark.parametrize("mode", ["fused", "graph", "streams"])
