@@ -46,6 +46,7 @@ def parse_args():
     p.add_argument("--no-fusion", action="store_true", help="one kernel per system (CUDA graph of the DAG)")
     p.add_argument("--no-cpu-baseline", action="store_true")
     p.add_argument("--no-e2e", action="store_true")
+    p.add_argument("--stats-bucket", type=int, default=8, help="steps whose statistics share one NCCL all-reduce (N > 1)")
     p.add_argument("--cpu-steps", type=int, default=0, help="steps of the CPU arm (0 = sized for ~15 s)")
     return p.parse_args()
 
@@ -178,38 +179,54 @@ def run_b200(args) -> None:
     # End-of-step statistics all-reduce (the path's only collective): after every generation a 64-byte
     # snapshot is taken in stream order, then reduced over NCCL on a side stream so that it overlaps the
     # next generation.  Buffers rotate; the group's stream never waits for the collective.
-    snaps = [torch.zeros(abi.STAT_WORDS, dtype=torch.int64, device="cuda") for _ in range(8)]
+    # The snapshot costs nothing on the group's stream: the kernel that publishes the statistics also stores them in
+    # slot `generation % slots` of a ring in HBM (FimoB200_GroupDeviceExt.stats_ring).  Bucketing: the snapshots of
+    # BUCKET consecutive steps share ONE all-reduce (a [bucket][8] u64 block of the ring, in place), so every step's
+    # statistics are still reduced, at 1/BUCKET of the launch latency and of the SM contention (the persistent
+    # world-step grid leaves no room for NCCL's CTA, so a per-step collective runs in the gaps between
+    # generations).  A block is overwritten by the kernel only after its previous all-reduce has finished.
+    BUCKET, NBLK = max(1, args.stats_bucket), 4
+    ring = torch.zeros((NBLK * BUCKET, abi.STAT_WORDS), dtype=torch.int64, device="cuda")
     side = torch.cuda.Stream()
-    copied = [torch.cuda.Event() for _ in snaps]   # snapshot i has been taken (group stream)
-    reduced = [torch.cuda.Event() for _ in snaps]  # snapshot i has been all-reduced (side stream)
-    state = {"ext": None, "n": 0, "stats_ptr": None}
+    written = [torch.cuda.Event() for _ in range(NBLK)]  # the block's last snapshot has been written (group stream)
+    reduced = [torch.cuda.Event() for _ in range(NBLK)]  # the block has been all-reduced (side stream)
+    state = {"ext": None, "n": 0, "flushed": 0}
+
+    def reduce_upto(n: int):
+        """All-reduce the snapshots of generations [flushed, n) — they lie in one block — on the side stream."""
+        first = state["flushed"]
+        if n <= first:
+            return
+        blk = ((n - 1) // BUCKET) % NBLK
+        assert first // BUCKET == (n - 1) // BUCKET
+        lo, hi = first % (NBLK * BUCKET), (n - 1) % (NBLK * BUCKET) + 1
+        written[blk].record(state["ext"])
+        side.wait_event(written[blk])
+        with torch.cuda.stream(side):
+            dist.all_reduce(ring[lo:hi])
+        reduced[blk].record(side)
+        state["flushed"] = n
 
     def post_step(_user, stream, generation):
+        # generation `generation` has just been enqueued; its kernel writes ring slot generation % (NBLK * BUCKET)
         if state["ext"] is None:
             state["ext"] = torch.cuda.ExternalStream(stream, device=torch.device("cuda", local_rank))
-        ext = state["ext"]
-        i = state["n"] % len(snaps)
-        buf = snaps[i]
-        if state["n"] >= len(snaps):
-            ext.wait_event(reduced[i])  # the buffer is reused: its previous all-reduce must have finished
-        state["n"] += 1
-        with torch.cuda.stream(ext):
-            buf.copy_(state["stats"], non_blocking=True)
-        copied[i].record(ext)
-        side.wait_event(copied[i])
-        with torch.cuda.stream(side):
-            dist.all_reduce(buf)
-        reduced[i].record(side)
+        n = int(generation) + 1  # generations enqueued so far
+        state["n"] = n
+        if n % BUCKET == 0:
+            reduce_upto(n)
+            if n >= NBLK * BUCKET:  # the next generation starts overwriting the oldest block: wait for its collective
+                state["ext"].wait_event(reduced[(n // BUCKET) % NBLK])
+
+    def flush_stats():
+        """All-reduce the tail of the current block (called inside the timed region, after the last schedule)."""
+        reduce_upto(state["n"])
 
     options = synth.RigOptions(fused=not args.no_fusion, device=local_rank)
+    if distributed:
+        options.stats_ring, options.stats_ring_slots = ring.data_ptr(), NBLK * BUCKET
     rig = synth.WorldStepRig(lib, W, E, D, data=data, options=options,
                              post_step=post_step if distributed else None, dag=args.dag)
-    if distributed:
-        # a torch view over the stats resource in HBM (locked once to fetch the device pointer)
-        view = rig._locked_view("stats", exclusive=False)
-        ptr = view.device_ptr
-        rig.resources["stats"].unlock_in_world(rig.world, False)
-        state["stats"] = _tensor_from_ptr(torch, ptr, abi.STAT_WORDS, local_rank)
     info = rig.executor_info()
 
     def barrier():
@@ -226,6 +243,9 @@ def run_b200(args) -> None:
     barrier()
     t0 = time.time()
     rig.schedule(K)
+    if distributed:
+        state["last_row"] = (state["n"] - 1) % (NBLK * BUCKET)
+        flush_stats()
     rig.wait()
     torch.cuda.synchronize()
     t1 = time.time()
@@ -244,7 +264,7 @@ def run_b200(args) -> None:
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
         t_ms = float(tt.item())
         side.synchronize()
-        global_stats = snaps[(state["n"] - 1) % len(snaps)].cpu().numpy().astype(np.uint64)
+        global_stats = ring[state["last_row"]].cpu().numpy().astype(np.uint64)
     value = world_size * W * K / (t_ms * 1e-3)
 
     # ---- roofline of the dominant kernel ---------------------------------------------------------------
@@ -284,7 +304,8 @@ def run_b200(args) -> None:
                    "worlds_per_gpu": W, "entities_per_world": E, "depth": D, "executor": "fused world-step kernel in a CUDA graph"
                    if info.fused_world_step else "CUDA graph of per-system kernels",
                    "l2": "inputs larger than L2 (state touched per step = %.0f MB > 126 MB)" % (alg_bytes / 1e6),
-                   "sharding": "worlds by global index, no data-path collective; stats all-reduce (64 B, NCCL, side stream)"},
+                   "sharding": "worlds by global index, no data-path collective; every step's statistics (64 B) all-reduced over NCCL on a "
+                               f"side stream, {args.stats_bucket} steps per collective"},
         "wall_ms_per_step": wall_ms / K, "device_ms_per_step": kernel_ms,
         "gpu_launches": int(info.kernel_launches_per_generation) * K,
         "roofline": roofline, "clocks": clocks,

@@ -27,7 +27,7 @@ GSTAT_VISIBLE_LO, GSTAT_WORLDS_LO, GSTAT_BOUNDS, GSTAT_WORDS = 0, 2, 4, 16
 STAT_VISIBLE, STAT_ENTITIES, STAT_MASK_SUM, STAT_WORLDS, STAT_STEPS, STAT_WORDS = 0, 1, 2, 3, 4, 8
 PARENT_ROOT = 0xFFFFFFFF
 DEP_WEAK, DEP_IGNORE_DEFERRED = 1, 2
-GROUP_FLAG_NO_FUSION, GROUP_FLAG_NO_GRAPH = 1, 2
+GROUP_FLAG_NO_FUSION, GROUP_FLAG_NO_GRAPH, GROUP_FLAG_STATS_RING = 1, 2, 4
 VIEW_FLAG_EXTERNAL = 1
 
 ALLOC_TRANSIENT, ALLOC_SINGLE_GENERATION, ALLOC_MULTI_GENERATION, ALLOC_SYSTEM_PERSISTENT = 0, 1, 2, 3
@@ -283,6 +283,9 @@ class GroupDeviceExt(C.Structure):
         ("reserved", c_uint32),
         ("post_step", PostStepFn),
         ("post_step_user", c_void_p),
+        ("stats_ring", c_void_p),       # with GROUP_FLAG_STATS_RING: device [slots][STAT_WORDS] u64, slot = generation % slots
+        ("stats_ring_slots", c_uint32),
+        ("reserved2", c_uint32),
     ]
 
 

@@ -94,6 +94,8 @@ uint32_t builtin_propagate_kernels(const FimoB200_ResourceView *world, const Fim
 struct BuiltinState {
     void *scratch; // HBM: statistics accumulators + completion ticket (cull only)
     int device;
+    void *stats_ring = nullptr; // FimoB200_GroupDeviceExt::stats_ring, if this is the group's first cull system
+    uint32_t stats_ring_slots = 0;
 };
 
 // The fused world-step: integrate -> propagate -> cull of one batch in ONE kernel; every live-in
@@ -114,6 +116,8 @@ struct WorldStepViews {
                                 *sleep = nullptr, *lod = nullptr, *vis_mask2 = nullptr, *vis_list2 = nullptr, *vis_count2 = nullptr,
                                 *stats2 = nullptr, *vbounds = nullptr, *gstats2 = nullptr;
     void *scratch2 = nullptr; // cull2's statistics accumulator block (its BuiltinState)
+    void *stats_ring = nullptr; // FimoB200_GroupDeviceExt::stats_ring (per-generation snapshots of `stats`)
+    uint32_t stats_ring_slots = 0;
 };
 // How the fused kernel is launched for a given batch; made once when the executor is compiled (it reads
 // level_start from HBM to size the shared-memory parent window), then reused by every launch.

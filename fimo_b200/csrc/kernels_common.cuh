@@ -111,7 +111,9 @@ struct StepArgs {
     Plane vis_mask, vis_list, vis_count;            // cull outputs
     Plane aabb_c, aabb_h, frustum;                  // cull inputs
     unsigned long long *stats;                      // FIMO_B200_STAT_* words of the batch
-    unsigned long long *scratch;                    // [0..3] accumulators, [4] ticket
+    unsigned long long *scratch;                    // [0..3] accumulators, [4] ticket, [5] generations published
+    unsigned long long *ring;                       // per-generation snapshots of `stats` ([ring_slots][8]) or nullptr
+    uint32_t ring_slots;
     // the fused 8-system DAG (world_step.cu, kSet = 1) additionally uses:
     Plane angvel, gravity, vmax, waabb, wbounds;
     uint32_t *gstats;     // FIMO_B200_GSTAT_* words of the batch
@@ -164,6 +166,8 @@ struct StatsSink { // where one cull's batch statistics go (the DAGs have up to 
     uint32_t *gstats; // group statistics fed by this cull (nullptr: none)
     int *bounds_keys; // batch bounds accumulators that go with gstats
     uint32_t entities;
+    unsigned long long *ring = nullptr; // FimoB200_GroupDeviceExt::stats_ring
+    uint32_t ring_slots = 0;
 };
 template <bool kGroupStats>
 __device__ __forceinline__ bool publish_stats_to(const StatsSink &a, unsigned long long visible, unsigned long long mask_sum,
@@ -183,6 +187,12 @@ __device__ __forceinline__ bool publish_stats_to(const StatsSink &a, unsigned lo
     a.stats[FIMO_B200_STAT_MASK_SUM] = m;
     a.stats[FIMO_B200_STAT_WORLDS] = n;
     a.stats[FIMO_B200_STAT_STEPS] += n;
+    if (a.ring) { // the snapshot of this generation: slot = generations published so far % slots
+        const unsigned long long gen = a.scratch[5];
+        a.scratch[5] = gen + 1;
+        unsigned long long *slot = a.ring + (gen % a.ring_slots) * FIMO_B200_STAT_WORDS;
+        for (int i = 0; i < FIMO_B200_STAT_WORDS; i++) slot[i] = a.stats[i];
+    }
     if (kGroupStats) {
         uint32_t *g = a.gstats;
         for (int i = 0; i < FIMO_B200_GSTAT_WORDS; i++) g[i] = 0u;
@@ -199,7 +209,8 @@ __device__ __forceinline__ bool publish_stats_to(const StatsSink &a, unsigned lo
 template <bool kGroupStats = false>
 __device__ __forceinline__ bool publish_stats(const StepArgs &a, unsigned long long visible, unsigned long long mask_sum,
                                               unsigned long long worlds, unsigned long long n_ctas) {
-    return publish_stats_to<kGroupStats>(StatsSink{a.stats, a.scratch, a.gstats, a.bounds_keys, a.entities}, visible, mask_sum, worlds, n_ctas);
+    return publish_stats_to<kGroupStats>(StatsSink{a.stats, a.scratch, a.gstats, a.bounds_keys, a.entities, a.ring, a.ring_slots}, visible, mask_sum,
+                                         worlds, n_ctas);
 }
 __device__ __forceinline__ bool publish_stats(const StepArgs &a, unsigned long long visible, unsigned long long mask_sum,
                                               unsigned long long worlds) {

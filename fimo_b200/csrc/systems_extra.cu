@@ -376,6 +376,7 @@ ENTRY(builtin_cull_waabb) {
         if (!x[3] || !x[3]->device_ptr || x[3]->scope != FIMO_B200_SCOPE_BATCH || x[3]->components != 2 * FIMO_B200_STAT_WORDS) throw Fail{"stats"};
         a.stats = (unsigned long long *)x[3]->device_ptr;
         a.scratch = (unsigned long long *)((BuiltinState *)system)->scratch;
+        a.ring = (unsigned long long *)((BuiltinState *)system)->stats_ring, a.ring_slots = ((BuiltinState *)system)->stats_ring_slots;
         if (!a.scratch) throw Fail{"cull scratch"};
         a.frustum = per_world(s[1], 24, d, "frustum");
         a.mask_words = (uint32_t)((d.E + 31) / 32);

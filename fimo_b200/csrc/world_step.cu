@@ -840,6 +840,7 @@ bool world_step_plan(const WorldStepViews &v, int device, WorldStepPlan &plan) {
     // keeps the kernel on the HBM roofline, so the plan that holds the largest share of the parents in its window
     // wins; among equals, more and smaller CTAs (they hide the level barriers best).  A 3-deep ring beats deeper
     // ones on every shape measured.  Parents outside the window travel through `rows`.
+    double window_coverage = 1.0;
     if (!planned) {
         static const struct { int T; uint32_t blocks, stages; } kCandidates[] = {{128, 4, 3}, {256, 3, 3}, {256, 2, 3}, {512, 1, 3}};
         double best = -1.0;
@@ -850,10 +851,17 @@ bool world_step_plan(const WorldStepViews &v, int device, WorldStepPlan &plan) {
             if (coverage > best + 1e-9) best = coverage, plan = trial;
         }
         if (best < 0.0) return false;
+        window_coverage = best;
     }
     // Few worlds (or a forced team size): CTA teams, with the geometry that suits them (no window needed).
-    const char *team_env = std::getenv("FIMO_B200_TEAM"); // force the team size (1 = one CTA per world)
-    const uint64_t forced = team_env ? std::strtoull(team_env, nullptr, 10) : 0;
+    const char *team_var = std::getenv("FIMO_B200_TEAM"); // force the team size (1 = one CTA per world)
+    bool team_env = team_var != nullptr;
+    uint64_t forced = team_env ? std::strtoull(team_var, nullptr, 10) : 0;
+    // Many LARGE worlds: with the window holding under 30 % of the parents a lone CTA gathers most rows from L2 with
+    // nothing to overlap them (592 x 64k entities: 0.24 of the HBM peak); teams of 16 prefetch the rows one chunk ahead
+    // and keep far fewer worlds' rows live in L2 (0.52, profiles/r1m_two_world_interleave_rejected.txt).
+    if (!team_env && !planned && v.set != 2 && window_coverage < 0.3 && (E + 127) / 128 >= 32 && W * 2 > 4ull * sm_count(device))
+        team_env = true, forced = 16;
     if (!planned && v.set != 2 && (!team_env || forced > 1)) {
         WorldStepPlan trial = plan;
         make_plan(trial, 128, 4, 3, 0, E);
@@ -929,6 +937,7 @@ FimoStatus world_step_launch(const WorldStepViews &v, const WorldStepPlan &plan,
         a.n_worlds = (uint32_t)W, a.entities = (uint32_t)E;
         fill_propagate(a, v.world, v.pos, v.rot, v.scale, v.parent, v.level_start, W, E);
         fill_cull(a, v.vis_mask, v.vis_list, v.vis_count, v.stats, v.world, v.aabb_c, v.aabb_h, v.frustum, cull_scratch, W, E);
+        a.ring = (unsigned long long *)v.stats_ring, a.ring_slots = v.stats_ring_slots;
         a.vel = plane_of(v.vel, FIMO_B200_SCOPE_ENTITY, 3, E, W, "vel");
         a.dt = plane_of(v.dt, FIMO_B200_SCOPE_WORLD, 1, 1, W, "dt");
         pa.stages = plan.stages;

@@ -620,6 +620,8 @@ struct Group {
     uint32_t ext_flags = 0;
     FimoB200_post_step post_step = nullptr;
     void *post_step_user = nullptr;
+    void *stats_ring = nullptr; // FimoB200_GroupDeviceExt::stats_ring
+    uint32_t stats_ring_slots = 0;
 
     std::mutex m; // the graph mutex (SystemGroup.zig:40-52)
     bool dirty = true;
@@ -1024,6 +1026,23 @@ bool build_device_executor(Group *g, const char **err) {
         }
         return !set.empty();
     };
+    // per-generation statistics snapshots (FimoB200_GroupDeviceExt::stats_ring): written by whichever kernel publishes
+    // the statistics of the group's FIRST cull system — the fused world-step if that system is fused, its own kernel otherwise
+    {
+        Member *first_cull = nullptr;
+        for (Member *m : g->order) {
+            const uint32_t id = m->type->builtin_id;
+            if (!m->type->device_entry || (id != FIMO_B200_BUILTIN_CULL && id != FIMO_B200_BUILTIN_CULL_WAABB)) continue;
+            dev::BuiltinState *st = (dev::BuiltinState *)m->state;
+            st->stats_ring = first_cull ? nullptr : g->stats_ring;
+            st->stats_ring_slots = first_cull ? 0 : g->stats_ring_slots;
+            if (!first_cull) first_cull = m;
+        }
+        if (mc && mc == first_cull) {
+            views.stats_ring = views16.stats_ring = g->stats_ring;
+            views.stats_ring_slots = views16.stats_ring_slots = g->stats_ring_slots;
+        }
+    }
     bool fuse = false;
     if (!fused16.empty() && !std::getenv("FIMO_B200_NO_SET2") && convex(fused16) && dev::world_step_plan(views16, g->world->device, plan))
         fuse = true, fused = fused16, views = views16;
@@ -1484,6 +1503,8 @@ Group *group_create(const FimoWorldsMeta_SystemGroupDescriptor *d) {
         g->ext_flags = ext->flags;
         g->post_step = ext->post_step;
         g->post_step_user = ext->post_step_user;
+        if ((ext->flags & FIMO_B200_GROUP_FLAG_STATS_RING) && ext->stats_ring && ext->stats_ring_slots)
+            g->stats_ring = ext->stats_ring, g->stats_ring_slots = ext->stats_ring_slots;
     }
     char buf[64];
     std::snprintf(buf, sizeof buf, "%p systems", (void *)g); // :465
@@ -1545,6 +1566,8 @@ bool builtin_create(const void *factory, FimoWorldsMeta_SystemContext *context, 
     dev::BuiltinState *state = (dev::BuiltinState *)system;
     state->device = m->group->world->device;
     state->scratch = nullptr;
+    state->stats_ring = nullptr;
+    state->stats_ring_slots = 0;
     if (state->device < 0) return false; // built-in systems exist on the device only
     if (m->type->builtin_id == FIMO_B200_BUILTIN_CULL || m->type->builtin_id == FIMO_B200_BUILTIN_CULL_WAABB) {
         state->scratch = dev::hbm_alloc(state->device, 64);

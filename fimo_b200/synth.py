@@ -273,6 +273,8 @@ class RigOptions:
     graph: bool = True  # CUDA graph executor (False: plain stream launches with fork/join events)
     device: int = -1
     keep_host_copy: bool = True
+    stats_ring: int = 0        # device pointer of a [stats_ring_slots][8] u64 ring for per-generation statistics snapshots
+    stats_ring_slots: int = 0
 
 
 class WorldStepRig:
@@ -319,7 +321,10 @@ class WorldStepRig:
         if self.on_device:
             flags = (0 if self.opt.fused else abi.GROUP_FLAG_NO_FUSION) | (0 if self.opt.graph else abi.GROUP_FLAG_NO_GRAPH)
             self._post_step = abi.PostStepFn(post_step) if post_step is not None else abi.PostStepFn()
-            gext = abi.GroupDeviceExt(abi.ExtHeader(abi.STYPE_GROUP_DEVICE, 0, None), flags, 0, self._post_step, None)
+            if self.opt.stats_ring and self.opt.stats_ring_slots:
+                flags |= abi.GROUP_FLAG_STATS_RING
+            gext = abi.GroupDeviceExt(abi.ExtHeader(abi.STYPE_GROUP_DEVICE, 0, None), flags, 0, self._post_step, None,
+                                      self.opt.stats_ring or None, self.opt.stats_ring_slots, 0)
         self.group = self.world.add_system_group("world-step", pool=pool, ext=gext)
 
         R = self.resources

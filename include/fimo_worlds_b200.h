@@ -544,9 +544,17 @@ typedef struct FimoB200_GroupDeviceExt {
      * `stream` (e.g. to enqueue the end-of-step statistics allreduce). May be NULL. */
     FimoB200_post_step post_step;
     void *post_step_user;
+    /* Read only with FIMO_B200_GROUP_FLAG_STATS_RING: device memory [stats_ring_slots][FIMO_B200_STAT_WORDS] u64.
+     * The kernel that publishes the statistics of the group's first cull system also stores them in slot
+     * `generation % stats_ring_slots` (generation counted from the group's first one) — a per-step snapshot
+     * without an extra launch or copy, e.g. the send buffer of the end-of-step statistics all-reduce. */
+    void *stats_ring;
+    uint32_t stats_ring_slots;
+    uint32_t reserved2;
 } FimoB200_GroupDeviceExt;
 #define FIMO_B200_GROUP_FLAG_NO_FUSION 1u /* one kernel per system (CUDA graph of the DAG) */
 #define FIMO_B200_GROUP_FLAG_NO_GRAPH 2u  /* plain stream launches, no CUDA graph */
+#define FIMO_B200_GROUP_FLAG_STATS_RING 4u /* stats_ring / stats_ring_slots are valid */
 
 /* Statistics words written by BUILTIN_CULL into the `stats` resource (u64 each, 8 per batch). */
 enum {

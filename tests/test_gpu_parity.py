@@ -71,6 +71,7 @@ TEAM_CASES = [
     (2, 8192, 8, 2, 37),
     (40, 2048, 8, 3, 2),
     (9, 640, 5, 4, 4),         # last chunk ragged, 5 levels
+    (300, 32768, 8, 2, None),  # many LARGE worlds: the window would hold < 30 % of the parents -> teams of 16 by plan
 ]
 
 
@@ -303,6 +304,35 @@ def test_mixed_host_and_device_systems_match_oracle(oracle, product, W, E, D, st
     assert not problems, "\n".join(problems)
     assert got_census == want_census and got_census[1] == steps
     assert got_census[2] == int(got["vis_count"].sum())
+
+
+@pytest.mark.parametrize("dag,W,E,D,fused", [("chain3", 24, 512, 4, True), ("chain3", 24, 512, 4, False), ("chain3", 3, 8192, 8, True),
+                                            ("dag16", 700, 128, 4, True), ("dag8", 9, 1000, 4, True)])
+def test_stats_ring_holds_every_generation(product, dag, W, E, D, fused):
+    """FimoB200_GroupDeviceExt.stats_ring: the kernel that publishes the statistics also stores them in slot
+    generation % slots — K generations queued back to back leave the same words a step-by-step run reads from `stats`."""
+    import torch
+
+    slots, K = 4, 7
+    data = synth.generate(W, E, D, dag=dag)
+    rig = synth.WorldStepRig(product, W, E, D, data={k: v.copy() for k, v in data.items()}, options=synth.RigOptions(fused=fused), dag=dag)
+    try:
+        want = []
+        for _ in range(K):
+            rig.step(1)
+            want.append(rig.stats().copy())
+    finally:
+        rig.close()
+    ring = torch.zeros((slots, abi.STAT_WORDS), dtype=torch.int64, device="cuda")
+    opts = synth.RigOptions(fused=fused, stats_ring=ring.data_ptr(), stats_ring_slots=slots)
+    rig = synth.WorldStepRig(product, W, E, D, data={k: v.copy() for k, v in data.items()}, options=opts, dag=dag)
+    try:
+        rig.step(K)  # all K queued, then one wait
+        got = ring.cpu().numpy().astype(np.uint64)
+    finally:
+        rig.close()
+    for g in range(K - slots, K):
+        assert np.array_equal(got[g % slots], want[g]), (g, got[g % slots], want[g])
 
 
 DAG_CASES = [
