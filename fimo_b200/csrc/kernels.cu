@@ -245,7 +245,7 @@ FimoStatus builtin_propagate(void *, const FimoB200_ResourceView *const *exclusi
 FimoStatus builtin_cull(void *system, const FimoB200_ResourceView *const *exclusive, const FimoB200_ResourceView *const *shared,
                         const FimoB200_LaunchInfo *info) {
     const uint64_t W = info->n_worlds, E = info->entities_per_world;
-    if (W == 0 || E == 0) return FIMO_STATUS_OK;
+    if (W == 0) return FIMO_STATUS_OK; // empty worlds (E == 0) still publish their counts and the batch statistics
     try {
         StepArgs a{};
         a.n_worlds = (uint32_t)W, a.entities = (uint32_t)E;

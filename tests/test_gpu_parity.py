@@ -63,6 +63,18 @@ def test_three_system_chain_matches_oracle(oracle, product, monkeypatch, W, E, D
     assert st[abi.STAT_STEPS] == W * steps and st[abi.STAT_WORLDS] == W
 
 
+@pytest.mark.parametrize("fused", [True, False])
+def test_empty_worlds(oracle, product, fused):
+    """Worlds without entities: nothing to step, but a generation still runs — per-world counts are 0 and the batch
+    statistics count the worlds and the steps, as on the oracle."""
+    got, want, info = run_both(oracle, product, 3, 0, 4, 2, synth.RigOptions(fused=fused))
+    assert info.systems == 3 and info.fused_world_step == 0  # nothing to fuse over
+    problems = synth.compare_outputs(got, want, FLOAT_RTOL)
+    assert not problems, "\n".join(problems)
+    st = got["stats"].reshape(-1).view(np.uint64)
+    assert st[abi.STAT_WORLDS] == 3 and st[abi.STAT_STEPS] == 6 and st[abi.STAT_VISIBLE] == 0 and st[abi.STAT_ENTITIES] == 0
+
+
 TEAM_CASES = [
     # (worlds, entities, depth, steps, forced team size or None = heuristic)
     (3, 65536, 8, 3, None),    # configs[2] world shape: a world is stepped by ~197 CTAs
