@@ -363,6 +363,14 @@ COMMON_SYMBOLS = [
     ("fimo_tasks_create_worker_pool", FimoStatus, [POINTER(PoolConfig), POINTER(Pool)]),
 ]
 
+class TraceEvent(C.Structure):  # FimoB200_TraceEvent
+    _fields_ = [("group_label", C.c_void_p), ("group_label_len", c_size_t), ("generation", c_uint64), ("device_ms", c_double),
+                ("host_enqueue_ns", C.c_int64), ("host_complete_ns", C.c_int64), ("kernels", c_uint32), ("fused_world_step", c_uint32)]
+
+
+TraceSinkFn = C.CFUNCTYPE(None, c_void_p, POINTER(TraceEvent))
+
+
 # device-side helpers: product library only
 PRODUCT_SYMBOLS = [
     ("fimo_b200_builtin_system", FimoStatus, [c_uint32, POINTER(SystemDescriptor), POINTER(SystemDeviceExt)]),
@@ -375,6 +383,7 @@ PRODUCT_SYMBOLS = [
     ("fimo_b200_group_span_ms", c_double, [c_void_p]),
     ("fimo_b200_group_transfer", FimoStatus, [c_void_p, c_void_p, c_void_p, c_uint32, POINTER(Fence)]),
     ("fimo_b200_group_schedule_io", FimoStatus, [c_void_p, c_void_p, c_size_t, c_void_p, c_size_t, c_void_p, c_size_t, POINTER(Fence)]),
+    ("fimo_worlds_b200_set_trace_sink", None, [TraceSinkFn, c_void_p]),
     ("fimo_b200_host_alloc", c_void_p, [c_size_t]),
     ("fimo_b200_host_free", None, [c_void_p]),
 ]

@@ -103,6 +103,7 @@ struct Executor {
     uint64_t ms_count = 0;
     cudaEvent_t span_anchor = nullptr; // start of the first generation since the timers were read
     double span_ms = 0.0;              // anchor -> end of the latest generation (includes inter-generation gaps)
+    std::atomic<double> last_ms{0.0};  // device time of the generation being retired
 
     cudaEvent_t take_event() {
         {
@@ -135,6 +136,7 @@ void Completer::run() {
         float ms = 0.0f;
         const bool timed = c.generation && cudaEventElapsedTime(&ms, c.start, c.end) == cudaSuccess;
         if (c.generation && !timed) (void)cudaGetLastError();
+        if (timed) c.ex->last_ms.store((double)ms, std::memory_order_relaxed);
         if (c.done) c.done(c.user);
         Executor *ex = c.ex;
         std::lock_guard<std::mutex> g(ex->m);
@@ -474,6 +476,8 @@ double executor_device_ms(Executor *ex, uint64_t *generations) {
     ex->ms_count = 0;
     return avg;
 }
+
+double executor_last_generation_ms(Executor *ex) { return ex->last_ms.load(std::memory_order_relaxed); }
 
 double executor_span_ms(Executor *ex) {
     std::lock_guard<std::mutex> g(ex->m);

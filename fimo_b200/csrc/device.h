@@ -61,6 +61,7 @@ void *executor_stream(Executor *ex);
 bool executor_uses_graph(Executor *ex);
 uint32_t executor_kernels_per_generation(Executor *ex);
 double executor_device_ms(Executor *ex, uint64_t *generations);
+double executor_last_generation_ms(Executor *ex); // device time of the generation whose `done` is running (completion thread)
 double executor_span_ms(Executor *ex);
 
 // ---- built-in systems (kernels.cu) -------------------------------------------------------------

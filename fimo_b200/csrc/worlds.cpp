@@ -19,6 +19,7 @@
 //   * host systems still run on the pool through a command buffer, exactly as in the reference.
 #include <algorithm>
 #include <cstdlib>
+#include <chrono>
 #include <cstring>
 #include <deque>
 #include <memory>
@@ -1255,13 +1256,30 @@ void unlock_group_resources(Group *g) { // :477-481
 struct DeviceDone {
     Group *group;
     FimoWorldsMeta_Fence *signal;
+    uint64_t generation = 0;
+    int64_t enqueue_ns = 0;
 };
+
+std::atomic<FimoB200_trace_sink> g_trace_sink{nullptr};
+std::atomic<void *> g_trace_user{nullptr};
+int64_t monotonic_ns() {
+    return std::chrono::duration_cast<std::chrono::nanoseconds>(std::chrono::steady_clock::now().time_since_epoch()).count();
+}
 
 void device_generation_done(void *user) {
     // Runs on the completion thread once the device finished the generation: the second half of
     // SystemGroup.run (:477-486) and the Job cleanup (Job.zig:234-247).
     std::unique_ptr<DeviceDone> done((DeviceDone *)user);
     Group *g = done->group;
+    if (FimoB200_trace_sink sink = g_trace_sink.load(std::memory_order_acquire)) { // before the group may be destroyed
+        FimoB200_TraceEvent ev{};
+        ev.group_label = g->label.data(), ev.group_label_len = g->label.size();
+        ev.generation = done->generation;
+        ev.device_ms = dev::executor_last_generation_ms(g->executor_dev);
+        ev.host_enqueue_ns = done->enqueue_ns, ev.host_complete_ns = monotonic_ns();
+        ev.kernels = g->info.kernel_launches_per_generation, ev.fused_world_step = g->info.fused_world_step;
+        sink(g_trace_user.load(std::memory_order_acquire), &ev);
+    }
     size_t gen;
     {
         std::lock_guard<std::mutex> lock(g->m);
@@ -1332,7 +1350,7 @@ int start_device_generation(Group *g, Job *job, bool blocking, const char **err)
             else downs.push_back(dev::Copy{io.second, view->device_ptr, bytes});
         }
     g->in_flight++;
-    DeviceDone *done = new DeviceDone{g, job->signal};
+    DeviceDone *done = new DeviceDone{g, job->signal, (uint64_t)job->generation, g_trace_sink.load(std::memory_order_relaxed) ? monotonic_ns() : 0};
     if (!dev::executor_launch(g->executor_dev, &device_generation_done, done, ups.data(), ups.size(), downs.data(), downs.size())) {
         // The completion entry still drains through the completion thread (without `done`); undo here.
         delete done;
@@ -1864,6 +1882,10 @@ FimoStatus fimo_b200_group_schedule_io(FimoWorldsMeta_SystemGroup *group, const 
     const StepIo io{uploads, n_uploads, downloads, n_downloads};
     if (const char *err = group_schedule(g, wait_on, n_wait, signal, nullptr, &io)) return report(err);
     return FIMO_STATUS_OK;
+}
+void fimo_worlds_b200_set_trace_sink(FimoB200_trace_sink sink, void *user) {
+    g_trace_user.store(user, std::memory_order_release);
+    g_trace_sink.store(sink, std::memory_order_release);
 }
 void *fimo_b200_host_alloc(FimoUSize bytes) { return dev::host_alloc_pinned(bytes); }
 void fimo_b200_host_free(void *ptr) { dev::host_free_pinned(ptr); }

@@ -795,6 +795,25 @@ FIMO_B200_EXPORT FimoStatus fimo_b200_group_schedule_io(FimoWorldsMeta_SystemGro
 FIMO_B200_EXPORT void *fimo_b200_host_alloc(FimoUSize bytes); /* page-locked host memory; NULL on failure */
 FIMO_B200_EXPORT void fimo_b200_host_free(void *ptr);
 
+/* Tracing bridge.  The reference records spans and events through the context's tracing
+ * subsystem (pkgs/fimo_std/src/tracing.zig:387-554: enter_span / exit_span / log_message); device work has no
+ * call stack there.  With a sink installed the completion thread reports every finished device generation —
+ * group label, generation number, device time between the CUDA events that bracket it, host timestamps
+ * (CLOCK_MONOTONIC ns) of the enqueue and of the observed completion, kernels launched — and the module shim
+ * forwards it as a span / event of its own subscriber.  The sink runs outside any CUDA callback. */
+typedef struct FimoB200_TraceEvent {
+    const char *group_label;
+    FimoUSize group_label_len;
+    uint64_t generation;
+    double device_ms;
+    int64_t host_enqueue_ns;
+    int64_t host_complete_ns;
+    uint32_t kernels;
+    uint32_t fused_world_step;
+} FimoB200_TraceEvent;
+typedef void (*FimoB200_trace_sink)(void *user, const FimoB200_TraceEvent *event);
+FIMO_B200_EXPORT void fimo_worlds_b200_set_trace_sink(FimoB200_trace_sink sink, void *user);
+
 /* What the DAG compiler produced for the group's current system set. */
 typedef struct FimoB200_ExecutorInfo {
     uint32_t systems;          /* member systems */

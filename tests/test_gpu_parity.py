@@ -347,6 +347,32 @@ def test_stats_ring_holds_every_generation(product, dag, W, E, D, fused):
         assert np.array_equal(got[g % slots], want[g]), (g, got[g % slots], want[g])
 
 
+def test_trace_sink_reports_every_device_generation(product):
+    """with a sink installed the completion thread reports each finished device generation (label,
+    generation number, device time from the bracketing CUDA events, host timestamps, kernel count)."""
+    import ctypes as C
+
+    events = []
+
+    def sink(_user, ev):
+        e = ev.contents
+        events.append((C.string_at(e.group_label, e.group_label_len).decode(), int(e.generation), float(e.device_ms),
+                       int(e.host_enqueue_ns), int(e.host_complete_ns), int(e.kernels), int(e.fused_world_step)))
+
+    cb = abi.TraceSinkFn(sink)
+    rig = synth.WorldStepRig(product, 64, 1024, 4)
+    try:
+        rig.step(2)  # before the sink: not reported
+        product.fimo_worlds_b200_set_trace_sink(cb, None)
+        rig.step(5)
+    finally:
+        product.fimo_worlds_b200_set_trace_sink(abi.TraceSinkFn(), None)
+        rig.close()
+    assert [e[1] for e in events] == [2, 3, 4, 5, 6]
+    assert all(e[0] == "world-step" and e[5] in (1, 2) and e[6] == 1 for e in events)  # 2 = team kernel + list compaction
+    assert all(0.0 < e[2] < 50.0 and 0 < e[3] <= e[4] for e in events)
+
+
 DAG_CASES = [
     # (dag, worlds, entities, depth, steps)
     ("dag8", 1, 1024, 4, 8),
