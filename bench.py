@@ -44,6 +44,7 @@ def parse_args():
                    help="system set: the 3-system chain (configs[1]), the 8-system fan-out/fan-in DAG (configs[2]) or the "
                         "16-system DAG with mixed read/write conflicts (configs[4])")
     p.add_argument("--no-fusion", action="store_true", help="one kernel per system (CUDA graph of the DAG)")
+    p.add_argument("--no-graph", action="store_true", help="plain stream launches instead of a CUDA graph per generation")
     p.add_argument("--no-cpu-baseline", action="store_true")
     p.add_argument("--no-e2e", action="store_true")
     p.add_argument("--stats-bucket", type=int, default=8, help="steps whose statistics share one NCCL all-reduce (N > 1)")
@@ -222,7 +223,7 @@ def run_b200(args) -> None:
         """All-reduce the tail of the current block (called inside the timed region, after the last schedule)."""
         reduce_upto(state["n"])
 
-    options = synth.RigOptions(fused=not args.no_fusion, device=local_rank)
+    options = synth.RigOptions(fused=not args.no_fusion, graph=not args.no_graph, device=local_rank)
     if distributed:
         options.stats_ring, options.stats_ring_slots = ring.data_ptr(), NBLK * BUCKET
     rig = synth.WorldStepRig(lib, W, E, D, data=data, options=options,
@@ -301,8 +302,8 @@ def run_b200(args) -> None:
         "config": {"workload": f"{W} worlds x {E} entities per GPU, depth-{D} transform hierarchy, {DAG_TEXT[args.dag]}"
                                + (", BASELINE.json configs[1]" if (W, E, D, args.dag) == (4096, 1024, 4, "chain3") else ""),
                    "dag": args.dag,
-                   "worlds_per_gpu": W, "entities_per_world": E, "depth": D, "executor": "fused world-step kernel in a CUDA graph"
-                   if info.fused_world_step else "CUDA graph of per-system kernels",
+                   "worlds_per_gpu": W, "entities_per_world": E, "depth": D, "executor": ("fused world-step kernel" if info.fused_world_step else "one kernel per system")
+                   + (" in a CUDA graph" if info.uses_cuda_graph else ", plain stream launches"),
                    "l2": "inputs larger than L2 (state touched per step = %.0f MB > 126 MB)" % (alg_bytes / 1e6),
                    "sharding": "worlds by global index, no data-path collective; every step's statistics (64 B) all-reduced over NCCL on a "
                                f"side stream, {args.stats_bucket} steps per collective"},

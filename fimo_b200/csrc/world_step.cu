@@ -1,25 +1,26 @@
 // world_step.cu — the fused world-step as a persistent, TMA-fed pipeline (sm_100a).
 //
-// What it replaces: one generation of the 3-system chain integrate -> transform propagate -> AABB
-// frustum cull, which the reference dispatches as three fiber tasks per world through the pool's event
-// loop (modules/fimo_worlds/src/SystemGroup.zig:454-487, modules/fimo_tasks/src/CommandBuffer.zig:150-201).
-// Here ONE kernel steps every world of the batch; each live-in word is read from HBM once and each
-// live-out word written once (B3 = 132.125 + 4 f_vis bytes per entity-step).
+// What it replaces: one generation of a system group, which the reference dispatches as one fiber task per system and
+// world through the pool's event loop (modules/fimo_worlds/src/SystemGroup.zig:454-487,
+// modules/fimo_tasks/src/CommandBuffer.zig:150-201).  Here ONE kernel steps every world of the batch for a whole
+// fusable system set (SetTraits below: the 3-system chain, the 8-system DAG, 15 systems of the 16-system DAG); each
+// live-in word is read from HBM once and each live-out word written once.
 //
 // Structure (HBM-bound streaming; no tensor cores):
-//   * persistent CTAs (2 per SM with 256 threads, or 1 with 512), worlds strided over CTAs;
+//   * persistent, warp-specialised CTAs: T/32 compute warps + 1 TMA warp; (T, CTAs/SM) in {(128,4), (256,3), (256,2),
+//     (512,1)} chosen per batch by world_step_plan; worlds strided over CTAs, or — few / large worlds — over CTA teams;
 //   * a world is cut into chunks of T consecutive entities (entities are sorted by hierarchy level);
-//   * the 18 input planes of a chunk (pos3 vel3 rot4 scale parent aabb_c3 aabb_h3 = 72 B/entity) are
-//     brought into a shared-memory ring by 1-D bulk async copies (cp.async.bulk, the TMA engine,
-//     SASS UBLKCP) that signal an mbarrier with complete_tx; the ring is several chunks deep and runs
-//     across world boundaries, so HBM latency is hidden by the copy engine, not by occupancy;
-//   * one thread owns one entity of the chunk and does integrate, local TRS, composition with the
-//     parent's world matrix, the 6-plane AABB test — all in registers.  Only matrices of entities that
-//     can still be parents (all levels but the last) are kept in shared memory ([12][cap] planes);
-//     the levels present in a chunk are walked in order with a __syncthreads between them;
-//   * cull compaction: __ballot_sync gives the 32-entity mask word, __popc prefix inside the warp and a
-//     scan over the warps' counts give each visible entity its slot in the ASCENDING index list;
-//   * outputs go straight from registers to HBM as coalesced 128-byte rows per plane.
+//   * the input planes of a chunk are brought into a shared-memory ring by 1-D bulk async copies (cp.async.bulk, the
+//     TMA engine, SASS UBLKCP) that signal an mbarrier with complete_tx; the ring is three chunks deep and runs across
+//     world boundaries, so HBM latency is hidden by the copy engine, not by occupancy;
+//   * one thread owns one entity of the chunk and does all the systems' arithmetic in registers.  Matrices of
+//     entities that can still be parents live in a shared-memory window of 48-byte rows; parents beyond the window
+//     (and all parents in team mode) travel through a 48-byte-row buffer that stays L2-resident; the levels present
+//     in a chunk are walked in order with a named barrier (compute warps only) between them;
+//   * cull compaction: __ballot_sync gives the 32-entity mask word, __popc prefix inside the warp and a dp4a scan over
+//     the warps' count bytes give each visible entity its slot in the ASCENDING index list — never unordered atomics;
+//   * outputs overwrite the thread's own (dead) column of the ring stage and leave through bulk stores issued by the
+//     TMA warp; the last CTA publishes the batch statistics (and the per-generation snapshot ring).
 #include <algorithm>
 #include <cstdlib>
 #include <vector>
