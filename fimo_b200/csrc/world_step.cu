@@ -102,6 +102,14 @@ template <int kThreads> __device__ __forceinline__ void consumer_sync() { // the
 }
 
 
+// Debug build switch (make TIMING=1): per-CTA clock64 accounting of where the chunk loop's time goes, printed every 16th
+// launch when FIMO_B200_TIMING=1 and the group runs without a CUDA graph.  Compiled out by default.
+#ifdef FIMO_B200_TIMING_BUILD
+constexpr bool kTimingBuild = true;
+#else
+constexpr bool kTimingBuild = false;
+#endif
+
 struct PipeArgs {
     StepArgs a;
     uint32_t stages;   // ring depth (chunks)
@@ -116,6 +124,11 @@ struct PipeArgs {
     // Team mode: entities of (world, level) whose matrices are visible in `rows` — the dataflow counters the
     // CTAs of a team synchronise on ([n_worlds][kMaxLevels], zeroed by the compaction kernel).
     uint32_t *lvl_done;
+    // FIMO_B200_TIMING=1 (debug, plain stream launches only): thread 0 of every CTA accumulates clock64 ticks spent
+    // [0] waiting for chunk inputs, [1] waiting for a level to complete, [2] in the whole chunk loop, [3] chunks,
+    // [4] prefetch section (team mode), [5] thread 0 waiting for its parent row, [6] chunks whose rows were prefetched,
+    // [7] the longest chunk loop of any CTA.
+    unsigned long long *timing;
 };
 
 constexpr uint32_t kPipeVelClamp = 8u;         // kSet 1: vel_clamp sits between forces and integrate_lin
@@ -367,6 +380,8 @@ __global__ void __launch_bounds__(T + 32, kMinBlocks) k_world_step_pipe(const Pi
     float *waabb_out = nullptr;
     uint32_t *mask2_out = nullptr, *list2_out = nullptr, *sleep_out = nullptr, *lod_out = nullptr;
 
+    long long tm_input = 0, tm_level = 0, tm_pre = 0, tm_gather = 0, tm_prefetched = 0;
+    const long long tm_begin = (kTimingBuild && pa.timing && tid == 0) ? clock64() : 0;
     for (uint32_t it = 0; it < total; it++) {
         const WorldConst &wc = s_c[k & 1];
         if (c == wk.rank) { // a new world begins
@@ -396,12 +411,15 @@ __global__ void __launch_bounds__(T + 32, kMinBlocks) k_world_step_pipe(const Pi
         const bool may_be_parent = l_me + 1 < levels;
         if (kTeam && pend_level >= 0 && (int)l_lo > pend_level) flush_pending(lvl_done); // moved past that level
 
+        const long long t_in0 = (kTimingBuild && pa.timing && tid == 0) ? clock64() : 0;
         mbar_wait(&full[s], parity);
+        if (kTimingBuild && pa.timing && tid == 0) tm_input += clock64() - t_in0;
         float *st = ring + (size_t)s * kStage * T + tid;
         float lo[3] = {FIMO_B200_BOUNDS_EMPTY_MIN, FIMO_B200_BOUNDS_EMPTY_MIN, FIMO_B200_BOUNDS_EMPTY_MIN};
         float hi[3] = {-FIMO_B200_BOUNDS_EMPTY_MIN, -FIMO_B200_BOUNDS_EMPTY_MIN, -FIMO_B200_BOUNDS_EMPTY_MIN};
         bool vis = false, vis2 = false, asleep = false;
         bool pre_next = false;
+        const long long t_pre0 = (kTimingBuild && kTeam && pa.timing && tid == 0) ? clock64() : 0;
         if (kTeam) {
             // Parent rows come from L2 (~1 us under load): fetch the NEXT chunk's rows now, asynchronously and
             // without registers (cp.async), so that this chunk's arithmetic covers the latency.  Safe when this
@@ -425,6 +443,7 @@ __global__ void __launch_bounds__(T + 32, kMinBlocks) k_world_step_pipe(const Pi
                 }
             }
             cp_async_commit(); // one group per iteration, possibly empty
+            if (kTimingBuild && pa.timing && tid == 0) tm_pre += clock64() - t_pre0, tm_prefetched += pre_next ? 1 : 0;
         }
         for (uint32_t l = l_lo; l <= l_hi; l++) {
             if (kTeam && l >= 1 && ready_upto < (int)l - 1) {
@@ -432,7 +451,9 @@ __global__ void __launch_bounds__(T + 32, kMinBlocks) k_world_step_pipe(const Pi
                 // every entity of level l-1 — in whichever CTA's chunk — must be visible in `rows`
                 if (tid == 0) {
                     const uint32_t need = wc.ls[l] - wc.ls[l - 1];
+                    const long long t_lv0 = (kTimingBuild && pa.timing) ? clock64() : 0;
                     while (ld_acquire_gpu(lvl_done + (l - 1)) < need) __nanosleep(64);
+                    if (kTimingBuild && pa.timing) tm_level += clock64() - t_lv0;
                 }
                 consumer_sync<T>();
                 ready_upto = (int)l - 1;
@@ -469,12 +490,16 @@ __global__ void __launch_bounds__(T + 32, kMinBlocks) k_world_step_pipe(const Pi
                     if (!kTeam && p < cap) {
                         r0 = s_win[3 * p], r1 = s_win[3 * p + 1], r2 = s_win[3 * p + 2];
                     } else if (kTeam && pre_have) {
+                        const long long t_g0 = (kTimingBuild && pa.timing && tid == 0) ? clock64() : 0;
                         cp_async_wait_all_but_latest(); // the group committed one iteration ago
                         const float4 *row = s_pre + ((size_t)(it & 1) * T + tid) * 3;
                         r0 = row[0], r1 = row[1], r2 = row[2];
+                        if (kTimingBuild && pa.timing && tid == 0) tm_gather += clock64() - t_g0;
                     } else { // beyond the shared-memory window: the parent's row comes back through L2
                         const float4 *row = rows + (uint64_t)p * 3;
+                        const long long t_g0 = (kTimingBuild && pa.timing && tid == 0) ? clock64() : 0;
                         r0 = __ldcg(row), r1 = __ldcg(row + 1), r2 = __ldcg(row + 2);
+                        if (kTimingBuild && pa.timing && tid == 0) tm_gather += (long long)(r0.x != r1.x) * 0 + clock64() - t_g0;
                     }
                     const float P[12] = {r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, r1.w, r2.x, r2.y, r2.z, r2.w};
                     compose(Wm, P, L);
@@ -639,6 +664,16 @@ __global__ void __launch_bounds__(T + 32, kMinBlocks) k_world_step_pipe(const Pi
         pre_have = pre_next;
     }
 
+    if (kTimingBuild && pa.timing && tid == 0) {
+        atomicAdd(pa.timing + 0, (unsigned long long)tm_input);
+        atomicAdd(pa.timing + 1, (unsigned long long)tm_level);
+        atomicAdd(pa.timing + 2, (unsigned long long)(clock64() - tm_begin));
+        atomicAdd(pa.timing + 3, (unsigned long long)total);
+        atomicAdd(pa.timing + 4, (unsigned long long)tm_pre);
+        atomicAdd(pa.timing + 5, (unsigned long long)tm_gather);
+        atomicAdd(pa.timing + 6, (unsigned long long)tm_prefetched);
+        atomicMax(pa.timing + 7, (unsigned long long)(clock64() - tm_begin));
+    }
     if (!kTeam) { // fold the per-warp mask sums, publish the batch statistics
         if (lane == 0) atomicAdd(&s_sum, warp_mask_sum);
         if (kSet == 2 && lane == 0) atomicAdd(&s_sum2, warp_mask_sum2);
@@ -946,6 +981,11 @@ FimoStatus world_step_launch(const WorldStepViews &v, const WorldStepPlan &plan,
         pa.chunks = (uint32_t)((E + plan.threads - 1) / plan.threads);
         pa.rows = (float4 *)plan.rows.get();
         pa.lvl_done = (uint32_t *)plan.lvl_done.get();
+        static unsigned long long *timing_buf = nullptr; // debug only (FIMO_B200_TIMING=1 with plain stream launches)
+        static int timing_launches = 0;
+        const bool timing = kTimingBuild && std::getenv("FIMO_B200_TIMING") != nullptr && !(info->flags & FIMO_B200_LAUNCH_FLAG_CAPTURING);
+        if (timing && !timing_buf) timing_buf = (unsigned long long *)hbm_alloc(info->device, 8 * sizeof(unsigned long long));
+        pa.timing = timing ? timing_buf : nullptr;
         pa.flags = kPipePrefetchBlocking; // FIMO_B200_PREFETCH=0 / 1 (only if already landed) / 2 (default)
         if (const char *env = std::getenv("FIMO_B200_PREFETCH"))
             pa.flags = (pa.flags & ~kPipePrefetchBlocking) | (env[0] == '0' ? kPipeNoPrefetch : (env[0] == '2' ? kPipePrefetchBlocking : 0u));
@@ -982,6 +1022,26 @@ FimoStatus world_step_launch(const WorldStepViews &v, const WorldStepPlan &plan,
             a.bounds_keys2 = (int *)plan.bounds2.get();
         }
         const int key = plan.threads * 100 + (int)plan.blocks_per_sm * 10 + (int)plan.set;
+        struct TimingReport { // prints the accumulated ticks every 16th launch, after the launch below has been enqueued
+            bool on;
+            int device;
+            cudaStream_t stream;
+            ~TimingReport() {
+                if (!on || (++timing_launches % 16) != 0) return;
+                cudaStreamSynchronize(stream);
+                unsigned long long t[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+                hbm_download(device, t, timing_buf, sizeof t);
+                cudaMemsetAsync(timing_buf, 0, sizeof t, stream);
+                const double loop = (double)(t[2] ? t[2] : 1), chunks = (double)(t[3] ? t[3] : 1);
+                std::fprintf(stderr,
+                             "fimo_worlds_b200 timing (16 launches): of the chunk loop: input wait %.1f%%, level wait %.1f%%, prefetch section %.1f%%, "
+                             "row wait (thread 0) %.1f%%; %.0f ticks per chunk, %.0f%% of chunks prefetched; longest CTA loop %.0f ticks = %.2fx the mean\n",
+                             100.0 * t[0] / loop, 100.0 * t[1] / loop, 100.0 * t[4] / loop, 100.0 * t[5] / loop, loop / chunks, 100.0 * t[6] / chunks,
+                             (double)t[7], (double)t[7] * 16.0 * (double)grid_ctas / loop);
+            }
+            unsigned grid_ctas;
+        } report{timing, info->device, (cudaStream_t)info->stream,
+                 plan.team > 1 ? plan.team * plan.teams : (unsigned)((W + ((W + (uint64_t)plan.blocks_per_sm * sm_count(info->device) - 1) / ((uint64_t)plan.blocks_per_sm * sm_count(info->device))) - 1) / ((W + (uint64_t)plan.blocks_per_sm * sm_count(info->device) - 1) / ((uint64_t)plan.blocks_per_sm * sm_count(info->device))))};
         switch (key) {
         case 12840: case 12830: case 12820: case 12810: return launch_pipe<128, 4, 0>(pa, plan, W, info);
         case 12850: return launch_pipe<128, 5, 0>(pa, plan, W, info);
