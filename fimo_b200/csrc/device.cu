@@ -105,6 +105,14 @@ struct Executor {
     double span_ms = 0.0;              // anchor -> end of the latest generation (includes inter-generation gaps)
     std::atomic<double> last_ms{0.0};  // device time of the generation being retired
 
+    // Staged uploads (executor_launch): the next generation's inputs cross PCIe on `copy_stream` into one of two HBM
+    // staging slots while the previous generation still runs; in stream order only a device-to-device copy remains.
+    cudaStream_t copy_stream = nullptr;
+    void *staging[2] = {nullptr, nullptr};
+    size_t staging_bytes = 0;
+    cudaEvent_t staged[2] = {nullptr, nullptr}, slot_free[2] = {nullptr, nullptr};
+    uint64_t staged_count = 0;
+
     cudaEvent_t take_event() {
         {
             std::lock_guard<std::mutex> g(m);
@@ -293,6 +301,18 @@ Executor *executor_create(int device) {
         delete ex;
         return nullptr;
     }
+    // Without the copy stream uploads simply take the in-order path.
+    int least = 0, greatest = 0;
+    cudaDeviceGetStreamPriorityRange(&least, &greatest);
+    bool staged = cudaStreamCreateWithPriority(&ex->copy_stream, cudaStreamNonBlocking, greatest) == cudaSuccess;
+    for (int i = 0; i < 2 && staged; i++)
+        staged = cudaEventCreateWithFlags(&ex->staged[i], cudaEventDisableTiming) == cudaSuccess &&
+                 cudaEventCreateWithFlags(&ex->slot_free[i], cudaEventDisableTiming) == cudaSuccess;
+    if (!staged) {
+        cudaGetLastError();
+        if (ex->copy_stream) cudaStreamDestroy(ex->copy_stream);
+        ex->copy_stream = nullptr;
+    }
     return ex;
 }
 
@@ -311,6 +331,15 @@ void executor_destroy(Executor *ex) {
     for (cudaEvent_t e : ex->node_events) cudaEventDestroy(e);
     if (ex->fork_event) cudaEventDestroy(ex->fork_event);
     for (cudaStream_t s : ex->lanes) cudaStreamDestroy(s);
+    if (ex->copy_stream) {
+        cudaStreamSynchronize(ex->copy_stream);
+        cudaStreamDestroy(ex->copy_stream);
+    }
+    for (int i = 0; i < 2; i++) {
+        if (ex->staged[i]) cudaEventDestroy(ex->staged[i]);
+        if (ex->slot_free[i]) cudaEventDestroy(ex->slot_free[i]);
+        if (ex->staging[i]) cudaFree(ex->staging[i]);
+    }
     cudaStreamDestroy(ex->stream);
     delete ex;
 }
@@ -354,7 +383,7 @@ struct IoBatch {
     const void *src[kIoMaxCopies];
     unsigned long long bytes[kIoMaxCopies];
 };
-__global__ void __launch_bounds__(256) k_io_copy(const IoBatch b) {
+__global__ void __launch_bounds__(128) k_io_copy(const IoBatch b) {
     const int c = blockIdx.y;
     const unsigned long long bytes = b.bytes[c];
     const size_t stride = (size_t)gridDim.x * blockDim.x, first = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -379,11 +408,19 @@ void *device_alias(const void *host) {
     return attr.type == cudaMemoryTypeHost ? attr.devicePointer : nullptr;
 }
 
-bool enqueue_copies(cudaStream_t stream, const Copy *copies, size_t n, bool to_device) {
+bool launch_io_batch(cudaStream_t stream, const IoBatch &batch, size_t n, size_t largest) {
+    // 128-thread CTAs at <= 32 registers fit beside the resident world-step CTAs, so the staged PCIe leg can overlap them
+    const unsigned blocks = (unsigned)std::min<size_t>(std::max<size_t>((largest / 16 + 127) / 128, 1), 296);
+    k_io_copy<<<dim3(blocks, (unsigned)n), 128, 0, stream>>>(batch);
+    return ok(cudaGetLastError(), "k_io_copy");
+}
+
+// `ex` != nullptr (uploads only): stage through the executor's HBM slots on its copy stream, see Executor::staging.
+bool enqueue_copies(cudaStream_t stream, const Copy *copies, size_t n, bool to_device, Executor *ex = nullptr) {
     if (n == 0) return true;
     bool by_kernel = n <= (size_t)kIoMaxCopies && !std::getenv("FIMO_B200_IO_MEMCPY");
     IoBatch batch{};
-    size_t total = 0, largest = 0;
+    size_t total = 0, largest = 0, padded = 0;
     for (size_t i = 0; i < n && by_kernel; i++) {
         void *alias = device_alias(to_device ? copies[i].src : copies[i].dst);
         if (!alias || copies[i].bytes % 4) by_kernel = false;
@@ -391,12 +428,41 @@ bool enqueue_copies(cudaStream_t stream, const Copy *copies, size_t n, bool to_d
         batch.src[i] = to_device ? alias : copies[i].src;
         batch.bytes[i] = copies[i].bytes;
         total += copies[i].bytes, largest = std::max(largest, copies[i].bytes);
+        padded += (copies[i].bytes + 15 + 255) & ~(size_t)255;
     }
-    if (by_kernel && total <= kIoMaxBytes) {
-        const unsigned blocks = (unsigned)std::min<size_t>(std::max<size_t>((largest / 16 + 255) / 256, 1), 148);
-        k_io_copy<<<dim3(blocks, (unsigned)n), 256, 0, stream>>>(batch);
-        return ok(cudaGetLastError(), "k_io_copy");
+    if (by_kernel && total <= kIoMaxBytes && ex && to_device && ex->copy_stream && !std::getenv("FIMO_B200_IO_NO_STAGING")) {
+        if (!ex->staging[0] && padded <= kIoMaxBytes) { // slots are made once; a later, larger batch takes the direct path
+            const size_t want = std::max<size_t>(padded, 1u << 20);
+            if (cudaMalloc(&ex->staging[0], want) == cudaSuccess && cudaMalloc(&ex->staging[1], want) == cudaSuccess) ex->staging_bytes = want;
+            else cudaGetLastError();
+        }
+        if (padded <= ex->staging_bytes) {
+            const int slot = (int)(ex->staged_count & 1);
+            IoBatch in = batch, out = batch;
+            size_t at = 0;
+            for (size_t i = 0; i < n; i++) {
+                // keep the slot address congruent to the resource pointer modulo 16 so that the device-to-device
+                // leg stays on the 128-bit path
+                char *p = (char *)ex->staging[slot] + at + ((uintptr_t)batch.dst[i] & 15u);
+                in.dst[i] = p, out.src[i] = p;
+                at += (copies[i].bytes + 15 + 255) & ~(size_t)255;
+            }
+            bool queued = true;
+            if (ex->staged_count >= 2) queued = ok(cudaStreamWaitEvent(ex->copy_stream, ex->slot_free[slot], 0), "cudaStreamWaitEvent");
+            // The PCIe leg goes to the copy engine: it runs beside the resident world-step CTAs whatever they occupy
+            // (a copy kernel on the side stream waits for free SM resources and hides nothing: measured).
+            for (size_t i = 0; i < n && queued; i++)
+                queued = ok(cudaMemcpyAsync(in.dst[i], copies[i].src, copies[i].bytes, cudaMemcpyHostToDevice, ex->copy_stream),
+                            "cudaMemcpyAsync H2D (staging)");
+            queued = queued && ok(cudaEventRecord(ex->staged[slot], ex->copy_stream), "cudaEventRecord");
+            queued = queued && ok(cudaStreamWaitEvent(stream, ex->staged[slot], 0), "cudaStreamWaitEvent");
+            queued = queued && launch_io_batch(stream, out, n, largest);
+            queued = queued && ok(cudaEventRecord(ex->slot_free[slot], stream), "cudaEventRecord");
+            ex->staged_count++;
+            return queued;
+        }
     }
+    if (by_kernel && total <= kIoMaxBytes) return launch_io_batch(stream, batch, n, largest);
     for (size_t i = 0; i < n; i++)
         if (!ok(cudaMemcpyAsync(copies[i].dst, copies[i].src, copies[i].bytes, to_device ? cudaMemcpyHostToDevice : cudaMemcpyDeviceToHost, stream),
                 to_device ? "cudaMemcpyAsync H2D" : "cudaMemcpyAsync D2H"))
@@ -411,11 +477,13 @@ bool executor_launch(Executor *ex, void (*done)(void *), void *user, const Copy 
     Completion c{ex->take_event(), ex->take_event(), ex, done, user};
     if (!c.start || !c.end) return false;
     if (n_down && !(c.landed = ex->take_event())) return false;
+    bool busy;
     {
         std::lock_guard<std::mutex> g(ex->m);
-        ex->in_flight++;
+        busy = ex->in_flight++ > 0;
     }
-    bool launched = enqueue_copies(ex->stream, uploads, n_up, true); // this generation's inputs, in stream order in front of it
+    // staging pays only when an earlier generation is still running for the PCIe leg to hide behind
+    bool launched = enqueue_copies(ex->stream, uploads, n_up, true, busy ? ex : nullptr); // this generation's inputs, in stream order in front of it
     launched = ok(cudaEventRecord(c.start, ex->stream), "cudaEventRecord") && launched;
     if (launched) {
         if (ex->use_graph) launched = ok(cudaGraphLaunch(ex->graph_exec, ex->stream), "cudaGraphLaunch");

@@ -225,33 +225,38 @@ def test_stream_ordered_transfers_match_locked_host_access(oracle, product):
     assert not problems, "\n".join(problems)
 
 
-@pytest.mark.parametrize("pinned", [False, True])
+@pytest.mark.parametrize("pinned", [False, True, "misaligned"], ids=["pageable", "pinned", "pinned-misaligned"])
 def test_schedule_io_steps_in_flight_match_oracle(oracle, product, pinned):
     """fimo_b200_group_schedule_io: generations with their own input uploads and result downloads, several in
     flight, each with its own host buffers: every step's downloaded result equals the oracle's after the same
     uploads, and generation numbers advance by one per call.  pinned: page-locked buffers (fimo_b200_host_alloc) —
-    the whole batch of small copies is one kernel that addresses host memory directly; pageable: the copy engine."""
+    the whole batch of small copies is one kernel that addresses host memory directly, uploads staged through HBM
+    slots on the executor's copy stream while earlier generations run; misaligned: the same with host pointers that
+    are only 4-byte aligned (32-bit copy path); pageable: the copy engine."""
     from fimo_b200.worlds import Fence
 
-    W, E, D, K = 8, 512, 4, 6
+    W, E, D, K = 8, 512, 4, 9
     data = synth.generate(W, E, D)
     frusta = [synth.generate(W, E, D, world0=100 * (i + 1))["frustum"] for i in range(K)]
+    dts = [(data["dt"] * np.float32(1.0 + 0.25 * i)).astype(np.float32) for i in range(K)]
     locked = []
 
     def buffer_like(a):
         if not pinned:
             return np.empty_like(a)
-        ptr = product.fimo_b200_host_alloc(a.nbytes)
+        skew = 4 if pinned == "misaligned" else 0
+        ptr = product.fimo_b200_host_alloc(a.nbytes + skew)
         assert ptr
         locked.append(ptr)
         import ctypes as C
-        return np.ctypeslib.as_array(C.cast(ptr, C.POINTER(C.c_uint32)), shape=(a.size,)).view(a.dtype).reshape(a.shape)
+        return np.ctypeslib.as_array(C.cast(ptr + skew, C.POINTER(C.c_uint32)), shape=(a.size,)).view(a.dtype).reshape(a.shape)
 
     ref = synth.WorldStepRig(oracle, W, E, D, data={k: v.copy() for k, v in data.items()})
     want = []
     try:
         for i in range(K):
             ref.upload("frustum", frusta[i])
+            ref.upload("dt", dts[i])
             ref.step(1)
             want.append(ref.download(("vis_count", "stats", "vis_mask")))
     finally:
@@ -263,9 +268,9 @@ def test_schedule_io_steps_in_flight_match_oracle(oracle, product, pinned):
         got = [{n: buffer_like(rig.host[n]) for n in ("vis_count", "stats", "vis_mask")} for _ in range(K)]
         lists = []
         for i in range(K):  # all K steps queued before any is waited for
-            src = buffer_like(frusta[i])
-            src[...] = frusta[i]
-            up, down = rig.io_list({"frustum": src}), rig.io_list(got[i])
+            src, src_dt = buffer_like(frusta[i]), buffer_like(dts[i])
+            src[...], src_dt[...] = frusta[i], dts[i]
+            up, down = rig.io_list({"frustum": src, "dt": src_dt}), rig.io_list(got[i])
             lists.append((up, down))
             rig.schedule_io(up, down, fences[i])
         for f in fences:
