@@ -130,7 +130,11 @@ struct WorldStepPlan {
     uint32_t max_parents = 0;   // max over worlds of level_start[levels-1] when the plan was made
     uint32_t team = 1;          // CTAs that step one world together (> 1: large worlds / few worlds)
     uint32_t teams = 0;         // worlds in flight = grid / team
-    uint32_t kernels = 1;       // launches per generation (team mode adds the list-compaction kernel)
+    uint32_t kernels = 1;       // launches per generation (team mode adds the list-compaction kernel, a tail grid one launch)
+    // One CTA per world: the persistent grid steps worlds [0, tail_first) in whole rounds, a second grid launched
+    // beside it steps [tail_first, n_worlds) one world per CTA as slots free up (tail_first == n_worlds: no tail).
+    uint32_t grid = 0, tail_first = 0;
+    std::shared_ptr<void> tail;     // side stream + fork / join events of the tail grid
     size_t smem = 0;            // dynamic shared memory per CTA
     std::shared_ptr<void> rows;     // HBM: [n_worlds][E] 48-byte parent rows (parents outside the window)
     std::shared_ptr<void> lvl_done; // HBM: [n_worlds][32] level-completion counters (team mode)

@@ -117,6 +117,10 @@ struct PipeArgs {
     uint32_t chunks;   // chunks per world = ceil(E / T)
     uint32_t team;     // CTAs that step one world together (1 = a world belongs to one CTA)
     uint32_t teams;    // gridDim.x / team
+    // The worlds this launch steps: [world_first, world_end).  One generation of a one-CTA-per-world plan is two
+    // launches — a persistent grid over whole rounds of worlds and a tail grid of one world per CTA (launch_pipe) —
+    // whose CTAs share one completion ticket: `stat_ctas` CTAs in all.
+    uint32_t world_first, world_end, stat_ctas, trace_base;
     // Parent matrices that do not fit the shared-memory window: [n_worlds][E] rows of 48 bytes in HBM, written
     // by whoever computes the parent and read back through L2 with three 128-bit loads.  nullptr if unused.
     float4 *rows;
@@ -131,6 +135,7 @@ struct PipeArgs {
     unsigned long long *timing;
 };
 
+constexpr uint32_t kTimingCtas = 4096;      // timing build: CTAs whose (smid, start ns, end ns, chunks) are recorded
 constexpr uint32_t kPipeVelClamp = 8u;         // kSet 1: vel_clamp sits between forces and integrate_lin
 constexpr uint32_t kPipePublishPerChunk = 2u; // FIMO_B200_PUBLISH=chunk: announce level progress after every chunk
 constexpr uint32_t kPipePrefetchBlocking = 4u; // FIMO_B200_PREFETCH=2: wait for the next chunk's inputs before this chunk's math
@@ -162,13 +167,14 @@ __device__ __forceinline__ const uint32_t *plane_src(const StepArgs &a, int p, u
     return uptr(a.angvel, w) + (uint64_t)(p - 18) * E;
 }
 
-// Work of one CTA: worlds team_id, team_id + teams, ... and of each world the chunks rank, rank + team, ...
+// Work of one CTA: worlds world_first + team_id, + teams, ... (below world_end) and of each world the chunks rank, rank + team, ...
 struct Walk {
-    uint32_t team_id, rank, my_worlds, my_chunks, total;
+    uint32_t team_id, rank, my_worlds, my_chunks, total, first_world;
     __device__ __forceinline__ Walk(const PipeArgs &pa) {
         team_id = blockIdx.x / pa.team;
         rank = blockIdx.x % pa.team;
-        my_worlds = pa.a.n_worlds > team_id ? (pa.a.n_worlds - team_id + pa.teams - 1) / pa.teams : 0;
+        first_world = pa.world_first + team_id;
+        my_worlds = pa.world_end > first_world ? (pa.world_end - first_world + pa.teams - 1) / pa.teams : 0;
         my_chunks = pa.chunks > rank ? (pa.chunks - rank + pa.team - 1) / pa.team : 0;
         total = my_worlds * my_chunks;
     }
@@ -185,7 +191,7 @@ __device__ __forceinline__ void tma_warp(const PipeArgs &pa, const Walk &wk, flo
     uint32_t k = 0, c = wk.rank, s = 0, round = 0; // position of the chunk being loaded
     uint32_t sk = 0, sc = wk.rank;                  // position of the chunk being stored (N behind)
     auto store_chunk = [&](uint32_t stage, uint32_t wk_, uint32_t wc) {
-        const uint64_t w = wk.team_id + (uint64_t)wk_ * pa.teams;
+        const uint64_t w = wk.first_world + (uint64_t)wk_ * pa.teams;
         const uint32_t first = wc * T, bytes = min((uint32_t)T, E - first) * 4u;
         const float *st = ring + (size_t)stage * kStage * T;
         float *world = fptr(a.world, w) + first;
@@ -216,7 +222,7 @@ __device__ __forceinline__ void tma_warp(const PipeArgs &pa, const Walk &wk, flo
             if ((sc += G) >= nc) sc = wk.rank, sk++;
             bulk_wait_read_all();
         }
-        const uint64_t w = wk.team_id + (uint64_t)k * pa.teams;
+        const uint64_t w = wk.first_world + (uint64_t)k * pa.teams;
         const uint32_t first = c * T, bytes = min((uint32_t)T, E - first) * 4u; // multiple of 16 (E % 4 == 0)
         float *st = ring + (size_t)s * kStage * T;
         mbar_expect_tx(&full[s], bytes * kIn);
@@ -352,7 +358,7 @@ __global__ void __launch_bounds__(T + 32, kMinBlocks) k_world_step_pipe(const Pi
             if (tid >= 94 && tid < 97) c.lod_dist2[tid - 94] = __uint_as_float(v);
         }
     };
-    if (total) publish_const(s_c[0], const_word(wk.team_id));
+    if (total) publish_const(s_c[0], const_word(wk.first_world));
     consumer_sync<T>();
 
     uint32_t next_const = 0;
@@ -373,7 +379,7 @@ __global__ void __launch_bounds__(T + 32, kMinBlocks) k_world_step_pipe(const Pi
     };
     bool pre_have = false; // team mode: this thread's parent row of the current chunk is (being) prefetched into s_pre
     int ready_upto = -1; // team mode: levels [0, ready_upto] of the current world are known to be complete
-    uint64_t w = wk.team_id;
+    uint64_t w = wk.first_world;
     uint32_t *mask_out = nullptr, *list_out = nullptr;
     float4 *rows = nullptr;
     uint32_t *lvl_done = nullptr;
@@ -382,6 +388,8 @@ __global__ void __launch_bounds__(T + 32, kMinBlocks) k_world_step_pipe(const Pi
 
     long long tm_input = 0, tm_level = 0, tm_pre = 0, tm_gather = 0, tm_prefetched = 0;
     const long long tm_begin = (kTimingBuild && pa.timing && tid == 0) ? clock64() : 0;
+    unsigned long long tm_wall0 = 0;
+    if (kTimingBuild && pa.timing && tid == 0) asm volatile("mov.u64 %0, %globaltimer;" : "=l"(tm_wall0));
     for (uint32_t it = 0; it < total; it++) {
         const WorldConst &wc = s_c[k & 1];
         if (c == wk.rank) { // a new world begins
@@ -673,6 +681,14 @@ __global__ void __launch_bounds__(T + 32, kMinBlocks) k_world_step_pipe(const Pi
         atomicAdd(pa.timing + 5, (unsigned long long)tm_gather);
         atomicAdd(pa.timing + 6, (unsigned long long)tm_prefetched);
         atomicMax(pa.timing + 7, (unsigned long long)(clock64() - tm_begin));
+        if (pa.trace_base + blockIdx.x < kTimingCtas) { // per-CTA trace of the latest launch: where it ran, when, for how long
+            unsigned long long wall1;
+            unsigned smid;
+            asm volatile("mov.u64 %0, %globaltimer;" : "=l"(wall1));
+            asm volatile("mov.u32 %0, %smid;" : "=r"(smid));
+            unsigned long long *row = pa.timing + 8 + 4 * (size_t)(pa.trace_base + blockIdx.x);
+            row[0] = smid, row[1] = tm_wall0, row[2] = wall1, row[3] = (unsigned long long)total;
+        }
     }
     if (!kTeam) { // fold the per-warp mask sums, publish the batch statistics
         if (lane == 0) atomicAdd(&s_sum, warp_mask_sum);
@@ -687,10 +703,10 @@ __global__ void __launch_bounds__(T + 32, kMinBlocks) k_world_step_pipe(const Pi
         }
         consumer_sync<T>();
         if (tid == 0) {
-            publish_stats<kSet >= 1>(a, cta_visible, s_sum, my_worlds, (unsigned long long)gridDim.x);
+            publish_stats<kSet >= 1>(a, cta_visible, s_sum, my_worlds, (unsigned long long)pa.stat_ctas);
             if (kSet == 2)
                 publish_stats_to<true>(StatsSink{a.stats2, a.scratch2, a.gstats2, a.bounds_keys2, a.entities}, cta_visible2, s_sum2,
-                                       my_worlds, (unsigned long long)gridDim.x);
+                                       my_worlds, (unsigned long long)pa.stat_ctas);
         }
     }
 }
@@ -767,6 +783,17 @@ __global__ void __launch_bounds__(kCompactThreads) k_compact_lists(const StepArg
 namespace {
 
 bool aligned16(const FimoB200_ResourceView *v) { return v && ((uintptr_t)v->device_ptr % 16) == 0; }
+
+// Side stream and fork / join events of a plan's tail grid (WorldStepPlan::tail).
+struct TailLaunch {
+    cudaStream_t stream = nullptr;
+    cudaEvent_t fork = nullptr, join = nullptr;
+    ~TailLaunch() {
+        if (stream) cudaStreamDestroy(stream);
+        if (fork) cudaEventDestroy(fork);
+        if (join) cudaEventDestroy(join);
+    }
+};
 
 constexpr size_t kSmemPerSm = 227 * 1024;  // usable by CTAs on sm_100a
 constexpr size_t kSmemPerCtaReserve = 1024; // the hardware reserves 1 KB per resident CTA
@@ -922,6 +949,43 @@ bool world_step_plan(const WorldStepViews &v, int device, WorldStepPlan &plan) {
         plan.lvl_done = hbm_shared(device, (size_t)W * kMaxLevels * 4);
         if (!plan.lvl_done) return false;
     }
+    if (plan.team == 1) {
+        // Persistent grid with an even share of worlds per CTA: a ragged tail costs more than idle CTA slots on an
+        // HBM-bound kernel.
+        const uint64_t per_cta = std::max<uint64_t>((W + slots - 1) / slots, 1);
+        plan.grid = (uint32_t)((W + per_cta - 1) / per_cta), plan.tail_first = (uint32_t)W;
+        // CTAs do not all run at the same speed.  On the 8-system set whole groups of SMs (by %smid, the same ones every
+        // launch) step their chunks 5-16 % slower than the rest, so with an even static share the kernel ends with its
+        // slowest CTA, 1.23x the mean (profiles/r1zc_cta_trace.txt).  There the last round of worlds is not assigned
+        // ahead: it is a second grid of one-world CTAs launched beside the persistent one, and the hardware block
+        // scheduler hands them to whichever SM frees a slot first (4096 worlds 0.80 -> 0.84 of the HBM peak, 8192
+        // worlds 0.82 -> 0.88).  World ids stay arithmetic on blockIdx and kernel parameters in both grids (uniform
+        // datapath in the TMA thread; an atomic world queue inside the kernel is not, r1z_world_queue_experiment.txt).
+        // The 3-system chain and the 16-system set show no slow SM groups — only a ~10 % spread between the CTAs of one
+        // SM — and a one-world CTA's prologue and statistics epilogue cost them more than the tail returns (-1.5 % /
+        // -0.5 %), so they keep one grid.  FIMO_B200_TAIL=0 disables, =n moves about n rounds to the tail for any set.
+        uint64_t tail_rounds = plan.set == 1 ? 1 : 0;
+        if (const char *env = std::getenv("FIMO_B200_TAIL")) tail_rounds = std::strtoull(env, nullptr, 10);
+        const uint64_t rounds = W / slots; // whole rounds the batch fills
+        if (tail_rounds && rounds >= 2) { // single-round batches: measured slower (one-world CTAs everywhere)
+            // the remainder always goes to the tail; whole rounds join it until it holds at least tail_rounds - 1/2 rounds
+            uint64_t fixed = rounds;
+            while (fixed > 1 && (W - fixed * slots) * 2 < (2 * tail_rounds - 1) * slots) fixed--;
+            if (W - fixed * slots > 0) {
+                auto tail = std::make_shared<TailLaunch>();
+                int previous = -1; // the calling thread may belong to anyone: create on the plan's device, restore
+                if (cudaGetDevice(&previous) != cudaSuccess) previous = -1, (void)cudaGetLastError();
+                (void)cudaSetDevice(resolve_device(device));
+                if (cudaStreamCreateWithFlags(&tail->stream, cudaStreamNonBlocking) == cudaSuccess &&
+                    cudaEventCreateWithFlags(&tail->fork, cudaEventDisableTiming) == cudaSuccess &&
+                    cudaEventCreateWithFlags(&tail->join, cudaEventDisableTiming) == cudaSuccess) {
+                    plan.grid = (uint32_t)slots, plan.tail_first = (uint32_t)(fixed * slots), plan.kernels = 2;
+                    plan.tail = tail;
+                } else cudaGetLastError();
+                if (previous >= 0) (void)cudaSetDevice(previous);
+            }
+        }
+    }
     plan.rows = hbm_shared(device, (size_t)W * E * 48);
     return plan.rows != nullptr;
 }
@@ -942,6 +1006,7 @@ FimoStatus launch_pipe(PipeArgs &pa, const WorldStepPlan &plan, uint64_t W, cons
         auto kernel = k_world_step_pipe<T, kBlocks, true, kSet>;
         if (!allow_smem(kernel, plan.smem)) return check_launch("world_step (shared memory opt-in)");
         pa.team = plan.team, pa.teams = plan.teams;
+        pa.world_first = 0, pa.world_end = (uint32_t)W, pa.stat_ctas = plan.team * plan.teams, pa.trace_base = 0;
         kernel<<<plan.team * plan.teams, T + 32, plan.smem, stream>>>(pa);
         if (check_launch("world_step") != FIMO_STATUS_OK) return FIMO_STATUS_ERROR;
         const unsigned segments = (pa.a.mask_words + kCompactThreads - 1) / kCompactThreads;
@@ -951,14 +1016,27 @@ FimoStatus launch_pipe(PipeArgs &pa, const WorldStepPlan &plan, uint64_t W, cons
     }
     auto kernel = k_world_step_pipe<T, kBlocks, false, kSet>;
     if (!allow_smem(kernel, plan.smem)) return check_launch("world_step (shared memory opt-in)");
-    // Persistent grid with an even share of worlds per CTA: a ragged tail costs more than idle CTA slots
-    // on an HBM-bound kernel.
-    const uint64_t slots = (uint64_t)plan.blocks_per_sm * sm_count(info->device);
-    const uint64_t per_cta = (W + slots - 1) / slots;
-    const unsigned grid = (unsigned)((W + per_cta - 1) / per_cta);
+    const unsigned grid = plan.grid, tail_ctas = (unsigned)(W - plan.tail_first); // two worlds per tail CTA: measured slower
     pa.team = 1, pa.teams = grid;
+    pa.world_first = 0, pa.world_end = plan.tail_first, pa.stat_ctas = grid + tail_ctas, pa.trace_base = 0;
+    if (!tail_ctas) {
+        kernel<<<grid, T + 32, plan.smem, stream>>>(pa);
+        return check_launch("world_step");
+    }
+    // fork: the persistent grid first (it takes every slot), the tail grid beside it on the plan's side stream; join.
+    // Under stream capture the two become parallel kernel nodes of the generation's graph.
+    const TailLaunch *tail = (const TailLaunch *)plan.tail.get();
+    if (cudaEventRecord(tail->fork, stream) != cudaSuccess) return check_launch("world_step (fork)");
     kernel<<<grid, T + 32, plan.smem, stream>>>(pa);
-    return check_launch("world_step");
+    if (check_launch("world_step") != FIMO_STATUS_OK) return FIMO_STATUS_ERROR;
+    if (cudaStreamWaitEvent(tail->stream, tail->fork, 0) != cudaSuccess) return check_launch("world_step (fork)");
+    PipeArgs pt = pa;
+    pt.teams = tail_ctas, pt.world_first = plan.tail_first, pt.world_end = (uint32_t)W, pt.trace_base = grid;
+    kernel<<<tail_ctas, T + 32, plan.smem, tail->stream>>>(pt);
+    if (check_launch("world_step (tail)") != FIMO_STATUS_OK) return FIMO_STATUS_ERROR;
+    if (cudaEventRecord(tail->join, tail->stream) != cudaSuccess || cudaStreamWaitEvent(stream, tail->join, 0) != cudaSuccess)
+        return check_launch("world_step (join)");
+    return FIMO_STATUS_OK;
 }
 } // namespace
 
@@ -984,7 +1062,7 @@ FimoStatus world_step_launch(const WorldStepViews &v, const WorldStepPlan &plan,
         static unsigned long long *timing_buf = nullptr; // debug only (FIMO_B200_TIMING=1 with plain stream launches)
         static int timing_launches = 0;
         const bool timing = kTimingBuild && std::getenv("FIMO_B200_TIMING") != nullptr && !(info->flags & FIMO_B200_LAUNCH_FLAG_CAPTURING);
-        if (timing && !timing_buf) timing_buf = (unsigned long long *)hbm_alloc(info->device, 8 * sizeof(unsigned long long));
+        if (timing && !timing_buf) timing_buf = (unsigned long long *)hbm_alloc(info->device, (8 + 4 * (size_t)kTimingCtas) * sizeof(unsigned long long));
         pa.timing = timing ? timing_buf : nullptr;
         pa.flags = kPipePrefetchBlocking; // FIMO_B200_PREFETCH=0 / 1 (only if already landed) / 2 (default)
         if (const char *env = std::getenv("FIMO_B200_PREFETCH"))
@@ -1031,6 +1109,16 @@ FimoStatus world_step_launch(const WorldStepViews &v, const WorldStepPlan &plan,
                 cudaStreamSynchronize(stream);
                 unsigned long long t[8] = {0, 0, 0, 0, 0, 0, 0, 0};
                 hbm_download(device, t, timing_buf, sizeof t);
+                if (const char *path = std::getenv("FIMO_B200_TIMING_DUMP")) { // per-CTA trace of the latest launch as CSV
+                    std::vector<unsigned long long> rows(4 * (size_t)kTimingCtas);
+                    hbm_download(device, rows.data(), timing_buf + 8, rows.size() * sizeof(unsigned long long));
+                    if (FILE *f = std::fopen(path, "w")) {
+                        std::fprintf(f, "cta,smid,start_ns,end_ns,chunks\n");
+                        for (unsigned i = 0; i < grid_ctas && i < kTimingCtas; i++)
+                            std::fprintf(f, "%u,%llu,%llu,%llu,%llu\n", i, rows[4 * i], rows[4 * i + 1], rows[4 * i + 2], rows[4 * i + 3]);
+                        std::fclose(f);
+                    }
+                }
                 cudaMemsetAsync(timing_buf, 0, sizeof t, stream);
                 const double loop = (double)(t[2] ? t[2] : 1), chunks = (double)(t[3] ? t[3] : 1);
                 std::fprintf(stderr,
@@ -1041,7 +1129,7 @@ FimoStatus world_step_launch(const WorldStepViews &v, const WorldStepPlan &plan,
             }
             unsigned grid_ctas;
         } report{timing, info->device, (cudaStream_t)info->stream,
-                 plan.team > 1 ? plan.team * plan.teams : (unsigned)((W + ((W + (uint64_t)plan.blocks_per_sm * sm_count(info->device) - 1) / ((uint64_t)plan.blocks_per_sm * sm_count(info->device))) - 1) / ((W + (uint64_t)plan.blocks_per_sm * sm_count(info->device) - 1) / ((uint64_t)plan.blocks_per_sm * sm_count(info->device))))};
+                 plan.team > 1 ? plan.team * plan.teams : plan.grid + (unsigned)(W - plan.tail_first)};
         switch (key) {
         case 12840: case 12830: case 12820: case 12810: return launch_pipe<128, 4, 0>(pa, plan, W, info);
         case 12850: return launch_pipe<128, 5, 0>(pa, plan, W, info);

@@ -1,12 +1,17 @@
-# final verification of main: GPU tests, smoke, default bench (refreshes profiles), reference arm
+#!/bin/bash
+# end-of-round verification: full GPU suite, smoke, and the bench lines kept under profiles/
 mkdir -p gpurun_out
-timeout 900 python -m pytest tests -m gpu -x -q 2>&1 | tail -4
-python -c "import __graft_entry__ as g; g.smoke()" 2>&1 | tail -1
-python bench.py > gpurun_out/bench_final.json 2> gpurun_out/bench_final.err; echo "bench rc=$?"; python -c "
-import json; d=json.load(open('gpurun_out/bench_final.json')); print(d['value'], d['roofline']['frac'], d['e2e']['value'], d['cpu_baseline']['value'], d['clocks'], d['gpu_launches'])"
-python bench.py --dag dag8 --worlds 256 --entities 65536 --depth 8 --no-cpu-baseline --no-e2e > gpurun_out/bench_final_c3.json 2>>gpurun_out/bench_final.err
-python bench.py --dag dag16 --worlds 1024 --entities 1024 --no-cpu-baseline --no-e2e > gpurun_out/bench_final_c5.json 2>>gpurun_out/bench_final.err
-python -c "
+timeout 1500 python -m pytest tests -x -q -m gpu 2>&1 | tail -4
+python -c "import __graft_entry__ as g; g.smoke(); print('smoke ok')" 2>&1 | tail -2
+timeout 600 python bench.py > gpurun_out/final_c2.json 2> gpurun_out/final_c2.err
+timeout 300 python bench.py --no-cpu-baseline --dag dag8 --worlds 256 --entities 65536 --depth 8 > gpurun_out/final_c3_dag8.json 2>> gpurun_out/final.err
+timeout 300 python bench.py --no-cpu-baseline --dag dag16 --worlds 1024 --entities 1024 > gpurun_out/final_c5_dag16.json 2>> gpurun_out/final.err
+timeout 300 python bench.py --no-cpu-baseline --dag dag8 > gpurun_out/final_dag8_4096.json 2>> gpurun_out/final.err
+python - <<'P'
 import json
-for f in ('c3','c5'):
-    d=json.load(open('gpurun_out/bench_final_%s.json'%f)); print(f, d['value'], d['ms_per_step'], d['roofline']['frac'], d['gpu_launches']//d['steps'])"
+for n in ("c2","c3_dag8","c5_dag16","dag8_4096"):
+    try:
+        d=json.loads(open(f"gpurun_out/final_{n}.json").read().strip().splitlines()[-1])
+        print(n, d["value"], d["roofline"]["frac"], d["e2e"]["value"], (d.get("cpu_baseline") or {}).get("value"), d["gpu_launches"])
+    except Exception as e: print(n, "failed", e)
+P

@@ -101,6 +101,49 @@ def test_cta_teams_match_oracle(oracle, product, monkeypatch, W, E, D, steps, te
     assert st[abi.STAT_STEPS] == W * steps and st[abi.STAT_WORLDS] == W and st[abi.STAT_ENTITIES] == W * E
 
 
+TAIL_CASES = [
+    # (dag, worlds, entities, depth, steps, FIMO_B200_PIPE or None, FIMO_B200_TAIL or None, graph)
+    ("chain3", 1300, 64, 4, 3, None, "1", True),         # 2 rounds of 592 slots + 116 worlds: tail grid of 116 CTAs
+    ("chain3", 1300, 64, 4, 3, None, "2", False),        # a whole round joins the tail (708 CTAs); plain stream launches
+    ("chain3", 700, 520, 5, 3, "512,1,3", "1", True),    # 148 slots: 4 rounds + 108, two chunks per world (ragged)
+    ("dag8", 1250, 100, 4, 3, None, None, True),          # the 8-system set uses the tail grid by default
+    ("dag16", 1190, 36, 3, 4, None, "1", True),           # 2 rounds + 6 worlds: a round joins them (tail of 598)
+    ("dag16", 640, 1024, 4, 2, "256,2,3", "3", False),   # 296 slots: 1 fixed round, 344 tail CTAs
+]
+
+
+@pytest.mark.parametrize("dag,W,E,D,steps,pipe,tail,graph", TAIL_CASES)
+def test_tail_grid_matches_oracle(oracle, product, monkeypatch, dag, W, E, D, steps, pipe, tail, graph):
+    """One CTA per world with at least two rounds of worlds per CTA slot: the last round runs as a second grid of
+    one-world CTAs beside the persistent grid (two launches, one completion ticket).  Same bit-exact bar, and the
+    statistics count every world once."""
+    monkeypatch.setenv("FIMO_B200_TEAM", "1")
+    if pipe:
+        monkeypatch.setenv("FIMO_B200_PIPE", pipe)
+    if tail:
+        monkeypatch.setenv("FIMO_B200_TAIL", tail)
+    kw = {} if dag == "chain3" else {"dag": dag}
+    got, want, info = run_both(oracle, product, W, E, D, steps, synth.RigOptions(fused=True, graph=graph), **kw)
+    assert info.fused_world_step == 1
+    assert info.kernel_launches_per_generation == (2 if dag != "dag16" else 3)  # + prev_copy outside the fused kernel
+    problems = synth.compare_outputs(got, want, FLOAT_RTOL)
+    assert not problems, "\n".join(problems)
+    st = got["stats"].reshape(-1).view(np.uint64)
+    assert st[abi.STAT_STEPS] == W * steps and st[abi.STAT_WORLDS] == W and st[abi.STAT_ENTITIES] == W * E
+
+
+@pytest.mark.parametrize("dag,disable", [("dag8", True), ("chain3", False)])
+def test_tail_grid_off(oracle, product, monkeypatch, dag, disable):
+    """FIMO_B200_TAIL=0 keeps the 8-system set on one grid; the 3-system chain is on one grid by default."""
+    monkeypatch.setenv("FIMO_B200_TEAM", "1")
+    if disable:
+        monkeypatch.setenv("FIMO_B200_TAIL", "0")
+    got, want, info = run_both(oracle, product, 1300, 64, 4, 2, dag=dag)
+    assert info.fused_world_step == 1 and info.kernel_launches_per_generation == 1
+    problems = synth.compare_outputs(got, want, FLOAT_RTOL)
+    assert not problems, "\n".join(problems)
+
+
 def test_large_world_per_level_propagate(oracle, product):
     """configs[2] world shape (64k entities, depth 8), one kernel per system: the world is too large for one
     CTA's shared memory, so propagate runs as one launch per hierarchy level."""
