@@ -135,7 +135,8 @@ struct PipeArgs {
     unsigned long long *timing;
 };
 
-constexpr uint32_t kTimingCtas = 4096;      // timing build: CTAs whose (smid, start ns, end ns, chunks) are recorded
+constexpr uint32_t kTimingCtas = 4096;      // timing build: CTAs whose (smid, loop start ns, loop end ns, chunks, entry ns, exit ns) are recorded
+constexpr uint32_t kTimingRow = 6;
 constexpr uint32_t kPipeVelClamp = 8u;         // kSet 1: vel_clamp sits between forces and integrate_lin
 constexpr uint32_t kPipePublishPerChunk = 2u; // FIMO_B200_PUBLISH=chunk: announce level progress after every chunk
 constexpr uint32_t kPipePrefetchBlocking = 4u; // FIMO_B200_PREFETCH=2: wait for the next chunk's inputs before this chunk's math
@@ -300,6 +301,8 @@ __global__ void __launch_bounds__(T + 32, kMinBlocks) k_world_step_pipe(const Pi
     static_assert(!(kTeam && kSet == 2), "the 16-system set is fused for one-CTA-per-world plans only");
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    unsigned long long tm_entry = 0;
+    if (kTimingBuild && pa.timing && tid == 0) asm volatile("mov.u64 %0, %globaltimer;" : "=l"(tm_entry));
     constexpr int kWarps = T / 32;
     static_assert(kWarps <= 16, "one count byte per warp in s_cnt");
     const int kEmptyKey = tid % 6 < 3 ? float_key(FIMO_B200_BOUNDS_EMPTY_MIN) : float_key(-FIMO_B200_BOUNDS_EMPTY_MIN);
@@ -686,8 +689,8 @@ __global__ void __launch_bounds__(T + 32, kMinBlocks) k_world_step_pipe(const Pi
             unsigned smid;
             asm volatile("mov.u64 %0, %globaltimer;" : "=l"(wall1));
             asm volatile("mov.u32 %0, %smid;" : "=r"(smid));
-            unsigned long long *row = pa.timing + 8 + 4 * (size_t)(pa.trace_base + blockIdx.x);
-            row[0] = smid, row[1] = tm_wall0, row[2] = wall1, row[3] = (unsigned long long)total;
+            unsigned long long *row = pa.timing + 8 + kTimingRow * (size_t)(pa.trace_base + blockIdx.x);
+            row[0] = smid, row[1] = tm_wall0, row[2] = wall1, row[3] = (unsigned long long)total, row[4] = tm_entry;
         }
     }
     if (!kTeam) { // fold the per-warp mask sums, publish the batch statistics
@@ -707,6 +710,11 @@ __global__ void __launch_bounds__(T + 32, kMinBlocks) k_world_step_pipe(const Pi
             if (kSet == 2)
                 publish_stats_to<true>(StatsSink{a.stats2, a.scratch2, a.gstats2, a.bounds_keys2, a.entities}, cta_visible2, s_sum2,
                                        my_worlds, (unsigned long long)pa.stat_ctas);
+            if (kTimingBuild && pa.timing && pa.trace_base + blockIdx.x < kTimingCtas) { // statistics published: thread 0 leaves
+                unsigned long long wall2;
+                asm volatile("mov.u64 %0, %globaltimer;" : "=l"(wall2));
+                pa.timing[8 + kTimingRow * (size_t)(pa.trace_base + blockIdx.x) + 5] = wall2;
+            }
         }
     }
 }
@@ -1062,7 +1070,7 @@ FimoStatus world_step_launch(const WorldStepViews &v, const WorldStepPlan &plan,
         static unsigned long long *timing_buf = nullptr; // debug only (FIMO_B200_TIMING=1 with plain stream launches)
         static int timing_launches = 0;
         const bool timing = kTimingBuild && std::getenv("FIMO_B200_TIMING") != nullptr && !(info->flags & FIMO_B200_LAUNCH_FLAG_CAPTURING);
-        if (timing && !timing_buf) timing_buf = (unsigned long long *)hbm_alloc(info->device, (8 + 4 * (size_t)kTimingCtas) * sizeof(unsigned long long));
+        if (timing && !timing_buf) timing_buf = (unsigned long long *)hbm_alloc(info->device, (8 + kTimingRow * (size_t)kTimingCtas) * sizeof(unsigned long long));
         pa.timing = timing ? timing_buf : nullptr;
         pa.flags = kPipePrefetchBlocking; // FIMO_B200_PREFETCH=0 / 1 (only if already landed) / 2 (default)
         if (const char *env = std::getenv("FIMO_B200_PREFETCH"))
@@ -1110,12 +1118,14 @@ FimoStatus world_step_launch(const WorldStepViews &v, const WorldStepPlan &plan,
                 unsigned long long t[8] = {0, 0, 0, 0, 0, 0, 0, 0};
                 hbm_download(device, t, timing_buf, sizeof t);
                 if (const char *path = std::getenv("FIMO_B200_TIMING_DUMP")) { // per-CTA trace of the latest launch as CSV
-                    std::vector<unsigned long long> rows(4 * (size_t)kTimingCtas);
+                    std::vector<unsigned long long> rows(kTimingRow * (size_t)kTimingCtas);
                     hbm_download(device, rows.data(), timing_buf + 8, rows.size() * sizeof(unsigned long long));
                     if (FILE *f = std::fopen(path, "w")) {
-                        std::fprintf(f, "cta,smid,start_ns,end_ns,chunks\n");
-                        for (unsigned i = 0; i < grid_ctas && i < kTimingCtas; i++)
-                            std::fprintf(f, "%u,%llu,%llu,%llu,%llu\n", i, rows[4 * i], rows[4 * i + 1], rows[4 * i + 2], rows[4 * i + 3]);
+                        std::fprintf(f, "cta,smid,start_ns,end_ns,chunks,entry_ns,exit_ns\n");
+                        for (unsigned i = 0; i < grid_ctas && i < kTimingCtas; i++) {
+                            const unsigned long long *r = rows.data() + kTimingRow * (size_t)i;
+                            std::fprintf(f, "%u,%llu,%llu,%llu,%llu,%llu,%llu\n", i, r[0], r[1], r[2], r[3], r[4], r[5]);
+                        }
                         std::fclose(f);
                     }
                 }

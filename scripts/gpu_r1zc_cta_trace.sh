@@ -1,11 +1,9 @@
 #!/bin/bash
-# TIMING build only: per-CTA (smid, start, end) trace of the one-CTA-per-world kernel on C2, 4096x4096 and C5
+# TIMING build only: per-CTA (smid, entry, loop start, loop end, exit) trace of the one-CTA-per-world kernel
 mkdir -p gpurun_out
-run() { tag=$1; shift; FIMO_B200_TIMING=1 FIMO_B200_TIMING_DUMP=gpurun_out/r1zc_trace_$tag.csv timeout 300 python bench.py --no-graph --no-e2e --no-cpu-baseline --steps 64 --warmup 16 "$@" 2>gpurun_out/r1zc_$tag.err | python -c "
+run() { tag=$1; shift; FIMO_B200_TIMING=1 FIMO_B200_TIMING_DUMP=gpurun_out/r1ze_trace_$tag.csv timeout 300 python bench.py --no-graph --no-e2e --no-cpu-baseline --steps 64 --warmup 16 "$@" 2>gpurun_out/r1ze_$tag.err | python -c "
 import json,sys
-d=json.loads(sys.stdin.read().strip().splitlines()[-1]); print('$tag', 'ms/step %.4f'%d['ms_per_step'], 'frac', d['roofline']['frac'])"; grep timing gpurun_out/r1zc_$tag.err | tail -1; }
+d=json.loads(sys.stdin.read().strip().splitlines()[-1]); print('$tag', 'ms/step %.4f'%d['ms_per_step'], 'frac', d['roofline']['frac'])"; grep timing gpurun_out/r1ze_$tag.err | tail -1; }
 run c2
-run c2b
-run w4096e4096 --worlds 4096 --entities 4096
-run c5 --dag dag16 --worlds 1024 --entities 1024
 run dag8 --dag dag8
+FIMO_B200_TAIL=1 run c2tail
