@@ -367,7 +367,8 @@ def test_mixed_host_and_device_systems_match_oracle(oracle, product, W, E, D, st
 
 
 @pytest.mark.parametrize("dag,W,E,D,fused", [("chain3", 24, 512, 4, True), ("chain3", 24, 512, 4, False), ("chain3", 3, 8192, 8, True),
-                                            ("dag16", 700, 128, 4, True), ("dag8", 9, 1000, 4, True)])
+                                            ("dag16", 700, 128, 4, True), ("dag8", 9, 1000, 4, True),
+                                            ("dag8", 1300, 64, 4, True)])  # persistent + tail grid share one ticket
 def test_stats_ring_holds_every_generation(product, dag, W, E, D, fused):
     """FimoB200_GroupDeviceExt.stats_ring: the kernel that publishes the statistics also stores them in slot
     generation % slots — K generations queued back to back leave the same words a step-by-step run reads from `stats`."""
