@@ -57,6 +57,7 @@ struct Completion {
     void *user;
     bool generation = true; // false: a stream-ordered transfer (not part of the per-generation timers)
     cudaEvent_t landed = nullptr; // a generation with result copies behind it: completes when they have landed
+    uint64_t seq = 0;             // position in the executor's queue (Executor::posted_seq)
 };
 
 struct Completer {
@@ -112,6 +113,28 @@ struct Executor {
     size_t staging_bytes = 0;
     cudaEvent_t staged[2] = {nullptr, nullptr}, slot_free[2] = {nullptr, nullptr};
     uint64_t staged_count = 0;
+    // Host memory that queued device -> host copies have yet to write.  An upload that reads such memory (a result fed
+    // back as the next step's input without waiting) must stay in stream order behind that copy: it is not staged.
+    struct HostRange {
+        const char *lo, *hi;
+        uint64_t seq;
+    };
+    std::vector<HostRange> host_writes; // guarded by m
+    uint64_t posted_seq = 0, retired_seq = 0;
+    // m held.  Registers `writes` under a new sequence number; returns whether any of `reads` overlaps a pending write.
+    bool post(const Copy *reads, size_t n_reads, const Copy *writes, size_t n_writes, uint64_t *seq) {
+        host_writes.erase(std::remove_if(host_writes.begin(), host_writes.end(), [&](const HostRange &r) { return r.seq <= retired_seq; }),
+                          host_writes.end());
+        bool overlap = false;
+        for (size_t i = 0; i < n_reads && !overlap; i++) {
+            const char *lo = (const char *)reads[i].src, *hi = lo + reads[i].bytes;
+            for (const HostRange &r : host_writes)
+                if (lo < r.hi && r.lo < hi) overlap = true;
+        }
+        *seq = ++posted_seq;
+        for (size_t i = 0; i < n_writes; i++) host_writes.push_back(HostRange{(const char *)writes[i].dst, (const char *)writes[i].dst + writes[i].bytes, *seq});
+        return overlap;
+    }
 
     cudaEvent_t take_event() {
         {
@@ -163,6 +186,7 @@ void Completer::run() {
         }
         ex->free_events.push_back(c.end);
         if (c.landed) ex->free_events.push_back(c.landed);
+        if (c.seq > ex->retired_seq) ex->retired_seq = c.seq;
         if (--ex->in_flight == 0) ex->idle_cv.notify_all();
     }
 }
@@ -477,13 +501,15 @@ bool executor_launch(Executor *ex, void (*done)(void *), void *user, const Copy 
     Completion c{ex->take_event(), ex->take_event(), ex, done, user};
     if (!c.start || !c.end) return false;
     if (n_down && !(c.landed = ex->take_event())) return false;
-    bool busy;
+    bool busy, feedback;
     {
         std::lock_guard<std::mutex> g(ex->m);
         busy = ex->in_flight++ > 0;
+        feedback = ex->post(uploads, n_up, downloads, n_down, &c.seq);
     }
-    // staging pays only when an earlier generation is still running for the PCIe leg to hide behind
-    bool launched = enqueue_copies(ex->stream, uploads, n_up, true, busy ? ex : nullptr); // this generation's inputs, in stream order in front of it
+    // staging pays only when an earlier generation is still running for the PCIe leg to hide behind, and is only
+    // correct when no queued result copy has yet to write the memory this upload reads
+    bool launched = enqueue_copies(ex->stream, uploads, n_up, true, busy && !feedback ? ex : nullptr); // this generation's inputs, in stream order in front of it
     launched = ok(cudaEventRecord(c.start, ex->stream), "cudaEventRecord") && launched;
     if (launched) {
         if (ex->use_graph) launched = ok(cudaGraphLaunch(ex->graph_exec, ex->stream), "cudaGraphLaunch");
@@ -504,6 +530,8 @@ bool executor_transfer(Executor *ex, void *dst, const void *src, size_t bytes, b
     {
         std::lock_guard<std::mutex> g(ex->m);
         ex->in_flight++;
+        const Copy copy{dst, src, bytes};
+        ex->post(nullptr, 0, &copy, to_device ? 0 : 1, &c.seq);
     }
     bool queued = ok(cudaMemcpyAsync(dst, src, bytes, to_device ? cudaMemcpyHostToDevice : cudaMemcpyDeviceToHost, ex->stream),
                      "cudaMemcpyAsync");

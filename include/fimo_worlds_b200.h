@@ -782,9 +782,11 @@ FIMO_B200_EXPORT FimoStatus fimo_b200_group_transfer(FimoWorldsMeta_SystemGroup 
  * other generation / transfer of the group.  It consumes one generation number; `signal` (nullable) fires once
  * the generation has completed AND the downloads have landed.  Buffers follow fimo_b200_group_transfer's rules
  * (whole resource, valid until `signal`; pinned memory for asynchronous copies).  Several such steps may be in
- * flight; each needs its own host buffers, and upload buffers must not change between the call (once `wait_on`
- * is satisfied) and `signal`: pinned uploads are read early, into HBM staging slots beside the generation still
- * running, and reach the resources in stream order in front of their own generation. */
+ * flight; each needs its own host buffers, and the caller must not write an upload buffer between the call (once
+ * `wait_on` is satisfied) and `signal`: pinned uploads are read early, into HBM staging slots beside the generation
+ * still running, and reach the resources in stream order in front of their own generation.  The one writer that IS
+ * honoured is the group itself: an upload that reads host memory which a download or transfer queued earlier has
+ * yet to write (a result fed back as the next step's input) stays in stream order behind that copy. */
 typedef struct FimoB200_StepTransfer {
     FimoWorldsMeta_ResourceHandle resource;
     void *host;

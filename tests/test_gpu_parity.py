@@ -331,6 +331,46 @@ def test_schedule_io_steps_in_flight_match_oracle(oracle, product, pinned):
             product.fimo_b200_host_free(ptr)
 
 
+def test_schedule_io_result_fed_back_through_host_memory(oracle, product):
+    """A step's download and the next step's upload share ONE pinned host buffer, all steps queued without waiting:
+    positions read back by step i become the velocities uploaded for step i+1.  The copies must stay in stream
+    order (the staged, early PCIe read of an upload would see the buffer before the earlier download has landed)."""
+    import ctypes as C
+    from fimo_b200.worlds import Fence
+
+    W, E, D, K = 6, 768, 4, 7
+    data = synth.generate(W, E, D)
+    ref = synth.WorldStepRig(oracle, W, E, D, data={k: v.copy() for k, v in data.items()})
+    try:
+        x = data["vel"].copy()
+        for _ in range(K):
+            ref.upload("vel", x)
+            ref.step(1)
+            x = ref.download(("pos",))["pos"]
+        want = ref.download()
+    finally:
+        ref.close()
+    ptr = product.fimo_b200_host_alloc(data["vel"].nbytes)
+    assert ptr
+    rig = synth.WorldStepRig(product, W, E, D, data={k: v.copy() for k, v in data.items()})
+    try:
+        buf = np.ctypeslib.as_array(C.cast(ptr, C.POINTER(C.c_uint32)), shape=(data["vel"].size,)).view(np.float32).reshape(data["vel"].shape)
+        buf[...] = data["vel"]
+        fences = [Fence(product) for _ in range(K)]
+        up, down = rig.io_list({"vel": buf}), rig.io_list({"pos": buf})
+        for i in range(K):
+            rig.schedule_io(up, down, fences[i])
+        for f in fences:
+            f.wait()
+        got = rig.download()
+        assert np.array_equal(buf.view(np.uint32), want["pos"].view(np.uint32))
+    finally:
+        rig.close()
+        product.fimo_b200_host_free(ptr)
+    problems = synth.compare_outputs(got, want, 0.0)
+    assert not problems, "\n".join(problems)
+
+
 @pytest.mark.parametrize("mode", ["fused", "graph", "streams"])
 @pytest.mark.parametrize("W,E,D,steps", [(16, 1024, 4, 6), (40, 260, 5, 4), (3, 8192, 8, 3)])
 def test_mixed_host_and_device_systems_match_oracle(oracle, product, W, E, D, steps, mode):
