@@ -169,16 +169,23 @@ struct StatsSink { // where one cull's batch statistics go (the DAGs have up to 
     unsigned long long *ring = nullptr; // FimoB200_GroupDeviceExt::stats_ring
     uint32_t ring_slots = 0;
 };
-template <bool kGroupStats>
-__device__ __forceinline__ bool publish_stats_to(const StatsSink &a, unsigned long long visible, unsigned long long mask_sum,
-                                                 unsigned long long worlds, unsigned long long n_ctas) {
+// The three steps of publishing: every CTA adds its sums (fire-and-forget reductions), draws a ticket behind a fence,
+// and the CTA that drew the last one turns the accumulators into the published words and re-arms them.
+__device__ __forceinline__ void stats_contribute(const StatsSink &a, unsigned long long visible, unsigned long long mask_sum,
+                                                 unsigned long long worlds) {
     atomicAdd(&a.scratch[0], visible);
     atomicAdd(&a.scratch[1], mask_sum);
     atomicAdd(&a.scratch[2], worlds);
+}
+__device__ __forceinline__ bool stats_last_ticket(const StatsSink &a, unsigned long long n_ctas) {
     __threadfence();
     const unsigned long long ticket = atomicAdd(&a.scratch[4], 1ull);
     if (ticket != n_ctas - 1) return false;
     __threadfence();
+    return true;
+}
+template <bool kGroupStats>
+__device__ __forceinline__ void stats_finalize(const StatsSink &a) {
     const unsigned long long v = atomicExch(&a.scratch[0], 0ull);
     const unsigned long long m = atomicExch(&a.scratch[1], 0ull);
     const unsigned long long n = atomicExch(&a.scratch[2], 0ull);
@@ -203,6 +210,26 @@ __device__ __forceinline__ bool publish_stats_to(const StatsSink &a, unsigned lo
             g[FIMO_B200_GSTAT_BOUNDS + i] = __float_as_uint(key_float(atomicExch(a.bounds_keys + i, empty)));
         }
     }
+}
+template <bool kGroupStats>
+__device__ __forceinline__ bool publish_stats_to(const StatsSink &a, unsigned long long visible, unsigned long long mask_sum,
+                                                 unsigned long long worlds, unsigned long long n_ctas) {
+    stats_contribute(a, visible, mask_sum, worlds);
+    if (!stats_last_ticket(a, n_ctas)) return false;
+    stats_finalize<kGroupStats>(a);
+    atomicExch(&a.scratch[4], 0ull);
+    return true;
+}
+// Two culls published by one kernel (the 16-system set): one fence and one ticket (the first sink's) for both.
+template <bool kGroupStats>
+__device__ __forceinline__ bool publish_stats_pair(const StatsSink &a, const StatsSink &b, unsigned long long visible_a,
+                                                   unsigned long long mask_sum_a, unsigned long long visible_b, unsigned long long mask_sum_b,
+                                                   unsigned long long worlds, unsigned long long n_ctas) {
+    stats_contribute(a, visible_a, mask_sum_a, worlds);
+    stats_contribute(b, visible_b, mask_sum_b, worlds);
+    if (!stats_last_ticket(a, n_ctas)) return false;
+    stats_finalize<kGroupStats>(a);
+    stats_finalize<kGroupStats>(b);
     atomicExch(&a.scratch[4], 0ull);
     return true;
 }

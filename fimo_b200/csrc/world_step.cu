@@ -706,10 +706,11 @@ __global__ void __launch_bounds__(T + 32, kMinBlocks) k_world_step_pipe(const Pi
         }
         consumer_sync<T>();
         if (tid == 0) {
-            publish_stats<kSet >= 1>(a, cta_visible, s_sum, my_worlds, (unsigned long long)pa.stat_ctas);
             if (kSet == 2)
-                publish_stats_to<true>(StatsSink{a.stats2, a.scratch2, a.gstats2, a.bounds_keys2, a.entities}, cta_visible2, s_sum2,
-                                       my_worlds, (unsigned long long)pa.stat_ctas);
+                publish_stats_pair<true>(StatsSink{a.stats, a.scratch, a.gstats, a.bounds_keys, a.entities, a.ring, a.ring_slots},
+                                         StatsSink{a.stats2, a.scratch2, a.gstats2, a.bounds_keys2, a.entities}, cta_visible, s_sum,
+                                         cta_visible2, s_sum2, my_worlds, (unsigned long long)pa.stat_ctas);
+            else publish_stats<kSet >= 1>(a, cta_visible, s_sum, my_worlds, (unsigned long long)pa.stat_ctas);
             if (kTimingBuild && pa.timing && pa.trace_base + blockIdx.x < kTimingCtas) { // statistics published: thread 0 leaves
                 unsigned long long wall2;
                 asm volatile("mov.u64 %0, %globaltimer;" : "=l"(wall2));
