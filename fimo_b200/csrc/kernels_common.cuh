@@ -186,19 +186,30 @@ __device__ __forceinline__ bool stats_last_ticket(const StatsSink &a, unsigned l
 }
 template <bool kGroupStats>
 __device__ __forceinline__ void stats_finalize(const StatsSink &a) {
+    // This runs on the kernel's critical path (the last CTA, after everyone else has left): the loads that do not
+    // depend on the accumulators go first so that their latency overlaps the exchanges, and the ring slot is written
+    // from registers instead of reading `stats` back.
+    const unsigned long long steps_before = a.stats[FIMO_B200_STAT_STEPS];
+    unsigned long long gen = 0, rest[FIMO_B200_STAT_WORDS - 5] = {};
+    if (a.ring) {
+        gen = a.scratch[5];
+        for (int i = 5; i < FIMO_B200_STAT_WORDS; i++) rest[i - 5] = a.stats[i];
+    }
     const unsigned long long v = atomicExch(&a.scratch[0], 0ull);
     const unsigned long long m = atomicExch(&a.scratch[1], 0ull);
     const unsigned long long n = atomicExch(&a.scratch[2], 0ull);
-    a.stats[FIMO_B200_STAT_VISIBLE] = v;
-    a.stats[FIMO_B200_STAT_ENTITIES] = n * (unsigned long long)a.entities;
-    a.stats[FIMO_B200_STAT_MASK_SUM] = m;
-    a.stats[FIMO_B200_STAT_WORLDS] = n;
-    a.stats[FIMO_B200_STAT_STEPS] += n;
+    unsigned long long words[5];
+    words[FIMO_B200_STAT_VISIBLE] = v;
+    words[FIMO_B200_STAT_ENTITIES] = n * (unsigned long long)a.entities;
+    words[FIMO_B200_STAT_MASK_SUM] = m;
+    words[FIMO_B200_STAT_WORLDS] = n;
+    words[FIMO_B200_STAT_STEPS] = steps_before + n;
+    for (int i = 0; i < 5; i++) a.stats[i] = words[i];
     if (a.ring) { // the snapshot of this generation: slot = generations published so far % slots
-        const unsigned long long gen = a.scratch[5];
         a.scratch[5] = gen + 1;
         unsigned long long *slot = a.ring + (gen % a.ring_slots) * FIMO_B200_STAT_WORDS;
-        for (int i = 0; i < FIMO_B200_STAT_WORDS; i++) slot[i] = a.stats[i];
+        for (int i = 0; i < 5; i++) slot[i] = words[i];
+        for (int i = 5; i < FIMO_B200_STAT_WORDS; i++) slot[i] = rest[i - 5];
     }
     if (kGroupStats) {
         uint32_t *g = a.gstats;
