@@ -188,6 +188,39 @@ def test_full_size_properties(product):
         assert np.array_equal(out["world"][:, 4 * k + 3, :][roots], out["pos"][:, k, :][roots])
 
 
+@pytest.mark.parametrize("dag", ["dag8", "dag16"])
+def test_full_size_dags_fused_equals_one_kernel_per_system(product, dag):
+    """The DAGs at BASELINE size (4096 x 1k; configs[4] is the dag16 shape): the fused world-step kernel — for dag8
+    the persistent grid plus the tail grid — leaves every resource bit-identical to the same generations run as
+    one kernel per system (the path the small cases pin against the oracle), plus the count / mask / list /
+    statistics properties."""
+    W, E, D, K = 4096, 1024, 4, 3
+    data = synth.generate(W, E, D, dag=dag)
+    outs = []
+    for fused in (True, False):
+        rig = synth.WorldStepRig(product, W, E, D, data={k: v.copy() for k, v in data.items()}, options=synth.RigOptions(fused=fused), dag=dag)
+        try:
+            rig.step(K)
+            info = rig.executor_info()
+            outs.append(rig.download())
+        finally:
+            rig.close()
+        assert info.fused_world_step == (1 if fused else 0)
+        if fused and dag == "dag8":
+            assert info.kernel_launches_per_generation == 2  # persistent grid + tail grid
+    got, want = outs
+    problems = synth.compare_outputs(got, want, 0.0)
+    assert not problems, "\n".join(problems)
+    counts = got["vis_count"][:, 0, 0].astype(np.int64)
+    bits = np.unpackbits(got["vis_mask"][:, 0, :].view(np.uint8), axis=1, bitorder="little")
+    assert np.array_equal(bits.sum(axis=1), counts)
+    st = got["stats"].reshape(-1).view(np.uint64)
+    assert st[abi.STAT_VISIBLE] == counts.sum() and st[abi.STAT_WORLDS] == W and st[abi.STAT_STEPS] == W * K
+    for w in (0, 591, 592, 3551, 3552, 4095):  # first / last world of the persistent grid's rounds and of the tail grid
+        idx = np.nonzero(bits[w])[0].astype(np.uint32)
+        assert np.array_equal(got["vis_list"][w, 0, :counts[w]], idx)
+
+
 def test_generations_pipeline_and_fences(product):
     """schedule is asynchronous; K queued generations run in order; the signal fence fires after the last."""
     rig = synth.WorldStepRig(product, 32, 256, 4)
