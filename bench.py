@@ -7,8 +7,14 @@
 A "step" is one generation (`system_group_schedule`) of the 3-system chain integrate -> transform propagate
 -> AABB frustum cull over one batch of synthetic worlds.  N=1 workload = BASELINE.json configs[1]:
 4096 worlds x 1024 entities, depth-4 hierarchy.  N>1: the same batch per GPU (weak scaling), worlds sharded by
-global index, no data-path collective; the end-of-step statistics are all-reduced over NCCL on a side stream.
-Prints ONE JSON line on rank 0.
+global index, no data-path collective; the end-of-step statistics are exchanged by the product itself
+(fimo_b200_group_stats_peers_bind: peer stores over NVLink from the publishing CTA; NCCL all-reduce as the checked
+second transport).  Prints ONE JSON line on rank 0 — and refuses to print it if the full-size parity gate (K = 2
+generations of this very workload against the CPU oracle, bit for bit) fails.
+
+Timing: W warm-up steps, then `--windows` windows of EXACTLY K steps each, every window bracketed by a barrier +
+synchronize on both sides and timed on the device (CUDA events on the group's stream, first generation's start ->
+last generation's end, max over ranks); `value` is taken from the MEDIAN window and min / max are reported beside it.
 """
 from __future__ import annotations
 
@@ -16,6 +22,7 @@ import argparse
 import ctypes as C
 import json
 import os
+import statistics
 import subprocess
 import sys
 import threading
@@ -29,6 +36,7 @@ METRIC = "batched world-steps/sec"
 UNIT = "world-steps/s"
 WORLDS_PER_GPU, ENTITIES, DEPTH = 4096, 1024, 4
 CPU_SAMPLE_WORLDS = 256  # bounded sample of the same workload for the CPU arm
+CPU_QUEUE_DEPTH = 32     # generations queued per group before the CPU arm waits (schedule is asynchronous)
 
 
 def parse_args():
@@ -36,6 +44,7 @@ def parse_args():
     p.add_argument("--gpus", type=int, default=1)
     p.add_argument("--steps", type=int, default=200)
     p.add_argument("--warmup", type=int, default=20)
+    p.add_argument("--windows", type=int, default=5, help="timed windows of --steps generations each; the median is reported")
     p.add_argument("--impl", default="b200", choices=["b200", "reference"])
     p.add_argument("--worlds", type=int, default=WORLDS_PER_GPU, help="worlds per GPU")
     p.add_argument("--entities", type=int, default=ENTITIES)
@@ -47,7 +56,10 @@ def parse_args():
     p.add_argument("--no-graph", action="store_true", help="plain stream launches instead of a CUDA graph per generation")
     p.add_argument("--no-cpu-baseline", action="store_true")
     p.add_argument("--no-e2e", action="store_true")
-    p.add_argument("--stats-bucket", type=int, default=8, help="steps whose statistics share one NCCL all-reduce (N > 1)")
+    p.add_argument("--no-parity-gate", action="store_true", help="skip the K=2 full-size check against the oracle (sweeps only)")
+    p.add_argument("--no-other-configs", action="store_true", help="skip the short configs[2] / configs[4]-shape measurements")
+    p.add_argument("--stats", default="peers", choices=["peers", "nccl"], help="transport of the statistics exchange (N > 1)")
+    p.add_argument("--stats-bucket", type=int, default=8, help="NCCL transport: generations per all-reduce")
     p.add_argument("--cpu-steps", type=int, default=0, help="steps of the CPU arm (0 = sized for ~15 s)")
     return p.parse_args()
 
@@ -60,16 +72,26 @@ def measured_peaks() -> tuple[float, str]:
         return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
 
 
+def ncu_traffic(dag: str, W: int, E: int, D: int):
+    """DRAM bytes per launch of the dominant kernel from the committed ncu --set full capture of THIS config, or None."""
+    try:
+        table = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
+        entry = table.get("configs", {}).get(f"{dag}:{W}x{E}:d{D}")
+        return (entry["dram_bytes_per_launch"], entry["source"]) if entry else (None, None)
+    except Exception:
+        return None, None
+
+
 # ------------------------------------------------------------------------------------------------
 # CPU arm: the reference's own structure — one World + one SystemGroup per world, every group scheduled
-# each step on ONE shared pool with all host threads, systems as system_run callbacks.
+# on ONE shared pool with all host threads (SURVEY.md §8d), systems as system_run callbacks.
 # ------------------------------------------------------------------------------------------------
 DAG_TEXT = {"chain3": "3-system chain (integrate -> propagate -> AABB frustum cull)",
             "dag8": "8-system fan-out/fan-in DAG (forces -> integrate_lin || integrate_ang -> propagate -> world_aabb -> cull || bounds -> stats)",
             "dag16": "16-system DAG with mixed read/write resource conflicts"}
 
 
-def cpu_arm(worlds: int, entities: int, depth: int, steps: int, warmup: int, dag: str = "chain3") -> dict:
+def cpu_arm(worlds: int, entities: int, depth: int, steps: int, warmup: int, dag: str = "chain3", seconds_budget: float = 15.0) -> dict:
     from fimo_b200 import synth
     from fimo_b200.worlds import create_pool
     from oracle import loader
@@ -83,36 +105,52 @@ def cpu_arm(worlds: int, entities: int, depth: int, steps: int, warmup: int, dag
         one = {k: (v if v.shape[0] != worlds else v[w:w + 1]).copy() for k, v in data.items()}
         rigs.append(synth.WorldStepRig(lib, 1, entities, depth, data=one, pool=pool, dag=dag))
     groups = (C.c_void_p * worlds)(*[r.group.handle for r in rigs])
-    if steps <= 0:  # size the run for ~15 s of CPU work
-        t = lib.fimo_oracle_step_groups(groups, worlds, 2)
-        steps = max(3, min(2000, int(15.0 / max(t / 2, 1e-6))))
-    lib.fimo_oracle_step_groups(groups, worlds, max(warmup, 1))
-    seconds = lib.fimo_oracle_step_groups(groups, worlds, steps)
+
+    def run(n):  # generations queue behind each group's timeline semaphore, CPU_QUEUE_DEPTH at a time (SystemGroup.zig:430-452)
+        t, left = 0.0, n
+        while left > 0:
+            k = min(left, CPU_QUEUE_DEPTH)
+            t += lib.fimo_oracle_step_groups_queued(groups, worlds, k)
+            left -= k
+        return t
+
+    if steps <= 0:  # size the run for ~seconds_budget of CPU work
+        t = run(4)
+        steps = max(4, min(4000, int(seconds_budget / max(t / 4, 1e-6))))
+    run(max(warmup, 1))
+    seconds = run(steps)
     for r in rigs:
         r.close()
     pool.unref()
     return {
         "value": worlds * steps / seconds, "unit": UNIT, "cores": cores, "kind": "port",
         "sample": f"{worlds} worlds x {entities} entities, depth {depth}, {dag}, {steps} steps, one World+SystemGroup "
-                  f"per world on one shared {cores}-thread pool (oracle restatement of fimo_worlds/fimo_tasks; the reference "
-                  f"itself needs zig + boost.context and cannot be built here)",
+                  f"per world on one shared {cores}-thread pool, {CPU_QUEUE_DEPTH} generations queued per group at a time (oracle "
+                  f"restatement of fimo_worlds/fimo_tasks, gcc -O3 -mavx2 -mfma; the reference itself needs zig + boost.context and cannot be built here)",
         "seconds": seconds, "steps": steps, "ms_per_step": 1e3 * seconds / steps,
     }
 
 
 def run_reference(args) -> None:
+    """The reference arm: the SAME config, steps and warm-up as the B200 arm wherever that ends within a few minutes —
+    every world of the batch gets its own World + SystemGroup, as on the reference — else (over 8 M entities) a
+    bounded sample of the worlds, said so in the line."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    steps = args.steps if args.steps != 200 else 0
-    sample_worlds = max(1, min(CPU_SAMPLE_WORLDS, args.worlds, (CPU_SAMPLE_WORLDS * 1024) // max(args.entities, 1)))
-    base = cpu_arm(sample_worlds, args.entities, args.depth, min(steps, 400), min(args.warmup, 3), args.dag)
+    worlds = args.worlds if args.worlds * args.entities <= (8 << 20) else max(1, (8 << 20) // max(args.entities, 1))
+    steps, warmup = args.steps, max(args.warmup, 3)
+    base = cpu_arm(worlds, args.entities, args.depth, steps, warmup, args.dag)
+    sampled = "" if worlds == args.worlds else f"; CPU arm steps a {worlds}-world sample per step"
     line = {
         "impl": "reference", "metric": METRIC, "value": base["value"], "unit": UNIT, "n_gpus": args.gpus,
-        "steps": base["steps"], "warmup": min(args.warmup, 3), "ms_per_step": base["ms_per_step"], "higher_is_better": True,
+        "steps": base["steps"], "warmup": warmup, "ms_per_step": base["ms_per_step"], "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": f"{args.worlds} worlds x {args.entities} entities, depth {args.depth}, {DAG_TEXT[args.dag]}; "
-                               f"CPU arm steps a {sample_worlds}-world sample per step"},
+        "config": {"workload": f"{args.worlds} worlds x {args.entities} entities per GPU, depth-{args.depth} transform hierarchy, {DAG_TEXT[args.dag]}"
+                               + (", BASELINE.json configs[1]" if (args.worlds, args.entities, args.depth, args.dag) == (4096, 1024, 4, "chain3") else "")
+                               + sampled,
+                   "dag": args.dag, "worlds_per_gpu": args.worlds, "entities_per_world": args.entities, "depth": args.depth,
+                   "same_config": worlds == args.worlds},
         "cpu_baseline": {k: base[k] for k in ("value", "unit", "cores", "kind", "sample")},
         "e2e": {"value": base["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
@@ -152,6 +190,95 @@ class ClockSampler:
 
 
 # ------------------------------------------------------------------------------------------------
+# the parity gate: K = 2 generations of the benched workload, product vs oracle, bit for bit
+# ------------------------------------------------------------------------------------------------
+def parity_gate(lib, data, W, E, D, dag, options, steps: int = 2) -> dict:
+    from fimo_b200 import synth
+    from oracle import loader
+
+    t0 = time.time()
+    rig = synth.WorldStepRig(lib, W, E, D, data=data, options=options, dag=dag)  # uploads `data`, never writes it
+    try:
+        rig.step(steps)
+        got = rig.download()
+    finally:
+        rig.close()
+    want = synth.step_in_slices(loader.load(), {k: v.copy() for k, v in data.items()}, E, D, steps, dag=dag)
+    problems = synth.compare_outputs(got, want, 0.0)
+    return {"ok": not problems, "problems": problems[:4], "steps": steps, "seconds": round(time.time() - t0, 2),
+            "checked": f"{W} x {E}, {dag}: every written resource after {steps} generations, bit-exact vs the CPU oracle"}
+
+
+# ------------------------------------------------------------------------------------------------
+# device-resident measurement of one configuration
+# ------------------------------------------------------------------------------------------------
+def timed_windows(rig, K: int, windows: int, barrier, reduce_max=None):
+    """`windows` x exactly K generations, each bracketed by barrier + synchronize; per window (span_ms, kernel_ms)."""
+    spans, kernels, walls = [], [], []
+    for _ in range(windows):
+        rig.device_ms()
+        rig.span_ms()
+        barrier()
+        t0 = time.perf_counter()
+        rig.schedule(K)
+        rig.wait()
+        barrier()
+        walls.append(1e3 * (time.perf_counter() - t0))
+        kernel_ms, timed = rig.device_ms()
+        span_ms = rig.span_ms()
+        spans.append(span_ms if (timed == K and span_ms > 0.0) else walls[-1])
+        kernels.append(kernel_ms)
+    if reduce_max is not None:
+        spans = reduce_max(spans)
+    return spans, kernels, walls
+
+
+def roofline_of(rig, np, abi, synth, dag, W, E, D, kernel_ms, step_ms, peak, peak_src, info) -> dict:
+    stats = rig.stats()
+    f_vis = float(stats[abi.STAT_VISIBLE]) / max(float(stats[abi.STAT_ENTITIES]), 1.0)
+    f_vis2 = 0.0
+    if dag == "dag16":
+        st2 = rig.download(("stats2",))["stats2"].reshape(-1).view(np.uint64)
+        f_vis2 = float(st2[abi.STAT_VISIBLE]) / max(float(st2[abi.STAT_ENTITIES]), 1.0)
+    b3 = synth.dag_bytes_per_entity_step(dag, f_vis, f_vis2)
+    alg_bytes = b3 * W * E
+    achieved = alg_bytes / (kernel_ms * 1e-3) / 1e9 if kernel_ms > 0 else 0.0
+    achieved_step = alg_bytes / (step_ms * 1e-3) / 1e9 if step_ms > 0 else 0.0
+    traffic, traffic_src = ncu_traffic(dag, W, E, D)
+    return {"bound": "hbm", "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s", "frac": round(achieved / peak, 4),
+            "achieved_step": round(achieved_step, 1), "frac_step": round(achieved_step / peak, 4),
+            "traffic": traffic, "kernel": rig.executor_text(),
+            "algorithmic_bytes_per_launch": int(alg_bytes), "bytes_per_entity_step": round(b3, 3), "f_vis": round(f_vis, 4),
+            "kernel_ms": round(kernel_ms, 5), "step_ms": round(step_ms, 5), "peak_source": peak_src,
+            "traffic_source": traffic_src,
+            "note": "frac: algorithmic bytes / average per-generation device time (CUDA events around each generation); "
+                    "frac_step: the same bytes / ms_per_step (gaps between generations included), per GPU"}
+
+
+def measure_config(lib, np, torch, abi, synth, dag, W, E, D, K, WU, windows, peak, peak_src, gate: bool) -> dict:
+    """A short device-resident measurement of another BASELINE config on this GPU (N = 1), parity-gated the same way."""
+    data = synth.generate(W, E, D, dag=dag)
+    out = {"workload": f"{W} worlds x {E} entities, depth {D}, {dag}", "steps": K, "warmup": WU, "windows": windows}
+    if gate:
+        out["parity"] = parity_gate(lib, data, W, E, D, dag, synth.RigOptions(device=torch.cuda.current_device()))
+        if not out["parity"]["ok"]:
+            return out
+    rig = synth.WorldStepRig(lib, W, E, D, data=data, options=synth.RigOptions(device=torch.cuda.current_device()), dag=dag)
+    try:
+        info = rig.executor_info()
+        rig.step(WU)
+        spans, kernels, _ = timed_windows(rig, K, windows, torch.cuda.synchronize)
+        t_ms = statistics.median(spans)
+        kernel_ms = statistics.median(kernels)
+        out.update({"value": W * K / (t_ms * 1e-3), "unit": UNIT, "ms_per_step": t_ms / K,
+                    "gpu_launches": int(info.kernel_launches_per_generation) * K,
+                    "roofline": roofline_of(rig, np, abi, synth, dag, W, E, D, kernel_ms, t_ms / K, peak, peak_src, info)})
+    finally:
+        rig.close()
+    return out
+
+
+# ------------------------------------------------------------------------------------------------
 # the CUDA arm
 # ------------------------------------------------------------------------------------------------
 def run_b200(args) -> None:
@@ -159,7 +286,7 @@ def run_b200(args) -> None:
     import torch
     import torch.distributed as dist
 
-    from fimo_b200 import abi, library, synth
+    from fimo_b200 import abi, library, sharding, synth
 
     rank = int(os.environ.get("RANK", "0"))
     world_size = int(os.environ.get("WORLD_SIZE", "1"))
@@ -174,153 +301,136 @@ def run_b200(args) -> None:
 
     lib = library.load()
     W, E, D = args.worlds, args.entities, args.depth
-    K, WU = args.steps, max(args.warmup, 3)
+    K, WU, R = args.steps, max(args.warmup, 3), max(args.windows, 1)
     data = synth.generate(W, E, D, world0=rank * W, dag=args.dag)  # shard = contiguous block of global world indices
-
-    # End-of-step statistics all-reduce (the path's only collective): after every generation a 64-byte
-    # snapshot is taken in stream order, then reduced over NCCL on a side stream so that it overlaps the
-    # next generation.  Buffers rotate; the group's stream never waits for the collective.
-    # The snapshot costs nothing on the group's stream: the kernel that publishes the statistics also stores them in
-    # slot `generation % slots` of a ring in HBM (FimoB200_GroupDeviceExt.stats_ring).  Bucketing: the snapshots of
-    # BUCKET consecutive steps share ONE all-reduce (a [bucket][8] u64 block of the ring, in place), so every step's
-    # statistics are still reduced, at 1/BUCKET of the launch latency and of the SM contention (the persistent
-    # world-step grid leaves no room for NCCL's CTA, so a per-step collective runs in the gaps between
-    # generations).  A block is overwritten by the kernel only after its previous all-reduce has finished.
-    BUCKET, NBLK = max(1, args.stats_bucket), 4
-    ring = torch.zeros((NBLK * BUCKET, abi.STAT_WORDS), dtype=torch.int64, device="cuda")
-    side = torch.cuda.Stream()
-    written = [torch.cuda.Event() for _ in range(NBLK)]  # the block's last snapshot has been written (group stream)
-    reduced = [torch.cuda.Event() for _ in range(NBLK)]  # the block has been all-reduced (side stream)
-    state = {"ext": None, "n": 0, "flushed": 0}
-
-    def reduce_upto(n: int):
-        """All-reduce the snapshots of generations [flushed, n) — they lie in one block — on the side stream."""
-        first = state["flushed"]
-        if n <= first:
-            return
-        blk = ((n - 1) // BUCKET) % NBLK
-        assert first // BUCKET == (n - 1) // BUCKET
-        lo, hi = first % (NBLK * BUCKET), (n - 1) % (NBLK * BUCKET) + 1
-        written[blk].record(state["ext"])
-        side.wait_event(written[blk])
-        with torch.cuda.stream(side):
-            dist.all_reduce(ring[lo:hi])
-        reduced[blk].record(side)
-        state["flushed"] = n
-
-    def post_step(_user, stream, generation):
-        # generation `generation` has just been enqueued; its kernel writes ring slot generation % (NBLK * BUCKET)
-        if state["ext"] is None:
-            state["ext"] = torch.cuda.ExternalStream(stream, device=torch.device("cuda", local_rank))
-        n = int(generation) + 1  # generations enqueued so far
-        state["n"] = n
-        if n % BUCKET == 0:
-            reduce_upto(n)
-            if n >= NBLK * BUCKET:  # the next generation starts overwriting the oldest block: wait for its collective
-                state["ext"].wait_event(reduced[(n // BUCKET) % NBLK])
-
-    def flush_stats():
-        """All-reduce the tail of the current block (called inside the timed region, after the last schedule)."""
-        reduce_upto(state["n"])
-
     options = synth.RigOptions(fused=not args.no_fusion, graph=not args.no_graph, device=local_rank)
-    if distributed:
-        options.stats_ring, options.stats_ring_slots = ring.data_ptr(), NBLK * BUCKET
-    rig = synth.WorldStepRig(lib, W, E, D, data=data, options=options,
-                             post_step=post_step if distributed else None, dag=args.dag)
-    info = rig.executor_info()
+    device = torch.device("cuda", local_rank)
 
     def barrier():
         if distributed:
             dist.barrier()
         torch.cuda.synchronize()
 
-    # ---- value: inputs resident in HBM, K generations back to back -------------------------------------
+    def reduce_max(values):
+        if not distributed:
+            return values
+        t = torch.tensor(values, dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return [float(v) for v in t.cpu()]
+
+    # ---- parity gate: this workload, this launch plan, 2 generations, against the oracle (rank 0's shard) -------------
+    parity = None
+    if not args.no_parity_gate:
+        if rank == 0:
+            parity = parity_gate(lib, data, W, E, D, args.dag, options)
+        if distributed:
+            flag = torch.tensor([1 if (parity is None or parity["ok"]) else 0], device="cuda")
+            dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+            failed = int(flag.item()) == 0
+        else:
+            failed = not parity["ok"]
+        if failed:
+            if rank == 0:
+                print("bench.py: PARITY GATE FAILED — no bench line:\n" + "\n".join(parity["problems"]), file=sys.stderr, flush=True)
+            raise SystemExit(3)
+
+    rig = synth.WorldStepRig(lib, W, E, D, data=data, options=options, dag=args.dag)
+    stats_mode = None
+    if distributed:  # the statistics exchange is the product's: bound once, before the first generation
+        stats_mode = abi.STATS_MODE_PEERS if args.stats == "peers" else abi.STATS_MODE_NCCL
+        if stats_mode == abi.STATS_MODE_PEERS:
+            sharding.bind_stats_peers(lib, rig.group.handle, dist, torch, slots=64, device=device)
+        else:
+            sharding.bind_stats_nccl(lib, rig.group.handle, dist, torch, bucket=max(1, args.stats_bucket), device=device)
+            WU = max(WU, 2 * max(1, args.stats_bucket))  # warm at least one full bucket's collective
+    info = rig.executor_info()
+
+    # ---- value: inputs resident in HBM, windows of K generations back to back ---------------------------------------
     rig.step(WU)
-    rig.device_ms()  # reset the per-generation timers
-    rig.span_ms()
     sampler = ClockSampler(local_rank)
     time.sleep(0.25)
-    barrier()
     t0 = time.time()
-    rig.schedule(K)
-    if distributed:
-        state["last_row"] = (state["n"] - 1) % (NBLK * BUCKET)
-        flush_stats()
-    rig.wait()
-    torch.cuda.synchronize()
+    spans, kernels, walls = timed_windows(rig, K, R, barrier, reduce_max)
     t1 = time.time()
-    kernel_ms, timed = rig.device_ms()  # CUDA events on the group's stream around each generation (device time)
-    span_ms = rig.span_ms()  # first generation's start -> last generation's end, on the device
-    barrier()
     clocks = sampler.summary(t0, t1)
-    stats = rig.stats()
-    f_vis = float(stats[abi.STAT_VISIBLE]) / float(stats[abi.STAT_ENTITIES])
-    wall_ms = 1e3 * (t1 - t0)
-    # the job's time: CUDA events on the group's stream spanning the K generations (gaps included);
-    # the host wall clock over the same region is reported beside it
-    t_ms = span_ms if (timed == K and span_ms > 0.0) else wall_ms
-    if distributed:
-        tt = torch.tensor([t_ms], dtype=torch.float64, device="cuda")
-        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-        t_ms = float(tt.item())
-        side.synchronize()
-        global_stats = ring[state["last_row"]].cpu().numpy().astype(np.uint64)
+    t_ms = statistics.median(spans)
+    kernel_ms = statistics.median(kernels)
     value = world_size * W * K / (t_ms * 1e-3)
+    generations_done = WU + K * R
 
-    # ---- roofline of the dominant kernel ---------------------------------------------------------------
+    # ---- N > 1: the exchanged statistics are checked, not just printed --------------------------------------------
+    global_stats = None
+    if distributed:
+        local = rig.stats()
+        last = generations_done - 1
+        got = sharding.global_stats(lib, rig.group.handle, last, stats_mode)
+        want = sharding.allreduce_stats(dist, torch, local, device=device)  # the harness's own NCCL all-reduce of the same words
+        if not np.array_equal(got[:5], want[:5]) or int(got[abi.STAT_ENTITIES]) != world_size * W * E or int(got[abi.STAT_WORLDS]) != world_size * W:
+            raise SystemExit(f"bench.py: rank {rank}: exchanged statistics {got[:5]} differ from the all-reduced local ones {want[:5]}")
+        global_stats = {"visible": int(got[abi.STAT_VISIBLE]), "entities": int(got[abi.STAT_ENTITIES]), "worlds": int(got[abi.STAT_WORLDS]),
+                        "world_steps": int(got[abi.STAT_STEPS]), "generation": last, "transport": args.stats,
+                        "checked": "== torch.distributed all_reduce(SUM) of every rank's local statistics; entities / worlds == N x shard"}
+
+    # ---- roofline of the dominant kernel -----------------------------------------------------------------------------
     peak, peak_src = measured_peaks()
-    f_vis2 = 0.0
-    if args.dag == "dag16":
-        st2 = rig.download(("stats2",))["stats2"].reshape(-1).view(np.uint64)
-        f_vis2 = float(st2[abi.STAT_VISIBLE]) / float(st2[abi.STAT_ENTITIES])
-    b3 = synth.dag_bytes_per_entity_step(args.dag, f_vis, f_vis2)
-    alg_bytes = b3 * W * E
-    achieved = alg_bytes / (kernel_ms * 1e-3) / 1e9 if kernel_ms > 0 else 0.0
-    traffic = None
-    try:
-        traffic = json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get("world_step_bytes_per_launch")
-    except Exception:
-        pass
-    roofline = {"bound": "hbm", "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s", "frac": round(achieved / peak, 4),
-                "traffic": traffic, "kernel": (("k_world_step_pipe (TMA-fed persistent fused world-step)" if info.kernel_launches_per_generation == 1 else
-                            "k_world_step_pipe<team> + k_compact_lists (CTA teams per world)") if E % 4 == 0 else
-                           "k_world_cta (fused, one CTA per world)") if info.fused_world_step else
-                          f"CUDA graph of {info.nodes} per-system kernels (whole generation)",
-                "algorithmic_bytes_per_launch": int(alg_bytes), "bytes_per_entity_step": round(b3, 3), "f_vis": round(f_vis, 4),
-                "kernel_ms": round(kernel_ms, 5), "peak_source": peak_src, "traffic_source": "profiles/traffic.json (ncu --set full)"}
+    roofline = roofline_of(rig, np, abi, synth, args.dag, W, E, D, kernel_ms, t_ms / K, peak, peak_src, info)
+    alg_bytes = roofline["algorithmic_bytes_per_launch"]
 
     # ---- e2e: through the C ABI with HOST buffers, copies inside the timed region --------------------
     e2e = None
     if not args.no_e2e:
-        e2e = run_e2e(rig, torch, np, abi, W, K, distributed, dist, world_size)
+        e2e = run_e2e(rig, torch, np, abi, W, E, K, distributed, dist, world_size, roofline["f_vis"])
 
+    default_config = (W, E, D, args.dag) == (4096, 1024, 4, "chain3")
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world_size, "steps": K, "warmup": WU,
         "ms_per_step": t_ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
         "data": "synthetic",
         "config": {"workload": f"{W} worlds x {E} entities per GPU, depth-{D} transform hierarchy, {DAG_TEXT[args.dag]}"
-                               + (", BASELINE.json configs[1]" if (W, E, D, args.dag) == (4096, 1024, 4, "chain3") else ""),
+                               + (", BASELINE.json configs[1]" if default_config else ""),
                    "dag": args.dag,
                    "worlds_per_gpu": W, "entities_per_world": E, "depth": D, "executor": ("fused world-step kernel" if info.fused_world_step else "one kernel per system")
                    + (" in a CUDA graph" if info.uses_cuda_graph else ", plain stream launches"),
-                   "l2": "inputs larger than L2 (state touched per step = %.0f MB > 126 MB)" % (alg_bytes / 1e6),
-                   "sharding": "worlds by global index, no data-path collective; every step's statistics (64 B) all-reduced over NCCL on a "
-                               f"side stream, {args.stats_bucket} steps per collective"},
-        "wall_ms_per_step": wall_ms / K, "device_ms_per_step": kernel_ms,
+                   "l2": "inputs larger than L2 (state touched per step = %.0f MB > 126 MB)" % (alg_bytes / 1e6) if alg_bytes > 126e6 else
+                         "state touched per step = %.0f MB (partly L2-resident between steps; no flush)" % (alg_bytes / 1e6),
+                   "timing": f"{R} windows of exactly {K} generations, each bracketed by barrier + synchronize, device-timed (CUDA events on the "
+                             "group's stream), max over ranks; value = median window",
+                   "sharding": "worlds by global index, no data-path collective; every generation's statistics (64 B) exchanged by the product: "
+                               + ("peer stores over NVLink from the publishing CTA" if args.stats == "peers" else
+                                  f"ncclAllReduce on a library side stream, {args.stats_bucket} generations per collective")},
+        "windows": {"n": R, "ms_per_step_median": t_ms / K, "ms_per_step_min": min(spans) / K, "ms_per_step_max": max(spans) / K,
+                    "value_min": world_size * W * K / (max(spans) * 1e-3), "value_max": world_size * W * K / (min(spans) * 1e-3)},
+        "wall_ms_per_step": statistics.median(walls) / K, "device_ms_per_step": kernel_ms,
         "gpu_launches": int(info.kernel_launches_per_generation) * K,
         "roofline": roofline, "clocks": clocks,
     }
+    if parity is not None:
+        line["parity"] = {k: parity[k] for k in ("ok", "checked", "seconds")}
     if e2e is not None:
         line["e2e"] = e2e["headline"]
+        line["e2e_constants_only"] = e2e["constants_only"]
         line["e2e_full_state"] = e2e["full_state"]
+    if global_stats is not None:
+        line["global_stats"] = global_stats
     if distributed:
-        line["global_stats"] = {"visible": int(global_stats[abi.STAT_VISIBLE]), "entities": int(global_stats[abi.STAT_ENTITIES]),
-                                "worlds": int(global_stats[abi.STAT_WORLDS])}
+        dist.barrier()  # every rank has finished storing into its peers' inboxes before anyone tears down
     rig.close()
+    if rank == 0 and world_size == 1 and default_config and not args.no_other_configs:
+        # the other single-GPU BASELINE shapes, short, so that the driver's record carries them (not bench lines of their own)
+        line["other_configs"] = {
+            "configs[2]": measure_config(lib, np, torch, abi, synth, "dag8", 256, 65536, 8, 20, 5, 3, peak, peak_src, not args.no_parity_gate),
+            "configs[4] per-GPU shape": measure_config(lib, np, torch, abi, synth, "dag16", 1024, 1024, 4, 20, 5, 3, peak, peak_src, not args.no_parity_gate),
+        }
+        for name, cfg in line["other_configs"].items():
+            if "parity" in cfg and not cfg["parity"]["ok"]:
+                print(f"bench.py: PARITY GATE FAILED for {name} — no bench line:\n" + "\n".join(cfg["parity"]["problems"]), file=sys.stderr, flush=True)
+                raise SystemExit(3)
     if rank == 0 and not args.no_cpu_baseline and world_size == 1:
-        base = cpu_arm(max(1, min(CPU_SAMPLE_WORLDS, W, (CPU_SAMPLE_WORLDS * 1024) // max(E, 1))), E, D, args.cpu_steps, 2, args.dag)
+        base = cpu_arm(max(1, min(CPU_SAMPLE_WORLDS, W, (CPU_SAMPLE_WORLDS * 1024) // max(E, 1))), E, D, args.cpu_steps, 2, args.dag, seconds_budget=10.0)
         line["cpu_baseline"] = {k: base[k] for k in ("value", "unit", "cores", "kind", "sample")}
+        if default_config:  # BASELINE.json configs[0]: a single world x 1k entities on the CPU workers
+            c1 = cpu_arm(1, 1024, 4, 0, 20, "chain3", seconds_budget=3.0)
+            line["cpu_baseline_configs0"] = {k: c1[k] for k in ("value", "unit", "cores", "kind", "sample")}
     if rank == 0:
         print(json.dumps(line), flush=True)
     if distributed:
@@ -328,87 +438,32 @@ def run_b200(args) -> None:
         dist.destroy_process_group()
 
 
-def _tensor_from_ptr(torch, ptr: int, n_int64: int, device: int):
-    """A torch int64 view over device memory owned by the library (CUDA array interface)."""
+def run_e2e(rig, torch, np, abi, W, E, K, distributed, dist, world_size, f_vis) -> dict:
+    """The same metric end to end: every step copies that step's inputs host->device from pinned memory and reads the
+    step's result device->host, all through the C ABI, several steps in flight (schedule is asynchronous in the
+    reference too, SystemGroup.zig:430-452), every result waited for inside the timed region.
 
-    class _Holder:
-        __cuda_array_interface__ = {"shape": (n_int64,), "typestr": "<i8", "data": (int(ptr), False), "version": 3}
+    headline (`e2e`): inputs = camera frustum + dt of every world (what a host changes each frame; the entity state
+                stays resident like model weights); result = WHAT CULL PRODUCES: per-world visible counts, the
+                visibility masks and the ordered visible lists packed back to back (fimo_b200_group_schedule_readback).
+    constants_only: same inputs, result = statistics + per-world counts only (fimo_b200_group_schedule_io).
+    full_state: every live-in resource uploaded and every live-out resource downloaded each step — the worst case.
+    Each leg is warmed for >= 2 x the pipeline depth, then timed for at least 200 steps and 0.4 s, three times; the
+    median is reported."""
+    from fimo_b200 import synth
+    from fimo_b200.worlds import Fence
 
-    return torch.as_tensor(_Holder(), device=torch.device("cuda", device))
-
-
-def run_e2e(rig, torch, np, abi, W, K, distributed, dist, world_size) -> dict:
-    """The same metric end to end: every step copies that step's inputs host->device from pinned memory
-    and reads the step's result device->host, all through the C ABI (world_lock_resources +
-    fimo_b200_resource_upload/download + system_group_schedule + fence wait).
-
-    headline:   per-step inputs = camera frustum + dt of every world (what a host changes each frame; the
-                entity state stays resident like model weights); result = statistics + per-world visible counts.
-    full_state: every live-in resource uploaded and every live-out resource downloaded each step (the
-                whole 72 B + 60 B per entity crosses PCIe) — the worst case, reported for completeness."""
     def pinned_like(a):
         t = torch.empty(a.shape, dtype=torch.float32 if a.dtype == np.float32 else torch.int32).pin_memory()
         v = t.numpy().view(a.dtype)
         v[...] = a
         return t, v
 
-    steps = max(3, min(K, 50))
     keep = []
-    ins = {}
-    for name in ("frustum", "dt"):
-        t, v = pinned_like(rig.host[name])
-        keep.append(t)
-        ins[name] = v
-    outs = {}
-    for name in ("stats", "vis_count"):
-        t, v = pinned_like(rig.host[name])
-        keep.append(t)
-        outs[name] = v
-
-    from fimo_b200.worlds import Fence
-    landed = Fence(rig.lib)
-
-    def step_headline():
-        # stream-ordered: H2D inputs -> one generation -> D2H result, all queued on the group's stream through
-        # fimo_b200_group_transfer / system_group_schedule; ONE host wait per step, on the last copy's fence
-        for name, v in ins.items():
-            rig.upload_async(name, v)
-        rig.schedule(1, signal_last=False)
-        rig.download_async("stats", outs["stats"])
-        landed.reset()
-        rig.download_async("vis_count", outs["vis_count"], landed)
-        landed.wait()
-
-    def step_locked():
-        # the reference's host-access protocol: world_lock_resources -> blocking copy -> unlock, per resource
-        for name, v in ins.items():
-            rig.upload(name, v)
-        rig.step(1)
-        for name, v in outs.items():
-            rig.download_into(name, v)
-
-    def timed(fn, n):
-        fn()
-        if distributed:
-            dist.barrier()
-        torch.cuda.synchronize()
-        t0 = time.perf_counter()
-        for _ in range(n):
-            fn()
-        torch.cuda.synchronize()
-        dt = time.perf_counter() - t0
-        if distributed:
-            tt = torch.tensor([dt], dtype=torch.float64, device="cuda")
-            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-            dt = float(tt.item())
-        return dt
-
-    # Pipelined: up to DEPTH steps in flight (schedule is asynchronous in the reference too, SystemGroup.zig:430-452).
-    # Every step still uploads ITS inputs from its own pinned slot and downloads ITS result into its own pinned
-    # slot; the host waits for step i's result before it reuses slot i % DEPTH, and for all of them before the
-    # clock stops.  The stream keeps the order H2D(i) -> generation(i) -> D2H(i) -> H2D(i+1) ...
     DEPTH = 4
-    pin_slots, pout_slots, fences = [], [], []
+    in_slots, out_slots, rb_slots, fences = [], [], [], [Fence(rig.lib) for _ in range(DEPTH)]
+    capacity = int(1.15 * f_vis * W * E) + 1024  # list entries the read-back buffer holds (measured visible fraction + 15 %)
+    rb_words = rig.readback_words(capacity)
     for _ in range(DEPTH):
         si, so = {}, {}
         for name in ("frustum", "dt"):
@@ -419,71 +474,91 @@ def run_e2e(rig, torch, np, abi, W, K, distributed, dist, world_size) -> dict:
             t, v = pinned_like(rig.host[name])
             keep.append(t)
             so[name] = v
-        pin_slots.append(si), pout_slots.append(so), fences.append(Fence(rig.lib))
-    io_slots = [(rig.io_list(pin_slots[i]), rig.io_list(pout_slots[i])) for i in range(DEPTH)]
-    pipe = {"i": 0, "pending": [False] * DEPTH}
+        t = torch.zeros(rb_words, dtype=torch.int32).pin_memory()
+        keep.append(t)
+        in_slots.append(si), out_slots.append(so), rb_slots.append(t.numpy().view(np.uint32))
+    up_lists = [rig.io_list(in_slots[i]) for i in range(DEPTH)]
+    down_lists = [rig.io_list(out_slots[i]) for i in range(DEPTH)]
+    rb_descs = [rig.readback_desc(rb_slots[i]) for i in range(DEPTH)]
 
-    def step_pipelined():
-        slot = pipe["i"] % DEPTH
-        pipe["i"] += 1
-        if pipe["pending"][slot]:
-            fences[slot].wait()  # the result of the step that used this slot DEPTH steps ago has landed
-        fences[slot].reset()
-        rig.schedule_io(io_slots[slot][0], io_slots[slot][1], fences[slot])  # H2D inputs -> generation -> D2H result
-        pipe["pending"][slot] = True
+    def make_pipeline(submit):
+        state = {"i": 0, "pending": [False] * DEPTH}
+
+        def step():
+            slot = state["i"] % DEPTH
+            state["i"] += 1
+            if state["pending"][slot]:
+                fences[slot].wait()  # the result of the step that used this slot DEPTH steps ago has landed
+            fences[slot].reset()
+            submit(slot)
+            state["pending"][slot] = True
+
+        def drain():
+            for slot in range(DEPTH):
+                if state["pending"][slot]:
+                    fences[slot].wait()
+                    state["pending"][slot] = False
+
+        return step, drain
+
+    def timed_leg(step, drain, min_steps=200, min_seconds=0.4, repeats=3):
+        for _ in range(3 * DEPTH):
+            step()
+        drain()
+        rates = []
+        for _ in range(repeats):
+            if distributed:
+                dist.barrier()
+            torch.cuda.synchronize()
+            n, t0 = 0, time.perf_counter()
+            while n < min_steps or time.perf_counter() - t0 < min_seconds:
+                step()
+                n += 1
+            drain()
+            torch.cuda.synchronize()
+            dt = time.perf_counter() - t0
+            if distributed:  # all ranks run the same number of steps per second of the slowest: rate = min over ranks
+                tt = torch.tensor([n / dt], dtype=torch.float64, device="cuda")
+                dist.all_reduce(tt, op=dist.ReduceOp.MIN)
+                rates.append(float(tt.item()))
+            else:
+                rates.append(n / dt)
+        return statistics.median(rates), min(rates), max(rates), n
+
+    # headline: cull outputs come back
+    step_rb, drain_rb = make_pipeline(lambda s: rig.schedule_readback(up_lists[s], rb_descs[s], fences[s]))
+    rate, lo, hi, n = timed_leg(step_rb, drain_rb)
+    last = rig.parse_readback(rb_slots[0])
+    if last["truncated"] or last["n_worlds"] != W or int(last["counts"].sum()) != last["total"]:
+        raise SystemExit(f"bench.py: read-back buffer inconsistent: {last['total']} visible, truncated={last['truncated']}")
+    h2d = int(sum(v.nbytes for v in in_slots[0].values()))
+    head = {"value": world_size * W * rate, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": int(rb_words * 4),
+            "ms_per_step": 1e3 / rate, "value_min": world_size * W * lo, "value_max": world_size * W * hi, "steps_per_repeat": n, "repeats": 3,
+            "inputs": "frustum + dt of every world from pinned host memory",
+            "result": f"what cull produces: per-world visible counts + offsets, visibility masks, ordered visible lists packed back to back "
+                      f"({last['total']} entries of a {capacity}-entry buffer)",
+            "api": "fimo_b200_group_schedule_readback: one C-ABI call per step = H2D of the step's inputs (staged beside the running generation) "
+                   "+ one generation + device-side pack of the cull outputs + ONE copy-engine D2H beside the next generation + completion fence; "
+                   f"{DEPTH} steps in flight, every result waited for inside the timed region",
+            "in_flight": DEPTH}
+
+    # constants only (round 1's headline)
+    step_io, drain_io = make_pipeline(lambda s: rig.schedule_io(up_lists[s], down_lists[s], fences[s]))
+    rate_c, lo_c, hi_c, n_c = timed_leg(step_io, drain_io)
 
     def step_io_sync():
         fences[0].reset()
-        rig.schedule_io(io_slots[0][0], io_slots[0][1], fences[0])
+        rig.schedule_io(up_lists[0], down_lists[0], fences[0])
         fences[0].wait()
 
-    def drain_pipeline():
-        for slot in range(DEPTH):
-            if pipe["pending"][slot]:
-                fences[slot].wait()
-                pipe["pending"][slot] = False
+    rate_s, _, _, _ = timed_leg(step_io_sync, lambda: None, min_steps=100, min_seconds=0.2)
+    consts = {"value": world_size * W * rate_c, "unit": UNIT, "h2d_bytes_per_step": h2d,
+              "d2h_bytes_per_step": int(sum(v.nbytes for v in out_slots[0].values())), "ms_per_step": 1e3 / rate_c,
+              "value_min": world_size * W * lo_c, "value_max": world_size * W * hi_c, "steps_per_repeat": n_c,
+              "result": "statistics + per-world visible counts", "api": f"fimo_b200_group_schedule_io, {DEPTH} steps in flight",
+              "sync_value": world_size * W * rate_s, "sync_api": "same call, one step in flight: the host waits for each result before queuing the next"}
 
-    def timed_pipelined(n):
-        step_pipelined()
-        drain_pipeline()
-        if distributed:
-            dist.barrier()
-        torch.cuda.synchronize()
-        t0 = time.perf_counter()
-        for _ in range(n):
-            step_pipelined()
-        drain_pipeline()
-        torch.cuda.synchronize()
-        dt = time.perf_counter() - t0
-        if distributed:
-            tt = torch.tensor([dt], dtype=torch.float64, device="cuda")
-            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-            dt = float(tt.item())
-        return dt
-
-    psteps = max(steps, min(K, 200))
-    dt_pipe = timed_pipelined(psteps)
-    dt_head = timed(step_io_sync, steps)
-    dt_xfer = timed(step_headline, steps)
-    head = {"value": world_size * W * psteps / dt_pipe, "unit": UNIT,
-            "h2d_bytes_per_step": int(sum(v.nbytes for v in ins.values())),
-            "d2h_bytes_per_step": int(sum(v.nbytes for v in outs.values())), "steps": psteps,
-            "ms_per_step": 1e3 * dt_pipe / psteps,
-            "inputs": "frustum + dt of every world from pinned host memory", "result": "stats + per-world visible counts",
-            "api": "fimo_b200_group_schedule_io: one C-ABI call per step = stream-ordered H2D of the step's inputs + one "
-                   f"generation + D2H of its result + completion fence; up to {DEPTH} steps in flight (each with its own pinned "
-                   "input/result slot), every result waited for inside the timed region",
-            "in_flight": DEPTH,
-            "sync_value": world_size * W * steps / dt_head, "sync_ms_per_step": 1e3 * dt_head / steps,
-            "sync_api": "same call, one step in flight: the host waits for each step's result before it queues the next",
-            "transfer_value": world_size * W * steps / dt_xfer,
-            "transfer_api": "fimo_b200_group_transfer x2 (H2D) + system_group_schedule + fimo_b200_group_transfer x2 (D2H) + fence "
-                            "wait, one step in flight"}
-    dt_lock = timed(step_locked, steps)
-    head["locked_value"] = world_size * W * steps / dt_lock
-    head["locked_api"] = "world_lock_resources + blocking fimo_b200_resource_upload/download + schedule + fence wait"
-
-    from fimo_b200 import synth
+    # full state
     fins, fouts = {}, {}
     for name in synth.LIVE_IN + ("frustum", "dt"):
         t, v = pinned_like(rig.host[name])
@@ -501,13 +576,19 @@ def run_e2e(rig, torch, np, abi, W, K, distributed, dist, world_size) -> dict:
         for name, v in fouts.items():
             rig.download_into(name, v)
 
-    fsteps = max(2, min(steps, 5))
-    dt_full = timed(step_full, fsteps)
+    step_full()
+    torch.cuda.synchronize()
+    fsteps = 4
+    t0 = time.perf_counter()
+    for _ in range(fsteps):
+        step_full()
+    torch.cuda.synchronize()
+    dt_full = time.perf_counter() - t0
     full = {"value": world_size * W * fsteps / dt_full, "unit": UNIT,
             "h2d_bytes_per_step": int(sum(v.nbytes for v in fins.values())),
             "d2h_bytes_per_step": int(sum(v.nbytes for v in fouts.values())), "steps": fsteps,
             "ms_per_step": 1e3 * dt_full / fsteps}
-    return {"headline": head, "full_state": full}
+    return {"headline": head, "constants_only": consts, "full_state": full}
 
 
 def main():

@@ -377,26 +377,43 @@ PRODUCT_SYMBOLS = [
     ("fimo_b200_resource_upload", FimoStatus, [POINTER(ResourceView), c_void_p]),
     ("fimo_b200_resource_download", FimoStatus, [POINTER(ResourceView), c_void_p]),
     ("fimo_b200_group_executor_info", FimoStatus, [c_void_p, POINTER(ExecutorInfo)]),
+    ("fimo_b200_group_executor_describe", c_size_t, [c_void_p, c_char_p, c_size_t]),
     ("fimo_b200_group_stream", c_void_p, [c_void_p]),
     ("fimo_b200_group_wait_idle", None, [c_void_p]),
     ("fimo_b200_group_device_ms", c_double, [c_void_p, POINTER(c_uint64)]),
     ("fimo_b200_group_span_ms", c_double, [c_void_p]),
     ("fimo_b200_group_transfer", FimoStatus, [c_void_p, c_void_p, c_void_p, c_uint32, POINTER(Fence)]),
     ("fimo_b200_group_schedule_io", FimoStatus, [c_void_p, c_void_p, c_size_t, c_void_p, c_size_t, c_void_p, c_size_t, POINTER(Fence)]),
+    ("fimo_b200_group_schedule_readback", FimoStatus, [c_void_p, c_void_p, c_size_t, c_void_p, c_void_p, c_size_t, POINTER(Fence)]),
     ("fimo_worlds_b200_set_trace_sink", None, [TraceSinkFn, c_void_p]),
     ("fimo_b200_host_alloc", c_void_p, [c_size_t]),
     ("fimo_b200_host_free", None, [c_void_p]),
+    ("fimo_b200_group_stats_peers_open", FimoStatus, [c_void_p, c_uint32, c_void_p]),
+    ("fimo_b200_group_stats_peers_bind", FimoStatus, [c_void_p, c_void_p, c_uint32, c_uint32]),
+    ("fimo_b200_stats_nccl_unique_id", FimoStatus, [c_void_p]),
+    ("fimo_b200_group_stats_nccl_bind", FimoStatus, [c_void_p, c_void_p, c_uint32, c_uint32, c_uint32]),
+    ("fimo_b200_group_global_stats", FimoStatus, [c_void_p, c_uint64, c_uint32, POINTER(c_uint64)]),
 ]
+STATS_PEER_HANDLE_BYTES, STATS_NCCL_ID_BYTES, STATS_MAX_RANKS = 64, 128, 16
+STATS_MODE_PEERS, STATS_MODE_NCCL = 1, 2
 TRANSFER_HOST_TO_DEVICE, TRANSFER_DEVICE_TO_HOST = 0, 1
 
 
 class StepTransfer(C.Structure):  # FimoB200_StepTransfer
     _fields_ = [("resource", c_void_p), ("host", c_void_p)]
 
+
+class CullReadback(C.Structure):  # FimoB200_CullReadback
+    _fields_ = [("vis_mask", c_void_p), ("vis_list", c_void_p), ("vis_count", c_void_p), ("host", c_void_p), ("host_bytes", c_uint64)]
+
+
+READBACK_HEADER_WORDS = 8
+
 # CPU-oracle-only helpers (tests / bench cpu_baseline only)
 ORACLE_SYMBOLS = [
     ("fimo_oracle_builtin_system", FimoStatus, [c_uint32, POINTER(SystemDescriptor)]),
     ("fimo_oracle_step_groups", c_double, [POINTER(c_void_p), c_size_t, c_size_t]),
+    ("fimo_oracle_step_groups_queued", c_double, [POINTER(c_void_p), c_size_t, c_size_t]),
     ("fimo_oracle_hardware_threads", c_uint32, []),
 ]
 

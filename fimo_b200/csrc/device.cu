@@ -113,6 +113,13 @@ struct Executor {
     size_t staging_bytes = 0;
     cudaEvent_t staged[2] = {nullptr, nullptr}, slot_free[2] = {nullptr, nullptr};
     uint64_t staged_count = 0;
+    // Packed cull read-back (executor_launch with a Readback): two HBM staging slots, drained by the copy engine on
+    // `readback_stream` while the next generation runs; `rb_drained[s]` fences the reuse of slot s.
+    cudaStream_t readback_stream = nullptr;
+    void *rb_staging[2] = {nullptr, nullptr};
+    size_t rb_bytes = 0;
+    cudaEvent_t rb_packed[2] = {nullptr, nullptr}, rb_drained[2] = {nullptr, nullptr};
+    uint64_t rb_count = 0;
     // Host memory that queued device -> host copies have yet to write.  An upload that reads such memory (a result fed
     // back as the next step's input without waiting) must stay in stream order behind that copy: it is not staged.
     struct HostRange {
@@ -359,10 +366,17 @@ void executor_destroy(Executor *ex) {
         cudaStreamSynchronize(ex->copy_stream);
         cudaStreamDestroy(ex->copy_stream);
     }
+    if (ex->readback_stream) {
+        cudaStreamSynchronize(ex->readback_stream);
+        cudaStreamDestroy(ex->readback_stream);
+    }
     for (int i = 0; i < 2; i++) {
         if (ex->staged[i]) cudaEventDestroy(ex->staged[i]);
         if (ex->slot_free[i]) cudaEventDestroy(ex->slot_free[i]);
         if (ex->staging[i]) cudaFree(ex->staging[i]);
+        if (ex->rb_packed[i]) cudaEventDestroy(ex->rb_packed[i]);
+        if (ex->rb_drained[i]) cudaEventDestroy(ex->rb_drained[i]);
+        if (ex->rb_staging[i]) cudaFree(ex->rb_staging[i]);
     }
     cudaStreamDestroy(ex->stream);
     delete ex;
@@ -495,17 +509,108 @@ bool enqueue_copies(cudaStream_t stream, const Copy *copies, size_t n, bool to_d
 }
 } // namespace
 
+// ---- packed cull read-back -------------------------------------------------------------------------------------
+// Host / staging layout, u32 words: header[8] = {total visible, n_worlds, mask_words, list capacity (entries), truncated,
+// generation lo, generation hi, entities}; counts[n_worlds]; offsets[n_worlds] (exclusive prefix of counts);
+// mask[n_worlds][mask_words]; list[capacity] = the worlds' ordered visible lists back to back.
+namespace {
+constexpr int kScanThreads = 1024;
+__global__ void __launch_bounds__(kScanThreads) k_readback_scan(const uint32_t *__restrict__ count, uint32_t W, uint32_t mask_words, uint32_t entities,
+                                                                uint32_t capacity, unsigned long long generation, uint32_t *__restrict__ out) {
+    __shared__ uint32_t s_warp[kScanThreads / 32];
+    __shared__ uint32_t s_carry;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    uint32_t *counts = out + 8, *offsets = out + 8 + W;
+    if (tid == 0) s_carry = 0;
+    __syncthreads();
+    for (uint32_t base = 0; base < W; base += kScanThreads) {
+        const uint32_t w = base + tid;
+        const uint32_t c = w < W ? count[w] : 0u;
+        uint32_t incl = c;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const uint32_t v = __shfl_up_sync(0xFFFFFFFFu, incl, d);
+            if (lane >= d) incl += v;
+        }
+        if (lane == 31) s_warp[warp] = incl;
+        __syncthreads();
+        uint32_t before = s_carry;
+        for (int i = 0; i < warp; i++) before += s_warp[i];
+        if (w < W) counts[w] = c, offsets[w] = before + incl - c;
+        __syncthreads();
+        if (tid == kScanThreads - 1) s_carry = before + incl;
+        __syncthreads();
+    }
+    if (tid == 0) {
+        const uint32_t total = s_carry;
+        out[0] = total, out[1] = W, out[2] = mask_words, out[3] = capacity, out[4] = total > capacity ? 1u : 0u;
+        out[5] = (uint32_t)(generation & 0xFFFFFFFFull), out[6] = (uint32_t)(generation >> 32), out[7] = entities;
+    }
+}
+__global__ void __launch_bounds__(128) k_readback_pack(const uint32_t *__restrict__ mask, const uint32_t *__restrict__ list, uint32_t W, uint32_t mask_words,
+                                                       uint32_t entities, uint32_t capacity, uint32_t *__restrict__ out) {
+    const uint32_t w = blockIdx.x;
+    const uint32_t n = out[8 + w], at = out[8 + W + w];
+    uint32_t *dst_mask = out + 8 + 2ull * W + (uint64_t)w * mask_words;
+    uint32_t *dst_list = out + 8 + 2ull * W + (uint64_t)W * mask_words;
+    const uint32_t *src_mask = mask + (uint64_t)w * mask_words, *src_list = list + (uint64_t)w * entities;
+    for (uint32_t i = threadIdx.x; i < mask_words; i += blockDim.x) dst_mask[i] = src_mask[i];
+    for (uint32_t i = threadIdx.x; i < n; i += blockDim.x)
+        if (at + i < capacity) dst_list[at + i] = src_list[i];
+}
+
+bool enqueue_readback(Executor *ex, const Readback &rb, cudaEvent_t landed) {
+    const uint64_t fixed_words = 8 + 2 * rb.n_worlds + rb.n_worlds * rb.mask_words;
+    if (rb.host_bytes < fixed_words * 4 || rb.n_worlds > 0xFFFFFFFFull) return false;
+    const uint64_t capacity = std::min<uint64_t>(rb.host_bytes / 4 - fixed_words, rb.n_worlds * rb.entities);
+    const size_t bytes = (size_t)(fixed_words + capacity) * 4;
+    if (!ex->readback_stream) {
+        if (!ok(cudaStreamCreateWithFlags(&ex->readback_stream, cudaStreamNonBlocking), "cudaStreamCreate")) return false;
+        for (int i = 0; i < 2; i++)
+            if (!ok(cudaEventCreateWithFlags(&ex->rb_packed[i], cudaEventDisableTiming), "cudaEventCreate") ||
+                !ok(cudaEventCreateWithFlags(&ex->rb_drained[i], cudaEventDisableTiming), "cudaEventCreate"))
+                return false;
+    }
+    if (bytes > ex->rb_bytes) { // (re)size the slots: cold path, drains what is in flight
+        if (!ok(cudaStreamSynchronize(ex->readback_stream), "cudaStreamSynchronize")) return false;
+        for (int i = 0; i < 2; i++) {
+            if (ex->rb_staging[i]) cudaFree(ex->rb_staging[i]);
+            ex->rb_staging[i] = nullptr;
+            if (!ok(cudaMalloc(&ex->rb_staging[i], bytes), "cudaMalloc (read-back staging)")) return false;
+        }
+        ex->rb_bytes = bytes, ex->rb_count = 0;
+    }
+    const int slot = (int)(ex->rb_count & 1);
+    uint32_t *out = (uint32_t *)ex->rb_staging[slot];
+    if (ex->rb_count >= 2 && !ok(cudaStreamWaitEvent(ex->stream, ex->rb_drained[slot], 0), "cudaStreamWaitEvent")) return false;
+    k_readback_scan<<<1, kScanThreads, 0, ex->stream>>>(rb.count, (uint32_t)rb.n_worlds, (uint32_t)rb.mask_words, (uint32_t)rb.entities, (uint32_t)capacity,
+                                                        rb.generation, out);
+    k_readback_pack<<<(unsigned)rb.n_worlds, 128, 0, ex->stream>>>(rb.mask, rb.list, (uint32_t)rb.n_worlds, (uint32_t)rb.mask_words, (uint32_t)rb.entities,
+                                                                    (uint32_t)capacity, out);
+    bool queued = ok(cudaGetLastError(), "k_readback_pack");
+    queued = queued && ok(cudaEventRecord(ex->rb_packed[slot], ex->stream), "cudaEventRecord");
+    queued = queued && ok(cudaStreamWaitEvent(ex->readback_stream, ex->rb_packed[slot], 0), "cudaStreamWaitEvent");
+    queued = queued && ok(cudaMemcpyAsync(rb.host, out, bytes, cudaMemcpyDeviceToHost, ex->readback_stream), "cudaMemcpyAsync D2H (read-back)");
+    queued = queued && ok(cudaEventRecord(ex->rb_drained[slot], ex->readback_stream), "cudaEventRecord");
+    queued = queued && ok(cudaEventRecord(landed, ex->readback_stream), "cudaEventRecord");
+    ex->rb_count++;
+    return queued;
+}
+} // namespace
+
 bool executor_launch(Executor *ex, void (*done)(void *), void *user, const Copy *uploads, size_t n_up, const Copy *downloads,
-                     size_t n_down) {
+                     size_t n_down, const Readback *readback) {
     DeviceGuard guard(ex->device);
     Completion c{ex->take_event(), ex->take_event(), ex, done, user};
     if (!c.start || !c.end) return false;
-    if (n_down && !(c.landed = ex->take_event())) return false;
+    if ((n_down || readback) && !(c.landed = ex->take_event())) return false;
     bool busy, feedback;
     {
         std::lock_guard<std::mutex> g(ex->m);
         busy = ex->in_flight++ > 0;
-        feedback = ex->post(uploads, n_up, downloads, n_down, &c.seq);
+        std::vector<Copy> writes(downloads, downloads + n_down); // host memory this step will write
+        if (readback) writes.push_back(Copy{readback->host, nullptr, readback->host_bytes});
+        feedback = ex->post(uploads, n_up, writes.data(), writes.size(), &c.seq);
     }
     // staging pays only when an earlier generation is still running for the PCIe leg to hide behind, and is only
     // correct when no queued result copy has yet to write the memory this upload reads
@@ -517,7 +622,8 @@ bool executor_launch(Executor *ex, void (*done)(void *), void *user, const Copy 
     }
     launched = ok(cudaEventRecord(c.end, ex->stream), "cudaEventRecord") && launched;
     if (launched) launched = enqueue_copies(ex->stream, downloads, n_down, false); // its results, behind it
-    if (c.landed) launched = ok(cudaEventRecord(c.landed, ex->stream), "cudaEventRecord") && launched;
+    if (readback) launched = launched && enqueue_readback(ex, *readback, c.landed);
+    if (c.landed && (!readback || !launched)) launched = ok(cudaEventRecord(c.landed, ex->stream), "cudaEventRecord") && launched;
     if (!launched) c.done = nullptr; // the caller reports the failure itself
     completer().post(c);
     return launched;

@@ -6,6 +6,7 @@
 #include <cstdint>
 #include <functional>
 #include <memory>
+#include <string>
 #include <vector>
 
 #include "fimo_worlds_b200.h"
@@ -46,8 +47,18 @@ struct Copy {
     const void *src;
     size_t bytes;
 };
+// `readback` (fimo_b200_group_schedule_readback): behind the generation, one small pack of the cull outputs of every
+// world — counts, exclusive offsets, mask words and the first `count` entries of each ordered visible list, back to
+// back — into an HBM staging slot in stream order, then ONE copy-engine transfer of `host_bytes` to `host` on the
+// executor's read-back stream, beside the next generation; `done` runs once it has landed.
+struct Readback {
+    const uint32_t *mask, *list, *count; // HBM: [n_worlds][mask_words], [n_worlds][entities], [n_worlds]
+    uint64_t n_worlds, entities, mask_words, generation;
+    void *host;
+    size_t host_bytes;
+};
 bool executor_launch(Executor *ex, void (*done)(void *), void *user, const Copy *uploads = nullptr, size_t n_up = 0,
-                     const Copy *downloads = nullptr, size_t n_down = 0);
+                     const Copy *downloads = nullptr, size_t n_down = 0, const Readback *readback = nullptr);
 // Enqueue a stream-ordered copy between host memory and HBM behind everything launched so far.
 bool executor_transfer(Executor *ex, void *dst, const void *src, size_t bytes, bool to_device, void (*done)(void *), void *user);
 // A host system inside a device group: `d2h` copies (HBM -> pinned mirrors) in front, `fn(user)` as a host node
@@ -63,6 +74,22 @@ uint32_t executor_kernels_per_generation(Executor *ex);
 double executor_device_ms(Executor *ex, uint64_t *generations);
 double executor_last_generation_ms(Executor *ex); // device time of the generation whose `done` is running (completion thread)
 double executor_span_ms(Executor *ex);
+
+// ---- multi-GPU statistics exchange (stats_exchange.cu) -------------------------------------------
+// See include/fimo_worlds_b200.h "Multi-GPU".  `before` / `after_launch` are called by the launcher thread around
+// the enqueue of `n` generations on the group's stream (NCCL mode: ring-block reuse and the bucketed all-reduce).
+struct StatsExchange;
+StatsExchange *stats_exchange_create(int device);
+void stats_exchange_destroy(StatsExchange *x);
+bool stats_exchange_peers_open(StatsExchange *x, uint32_t slots, void *handle_out);
+bool stats_exchange_peers_bind(StatsExchange *x, const void *handles, uint32_t rank, uint32_t nranks);
+const void *stats_exchange_peer_table(StatsExchange *x); // HBM table the statistics kernel reads, or nullptr
+bool stats_nccl_unique_id(void *out);
+bool stats_exchange_nccl_bind(StatsExchange *x, const void *unique_id, uint32_t rank, uint32_t nranks, uint32_t bucket);
+void *stats_exchange_ring(StatsExchange *x, uint32_t *slots); // NCCL mode: the ring the kernel snapshots into
+bool stats_exchange_before_launch(StatsExchange *x, void *stream, uint32_t n);
+bool stats_exchange_after_launch(StatsExchange *x, void *stream, uint32_t n);
+bool stats_exchange_read(StatsExchange *x, uint64_t generation, uint32_t mode, uint64_t *out);
 
 // ---- built-in systems (kernels.cu) -------------------------------------------------------------
 // device_entry of FIMO_B200_BUILTIN_{INTEGRATE,PROPAGATE,CULL}.
@@ -97,6 +124,7 @@ struct BuiltinState {
     int device;
     void *stats_ring = nullptr; // FimoB200_GroupDeviceExt::stats_ring, if this is the group's first cull system
     uint32_t stats_ring_slots = 0;
+    const void *stats_peers = nullptr; // PeerTable in HBM (multi-GPU statistics exchange), same condition
 };
 
 // The fused world-step: integrate -> propagate -> cull of one batch in ONE kernel; every live-in
@@ -119,6 +147,7 @@ struct WorldStepViews {
     void *scratch2 = nullptr; // cull2's statistics accumulator block (its BuiltinState)
     void *stats_ring = nullptr; // FimoB200_GroupDeviceExt::stats_ring (per-generation snapshots of `stats`)
     uint32_t stats_ring_slots = 0;
+    const void *stats_peers = nullptr; // PeerTable in HBM (fimo_b200_group_stats_peers_bind)
 };
 // How the fused kernel is launched for a given batch; made once when the executor is compiled (it reads
 // level_start from HBM to size the shared-memory parent window), then reused by every launch.
@@ -146,6 +175,7 @@ bool world_step_plan(const WorldStepViews &v, int device, WorldStepPlan &plan); 
 FimoStatus world_step_launch(const WorldStepViews &v, const WorldStepPlan &plan, void *cull_scratch,
                              const FimoB200_LaunchInfo *info);
 const char *world_step_kernel_name(const WorldStepPlan &plan); // which kernel world_step_launch picks
+std::string world_step_describe(const WorldStepPlan &plan, uint64_t n_worlds); // ... and with which geometry
 // v1: one CTA per world, whole world's matrices in shared memory, loads through registers (kernels.cu)
 bool world_step_supported_v1(const WorldStepViews &v);
 FimoStatus world_step_launch_v1(const WorldStepViews &v, void *cull_scratch, const FimoB200_LaunchInfo *info);

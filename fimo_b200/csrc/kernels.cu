@@ -252,6 +252,7 @@ FimoStatus builtin_cull(void *system, const FimoB200_ResourceView *const *exclus
         fill_cull(a, exclusive[0], exclusive[1], exclusive[2], exclusive[3], shared[0], shared[1], shared[2], shared[3],
                   ((BuiltinState *)system)->scratch, W, E);
         a.ring = (unsigned long long *)((BuiltinState *)system)->stats_ring, a.ring_slots = ((BuiltinState *)system)->stats_ring_slots;
+        a.peers = (const PeerTable *)((BuiltinState *)system)->stats_peers;
         cudaStream_t stream = (cudaStream_t)info->stream;
         const unsigned grid = (unsigned)(W < 8ull * sm_count(info->device) ? W : 8ull * sm_count(info->device));
         if (E <= 2048) k_cull_cta<256><<<grid, 256, 0, stream>>>(a);
@@ -274,7 +275,7 @@ FimoStatus world_step_launch_v1(const WorldStepViews &v, void *cull_scratch, con
         a.n_worlds = (uint32_t)W, a.entities = (uint32_t)E;
         fill_propagate(a, v.world, v.pos, v.rot, v.scale, v.parent, v.level_start, W, E);
         fill_cull(a, v.vis_mask, v.vis_list, v.vis_count, v.stats, v.world, v.aabb_c, v.aabb_h, v.frustum, cull_scratch, W, E);
-        a.ring = (unsigned long long *)v.stats_ring, a.ring_slots = v.stats_ring_slots;
+        a.ring = (unsigned long long *)v.stats_ring, a.ring_slots = v.stats_ring_slots, a.peers = (const PeerTable *)v.stats_peers;
         a.vel = plane_of(v.vel, FIMO_B200_SCOPE_ENTITY, 3, E, W, "vel");
         a.dt = plane_of(v.dt, FIMO_B200_SCOPE_WORLD, 1, 1, W, "dt");
         cudaStream_t stream = (cudaStream_t)info->stream;

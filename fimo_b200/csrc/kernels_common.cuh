@@ -105,6 +105,20 @@ struct Plane { // a resource of the batch
 __device__ __forceinline__ float *fptr(const Plane &p, uint64_t w) { return (float *)(p.base + w * p.world_words); }
 __device__ __forceinline__ uint32_t *uptr(const Plane &p, uint64_t w) { return p.base + w * p.world_words; }
 
+// Multi-GPU statistics exchange over peer memory (fimo_b200_group_stats_peers_bind): where the publishing CTA stores
+// a generation's statistics — every rank's inbox, [slots][kStatsMaxRanks][16] u64 in that rank's HBM, mapped here
+// through cudaIpc (NVLink).  Each u64 is {generation tag : 32, half of a statistics word : 32}: an aligned 8-byte
+// store arrives whole, so a reader that finds all 16 tags of (slot, rank) equal to the generation's tag has the
+// words — no fence, no flag (the LL protocol of NCCL, used here for 64 bytes per generation).
+constexpr int kStatsMaxRanks = FIMO_B200_STATS_MAX_RANKS;
+struct __align__(16) PeerTable {
+    uint32_t nranks, rank, slots, pad;
+    unsigned long long *inbox[kStatsMaxRanks];
+};
+__device__ __forceinline__ void st_relaxed_sys(unsigned long long *p, unsigned long long v) {
+    asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+
 struct StepArgs {
     Plane pos, vel, dt;                             // integrate
     Plane world, rot, scale, parent, level_start;   // propagate
@@ -114,6 +128,7 @@ struct StepArgs {
     unsigned long long *scratch;                    // [0..3] accumulators, [4] ticket, [5] generations published
     unsigned long long *ring;                       // per-generation snapshots of `stats` ([ring_slots][8]) or nullptr
     uint32_t ring_slots;
+    const PeerTable *peers;                         // multi-GPU statistics exchange over peer memory, or nullptr
     // the fused 8-system DAG (world_step.cu, kSet = 1) additionally uses:
     Plane angvel, gravity, vmax, waabb, wbounds;
     uint32_t *gstats;     // FIMO_B200_GSTAT_* words of the batch
@@ -168,6 +183,7 @@ struct StatsSink { // where one cull's batch statistics go (the DAGs have up to 
     uint32_t entities;
     unsigned long long *ring = nullptr; // FimoB200_GroupDeviceExt::stats_ring
     uint32_t ring_slots = 0;
+    const PeerTable *peers = nullptr;   // fimo_b200_group_stats_peers_bind
 };
 // The three steps of publishing: every CTA adds its sums (fire-and-forget reductions), draws a ticket behind a fence,
 // and the CTA that drew the last one turns the accumulators into the published words and re-arms them.
@@ -191,7 +207,9 @@ __device__ __forceinline__ void stats_finalize(const StatsSink &a) {
     // from registers instead of reading `stats` back.
     const unsigned long long steps_before = a.stats[FIMO_B200_STAT_STEPS];
     unsigned long long gen = 0, rest[FIMO_B200_STAT_WORDS - 5] = {};
-    if (a.ring) {
+    uint4 peers = make_uint4(0u, 0u, 1u, 0u); // nranks, rank, slots
+    if (a.peers) peers = *(const uint4 *)a.peers;
+    if (a.ring || a.peers) {
         gen = a.scratch[5];
         for (int i = 5; i < FIMO_B200_STAT_WORDS; i++) rest[i - 5] = a.stats[i];
     }
@@ -205,11 +223,23 @@ __device__ __forceinline__ void stats_finalize(const StatsSink &a) {
     words[FIMO_B200_STAT_WORLDS] = n;
     words[FIMO_B200_STAT_STEPS] = steps_before + n;
     for (int i = 0; i < 5; i++) a.stats[i] = words[i];
+    if (a.ring || a.peers) a.scratch[5] = gen + 1;
     if (a.ring) { // the snapshot of this generation: slot = generations published so far % slots
-        a.scratch[5] = gen + 1;
         unsigned long long *slot = a.ring + (gen % a.ring_slots) * FIMO_B200_STAT_WORDS;
         for (int i = 0; i < 5; i++) slot[i] = words[i];
         for (int i = 5; i < FIMO_B200_STAT_WORDS; i++) slot[i] = rest[i - 5];
+    }
+    if (a.peers) { // the same words into every rank's inbox (our own included), tagged with the generation
+        const unsigned long long tag = ((gen + 1) & 0xFFFFFFFFull) << 32;
+        const unsigned long long at = ((gen % peers.z) * kStatsMaxRanks + peers.y) * 16ull;
+        for (uint32_t r = 0; r < peers.x; r++) {
+            unsigned long long *dst = a.peers->inbox[r] + at;
+            for (int i = 0; i < FIMO_B200_STAT_WORDS; i++) {
+                const unsigned long long w = i < 5 ? words[i] : rest[i - 5];
+                st_relaxed_sys(dst + 2 * i, tag | (w & 0xFFFFFFFFull));
+                st_relaxed_sys(dst + 2 * i + 1, tag | (w >> 32));
+            }
+        }
     }
     if (kGroupStats) {
         uint32_t *g = a.gstats;
@@ -247,8 +277,8 @@ __device__ __forceinline__ bool publish_stats_pair(const StatsSink &a, const Sta
 template <bool kGroupStats = false>
 __device__ __forceinline__ bool publish_stats(const StepArgs &a, unsigned long long visible, unsigned long long mask_sum,
                                               unsigned long long worlds, unsigned long long n_ctas) {
-    return publish_stats_to<kGroupStats>(StatsSink{a.stats, a.scratch, a.gstats, a.bounds_keys, a.entities, a.ring, a.ring_slots}, visible, mask_sum,
-                                         worlds, n_ctas);
+    return publish_stats_to<kGroupStats>(StatsSink{a.stats, a.scratch, a.gstats, a.bounds_keys, a.entities, a.ring, a.ring_slots, a.peers}, visible,
+                                         mask_sum, worlds, n_ctas);
 }
 __device__ __forceinline__ bool publish_stats(const StepArgs &a, unsigned long long visible, unsigned long long mask_sum,
                                               unsigned long long worlds) {

@@ -377,6 +377,7 @@ ENTRY(builtin_cull_waabb) {
         a.stats = (unsigned long long *)x[3]->device_ptr;
         a.scratch = (unsigned long long *)((BuiltinState *)system)->scratch;
         a.ring = (unsigned long long *)((BuiltinState *)system)->stats_ring, a.ring_slots = ((BuiltinState *)system)->stats_ring_slots;
+        a.peers = (const PeerTable *)((BuiltinState *)system)->stats_peers;
         if (!a.scratch) throw Fail{"cull scratch"};
         a.frustum = per_world(s[1], 24, d, "frustum");
         a.mask_words = (uint32_t)((d.E + 31) / 32);

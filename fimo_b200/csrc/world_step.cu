@@ -23,6 +23,7 @@
 //     TMA warp; the last CTA publishes the batch statistics (and the per-generation snapshot ring).
 #include <algorithm>
 #include <cstdlib>
+#include <string>
 #include <vector>
 
 #include "kernels_common.cuh"
@@ -707,7 +708,7 @@ __global__ void __launch_bounds__(T + 32, kMinBlocks) k_world_step_pipe(const Pi
         consumer_sync<T>();
         if (tid == 0) {
             if (kSet == 2)
-                publish_stats_pair<true>(StatsSink{a.stats, a.scratch, a.gstats, a.bounds_keys, a.entities, a.ring, a.ring_slots},
+                publish_stats_pair<true>(StatsSink{a.stats, a.scratch, a.gstats, a.bounds_keys, a.entities, a.ring, a.ring_slots, a.peers},
                                          StatsSink{a.stats2, a.scratch2, a.gstats2, a.bounds_keys2, a.entities}, cta_visible, s_sum,
                                          cta_visible2, s_sum2, my_worlds, (unsigned long long)pa.stat_ctas);
             else publish_stats<kSet >= 1>(a, cta_visible, s_sum, my_worlds, (unsigned long long)pa.stat_ctas);
@@ -1005,6 +1006,24 @@ const char *world_step_kernel_name(const WorldStepPlan &plan) {
     return "k_world_step_pipe (TMA-fed persistent world-step)";
 }
 
+std::string world_step_describe(const WorldStepPlan &plan, uint64_t n_worlds) {
+    char buf[320];
+    if (plan.threads == 0) return world_step_kernel_name(plan);
+    if (plan.team > 1)
+        std::snprintf(buf, sizeof buf, "k_world_step_pipe<T=%d, %u CTAs/SM, team, set %u>: %u teams x %u CTAs, %u-deep TMA ring, parents through L2 rows; + k_compact_lists",
+                      plan.threads, plan.blocks_per_sm, plan.set, plan.teams, plan.team, plan.stages);
+    else if (plan.tail_first < n_worlds)
+        std::snprintf(buf, sizeof buf, "k_world_step_pipe<T=%d, %u CTAs/SM, set %u>: persistent grid %u over worlds [0, %u) + tail grid of %llu one-world CTAs, "
+                      "%u-deep TMA ring, window %u of %u parents",
+                      plan.threads, plan.blocks_per_sm, plan.set, plan.grid, plan.tail_first, (unsigned long long)(n_worlds - plan.tail_first), plan.stages,
+                      plan.lvl_cap, plan.max_parents);
+    else
+        std::snprintf(buf, sizeof buf, "k_world_step_pipe<T=%d, %u CTAs/SM, set %u>: persistent grid %u x %llu worlds per CTA, %u-deep TMA ring, window %u of %u parents",
+                      plan.threads, plan.blocks_per_sm, plan.set, plan.grid, (unsigned long long)((n_worlds + plan.grid - 1) / (plan.grid ? plan.grid : 1)),
+                      plan.stages, plan.lvl_cap, plan.max_parents);
+    return buf;
+}
+
 namespace {
 template <int T, int kBlocks, int kSet>
 FimoStatus launch_pipe(PipeArgs &pa, const WorldStepPlan &plan, uint64_t W, const FimoB200_LaunchInfo *info) {
@@ -1060,7 +1079,7 @@ FimoStatus world_step_launch(const WorldStepViews &v, const WorldStepPlan &plan,
         a.n_worlds = (uint32_t)W, a.entities = (uint32_t)E;
         fill_propagate(a, v.world, v.pos, v.rot, v.scale, v.parent, v.level_start, W, E);
         fill_cull(a, v.vis_mask, v.vis_list, v.vis_count, v.stats, v.world, v.aabb_c, v.aabb_h, v.frustum, cull_scratch, W, E);
-        a.ring = (unsigned long long *)v.stats_ring, a.ring_slots = v.stats_ring_slots;
+        a.ring = (unsigned long long *)v.stats_ring, a.ring_slots = v.stats_ring_slots, a.peers = (const PeerTable *)v.stats_peers;
         a.vel = plane_of(v.vel, FIMO_B200_SCOPE_ENTITY, 3, E, W, "vel");
         a.dt = plane_of(v.dt, FIMO_B200_SCOPE_WORLD, 1, 1, W, "dt");
         pa.stages = plan.stages;

@@ -611,6 +611,9 @@ struct Job { // one scheduled generation (Job.zig:216-264 wraps SystemGroup.run 
     bool xfer_to_device = false;
     // fimo_b200_group_schedule_io: a generation with its own input copies in front and result copies behind
     std::vector<std::pair<ResourceType *, void *>> io_up, io_down;
+    // fimo_b200_group_schedule_readback: the packed cull outputs of this generation go to host memory
+    bool has_readback = false;
+    FimoB200_CullReadback readback{};
 };
 
 struct Group {
@@ -623,6 +626,7 @@ struct Group {
     void *post_step_user = nullptr;
     void *stats_ring = nullptr; // FimoB200_GroupDeviceExt::stats_ring
     uint32_t stats_ring_slots = 0;
+    dev::StatsExchange *stats_x = nullptr; // multi-GPU statistics exchange (fimo_b200_group_stats_*_bind)
 
     std::mutex m; // the graph mutex (SystemGroup.zig:40-52)
     bool dirty = true;
@@ -642,6 +646,7 @@ struct Group {
     bool has_device_systems = false, has_host_systems = false;
     dev::Executor *executor_dev = nullptr;
     FimoB200_ExecutorInfo info{};
+    std::string plan_text; // what the DAG compiler produced, in words (fimo_b200_group_executor_describe)
     size_t in_flight = 0; // device generations enqueued and not yet completed (locks are held while > 0)
     uint64_t compiled_epoch = 0; // world->resource_epoch the executor was compiled against
 
@@ -1037,11 +1042,13 @@ bool build_device_executor(Group *g, const char **err) {
             dev::BuiltinState *st = (dev::BuiltinState *)m->state;
             st->stats_ring = first_cull ? nullptr : g->stats_ring;
             st->stats_ring_slots = first_cull ? 0 : g->stats_ring_slots;
+            st->stats_peers = first_cull ? nullptr : dev::stats_exchange_peer_table(g->stats_x);
             if (!first_cull) first_cull = m;
         }
         if (mc && mc == first_cull) {
             views.stats_ring = views16.stats_ring = g->stats_ring;
             views.stats_ring_slots = views16.stats_ring_slots = g->stats_ring_slots;
+            views.stats_peers = views16.stats_peers = dev::stats_exchange_peer_table(g->stats_x);
         }
     }
     bool fuse = false;
@@ -1114,6 +1121,8 @@ bool build_device_executor(Group *g, const char **err) {
     if (!dev::executor_compile(g->executor_dev, std::move(nodes), launch_info(g), use_graph)) return *err = "DeviceError", false;
     g->info.uses_cuda_graph = dev::executor_uses_graph(g->executor_dev) ? 1u : 0u;
     g->info.kernel_launches_per_generation = dev::executor_kernels_per_generation(g->executor_dev);
+    g->plan_text = fuse ? dev::world_step_describe(plan, g->world->n_worlds) : "one kernel per system";
+    if (g->info.nodes > 1) g->plan_text += " (" + std::to_string(g->info.nodes) + " graph nodes)";
     return true;
 }
 
@@ -1349,15 +1358,33 @@ int start_device_generation(Group *g, Job *job, bool blocking, const char **err)
             if (dir == 0) ups.push_back(dev::Copy{view->device_ptr, io.second, bytes});
             else downs.push_back(dev::Copy{io.second, view->device_ptr, bytes});
         }
+    dev::Readback rb{};
+    if (job->has_readback) {
+        const FimoB200_ResourceView *mask = view_of(g, (ResourceType *)job->readback.vis_mask), *list = view_of(g, (ResourceType *)job->readback.vis_list),
+                                    *count = view_of(g, (ResourceType *)job->readback.vis_count);
+        const uint64_t W = g->world->n_worlds, E = g->world->entities;
+        if (!mask || !list || !count || !mask->device_ptr || !list->device_ptr || !count->device_ptr || mask->scope != FIMO_B200_SCOPE_ENTITY_BITS ||
+            mask->components != 1 || list->scope != FIMO_B200_SCOPE_ENTITY || list->components != 1 || count->scope != FIMO_B200_SCOPE_WORLD ||
+            count->components != 1 || mask->n_worlds != W || list->n_worlds != W || count->n_worlds != W) {
+            if (g->in_flight == 0) unlock_group_resources(g);
+            *err = "NotFound";
+            return -1;
+        }
+        rb = dev::Readback{(const uint32_t *)mask->device_ptr, (const uint32_t *)list->device_ptr, (const uint32_t *)count->device_ptr, W, E,
+                           (E + 31) / 32, (uint64_t)job->generation, job->readback.host, (size_t)job->readback.host_bytes};
+    }
     g->in_flight++;
     DeviceDone *done = new DeviceDone{g, job->signal, (uint64_t)job->generation, g_trace_sink.load(std::memory_order_relaxed) ? monotonic_ns() : 0};
-    if (!dev::executor_launch(g->executor_dev, &device_generation_done, done, ups.data(), ups.size(), downs.data(), downs.size())) {
+    if (g->stats_x) dev::stats_exchange_before_launch(g->stats_x, dev::executor_stream(g->executor_dev), 1);
+    if (!dev::executor_launch(g->executor_dev, &device_generation_done, done, ups.data(), ups.size(), downs.data(), downs.size(),
+                              job->has_readback ? &rb : nullptr)) {
         // The completion entry still drains through the completion thread (without `done`); undo here.
         delete done;
         if (--g->in_flight == 0) unlock_group_resources(g);
         *err = "DeviceError";
         return -1;
     }
+    if (g->stats_x) dev::stats_exchange_after_launch(g->stats_x, dev::executor_stream(g->executor_dev), 1);
     if (g->post_step) g->post_step(g->post_step_user, dev::executor_stream(g->executor_dev), (uint64_t)job->generation);
     return 0;
 }
@@ -1455,6 +1482,7 @@ struct StepIo {
     size_t n_up;
     const FimoB200_StepTransfer *downloads;
     size_t n_down;
+    const FimoB200_CullReadback *readback = nullptr;
 };
 
 const char *group_schedule(Group *g, FimoWorldsMeta_Fence *const *wait_on, size_t n, FimoWorldsMeta_Fence *signal,
@@ -1465,6 +1493,7 @@ const char *group_schedule(Group *g, FimoWorldsMeta_Fence *const *wait_on, size_
     if (io) {
         for (size_t i = 0; i < io->n_up; i++) job->io_up.emplace_back((ResourceType *)io->uploads[i].resource, io->uploads[i].host);
         for (size_t i = 0; i < io->n_down; i++) job->io_down.emplace_back((ResourceType *)io->downloads[i].resource, io->downloads[i].host);
+        if (io->readback) job->has_readback = true, job->readback = *io->readback;
     }
     const size_t consumed = xfer ? 0 : 1; // a transfer rides between generations, it is not one
     if (xfer) job->xfer_resource = xfer->resource, job->xfer_host = xfer->host, job->xfer_to_device = xfer->to_device;
@@ -1542,6 +1571,7 @@ void group_destroy(Group *g) {
     }
     if (g->dispatcher.joinable()) g->dispatcher.join();
     if (g->executor_dev) dev::executor_destroy(g->executor_dev);
+    dev::stats_exchange_destroy(g->stats_x);
     g->world->groups.fetch_sub(1, std::memory_order_relaxed);
     g->executor.vtable->release(g->executor.data);
     delete g;
@@ -1586,6 +1616,7 @@ bool builtin_create(const void *factory, FimoWorldsMeta_SystemContext *context, 
     state->scratch = nullptr;
     state->stats_ring = nullptr;
     state->stats_ring_slots = 0;
+    state->stats_peers = nullptr;
     if (state->device < 0) return false; // built-in systems exist on the device only
     if (m->type->builtin_id == FIMO_B200_BUILTIN_CULL || m->type->builtin_id == FIMO_B200_BUILTIN_CULL_WAABB) {
         state->scratch = dev::hbm_alloc(state->device, 64);
@@ -1869,7 +1900,7 @@ FimoStatus fimo_b200_group_schedule_io(FimoWorldsMeta_SystemGroup *group, const 
     {
         std::lock_guard<std::mutex> lock(g->m);
         const char *err = nullptr;
-        if (g->dirty && g->in_flight == 0 && !compile(g, &err)) return report(err);
+        if (g->dirty && g->in_flight == 0 && g->backlog.empty() && !g->dispatcher_busy && !compile(g, &err)) return report(err); // never under a running generation
         if (!g->has_device_systems) return report("NoDevice");
         auto used = [&](FimoWorldsMeta_ResourceHandle h) {
             return std::find(g->resources.begin(), g->resources.end(), (ResourceType *)h) != g->resources.end();
@@ -1880,6 +1911,32 @@ FimoStatus fimo_b200_group_schedule_io(FimoWorldsMeta_SystemGroup *group, const 
             if (!used(downloads[i].resource)) return report("NotFound");
     }
     const StepIo io{uploads, n_uploads, downloads, n_downloads};
+    if (const char *err = group_schedule(g, wait_on, n_wait, signal, nullptr, &io)) return report(err);
+    return FIMO_STATUS_OK;
+}
+FimoStatus fimo_b200_group_schedule_readback(FimoWorldsMeta_SystemGroup *group, const FimoB200_StepTransfer *uploads, FimoUSize n_uploads,
+                                             const FimoB200_CullReadback *readback, FimoWorldsMeta_Fence *const *wait_on, FimoUSize n_wait,
+                                             FimoWorldsMeta_Fence *signal) {
+    Group *g = (Group *)group;
+    if ((n_uploads && !uploads) || !readback || !readback->host || !readback->vis_mask || !readback->vis_list || !readback->vis_count)
+        return report("InvalidArgument");
+    for (size_t i = 0; i < n_uploads; i++)
+        if (!uploads[i].resource || !uploads[i].host) return report("InvalidArgument");
+    {
+        std::lock_guard<std::mutex> lock(g->m);
+        const char *err = nullptr;
+        if (g->dirty && g->in_flight == 0 && g->backlog.empty() && !g->dispatcher_busy && !compile(g, &err)) return report(err);
+        if (!g->has_device_systems) return report("NoDevice");
+        auto used = [&](FimoWorldsMeta_ResourceHandle h) {
+            return std::find(g->resources.begin(), g->resources.end(), (ResourceType *)h) != g->resources.end();
+        };
+        for (size_t i = 0; i < n_uploads; i++)
+            if (!used(uploads[i].resource)) return report("NotFound");
+        if (!used(readback->vis_mask) || !used(readback->vis_list) || !used(readback->vis_count)) return report("NotFound");
+        const uint64_t W = g->world->n_worlds, words = (g->world->entities + 31) / 32;
+        if (readback->host_bytes < 4 * (8 + 2 * W + W * words)) return report("InvalidArgument"); // header + counts + offsets + masks must fit
+    }
+    const StepIo io{uploads, n_uploads, nullptr, 0, readback};
     if (const char *err = group_schedule(g, wait_on, n_wait, signal, nullptr, &io)) return report(err);
     return FIMO_STATUS_OK;
 }
@@ -1894,10 +1951,67 @@ FimoStatus fimo_b200_group_executor_info(FimoWorldsMeta_SystemGroup *group, Fimo
     Group *g = (Group *)group;
     std::lock_guard<std::mutex> lock(g->m);
     const char *err = nullptr;
-    if (g->dirty && g->in_flight == 0 && !compile(g, &err)) return report(err);
+    if (g->dirty && g->in_flight == 0 && g->backlog.empty() && !g->dispatcher_busy && !compile(g, &err)) return report(err); // never under a running generation
     *info = g->info;
     return FIMO_STATUS_OK;
 }
+// ---- multi-GPU statistics exchange ------------------------------------------------------------------------------
+static dev::StatsExchange *stats_exchange_of(Group *g) { // g->m held
+    if (!g->stats_x && g->world->device >= 0) g->stats_x = dev::stats_exchange_create(g->world->device);
+    return g->stats_x;
+}
+FimoStatus fimo_b200_group_stats_peers_open(FimoWorldsMeta_SystemGroup *group, uint32_t slots, void *handle_out) {
+    Group *g = (Group *)group;
+    std::lock_guard<std::mutex> lock(g->m);
+    dev::StatsExchange *x = stats_exchange_of(g);
+    if (!x) return report("NoDevice");
+    return dev::stats_exchange_peers_open(x, slots, handle_out) ? FIMO_STATUS_OK : report("DeviceError");
+}
+FimoStatus fimo_b200_group_stats_peers_bind(FimoWorldsMeta_SystemGroup *group, const void *handles, uint32_t rank, uint32_t nranks) {
+    Group *g = (Group *)group;
+    std::lock_guard<std::mutex> lock(g->m);
+    if (!g->stats_x) return report("NotFound"); // peers_open first
+    if (g->in_flight != 0 || !g->backlog.empty()) return report("InUse");
+    if (!dev::stats_exchange_peers_bind(g->stats_x, handles, rank, nranks)) return report("DeviceError");
+    g->dirty = true; // the executor picks the peer table up when it is (re)compiled
+    return FIMO_STATUS_OK;
+}
+FimoStatus fimo_b200_stats_nccl_unique_id(void *id_out) { return dev::stats_nccl_unique_id(id_out) ? FIMO_STATUS_OK : report("DeviceError"); }
+FimoStatus fimo_b200_group_stats_nccl_bind(FimoWorldsMeta_SystemGroup *group, const void *unique_id, uint32_t rank, uint32_t nranks,
+                                           uint32_t bucket) {
+    Group *g = (Group *)group;
+    std::lock_guard<std::mutex> lock(g->m);
+    dev::StatsExchange *x = stats_exchange_of(g);
+    if (!x) return report("NoDevice");
+    if (g->in_flight != 0 || !g->backlog.empty()) return report("InUse");
+    if (g->stats_ring) return report("Duplicate"); // the caller already supplied its own ring
+    if (!dev::stats_exchange_nccl_bind(x, unique_id, rank, nranks, bucket)) return report("DeviceError");
+    g->stats_ring = dev::stats_exchange_ring(x, &g->stats_ring_slots);
+    g->dirty = true;
+    return FIMO_STATUS_OK;
+}
+FimoStatus fimo_b200_group_global_stats(FimoWorldsMeta_SystemGroup *group, uint64_t generation, uint32_t mode, uint64_t *out_words) {
+    Group *g = (Group *)group;
+    dev::StatsExchange *x;
+    {
+        std::lock_guard<std::mutex> lock(g->m);
+        x = g->stats_x;
+    }
+    if (!x) return report("NotFound");
+    return dev::stats_exchange_read(x, generation, mode, out_words) ? FIMO_STATUS_OK : report("DeviceError");
+}
+
+FimoUSize fimo_b200_group_executor_describe(FimoWorldsMeta_SystemGroup *group, char *buffer, FimoUSize buffer_len) {
+    Group *g = (Group *)group;
+    std::lock_guard<std::mutex> lock(g->m);
+    if (buffer && buffer_len) {
+        const size_t n = std::min<size_t>(g->plan_text.size(), buffer_len - 1);
+        std::memcpy(buffer, g->plan_text.data(), n);
+        buffer[n] = 0;
+    }
+    return g->plan_text.size();
+}
+
 void *fimo_b200_group_stream(FimoWorldsMeta_SystemGroup *group) {
     Group *g = (Group *)group;
     std::lock_guard<std::mutex> lock(g->m);

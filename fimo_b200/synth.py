@@ -16,7 +16,7 @@ from dataclasses import dataclass
 import numpy as np
 
 from . import abi
-from .worlds import Fence, Resource, System, World
+from .worlds import Fence, Resource, System, World, create_pool
 
 SEED = 0x46494D4F  # "FIMO"
 DT = np.float32(1.0 / 60.0)
@@ -462,6 +462,13 @@ class WorldStepRig:
         self.lib.check(self.lib.fimo_b200_group_executor_info(self.group.handle, C.byref(info)))
         return info
 
+    def executor_text(self) -> str:
+        """fimo_b200_group_executor_describe: kernels and launch geometry of the compiled executor."""
+        self.executor_info()
+        buf = C.create_string_buffer(512)
+        self.lib.fimo_b200_group_executor_describe(self.group.handle, buf, 512)
+        return buf.value.decode()
+
     def device_ms(self) -> tuple[float, int]:
         n = C.c_uint64(0)
         ms = self.lib.fimo_b200_group_device_ms(self.group.handle, C.byref(n))
@@ -545,6 +552,33 @@ class WorldStepRig:
         self.lib.check(self.lib.fimo_b200_group_schedule_io(self.group.handle, uploads[0], uploads[1], downloads[0], downloads[1],
                                                             None, 0, signal.ptr() if signal else None))
 
+    def readback_words(self, capacity_entries: int) -> int:
+        """u32 words of a fimo_b200_group_schedule_readback host buffer whose list holds `capacity_entries`."""
+        return abi.READBACK_HEADER_WORDS + 2 * self.W + self.W * ((self.E + 31) // 32) + capacity_entries
+
+    def readback_desc(self, host: np.ndarray) -> abi.CullReadback:
+        R = self.resources
+        return abi.CullReadback(R["vis_mask"].handle, R["vis_list"].handle, R["vis_count"].handle, host.ctypes.data, host.nbytes)
+
+    def schedule_readback(self, uploads, desc: abi.CullReadback, signal: Fence | None = None) -> None:
+        """fimo_b200_group_schedule_readback: one generation whose packed cull outputs land in the host buffer of `desc`."""
+        self.lib.check(self.lib.fimo_b200_group_schedule_readback(self.group.handle, uploads[0], uploads[1], C.byref(desc), None, 0,
+                                                                  signal.ptr() if signal else None))
+
+    def parse_readback(self, host: np.ndarray) -> dict:
+        """Splits a landed read-back buffer into its parts (views of `host`)."""
+        W, words = self.W, (self.E + 31) // 32
+        h = host[:8]
+        at = 8
+        counts, offsets = host[at:at + W], host[at + W:at + 2 * W]
+        at += 2 * W
+        mask = host[at:at + W * words].reshape(W, words)
+        at += W * words
+        capacity = int(h[3])
+        return {"total": int(h[0]), "n_worlds": int(h[1]), "mask_words": int(h[2]), "capacity": capacity, "truncated": int(h[4]),
+                "generation": int(h[5]) | (int(h[6]) << 32), "entities": int(h[7]), "counts": counts, "offsets": offsets, "mask": mask,
+                "list": host[at:at + min(int(h[0]), capacity)]}
+
     def stats(self) -> np.ndarray:
         return self.download(("stats",))["stats"].reshape(-1).view(np.uint64)
 
@@ -562,6 +596,58 @@ class WorldStepRig:
             res.remove_from_world(self.world, out)
             res.unregister()
         self.world.deinit()
+
+
+BATCH_SCOPE = ("stats", "stats2", "gstats", "gstats2")  # one instance per batch: merged when a batch is stepped in slices
+
+
+def _merge_batch_words(name: str, parts: list[np.ndarray]) -> np.ndarray:
+    """Batch-scope words of a batch stepped as several sub-batches: every FIMO_B200_STAT_* word is an additive
+    count; FIMO_B200_GSTAT_*: two additive u64 counts and min / max bounds (exact in any order)."""
+    if name.startswith("stats"):
+        return np.sum([p.reshape(-1).view(np.uint64) for p in parts], axis=0, dtype=np.uint64).view(np.uint32).reshape(parts[0].shape)
+    out = np.zeros(abi.GSTAT_WORDS, dtype=np.uint32)
+    flat = [p.reshape(-1) for p in parts]
+    for lo in (abi.GSTAT_VISIBLE_LO, abi.GSTAT_WORLDS_LO):
+        out[lo:lo + 2] = np.sum([f[lo:lo + 2].view(np.uint64) for f in flat], axis=0, dtype=np.uint64).view(np.uint32)
+    b = abi.GSTAT_BOUNDS
+    out[b:b + 3] = np.min([f[b:b + 3].view(np.float32) for f in flat], axis=0).view(np.uint32)
+    out[b + 3:b + 6] = np.max([f[b + 3:b + 6].view(np.float32) for f in flat], axis=0).view(np.uint32)
+    return out.reshape(parts[0].shape)
+
+
+def step_in_slices(lib: abi.WorldsLib, data: dict[str, np.ndarray], entities: int, depth: int, steps: int, dag: str = "chain3",
+                   slices: int = 0, workers: int = 0) -> dict[str, np.ndarray]:
+    """Steps a whole batch on a CPU implementation (the oracle: tests / bench parity gate only) as `slices`
+    contiguous sub-batches of worlds — one World + SystemGroup each, all on ONE shared pool, every generation of every
+    slice queued before the first wait — so that a BASELINE-size batch takes seconds instead of minutes.  Worlds are
+    independent (World.zig:26), so the result equals the one-batch run; `data` is stepped IN PLACE (each slice's
+    resources are views of it) and the outputs are returned with the batch-scope words merged."""
+    import os
+
+    W = data["pos"].shape[0]
+    workers = workers or (os.cpu_count() or 1)
+    slices = max(1, min(slices or workers, W))
+    pool = create_pool(lib, "sliced-batch", workers)
+    bounds = [(i * W // slices, (i + 1) * W // slices) for i in range(slices)]
+    rigs, locals_ = [], []
+    try:
+        for lo, hi in bounds:
+            part = {k: (v[lo:hi] if k not in BATCH_SCOPE else v.copy()) for k, v in data.items()}
+            locals_.append(part)
+            rigs.append(WorldStepRig(lib, hi - lo, entities, depth, data=part, pool=pool, dag=dag))
+        for r in rigs:
+            r.schedule(steps)
+        for r in rigs:
+            r.wait()
+        out = {}
+        for name in outputs_for(dag):
+            out[name] = _merge_batch_words(name, [p[name] for p in locals_]) if name in BATCH_SCOPE else data[name]
+        return out
+    finally:
+        for r in rigs:
+            r.close()
+        pool.unref()
 
 
 def compare_outputs(got: dict[str, np.ndarray], want: dict[str, np.ndarray], float_rtol: float = 0.0) -> list[str]:

@@ -796,6 +796,28 @@ FIMO_B200_EXPORT FimoStatus fimo_b200_group_schedule_io(FimoWorldsMeta_SystemGro
                                                         const FimoB200_StepTransfer *downloads, FimoUSize n_downloads,
                                                         FimoWorldsMeta_Fence *const *wait_on, FimoUSize n_wait,
                                                         FimoWorldsMeta_Fence *signal);
+/* One generation whose CULL OUTPUTS come back to the host: what `cull` produces for a frame is the per-world visible
+ * count, the visibility mask and the ordered list of visible entities — of which only the first `count` entries of
+ * each world's `vis_list` are meaningful.  Behind the generation one small pack (two kernels, in stream order) writes
+ *     u32 header[8] = {total visible, n_worlds, mask_words, list capacity (entries), truncated (0/1), generation lo, hi, entities}
+ *     u32 counts[n_worlds]; u32 offsets[n_worlds] (exclusive prefix of counts)
+ *     u32 mask[n_worlds][mask_words]
+ *     u32 list[capacity]            the worlds' ordered visible lists back to back (world w at offsets[w])
+ * into an HBM staging slot, and ONE copy-engine transfer brings `host_bytes` of it to `host` (page-locked) on a side
+ * stream while the next generation already runs.  `capacity` = what fits in host_bytes (at most n_worlds * entities);
+ * if more entities are visible the list is cut there and `truncated` is set (counts, offsets and masks are always
+ * complete).  Same ordering, generation-number and `signal` rules as fimo_b200_group_schedule_io. */
+typedef struct FimoB200_CullReadback {
+    FimoWorldsMeta_ResourceHandle vis_mask, vis_list, vis_count;
+    void *host;
+    uint64_t host_bytes;
+} FimoB200_CullReadback;
+#define FIMO_B200_READBACK_HEADER_WORDS 8
+FIMO_B200_EXPORT FimoStatus fimo_b200_group_schedule_readback(FimoWorldsMeta_SystemGroup *group,
+                                                              const FimoB200_StepTransfer *uploads, FimoUSize n_uploads,
+                                                              const FimoB200_CullReadback *readback,
+                                                              FimoWorldsMeta_Fence *const *wait_on, FimoUSize n_wait,
+                                                              FimoWorldsMeta_Fence *signal);
 FIMO_B200_EXPORT void *fimo_b200_host_alloc(FimoUSize bytes); /* page-locked host memory; NULL on failure */
 FIMO_B200_EXPORT void fimo_b200_host_free(void *ptr);
 
@@ -833,6 +855,11 @@ typedef struct FimoB200_ExecutorInfo {
 FIMO_B200_EXPORT FimoStatus fimo_b200_group_executor_info(FimoWorldsMeta_SystemGroup *group,
                                                           FimoB200_ExecutorInfo *info);
 
+/* The same in words — which kernels, with which launch geometry (the text a bench line or a trace quotes).  Call
+ * fimo_b200_group_executor_info first (it compiles a dirty group).  Returns the length of the full text; at most
+ * buffer_len - 1 characters + NUL are written. */
+FIMO_B200_EXPORT FimoUSize fimo_b200_group_executor_describe(FimoWorldsMeta_SystemGroup *group, char *buffer, FimoUSize buffer_len);
+
 /* The CUDA stream (cudaStream_t) generations of this group are enqueued on. */
 FIMO_B200_EXPORT void *fimo_b200_group_stream(FimoWorldsMeta_SystemGroup *group);
 
@@ -847,6 +874,53 @@ FIMO_B200_EXPORT double fimo_b200_group_device_ms(FimoWorldsMeta_SystemGroup *gr
  * of the last generation completed since the previous call — i.e. including any gap between generations.
  * Resets the span; call fimo_b200_group_device_ms first if both are wanted for the same window. */
 FIMO_B200_EXPORT double fimo_b200_group_span_ms(FimoWorldsMeta_SystemGroup *group);
+
+/* ------------------------------------------------------------------------- */
+/* Multi-GPU: worlds sharded by index, one process per GPU    */
+/*                                                                            */
+/* Worlds are independent units (modules/fimo_worlds/src/World.zig:26,45-52): */
+/* rank r owns a contiguous block of global world indices and steps it with   */
+/* no data-path collective.  The one exchange is the end-of-step statistics   */
+/* (the FIMO_B200_STAT_* words of the group's first cull system), summed over  */
+/* ranks for EVERY generation, off the group's stream.  Two transports:       */
+/*                                                                            */
+/* PEERS — the kernel that publishes a generation's statistics (its last CTA) */
+/*   also stores them straight into every peer's inbox in HBM over NVLink     */
+/*   (cudaIpc-mapped peer memory): 16 eight-byte {value half, generation tag} */
+/*   words per rank and generation, self-validating, so no fence, no extra    */
+/*   launch and no collective kernel competing with the persistent grid for   */
+/*   SM slots.  Every rank holds every rank's words; the sum is taken on read. */
+/* NCCL  — the generation's snapshot goes to a ring in HBM and blocks of      */
+/*   `bucket` consecutive generations are all-reduced in place               */
+/*   (ncclAllReduce, ncclUint64, ncclSum) on a library side stream, enqueued  */
+/*   from the launcher thread; the group's stream waits for a block's         */
+/*   collective only before the kernel overwrites that block.  libnccl.so.2   */
+/*   is dlopen()ed when this mode is bound (no link-time dependency).         */
+/*                                                                            */
+/* Both are bound after system_group_create and before the first schedule;    */
+/* `generation` below counts the generations the group's first cull system    */
+/* has published (== the group's generation number when that system has been  */
+/* a member from the start).  All ranks must have drained (a host barrier)    */
+/* before any rank destroys a group bound to peers.                           */
+/* ------------------------------------------------------------------------- */
+#define FIMO_B200_STATS_PEER_HANDLE_BYTES 64   /* cudaIpcMemHandle_t */
+#define FIMO_B200_STATS_NCCL_ID_BYTES 128      /* ncclUniqueId */
+#define FIMO_B200_STATS_MAX_RANKS 16
+enum { FIMO_B200_STATS_MODE_PEERS = 1, FIMO_B200_STATS_MODE_NCCL = 2 };
+/* Allocates this rank's inbox ([slots][FIMO_B200_STATS_MAX_RANKS][16] u64, zeroed) and returns the handle the
+ * other ranks open; the caller exchanges the handles out of band (e.g. an all-gather of 64 bytes). */
+FIMO_B200_EXPORT FimoStatus fimo_b200_group_stats_peers_open(FimoWorldsMeta_SystemGroup *group, uint32_t slots, void *handle_out);
+/* `handles`: [nranks][FIMO_B200_STATS_PEER_HANDLE_BYTES], rank order (own entry ignored). */
+FIMO_B200_EXPORT FimoStatus fimo_b200_group_stats_peers_bind(FimoWorldsMeta_SystemGroup *group, const void *handles,
+                                                             uint32_t rank, uint32_t nranks);
+FIMO_B200_EXPORT FimoStatus fimo_b200_stats_nccl_unique_id(void *id_out); /* ncclGetUniqueId; rank 0 calls, broadcasts */
+FIMO_B200_EXPORT FimoStatus fimo_b200_group_stats_nccl_bind(FimoWorldsMeta_SystemGroup *group, const void *unique_id,
+                                                            uint32_t rank, uint32_t nranks, uint32_t bucket);
+/* The statistics of `generation` summed over all ranks (8 u64 words).  PEERS: waits (bounded) until every rank's
+ * words of that generation have arrived; valid for the last `slots` generations.  NCCL: collective — every rank
+ * calls it for the same generation, with nothing scheduled after it; flushes the partial block. */
+FIMO_B200_EXPORT FimoStatus fimo_b200_group_global_stats(FimoWorldsMeta_SystemGroup *group, uint64_t generation,
+                                                         uint32_t mode, uint64_t *out_words);
 
 /* ------------------------------------------------------------------------- */
 /* Layout pins (sizes measured with gcc on x86-64)       */

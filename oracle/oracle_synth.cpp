@@ -225,6 +225,22 @@ FIMO_B200_EXPORT double fimo_oracle_step_groups(FimoWorldsMeta_SystemGroup *cons
     return std::chrono::duration<double>(t1 - t0).count();
 }
 
+// The same work the way the reference lets callers drive it: `schedule` is asynchronous and generations of one
+// group queue behind its timeline semaphore (SystemGroup.zig:430-452), so every group gets all `steps` generations
+// up front and only the last one of each carries a fence — no barrier across worlds between steps.
+FIMO_B200_EXPORT double fimo_oracle_step_groups_queued(FimoWorldsMeta_SystemGroup *const *groups, size_t n, size_t steps) {
+    std::vector<FimoWorldsMeta_Fence> fences(n);
+    const auto t0 = std::chrono::steady_clock::now();
+    for (size_t i = 0; i < n; i++) FimoWorldsMeta_fence_init(&fences[i]);
+    for (size_t s = 0; s < steps; s++)
+        for (size_t i = 0; i < n; i++)
+            if (fimo_worlds_system_group_schedule(groups[i], nullptr, 0, s + 1 == steps ? &fences[i] : nullptr) != FIMO_STATUS_OK)
+                oracle::panic("schedule failed");
+    for (size_t i = 0; i < n; i++) oracle::fence_wait(&fences[i]);
+    const auto t1 = std::chrono::steady_clock::now();
+    return std::chrono::duration<double>(t1 - t0).count();
+}
+
 // Raw single-thread math loop without any scheduling: the floor of what one host core can do,
 // reported next to the scheduled number so the dispatch overhead is visible.
 FIMO_B200_EXPORT unsigned fimo_oracle_hardware_threads(void) { return std::thread::hardware_concurrency(); }

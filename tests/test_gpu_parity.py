@@ -188,37 +188,49 @@ def test_full_size_properties(product):
         assert np.array_equal(out["world"][:, 4 * k + 3, :][roots], out["pos"][:, k, :][roots])
 
 
-@pytest.mark.parametrize("dag", ["dag8", "dag16"])
-def test_full_size_dags_fused_equals_one_kernel_per_system(product, dag):
-    """The DAGs at BASELINE size (4096 x 1k; configs[4] is the dag16 shape): the fused world-step kernel — for dag8
-    the persistent grid plus the tail grid — leaves every resource bit-identical to the same generations run as
-    one kernel per system (the path the small cases pin against the oracle), plus the count / mask / list /
-    statistics properties."""
-    W, E, D, K = 4096, 1024, 4, 3
+def run_full_size(oracle, product, W, E, D, K, dag):
+    """One BASELINE-size batch through the product with the DEFAULT launch plan (no FIMO_B200_* overrides), then the
+    same generations on the oracle (stepped in place, in world slices on the host threads): outputs and executor info."""
     data = synth.generate(W, E, D, dag=dag)
-    outs = []
-    for fused in (True, False):
-        rig = synth.WorldStepRig(product, W, E, D, data={k: v.copy() for k, v in data.items()}, options=synth.RigOptions(fused=fused), dag=dag)
-        try:
-            rig.step(K)
-            info = rig.executor_info()
-            outs.append(rig.download())
-        finally:
-            rig.close()
-        assert info.fused_world_step == (1 if fused else 0)
-        if fused and dag == "dag8":
-            assert info.kernel_launches_per_generation == 2  # persistent grid + tail grid
-    got, want = outs
-    problems = synth.compare_outputs(got, want, 0.0)
+    dev = synth.WorldStepRig(product, W, E, D, data=data, dag=dag)  # uploads `data`; never writes it
+    try:
+        info = dev.executor_info()
+        dev.step(K)
+        got = dev.download()
+    finally:
+        dev.close()
+    want = synth.step_in_slices(oracle, data, E, D, K, dag=dag)
+    return got, want, info
+
+
+FULL_SIZE_CASES = [
+    # (id, dag, worlds, entities, depth, steps, kernel launches per generation of the default plan)
+    ("C2", "chain3", 4096, 1024, 4, 16, 1),    # BASELINE configs[1]: grid 586 x 7 worlds per CTA
+    ("C3", "dag8", 256, 65536, 8, 4, 2),        # configs[2]: CTA teams per world + list compaction
+    ("C4-per-gpu", "chain3", 4096, 4096, 4, 4, 1),  # configs[3] = 32768 x 4k over 8 GPUs: the shard one GPU steps
+    ("C5-per-gpu", "dag16", 1024, 1024, 4, 16, None),  # configs[4]: 16-system DAG, 1 M entities per GPU
+    ("dag8-4096", "dag8", 4096, 1024, 4, 4, 2),  # persistent grid + tail grid at bench size
+    ("dag16-4096", "dag16", 4096, 1024, 4, 3, None),
+]
+
+
+@pytest.mark.parametrize("name,dag,W,E,D,K,launches", FULL_SIZE_CASES, ids=[c[0] for c in FULL_SIZE_CASES])
+def test_baseline_configs_at_full_size_match_oracle(oracle, product, monkeypatch, name, dag, W, E, D, K, launches):
+    """Every BASELINE.json config at its STATED size, on the launch plan bench.py times (the plan is a function of the
+    batch: worlds per CTA, tail-grid split, team choice — world_step.cu: world_step_plan), bit for bit against the
+    oracle: every resource any system writes, after K generations."""
+    for var in ("FIMO_B200_TEAM", "FIMO_B200_PIPE", "FIMO_B200_TAIL", "FIMO_B200_PREFETCH", "FIMO_B200_NO_SET2", "FIMO_B200_GENS"):
+        monkeypatch.delenv(var, raising=False)
+    got, want, info = run_full_size(oracle, product, W, E, D, K, dag)
+    assert info.fused_world_step == 1
+    if launches is not None:
+        assert info.kernel_launches_per_generation == launches
+    problems = synth.compare_outputs(got, want, FLOAT_RTOL)
     assert not problems, "\n".join(problems)
-    counts = got["vis_count"][:, 0, 0].astype(np.int64)
-    bits = np.unpackbits(got["vis_mask"][:, 0, :].view(np.uint8), axis=1, bitorder="little")
-    assert np.array_equal(bits.sum(axis=1), counts)
     st = got["stats"].reshape(-1).view(np.uint64)
-    assert st[abi.STAT_VISIBLE] == counts.sum() and st[abi.STAT_WORLDS] == W and st[abi.STAT_STEPS] == W * K
-    for w in (0, 591, 592, 3551, 3552, 4095):  # first / last world of the persistent grid's rounds and of the tail grid
-        idx = np.nonzero(bits[w])[0].astype(np.uint32)
-        assert np.array_equal(got["vis_list"][w, 0, :counts[w]], idx)
+    assert st[abi.STAT_STEPS] == W * K and st[abi.STAT_WORLDS] == W and st[abi.STAT_ENTITIES] == W * E
+    counts = got["vis_count"][:, 0, 0].astype(np.int64)
+    assert st[abi.STAT_VISIBLE] == counts.sum()
 
 
 def test_generations_pipeline_and_fences(product):
@@ -402,6 +414,62 @@ def test_schedule_io_result_fed_back_through_host_memory(oracle, product):
         product.fimo_b200_host_free(ptr)
     problems = synth.compare_outputs(got, want, 0.0)
     assert not problems, "\n".join(problems)
+
+
+@pytest.mark.parametrize("W,E,D,K,margin", [(24, 1024, 4, 7, 1.0), (700, 96, 4, 5, 1.0), (3, 8192, 8, 4, 1.0), (24, 1024, 4, 3, 0.5)])
+def test_readback_returns_what_cull_produces(oracle, product, W, E, D, K, margin):
+    """fimo_b200_group_schedule_readback: every step uploads its frusta and gets back, in ONE packed pinned buffer, the
+    per-world visible counts, their exclusive offsets, the masks and the ordered visible lists back to back — all K
+    steps queued before the first wait, each with its own buffer; every buffer equals the oracle's outputs of that
+    step.  margin < 1: the list does not fit -> `truncated`, the prefix that fits is still exact."""
+    import ctypes as C
+    from fimo_b200.worlds import Fence
+
+    data = synth.generate(W, E, D)
+    frusta = [synth.generate(W, E, D, world0=100 * (i + 1))["frustum"] for i in range(K)]
+    ref = synth.WorldStepRig(oracle, W, E, D, data={k: v.copy() for k, v in data.items()})
+    want = []
+    try:
+        for i in range(K):
+            ref.upload("frustum", frusta[i])
+            ref.step(1)
+            want.append(ref.download(("vis_count", "vis_mask", "vis_list")))
+    finally:
+        ref.close()
+    rig = synth.WorldStepRig(product, W, E, D, data={k: v.copy() for k, v in data.items()})
+    locked = []
+    try:
+        capacity = int(margin * max(int(w["vis_count"].sum()) for w in want))
+        words = rig.readback_words(capacity)
+
+        def pinned(n_words):
+            ptr = product.fimo_b200_host_alloc(4 * n_words)
+            assert ptr
+            locked.append(ptr)
+            return np.ctypeslib.as_array(C.cast(ptr, C.POINTER(C.c_uint32)), shape=(n_words,))
+
+        bufs, fences, keep = [pinned(words) for _ in range(K)], [Fence(product) for _ in range(K)], []
+        for i in range(K):
+            src = pinned(frusta[i].size).view(np.float32).reshape(frusta[i].shape)
+            src[...] = frusta[i]
+            up, desc = rig.io_list({"frustum": src}), rig.readback_desc(bufs[i])
+            keep.append((up, desc))
+            rig.schedule_readback(up, desc, fences[i])
+        for f in fences:
+            f.wait()
+        for i in range(K):
+            rb = rig.parse_readback(bufs[i])
+            counts = want[i]["vis_count"][:, 0, 0]
+            assert rb["n_worlds"] == W and rb["entities"] == E and rb["generation"] == i and rb["total"] == int(counts.sum())
+            assert np.array_equal(rb["counts"], counts) and np.array_equal(rb["offsets"], np.cumsum(counts) - counts)
+            assert np.array_equal(rb["mask"], want[i]["vis_mask"][:, 0, :])
+            full = np.concatenate([want[i]["vis_list"][w, 0, :counts[w]] for w in range(W)])
+            assert rb["truncated"] == (1 if rb["total"] > capacity else 0)
+            assert np.array_equal(rb["list"], full[:capacity]), i
+    finally:
+        rig.close()
+        for ptr in locked:
+            product.fimo_b200_host_free(ptr)
 
 
 @pytest.mark.parametrize("mode", ["fused", "graph", "streams"])
