@@ -215,15 +215,18 @@ def parity_gate(lib, data, W, E, D, dag, options, steps: int = 2) -> dict:
 def timed_windows(rig, K: int, windows: int, barrier, reduce_max=None):
     """`windows` x exactly K generations, each bracketed by barrier + synchronize; per window (span_ms, kernel_ms)."""
     spans, kernels, walls = [], [], []
+    timed_windows.launches = []  # kernel launches inside each window, counted by the executor
     for _ in range(windows):
         rig.device_ms()
         rig.span_ms()
         barrier()
+        launched0 = rig.kernels_launched()
         t0 = time.perf_counter()
         rig.schedule(K)
         rig.wait()
         barrier()
         walls.append(1e3 * (time.perf_counter() - t0))
+        timed_windows.launches.append(rig.kernels_launched() - launched0)
         kernel_ms, timed = rig.device_ms()
         span_ms = rig.span_ms()
         spans.append(span_ms if (timed == K and span_ms > 0.0) else walls[-1])
@@ -271,7 +274,8 @@ def measure_config(lib, np, torch, abi, synth, dag, W, E, D, K, WU, windows, pea
         t_ms = statistics.median(spans)
         kernel_ms = statistics.median(kernels)
         out.update({"value": W * K / (t_ms * 1e-3), "unit": UNIT, "ms_per_step": t_ms / K,
-                    "gpu_launches": int(info.kernel_launches_per_generation) * K,
+                    "gpu_launches": int(statistics.median(timed_windows.launches)),
+                    "generations_per_launch_max": int(info.max_generations_per_launch),
                     "roofline": roofline_of(rig, np, abi, synth, dag, W, E, D, kernel_ms, t_ms / K, peak, peak_src, info)})
     finally:
         rig.close()
@@ -351,6 +355,7 @@ def run_b200(args) -> None:
     time.sleep(0.25)
     t0 = time.time()
     spans, kernels, walls = timed_windows(rig, K, R, barrier, reduce_max)
+    window_launches = list(timed_windows.launches)
     t1 = time.time()
     clocks = sampler.summary(t0, t1)
     t_ms = statistics.median(spans)
@@ -401,7 +406,10 @@ def run_b200(args) -> None:
         "windows": {"n": R, "ms_per_step_median": t_ms / K, "ms_per_step_min": min(spans) / K, "ms_per_step_max": max(spans) / K,
                     "value_min": world_size * W * K / (max(spans) * 1e-3), "value_max": world_size * W * K / (min(spans) * 1e-3)},
         "wall_ms_per_step": statistics.median(walls) / K, "device_ms_per_step": kernel_ms,
-        "gpu_launches": int(info.kernel_launches_per_generation) * K,
+        "gpu_launches": int(statistics.median(window_launches)),
+        "gpu_launches_note": f"kernel launches inside one timed window of {K} generations, counted by the executor (per window: {window_launches}); "
+                             f"one launch per generation would be {int(info.kernel_launches_per_generation) * K}: generations queued behind two "
+                             f"running launches leave together, up to {int(info.max_generations_per_launch)} per launch",
         "roofline": roofline, "clocks": clocks,
     }
     if parity is not None:

@@ -299,7 +299,8 @@ class ExecutorInfo(C.Structure):
         ("kernel_launches_per_generation", c_uint32),
         ("edges", c_uint64),
         ("algorithmic_bytes_per_step", c_uint64),
-        ("reserved", c_uint64 * 4),
+        ("max_generations_per_launch", c_uint64),
+        ("reserved", c_uint64 * 3),
     ]
 
 
@@ -378,6 +379,7 @@ PRODUCT_SYMBOLS = [
     ("fimo_b200_resource_download", FimoStatus, [POINTER(ResourceView), c_void_p]),
     ("fimo_b200_group_executor_info", FimoStatus, [c_void_p, POINTER(ExecutorInfo)]),
     ("fimo_b200_group_executor_describe", c_size_t, [c_void_p, c_char_p, c_size_t]),
+    ("fimo_b200_group_kernels_launched", c_uint64, [c_void_p]),
     ("fimo_b200_group_stream", c_void_p, [c_void_p]),
     ("fimo_b200_group_wait_idle", None, [c_void_p]),
     ("fimo_b200_group_device_ms", c_double, [c_void_p, POINTER(c_uint64)]),

@@ -58,6 +58,8 @@ struct Completion {
     bool generation = true; // false: a stream-ordered transfer (not part of the per-generation timers)
     cudaEvent_t landed = nullptr; // a generation with result copies behind it: completes when they have landed
     uint64_t seq = 0;             // position in the executor's queue (Executor::posted_seq)
+    uint32_t batch = 1;           // generations the start / end pair brackets (executor_launch_batch)
+    bool owns_events = true;      // the last generation of a batch recycles the shared events
 };
 
 struct Completer {
@@ -95,6 +97,7 @@ struct Executor {
     cudaGraphExec_t graph_exec = nullptr;
     bool use_graph = false;
     uint32_t kernels = 0;
+    std::atomic<uint64_t> kernels_launched{0}; // kernel launches of generations enqueued so far (copies not counted)
 
     std::mutex m; // event pool, in-flight count, timing
     std::condition_variable idle_cv;
@@ -174,6 +177,7 @@ void Completer::run() {
         float ms = 0.0f;
         const bool timed = c.generation && cudaEventElapsedTime(&ms, c.start, c.end) == cudaSuccess;
         if (c.generation && !timed) (void)cudaGetLastError();
+        ms /= (float)c.batch; // a multi-generation launch: every generation gets its share
         if (timed) c.ex->last_ms.store((double)ms, std::memory_order_relaxed);
         if (c.done) c.done(c.user);
         Executor *ex = c.ex;
@@ -182,7 +186,9 @@ void Completer::run() {
             ex->ms_sum += ms;
             ex->ms_count++;
         }
-        if (c.generation) {
+        if (!c.owns_events) {
+            // an earlier generation of a batch: the events belong to the batch's last generation
+        } else if (c.generation) {
             if (!ex->span_anchor) ex->span_anchor = c.start;
             else ex->free_events.push_back(c.start);
             float span = 0.0f;
@@ -191,7 +197,7 @@ void Completer::run() {
         } else if (c.start) {
             ex->free_events.push_back(c.start);
         }
-        ex->free_events.push_back(c.end);
+        if (c.owns_events) ex->free_events.push_back(c.end);
         if (c.landed) ex->free_events.push_back(c.landed);
         if (c.seq > ex->retired_seq) ex->retired_seq = c.seq;
         if (--ex->in_flight == 0) ex->idle_cv.notify_all();
@@ -621,11 +627,43 @@ bool executor_launch(Executor *ex, void (*done)(void *), void *user, const Copy 
         else launched = replay(ex, false);
     }
     launched = ok(cudaEventRecord(c.end, ex->stream), "cudaEventRecord") && launched;
+    ex->kernels_launched.fetch_add(ex->kernels, std::memory_order_relaxed);
     if (launched) launched = enqueue_copies(ex->stream, downloads, n_down, false); // its results, behind it
     if (readback) launched = launched && enqueue_readback(ex, *readback, c.landed);
     if (c.landed && (!readback || !launched)) launched = ok(cudaEventRecord(c.landed, ex->stream), "cudaEventRecord") && launched;
     if (!launched) c.done = nullptr; // the caller reports the failure itself
     completer().post(c);
+    return launched;
+}
+
+uint32_t executor_max_gens(Executor *ex) {
+    return ex->nodes.size() == 1 && ex->nodes[0].launch_gens ? std::max<uint32_t>(ex->nodes[0].max_gens, 1) : 1;
+}
+
+bool executor_launch_batch(Executor *ex, uint32_t gens, void (*done)(void *), void *const *users) {
+    if (gens == 0 || gens > executor_max_gens(ex)) return false;
+    DeviceGuard guard(ex->device);
+    Completion c{ex->take_event(), ex->take_event(), ex, done, nullptr};
+    if (!c.start || !c.end) return false;
+    c.batch = gens;
+    {
+        std::lock_guard<std::mutex> g(ex->m);
+        ex->in_flight += gens;
+        c.seq = ++ex->posted_seq;
+    }
+    FimoB200_LaunchInfo info = ex->info;
+    info.stream = ex->stream, info.flags = 0u;
+    bool launched = ok(cudaEventRecord(c.start, ex->stream), "cudaEventRecord");
+    launched = launched && ex->nodes[0].launch_gens(&info, gens) == FIMO_STATUS_OK; // a plain launch: the generation count is a kernel argument
+    launched = ok(cudaEventRecord(c.end, ex->stream), "cudaEventRecord") && launched;
+    ex->kernels_launched.fetch_add(ex->kernels, std::memory_order_relaxed); // one launch of the node's kernels for all `gens` generations
+    for (uint32_t i = 0; i < gens; i++) {
+        Completion one = c;
+        one.user = users[i];
+        one.owns_events = i + 1 == gens;
+        if (!launched) one.done = nullptr; // the caller reports the failure itself
+        completer().post(one);
+    }
     return launched;
 }
 
@@ -669,6 +707,7 @@ void host_free_pinned(void *p) {
 void *executor_stream(Executor *ex) { return ex->stream; }
 bool executor_uses_graph(Executor *ex) { return ex->use_graph; }
 uint32_t executor_kernels_per_generation(Executor *ex) { return ex->kernels; }
+uint64_t executor_kernels_launched(Executor *ex) { return ex->kernels_launched.load(std::memory_order_relaxed); }
 
 double executor_device_ms(Executor *ex, uint64_t *generations) {
     std::lock_guard<std::mutex> g(ex->m);

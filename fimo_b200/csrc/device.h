@@ -32,6 +32,11 @@ struct Node {
     std::function<FimoStatus(const FimoB200_LaunchInfo *)> launch;
     std::vector<uint32_t> deps; // indices of nodes that must finish first
     uint32_t kernels = 1;       // kernel launches this node issues (for ExecutorInfo / gpu_launches)
+    // Optional: enqueue `gens` consecutive generations of this node in ONE launch (the fused world-step kernel when a
+    // world belongs to one CTA).  Used when the node is the whole executor and the backlog holds several generations
+    // with nothing between them (executor_launch_batch).
+    std::function<FimoStatus(const FimoB200_LaunchInfo *, uint32_t gens)> launch_gens;
+    uint32_t max_gens = 1;
 };
 
 struct Executor;
@@ -59,6 +64,10 @@ struct Readback {
 };
 bool executor_launch(Executor *ex, void (*done)(void *), void *user, const Copy *uploads = nullptr, size_t n_up = 0,
                      const Copy *downloads = nullptr, size_t n_down = 0, const Readback *readback = nullptr);
+// `gens` (<= executor_max_gens) consecutive generations in one launch; `done(users[i])` runs once per generation, in
+// order, when the launch has finished (generation numbers, fences and semaphores stay per generation).
+uint32_t executor_max_gens(Executor *ex);
+bool executor_launch_batch(Executor *ex, uint32_t gens, void (*done)(void *), void *const *users);
 // Enqueue a stream-ordered copy between host memory and HBM behind everything launched so far.
 bool executor_transfer(Executor *ex, void *dst, const void *src, size_t bytes, bool to_device, void (*done)(void *), void *user);
 // A host system inside a device group: `d2h` copies (HBM -> pinned mirrors) in front, `fn(user)` as a host node
@@ -71,6 +80,7 @@ void executor_wait_idle(Executor *ex);
 void *executor_stream(Executor *ex);
 bool executor_uses_graph(Executor *ex);
 uint32_t executor_kernels_per_generation(Executor *ex);
+uint64_t executor_kernels_launched(Executor *ex); // kernel launches of all generations enqueued so far
 double executor_device_ms(Executor *ex, uint64_t *generations);
 double executor_last_generation_ms(Executor *ex); // device time of the generation whose `done` is running (completion thread)
 double executor_span_ms(Executor *ex);
@@ -118,6 +128,7 @@ FB_DECLARE_ENTRY(builtin_group_stats);
 #undef FB_DECLARE_ENTRY
 uint32_t builtin_propagate_kernels(const FimoB200_ResourceView *world, const FimoB200_ResourceView *level_start);
 
+constexpr size_t kBuiltinScratchBytes = 2048; // >= kStatScratchBytes (kernels_common.cuh)
 // State of a built-in system instance (what `system_create` builds into the system blob).
 struct BuiltinState {
     void *scratch; // HBM: statistics accumulators + completion ticket (cull only)
@@ -160,6 +171,7 @@ struct WorldStepPlan {
     uint32_t team = 1;          // CTAs that step one world together (> 1: large worlds / few worlds)
     uint32_t teams = 0;         // worlds in flight = grid / team
     uint32_t kernels = 1;       // launches per generation (team mode adds the list-compaction kernel, a tail grid one launch)
+    uint32_t max_gens = 1;      // generations ONE launch may step (> 1: one-CTA-per-world plans with enough chunks per CTA)
     // One CTA per world: the persistent grid steps worlds [0, tail_first) in whole rounds, a second grid launched
     // beside it steps [tail_first, n_worlds) one world per CTA as slots free up (tail_first == n_worlds: no tail).
     uint32_t grid = 0, tail_first = 0;
@@ -173,7 +185,7 @@ struct WorldStepPlan {
 };
 bool world_step_plan(const WorldStepViews &v, int device, WorldStepPlan &plan); // false: not fusable
 FimoStatus world_step_launch(const WorldStepViews &v, const WorldStepPlan &plan, void *cull_scratch,
-                             const FimoB200_LaunchInfo *info);
+                             const FimoB200_LaunchInfo *info, uint32_t gens = 1);
 const char *world_step_kernel_name(const WorldStepPlan &plan); // which kernel world_step_launch picks
 std::string world_step_describe(const WorldStepPlan &plan, uint64_t n_worlds); // ... and with which geometry
 // v1: one CTA per world, whole world's matrices in shared memory, loads through registers (kernels.cu)

@@ -125,20 +125,20 @@ struct StepArgs {
     Plane vis_mask, vis_list, vis_count;            // cull outputs
     Plane aabb_c, aabb_h, frustum;                  // cull inputs
     unsigned long long *stats;                      // FIMO_B200_STAT_* words of the batch
-    unsigned long long *scratch;                    // [0..3] accumulators, [4] ticket, [5] generations published
+    unsigned long long *scratch;                    // per-generation accumulator blocks + counters (kStatScratchBytes, see stats_contribute)
     unsigned long long *ring;                       // per-generation snapshots of `stats` ([ring_slots][8]) or nullptr
     uint32_t ring_slots;
     const PeerTable *peers;                         // multi-GPU statistics exchange over peer memory, or nullptr
     // the fused 8-system DAG (world_step.cu, kSet = 1) additionally uses:
     Plane angvel, gravity, vmax, waabb, wbounds;
     uint32_t *gstats;     // FIMO_B200_GSTAT_* words of the batch
-    int *bounds_keys;     // [0..5] batch bounds as float_key accumulators, then [n_worlds][6] per-world ones (team mode)
+    int *bounds_keys;     // [kStatSlots][6] batch bounds as float_key accumulators (one set per generation of a launch), then [n_worlds][6] per-world ones (team mode)
     // the fused 16-system DAG (kSet = 2) additionally uses:
     Plane damp, sleep_eps, campos, lod_dist2, frustum2;     // per-world constants
     Plane sleep, lod, vis_mask2, vis_list2, vis_count2, vbounds;
     unsigned long long *stats2, *scratch2; // cull2's statistics and its accumulator block
     uint32_t *gstats2;                     // group_stats2
-    int *bounds_keys2;                     // [0..5] batch bounds of the visible entities (float keys)
+    int *bounds_keys2;                     // [kStatSlots][6] batch bounds of the visible entities (float keys)
     uint32_t n_worlds, entities, levels, mask_words;
 };
 
@@ -185,23 +185,42 @@ struct StatsSink { // where one cull's batch statistics go (the DAGs have up to 
     uint32_t ring_slots = 0;
     const PeerTable *peers = nullptr;   // fimo_b200_group_stats_peers_bind
 };
+// Accumulator blocks in `scratch`, one per generation a launch steps (a multi-generation launch lets CTAs drift apart
+// by whole generations, so each generation gets its own sums and its own ticket): slot s at scratch[8 s ..]:
+// [0] visible, [1] mask sum, [2] worlds, [4] ticket.  Behind them scratch[kStatGlobals + 0] counts the generations
+// published since the system was created (ring / inbox slot index) and [kStatGlobals + 1] the generations published
+// within the running launch (finalisers run in generation order).
+constexpr int kStatSlots = 16;
+constexpr int kStatGlobals = kStatSlots * 8;
+constexpr size_t kStatScratchBytes = (kStatGlobals + 8) * 8;
+static_assert(kStatScratchBytes <= kBuiltinScratchBytes, "built-in scratch block too small");
+__device__ __forceinline__ unsigned long long ld_acquire_gpu_u64(const unsigned long long *p) {
+    unsigned long long v;
+    asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_release_gpu_u64(unsigned long long *p, unsigned long long v) {
+    asm volatile("st.release.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
 // The three steps of publishing: every CTA adds its sums (fire-and-forget reductions), draws a ticket behind a fence,
 // and the CTA that drew the last one turns the accumulators into the published words and re-arms them.
-__device__ __forceinline__ void stats_contribute(const StatsSink &a, unsigned long long visible, unsigned long long mask_sum,
+__device__ __forceinline__ void stats_contribute(const StatsSink &a, uint32_t slot, unsigned long long visible, unsigned long long mask_sum,
                                                  unsigned long long worlds) {
-    atomicAdd(&a.scratch[0], visible);
-    atomicAdd(&a.scratch[1], mask_sum);
-    atomicAdd(&a.scratch[2], worlds);
+    atomicAdd(&a.scratch[slot * 8 + 0], visible);
+    atomicAdd(&a.scratch[slot * 8 + 1], mask_sum);
+    atomicAdd(&a.scratch[slot * 8 + 2], worlds);
 }
-__device__ __forceinline__ bool stats_last_ticket(const StatsSink &a, unsigned long long n_ctas) {
+__device__ __forceinline__ bool stats_last_ticket(const StatsSink &a, uint32_t slot, unsigned long long n_ctas) {
     __threadfence();
-    const unsigned long long ticket = atomicAdd(&a.scratch[4], 1ull);
+    const unsigned long long ticket = atomicAdd(&a.scratch[slot * 8 + 4], 1ull);
     if (ticket != n_ctas - 1) return false;
     __threadfence();
     return true;
 }
+// `ordered`: this sink carries the launch's publication order (the first sink of a pair); generation `slot` of the
+// launch is published only after generation slot - 1 has been (their finalisers may be different CTAs).
 template <bool kGroupStats>
-__device__ __forceinline__ void stats_finalize(const StatsSink &a) {
+__device__ __forceinline__ void stats_finalize(const StatsSink &a, uint32_t slot) {
     // This runs on the kernel's critical path (the last CTA, after everyone else has left): the loads that do not
     // depend on the accumulators go first so that their latency overlaps the exchanges, and the ring slot is written
     // from registers instead of reading `stats` back.
@@ -210,12 +229,12 @@ __device__ __forceinline__ void stats_finalize(const StatsSink &a) {
     uint4 peers = make_uint4(0u, 0u, 1u, 0u); // nranks, rank, slots
     if (a.peers) peers = *(const uint4 *)a.peers;
     if (a.ring || a.peers) {
-        gen = a.scratch[5];
+        gen = a.scratch[kStatGlobals];
         for (int i = 5; i < FIMO_B200_STAT_WORDS; i++) rest[i - 5] = a.stats[i];
     }
-    const unsigned long long v = atomicExch(&a.scratch[0], 0ull);
-    const unsigned long long m = atomicExch(&a.scratch[1], 0ull);
-    const unsigned long long n = atomicExch(&a.scratch[2], 0ull);
+    const unsigned long long v = atomicExch(&a.scratch[slot * 8 + 0], 0ull);
+    const unsigned long long m = atomicExch(&a.scratch[slot * 8 + 1], 0ull);
+    const unsigned long long n = atomicExch(&a.scratch[slot * 8 + 2], 0ull);
     unsigned long long words[5];
     words[FIMO_B200_STAT_VISIBLE] = v;
     words[FIMO_B200_STAT_ENTITIES] = n * (unsigned long long)a.entities;
@@ -223,11 +242,11 @@ __device__ __forceinline__ void stats_finalize(const StatsSink &a) {
     words[FIMO_B200_STAT_WORLDS] = n;
     words[FIMO_B200_STAT_STEPS] = steps_before + n;
     for (int i = 0; i < 5; i++) a.stats[i] = words[i];
-    if (a.ring || a.peers) a.scratch[5] = gen + 1;
+    if (a.ring || a.peers) a.scratch[kStatGlobals] = gen + 1;
     if (a.ring) { // the snapshot of this generation: slot = generations published so far % slots
-        unsigned long long *slot = a.ring + (gen % a.ring_slots) * FIMO_B200_STAT_WORDS;
-        for (int i = 0; i < 5; i++) slot[i] = words[i];
-        for (int i = 5; i < FIMO_B200_STAT_WORDS; i++) slot[i] = rest[i - 5];
+        unsigned long long *row = a.ring + (gen % a.ring_slots) * FIMO_B200_STAT_WORDS;
+        for (int i = 0; i < 5; i++) row[i] = words[i];
+        for (int i = 5; i < FIMO_B200_STAT_WORDS; i++) row[i] = rest[i - 5];
     }
     if (a.peers) { // the same words into every rank's inbox (our own included), tagged with the generation
         const unsigned long long tag = ((gen + 1) & 0xFFFFFFFFull) << 32;
@@ -248,37 +267,49 @@ __device__ __forceinline__ void stats_finalize(const StatsSink &a) {
         g[FIMO_B200_GSTAT_WORLDS_LO] = (uint32_t)(n & 0xFFFFFFFFull), g[FIMO_B200_GSTAT_WORLDS_LO + 1] = (uint32_t)(n >> 32);
         for (int i = 0; i < 6; i++) {
             const int empty = i < 3 ? float_key(FIMO_B200_BOUNDS_EMPTY_MIN) : float_key(-FIMO_B200_BOUNDS_EMPTY_MIN);
-            g[FIMO_B200_GSTAT_BOUNDS + i] = __float_as_uint(key_float(atomicExch(a.bounds_keys + i, empty)));
+            g[FIMO_B200_GSTAT_BOUNDS + i] = __float_as_uint(key_float(atomicExch(a.bounds_keys + slot * 6 + i, empty)));
         }
     }
 }
+// Generations of one launch are published in order: the finaliser of generation `slot` waits for slot - 1's.
+__device__ __forceinline__ void stats_order_enter(const StatsSink &a, uint32_t slot) {
+    if (slot == 0) return;
+    while (ld_acquire_gpu_u64(a.scratch + kStatGlobals + 1) != slot) __nanosleep(100);
+}
+__device__ __forceinline__ void stats_order_leave(const StatsSink &a, uint32_t slot, bool last_of_launch) {
+    atomicExch(&a.scratch[slot * 8 + 4], 0ull); // re-arm the ticket
+    if (slot == 0 && last_of_launch) return;    // single-generation launch: nothing to order
+    st_release_gpu_u64(a.scratch + kStatGlobals + 1, last_of_launch ? 0ull : (unsigned long long)slot + 1ull);
+}
 template <bool kGroupStats>
 __device__ __forceinline__ bool publish_stats_to(const StatsSink &a, unsigned long long visible, unsigned long long mask_sum,
-                                                 unsigned long long worlds, unsigned long long n_ctas) {
-    stats_contribute(a, visible, mask_sum, worlds);
-    if (!stats_last_ticket(a, n_ctas)) return false;
-    stats_finalize<kGroupStats>(a);
-    atomicExch(&a.scratch[4], 0ull);
+                                                 unsigned long long worlds, unsigned long long n_ctas, uint32_t slot = 0, bool last_of_launch = true) {
+    stats_contribute(a, slot, visible, mask_sum, worlds);
+    if (!stats_last_ticket(a, slot, n_ctas)) return false;
+    stats_order_enter(a, slot);
+    stats_finalize<kGroupStats>(a, slot);
+    stats_order_leave(a, slot, last_of_launch);
     return true;
 }
 // Two culls published by one kernel (the 16-system set): one fence and one ticket (the first sink's) for both.
 template <bool kGroupStats>
 __device__ __forceinline__ bool publish_stats_pair(const StatsSink &a, const StatsSink &b, unsigned long long visible_a,
                                                    unsigned long long mask_sum_a, unsigned long long visible_b, unsigned long long mask_sum_b,
-                                                   unsigned long long worlds, unsigned long long n_ctas) {
-    stats_contribute(a, visible_a, mask_sum_a, worlds);
-    stats_contribute(b, visible_b, mask_sum_b, worlds);
-    if (!stats_last_ticket(a, n_ctas)) return false;
-    stats_finalize<kGroupStats>(a);
-    stats_finalize<kGroupStats>(b);
-    atomicExch(&a.scratch[4], 0ull);
+                                                   unsigned long long worlds, unsigned long long n_ctas, uint32_t slot = 0, bool last_of_launch = true) {
+    stats_contribute(a, slot, visible_a, mask_sum_a, worlds);
+    stats_contribute(b, slot, visible_b, mask_sum_b, worlds);
+    if (!stats_last_ticket(a, slot, n_ctas)) return false;
+    stats_order_enter(a, slot);
+    stats_finalize<kGroupStats>(a, slot);
+    stats_finalize<kGroupStats>(b, slot);
+    stats_order_leave(a, slot, last_of_launch);
     return true;
 }
 template <bool kGroupStats = false>
 __device__ __forceinline__ bool publish_stats(const StepArgs &a, unsigned long long visible, unsigned long long mask_sum,
-                                              unsigned long long worlds, unsigned long long n_ctas) {
+                                              unsigned long long worlds, unsigned long long n_ctas, uint32_t slot = 0, bool last_of_launch = true) {
     return publish_stats_to<kGroupStats>(StatsSink{a.stats, a.scratch, a.gstats, a.bounds_keys, a.entities, a.ring, a.ring_slots, a.peers}, visible,
-                                         mask_sum, worlds, n_ctas);
+                                         mask_sum, worlds, n_ctas, slot, last_of_launch);
 }
 __device__ __forceinline__ bool publish_stats(const StepArgs &a, unsigned long long visible, unsigned long long mask_sum,
                                               unsigned long long worlds) {

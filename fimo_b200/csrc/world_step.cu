@@ -93,6 +93,8 @@ __device__ __forceinline__ void bulk_store(void *dst, const void *src, uint32_t 
 __device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
 __device__ __forceinline__ void bulk_wait_read_all() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
 __device__ __forceinline__ void bulk_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+// all but the two most recent bulk groups have COMPLETED (their global writes are visible to this thread)
+__device__ __forceinline__ void bulk_wait_all_but_2() { asm volatile("cp.async.bulk.wait_group 2;" ::: "memory"); }
 __device__ __forceinline__ void mbar_arrive(uint64_t *bar) {
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_addr(bar)) : "memory");
 }
@@ -116,6 +118,11 @@ struct PipeArgs {
     uint32_t stages;   // ring depth (chunks)
     uint32_t lvl_cap;  // parent matrices kept in shared memory: entities [0, lvl_cap) of a world
     uint32_t chunks;   // chunks per world = ceil(E / T)
+    // Generations this launch steps (1..kStatSlots).  A world belongs to one CTA, so generation g + 1 of a CTA's worlds
+    // needs nothing but that CTA's own generation g: the ring simply runs on across generation boundaries (behind a
+    // bulk-group wait that orders a chunk's loads after the stores of its previous generation) and every generation
+    // publishes its own statistics.  One-CTA-per-world plans only.
+    uint32_t gens;
     uint32_t team;     // CTAs that step one world together (1 = a world belongs to one CTA)
     uint32_t teams;    // gridDim.x / team
     // The worlds this launch steps: [world_first, world_end).  One generation of a one-CTA-per-world plan is two
@@ -189,7 +196,7 @@ template <int T, int kSet>
 __device__ __forceinline__ void tma_warp(const PipeArgs &pa, const Walk &wk, float *ring, uint64_t *full, uint64_t *done) {
     constexpr int kIn = SetTraits<kSet>::kIn, kStage = SetTraits<kSet>::kStage;
     const StepArgs &a = pa.a;
-    const uint32_t E = a.entities, N = pa.stages, nc = pa.chunks, G = pa.team, total = wk.total;
+    const uint32_t E = a.entities, N = pa.stages, nc = pa.chunks, G = pa.team, total = wk.total, all = wk.total * pa.gens;
     uint32_t k = 0, c = wk.rank, s = 0, round = 0; // position of the chunk being loaded
     uint32_t sk = 0, sc = wk.rank;                  // position of the chunk being stored (N behind)
     auto store_chunk = [&](uint32_t stage, uint32_t wk_, uint32_t wc) {
@@ -217,29 +224,33 @@ __device__ __forceinline__ void tma_warp(const PipeArgs &pa, const Walk &wk, flo
         }
         bulk_commit();
     };
-    for (uint32_t it = 0; it < total; it++) {
+    for (uint32_t it = 0; it < all; it++) {
         if (it >= N) { // the stage still holds chunk it-N: wait for its outputs, drain them, then reuse it
             mbar_wait(&done[s], (round - 1) & 1u);
             store_chunk(s, sk, sc);
-            if ((sc += G) >= nc) sc = wk.rank, sk++;
+            if ((sc += G) >= nc) sc = wk.rank, sk = sk + 1 == wk.my_worlds ? 0 : sk + 1;
             bulk_wait_read_all();
         }
+        // A later generation reads what the previous one stored: bulk group it - total (this chunk, one generation ago)
+        // must have completed.  Groups 0 .. it - N are committed and total >= N + 2 (world_step_max_gens), so "all but
+        // the two most recent" covers it — and those stores were issued a whole generation ago, so this never waits.
+        if (it >= total) bulk_wait_all_but_2();
         const uint64_t w = wk.first_world + (uint64_t)k * pa.teams;
         const uint32_t first = c * T, bytes = min((uint32_t)T, E - first) * 4u; // multiple of 16 (E % 4 == 0)
         float *st = ring + (size_t)s * kStage * T;
         mbar_expect_tx(&full[s], bytes * kIn);
 #pragma unroll
         for (int p = 0; p < kIn; p++) bulk_load(st + p * T, plane_src(a, p, w, E) + first, bytes, &full[s]);
-        if ((c += G) >= nc) c = wk.rank, k++;
+        if ((c += G) >= nc) c = wk.rank, k = k + 1 == wk.my_worlds ? 0 : k + 1;
         if (++s == N) s = 0, round++;
     }
-    // drain the last min(N, total) chunks
-    const uint32_t tail = total < N ? total : N;
-    uint32_t ds = total < N ? 0 : s, dround = total < N ? 0 : round - 1;
+    // drain the last min(N, all) chunks
+    const uint32_t tail = all < N ? all : N;
+    uint32_t ds = all < N ? 0 : s, dround = all < N ? 0 : round - 1;
     for (uint32_t j = 0; j < tail; j++) {
         mbar_wait(&done[ds], dround & 1u);
         store_chunk(ds, sk, sc);
-        if ((sc += G) >= nc) sc = wk.rank, sk++;
+        if ((sc += G) >= nc) sc = wk.rank, sk = sk + 1 == wk.my_worlds ? 0 : sk + 1;
         if (++ds == N) ds = 0, dround++;
     }
     bulk_wait_all();
@@ -313,7 +324,7 @@ __global__ void __launch_bounds__(T + 32, kMinBlocks) k_world_step_pipe(const Pi
     int cta_vbounds_key = kEmptyKey;
     const uint32_t levels = a.levels;
     const Walk wk(pa);
-    const uint32_t my_worlds = wk.my_worlds, total = wk.total;
+    const uint32_t my_worlds = wk.my_worlds, total = wk.total * (kTeam ? 1u : pa.gens); // chunks of every generation of the launch
 
     if (tid == 0) {
         for (uint32_t s = 0; s < N; s++) {
@@ -371,6 +382,8 @@ __global__ void __launch_bounds__(T + 32, kMinBlocks) k_world_step_pipe(const Pi
     uint32_t running = 0;                                   // visible entities of the current world so far
     uint32_t running2 = 0;
     uint32_t k = 0, c = wk.rank, s = 0, parity = 0, l_lo = 0;
+    uint32_t kk = 0;  // worlds begun so far, over all generations of the launch: parity of the double-buffered per-world state
+    uint32_t gen = 0; // generation of the launch being stepped
     // team mode: entities of level pend_level this CTA has finished but not yet announced.  Dependants only
     // care about a level being COMPLETE, so a CTA announces its share once, when it moves past the level.
     int pend_level = -1;
@@ -395,10 +408,11 @@ __global__ void __launch_bounds__(T + 32, kMinBlocks) k_world_step_pipe(const Pi
     unsigned long long tm_wall0 = 0;
     if (kTimingBuild && pa.timing && tid == 0) asm volatile("mov.u64 %0, %globaltimer;" : "=l"(tm_wall0));
     for (uint32_t it = 0; it < total; it++) {
-        const WorldConst &wc = s_c[k & 1];
+        const WorldConst &wc = s_c[kk & 1];
+        const bool more_worlds = k + 1 < my_worlds || (!kTeam && gen + 1 < pa.gens); // this CTA steps another world after this one
         if (c == wk.rank) { // a new world begins
             if (kTeam && it != 0) consumer_sync<T>(); // its constants were published during the previous world
-            if (k + 1 < my_worlds) next_const = const_word(w + pa.teams);
+            if (more_worlds) next_const = const_word(k + 1 < my_worlds ? w + pa.teams : (uint64_t)wk.first_world);
             running = 0, running2 = 0, l_lo = 0, ready_upto = -1;
             mask_out = uptr(a.vis_mask, w);
             list_out = uptr(a.vis_list, w);
@@ -581,11 +595,11 @@ __global__ void __launch_bounds__(T + 32, kMinBlocks) k_world_step_pipe(const Pi
                     mine = lane == r ? key[r] : mine;
                     if (kSet == 2) vmine = lane == r ? vkey[r] : vmine;
                 }
-                if (lane < 3) atomicMin(&s_bounds[k & 1][lane], mine);
-                else atomicMax(&s_bounds[k & 1][lane], mine);
+                if (lane < 3) atomicMin(&s_bounds[kk & 1][lane], mine);
+                else atomicMax(&s_bounds[kk & 1][lane], mine);
                 if (kSet == 2) {
-                    if (lane < 3) atomicMin(&s_vbounds[k & 1][lane], vmine);
-                    else atomicMax(&s_vbounds[k & 1][lane], vmine);
+                    if (lane < 3) atomicMin(&s_vbounds[kk & 1][lane], vmine);
+                    else atomicMax(&s_vbounds[kk & 1][lane], vmine);
                 }
             }
         }
@@ -597,14 +611,14 @@ __global__ void __launch_bounds__(T + 32, kMinBlocks) k_world_step_pipe(const Pi
                 if ((e >> 5) < a.mask_words) mask_out[e >> 5] = ballot;
             }
             if (world_ends) flush_pending(lvl_done);
-            if (world_ends && k + 1 < my_worlds) publish_const(s_c[(k + 1) & 1], next_const);
+            if (world_ends && more_worlds) publish_const(s_c[(kk + 1) & 1], next_const);
             if (kSet >= 1 && world_ends) { // this CTA's share of the world's bounds joins the team's
                 consumer_sync<T>();
                 if (tid < 6) {
-                    int *dst = a.bounds_keys + 6 + w * 6 + tid;
-                    if (tid < 3) atomicMin(dst, s_bounds[k & 1][tid]);
-                    else atomicMax(dst, s_bounds[k & 1][tid]);
-                    s_bounds[k & 1][tid] = kEmptyKey;
+                    int *dst = a.bounds_keys + kStatSlots * 6 + w * 6 + tid;
+                    if (tid < 3) atomicMin(dst, s_bounds[kk & 1][tid]);
+                    else atomicMax(dst, s_bounds[kk & 1][tid]);
+                    s_bounds[kk & 1][tid] = kEmptyKey;
                 }
             }
         } else {
@@ -621,7 +635,7 @@ __global__ void __launch_bounds__(T + 32, kMinBlocks) k_world_step_pipe(const Pi
                     ((uint8_t *)s_cnt2[it & 1])[warp] = (uint8_t)__popc(ballot2);
                 }
             }
-            if (world_ends && k + 1 < my_worlds) publish_const(s_c[(k + 1) & 1], next_const);
+            if (world_ends && more_worlds) publish_const(s_c[(kk + 1) & 1], next_const);
             consumer_sync<T>();
             // the warps' counts are bytes: sums over "warps before me" and "all warps" are two dp4a per word
             uint32_t before = 0, chunk_total = 0;
@@ -657,18 +671,45 @@ __global__ void __launch_bounds__(T + 32, kMinBlocks) k_world_step_pipe(const Pi
                 if (kSet == 2) uptr(a.vis_count2, w)[0] = running2, cta_visible2 += running2;
             }
             if (kSet >= 1 && !kTeam && tid < 6) { // after this chunk's barrier: every warp's keys are in
-                const int key = s_bounds[k & 1][tid];
+                const int key = s_bounds[kk & 1][tid];
                 fptr(a.wbounds, w)[tid] = key_float(key);
                 cta_bounds_key = tid < 3 ? min(cta_bounds_key, key) : max(cta_bounds_key, key);
-                s_bounds[k & 1][tid] = kEmptyKey;
+                s_bounds[kk & 1][tid] = kEmptyKey;
                 if (kSet == 2) {
-                    const int vkey = s_vbounds[k & 1][tid];
+                    const int vkey = s_vbounds[kk & 1][tid];
                     fptr(a.vbounds, w)[tid] = key_float(vkey);
                     cta_vbounds_key = tid < 3 ? min(cta_vbounds_key, vkey) : max(cta_vbounds_key, vkey);
-                    s_vbounds[k & 1][tid] = kEmptyKey;
+                    s_vbounds[kk & 1][tid] = kEmptyKey;
                 }
             }
-            c = wk.rank, k++, w += pa.teams;
+            c = wk.rank, k++, kk++, w += pa.teams;
+            if (!kTeam && k == my_worlds) { // this CTA's share of generation `gen` is done: publish it, go round again
+                if (lane == 0) atomicAdd(&s_sum, warp_mask_sum), warp_mask_sum = 0;
+                if (kSet == 2 && lane == 0) atomicAdd(&s_sum2, warp_mask_sum2), warp_mask_sum2 = 0;
+                if (kSet >= 1 && tid < 6) {
+                    if (tid < 3) atomicMin(a.bounds_keys + gen * 6 + tid, cta_bounds_key);
+                    else atomicMax(a.bounds_keys + gen * 6 + tid, cta_bounds_key);
+                    cta_bounds_key = kEmptyKey;
+                    if (kSet == 2) {
+                        if (tid < 3) atomicMin(a.bounds_keys2 + gen * 6 + tid, cta_vbounds_key);
+                        else atomicMax(a.bounds_keys2 + gen * 6 + tid, cta_vbounds_key);
+                        cta_vbounds_key = kEmptyKey;
+                    }
+                }
+                consumer_sync<T>();
+                if (tid == 0) { // the other warps go on with the next generation's first chunk meanwhile
+                    const unsigned long long sum = s_sum, sum2 = s_sum2;
+                    s_sum = 0, s_sum2 = 0; // next added to after the next chunk's barrier at the earliest
+                    const bool last_gen = gen + 1 == pa.gens;
+                    if (kSet == 2)
+                        publish_stats_pair<true>(StatsSink{a.stats, a.scratch, a.gstats, a.bounds_keys, a.entities, a.ring, a.ring_slots, a.peers},
+                                                 StatsSink{a.stats2, a.scratch2, a.gstats2, a.bounds_keys2, a.entities}, cta_visible, sum,
+                                                 cta_visible2, sum2, my_worlds, (unsigned long long)pa.stat_ctas, gen, last_gen);
+                    else publish_stats<kSet >= 1>(a, cta_visible, sum, my_worlds, (unsigned long long)pa.stat_ctas, gen, last_gen);
+                    cta_visible = 0, cta_visible2 = 0;
+                }
+                k = 0, w = wk.first_world, gen++;
+            }
         } else {
             c += G;
         }
@@ -694,30 +735,19 @@ __global__ void __launch_bounds__(T + 32, kMinBlocks) k_world_step_pipe(const Pi
             row[0] = smid, row[1] = tm_wall0, row[2] = wall1, row[3] = (unsigned long long)total, row[4] = tm_entry;
         }
     }
-    if (!kTeam) { // fold the per-warp mask sums, publish the batch statistics
-        if (lane == 0) atomicAdd(&s_sum, warp_mask_sum);
-        if (kSet == 2 && lane == 0) atomicAdd(&s_sum2, warp_mask_sum2);
-        if (kSet >= 1 && tid < 6 && my_worlds) {
-            if (tid < 3) atomicMin(a.bounds_keys + tid, cta_bounds_key);
-            else atomicMax(a.bounds_keys + tid, cta_bounds_key);
-            if (kSet == 2) {
-                if (tid < 3) atomicMin(a.bounds_keys2 + tid, cta_vbounds_key);
-                else atomicMax(a.bounds_keys2 + tid, cta_vbounds_key);
-            }
-        }
-        consumer_sync<T>();
-        if (tid == 0) {
+    if (!kTeam && my_worlds == 0 && tid == 0) { // a CTA without worlds still draws its ticket in every generation
+        for (uint32_t g = 0; g < pa.gens; g++) {
             if (kSet == 2)
                 publish_stats_pair<true>(StatsSink{a.stats, a.scratch, a.gstats, a.bounds_keys, a.entities, a.ring, a.ring_slots, a.peers},
-                                         StatsSink{a.stats2, a.scratch2, a.gstats2, a.bounds_keys2, a.entities}, cta_visible, s_sum,
-                                         cta_visible2, s_sum2, my_worlds, (unsigned long long)pa.stat_ctas);
-            else publish_stats<kSet >= 1>(a, cta_visible, s_sum, my_worlds, (unsigned long long)pa.stat_ctas);
-            if (kTimingBuild && pa.timing && pa.trace_base + blockIdx.x < kTimingCtas) { // statistics published: thread 0 leaves
-                unsigned long long wall2;
-                asm volatile("mov.u64 %0, %globaltimer;" : "=l"(wall2));
-                pa.timing[8 + kTimingRow * (size_t)(pa.trace_base + blockIdx.x) + 5] = wall2;
-            }
+                                         StatsSink{a.stats2, a.scratch2, a.gstats2, a.bounds_keys2, a.entities}, 0, 0, 0, 0, 0,
+                                         (unsigned long long)pa.stat_ctas, g, g + 1 == pa.gens);
+            else publish_stats<kSet >= 1>(a, 0, 0, 0, (unsigned long long)pa.stat_ctas, g, g + 1 == pa.gens);
         }
+    }
+    if (kTimingBuild && !kTeam && pa.timing && tid == 0 && pa.trace_base + blockIdx.x < kTimingCtas) { // statistics published: thread 0 leaves
+        unsigned long long wall2;
+        asm volatile("mov.u64 %0, %globaltimer;" : "=l"(wall2));
+        pa.timing[8 + kTimingRow * (size_t)(pa.trace_base + blockIdx.x) + 5] = wall2;
     }
 }
 
@@ -739,7 +769,7 @@ __global__ void __launch_bounds__(kCompactThreads) k_compact_lists(const StepArg
     if (seg == 0 && tid < kMaxLevels && lvl_done_all) lvl_done_all[w * kMaxLevels + tid] = 0;
     if (kGroupStats && seg == 0 && tid < 6) { // the team's bounds of this world: publish, fold into the batch's, re-arm
         const int empty = tid < 3 ? float_key(FIMO_B200_BOUNDS_EMPTY_MIN) : float_key(-FIMO_B200_BOUNDS_EMPTY_MIN);
-        const int key = atomicExch(a.bounds_keys + 6 + w * 6 + tid, empty);
+        const int key = atomicExch(a.bounds_keys + kStatSlots * 6 + w * 6 + tid, empty);
         fptr(a.wbounds, w)[tid] = key_float(key);
         if (tid < 3) atomicMin(a.bounds_keys + tid, key);
         else atomicMax(a.bounds_keys + tid, key);
@@ -886,14 +916,14 @@ bool world_step_plan(const WorldStepViews &v, int device, WorldStepPlan &plan) {
     if (v.set >= 1) {
         if (!v.gravity || !v.angvel || !v.waabb || !v.wbounds || !v.gstats || (v.vel_clamp && !v.vmax) || !aligned16(v.angvel)) return false;
         // bounds accumulators: batch [0..5] then per world, armed "empty" (min slots +FLT_MAX, max slots -FLT_MAX as keys)
-        std::vector<int> keys(6 + 6 * W);
+        std::vector<int> keys(kStatSlots * 6 + 6 * W);
         const int32_t kMinKey = 0x7F7FFFFF, kMaxKey = (int32_t)(0xFF7FFFFFu ^ 0x7FFFFFFFu);
         for (size_t i = 0; i < keys.size(); i++) keys[i] = i % 6 < 3 ? kMinKey : kMaxKey;
         plan.bounds = hbm_shared(device, keys.size() * 4);
         if (!plan.bounds || !hbm_upload(device, plan.bounds.get(), keys.data(), keys.size() * 4)) return false;
         if (v.set == 2) {
-            plan.bounds2 = hbm_shared(device, 6 * 4);
-            if (!plan.bounds2 || !hbm_upload(device, plan.bounds2.get(), keys.data(), 6 * 4)) return false;
+            plan.bounds2 = hbm_shared(device, kStatSlots * 6 * 4);
+            if (!plan.bounds2 || !hbm_upload(device, plan.bounds2.get(), keys.data(), kStatSlots * 6 * 4)) return false;
         }
     }
     bool planned = false;
@@ -996,6 +1026,15 @@ bool world_step_plan(const WorldStepViews &v, int device, WorldStepPlan &plan) {
             }
         }
     }
+    // Multi-generation launches (PipeArgs::gens): every CTA — the tail grid's one-world CTAs included — must have at
+    // least stages + 2 chunks per generation, so that a chunk's previous-generation stores are covered by the TMA
+    // thread's "all but the two most recent bulk groups" wait.
+    plan.max_gens = 1;
+    if (plan.team == 1 && plan.grid) {
+        const uint64_t persist = plan.tail_first, min_worlds = plan.tail_first < W ? 1 : persist / plan.grid;
+        if (min_worlds >= 1 && min_worlds * chunks >= (uint64_t)plan.stages + 2) plan.max_gens = kStatSlots;
+    }
+    if (const char *env = std::getenv("FIMO_B200_GENS")) plan.max_gens = std::min<uint32_t>(plan.max_gens, (uint32_t)std::max(1, std::atoi(env)));
     plan.rows = hbm_shared(device, (size_t)W * E * 48);
     return plan.rows != nullptr;
 }
@@ -1028,6 +1067,7 @@ namespace {
 template <int T, int kBlocks, int kSet>
 FimoStatus launch_pipe(PipeArgs &pa, const WorldStepPlan &plan, uint64_t W, const FimoB200_LaunchInfo *info) {
     cudaStream_t stream = (cudaStream_t)info->stream;
+    if (pa.gens < 1 || pa.gens > plan.max_gens) return fail("world_step plan (generations per launch)");
     if (plan.team > 1) {
         if constexpr (kSet == 2) return fail("world_step plan (teams cannot run the 16-system set)");
         else {
@@ -1069,8 +1109,8 @@ FimoStatus launch_pipe(PipeArgs &pa, const WorldStepPlan &plan, uint64_t W, cons
 } // namespace
 
 FimoStatus world_step_launch(const WorldStepViews &v, const WorldStepPlan &plan, void *cull_scratch,
-                             const FimoB200_LaunchInfo *info) {
-    if (plan.threads == 0) return world_step_launch_v1(v, cull_scratch, info);
+                             const FimoB200_LaunchInfo *info, uint32_t gens) {
+    if (plan.threads == 0) return gens == 1 ? world_step_launch_v1(v, cull_scratch, info) : FIMO_STATUS_ERROR;
     const uint64_t W = info->n_worlds, E = info->entities_per_world;
     if (W == 0 || E == 0) return FIMO_STATUS_OK;
     try {
@@ -1083,6 +1123,7 @@ FimoStatus world_step_launch(const WorldStepViews &v, const WorldStepPlan &plan,
         a.vel = plane_of(v.vel, FIMO_B200_SCOPE_ENTITY, 3, E, W, "vel");
         a.dt = plane_of(v.dt, FIMO_B200_SCOPE_WORLD, 1, 1, W, "dt");
         pa.stages = plan.stages;
+        pa.gens = gens;
         pa.lvl_cap = plan.lvl_cap;
         pa.chunks = (uint32_t)((E + plan.threads - 1) / plan.threads);
         pa.rows = (float4 *)plan.rows.get();

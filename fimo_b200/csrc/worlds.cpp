@@ -648,6 +648,12 @@ struct Group {
     FimoB200_ExecutorInfo info{};
     std::string plan_text; // what the DAG compiler produced, in words (fimo_b200_group_executor_describe)
     size_t in_flight = 0; // device generations enqueued and not yet completed (locks are held while > 0)
+    // Multi-generation launches: when the executor is one fused world-step node that can step several generations per
+    // launch (dev::executor_max_gens) and two launches are already on the stream, further plain generations wait here
+    // and leave as ONE launch when a launch retires — fewer launch boundaries, same results, generation numbers and
+    // fences still per generation (SystemGroup.zig:430-452,483-486).
+    std::deque<Job *> batch_pending;
+    size_t launches_in_flight = 0;
     uint64_t compiled_epoch = 0; // world->resource_epoch the executor was compiled against
 
     // deferred path: generations that could not be started from inside `schedule`
@@ -1084,6 +1090,10 @@ bool build_device_executor(Group *g, const char **err) {
             dev::Node node;
             void *scratch = ((dev::BuiltinState *)mc->state)->scratch;
             node.launch = [views, plan, scratch](const FimoB200_LaunchInfo *info) { return dev::world_step_launch(views, plan, scratch, info); };
+            node.launch_gens = [views, plan, scratch](const FimoB200_LaunchInfo *info, uint32_t gens) {
+                return dev::world_step_launch(views, plan, scratch, info, gens);
+            };
+            node.max_gens = plan.max_gens;
             node.kernels = plan.kernels;
             nodes.push_back(std::move(node));
         }
@@ -1107,6 +1117,7 @@ bool build_device_executor(Group *g, const char **err) {
         }
     }
     if (!nodes_ok) return false;
+    const size_t nodes_count = nodes.size();
     if (!g->executor_dev) g->executor_dev = dev::executor_create(g->world->device);
     if (!g->executor_dev) return *err = "DeviceError", false;
     g->info = FimoB200_ExecutorInfo{};
@@ -1121,7 +1132,10 @@ bool build_device_executor(Group *g, const char **err) {
     if (!dev::executor_compile(g->executor_dev, std::move(nodes), launch_info(g), use_graph)) return *err = "DeviceError", false;
     g->info.uses_cuda_graph = dev::executor_uses_graph(g->executor_dev) ? 1u : 0u;
     g->info.kernel_launches_per_generation = dev::executor_kernels_per_generation(g->executor_dev);
+    g->info.max_generations_per_launch = dev::executor_max_gens(g->executor_dev);
     g->plan_text = fuse ? dev::world_step_describe(plan, g->world->n_worlds) : "one kernel per system";
+    if (fuse && nodes_count == 1 && plan.max_gens > 1)
+        g->plan_text += "; up to " + std::to_string(plan.max_gens) + " queued generations per launch";
     if (g->info.nodes > 1) g->plan_text += " (" + std::to_string(g->info.nodes) + " graph nodes)";
     return true;
 }
@@ -1267,7 +1281,10 @@ struct DeviceDone {
     FimoWorldsMeta_Fence *signal;
     uint64_t generation = 0;
     int64_t enqueue_ns = 0;
+    bool ends_launch = true; // the last generation of its launch
 };
+void launch_pending_batches(Group *g);
+void dispatcher_main(Group *g);
 
 std::atomic<FimoB200_trace_sink> g_trace_sink{nullptr};
 std::atomic<void *> g_trace_user{nullptr};
@@ -1292,6 +1309,10 @@ void device_generation_done(void *user) {
     size_t gen;
     {
         std::lock_guard<std::mutex> lock(g->m);
+        if (done->ends_launch) {
+            g->launches_in_flight--;
+            if (!g->batch_pending.empty()) launch_pending_batches(g); // keeps the stream fed: one launch is still running
+        }
         if (--g->in_flight == 0) unlock_group_resources(g);
         end_generation_locked(g);
         gen = g->generation.load(std::memory_order_acquire);
@@ -1374,12 +1395,14 @@ int start_device_generation(Group *g, Job *job, bool blocking, const char **err)
                            (E + 31) / 32, (uint64_t)job->generation, job->readback.host, (size_t)job->readback.host_bytes};
     }
     g->in_flight++;
+    g->launches_in_flight++;
     DeviceDone *done = new DeviceDone{g, job->signal, (uint64_t)job->generation, g_trace_sink.load(std::memory_order_relaxed) ? monotonic_ns() : 0};
     if (g->stats_x) dev::stats_exchange_before_launch(g->stats_x, dev::executor_stream(g->executor_dev), 1);
     if (!dev::executor_launch(g->executor_dev, &device_generation_done, done, ups.data(), ups.size(), downs.data(), downs.size(),
                               job->has_readback ? &rb : nullptr)) {
         // The completion entry still drains through the completion thread (without `done`); undo here.
         delete done;
+        g->launches_in_flight--;
         if (--g->in_flight == 0) unlock_group_resources(g);
         *err = "DeviceError";
         return -1;
@@ -1387,6 +1410,48 @@ int start_device_generation(Group *g, Job *job, bool blocking, const char **err)
     if (g->stats_x) dev::stats_exchange_after_launch(g->stats_x, dev::executor_stream(g->executor_dev), 1);
     if (g->post_step) g->post_step(g->post_step_user, dev::executor_stream(g->executor_dev), (uint64_t)job->generation);
     return 0;
+}
+
+// A generation that may share a launch with its neighbours: nothing but the generation itself.
+bool batchable(const Group *g, const Job *job) {
+    return !job->xfer_resource && job->io_up.empty() && job->io_down.empty() && !job->has_readback && job->wait_on.empty() && !g->post_step;
+}
+
+// g->m held, resources locked (in_flight > 0).  Launches everything in batch_pending, up to max_gens generations per
+// launch.  Called from the completion thread when a launch retires and from `schedule` when something that must
+// stay behind the pending generations arrives.
+void launch_pending_batches(Group *g) {
+    if (g->dirty || g->compiled_epoch != g->world->resource_epoch.load(std::memory_order_acquire)) {
+        // a recompile has to drain the stream, which this thread may be needed for: hand the jobs to the dispatcher
+        while (!g->batch_pending.empty()) g->backlog.push_front(g->batch_pending.back()), g->batch_pending.pop_back();
+        if (!g->dispatcher_running) {
+            if (g->dispatcher.joinable()) g->dispatcher.join();
+            g->dispatcher_running = true, g->stop_dispatcher = false;
+            g->dispatcher = std::thread(dispatcher_main, g);
+        }
+        g->backlog_cv.notify_one();
+        return;
+    }
+    const uint32_t max_gens = dev::executor_max_gens(g->executor_dev);
+    const int64_t now = g_trace_sink.load(std::memory_order_relaxed) ? monotonic_ns() : 0;
+    while (!g->batch_pending.empty()) {
+        const uint32_t n = (uint32_t)std::min<size_t>(g->batch_pending.size(), max_gens);
+        std::vector<void *> users(n);
+        for (uint32_t i = 0; i < n; i++) {
+            Job *job = g->batch_pending[i];
+            DeviceDone *done = new DeviceDone{g, job->signal, (uint64_t)job->generation, now};
+            done->ends_launch = i + 1 == n;
+            users[i] = done;
+        }
+        g->in_flight += n;
+        g->launches_in_flight++;
+        void *stream = dev::executor_stream(g->executor_dev);
+        if (g->stats_x) dev::stats_exchange_before_launch(g->stats_x, stream, n);
+        if (!dev::executor_launch_batch(g->executor_dev, n, &device_generation_done, users.data())) panic("device generations failed to start");
+        if (g->stats_x) dev::stats_exchange_after_launch(g->stats_x, stream, n);
+        for (uint32_t i = 0; i < n; i++) delete g->batch_pending[i];
+        g->batch_pending.erase(g->batch_pending.begin(), g->batch_pending.begin() + n);
+    }
 }
 
 bool fences_signaled(const Job *job) {
@@ -1514,7 +1579,15 @@ const char *group_schedule(Group *g, FimoWorldsMeta_Fence *const *wait_on, size_
                 device = g->has_device_systems;
             }
         }
-        if (device) {
+        if (device && dev::executor_max_gens(g->executor_dev) > 1 && g->in_flight != 0 &&
+            g->compiled_epoch == g->world->resource_epoch.load(std::memory_order_acquire)) {
+            if (batchable(g, job) && (g->launches_in_flight >= 2 || !g->batch_pending.empty())) {
+                g->batch_pending.push_back(job); // leaves with its neighbours when a launch retires
+                return nullptr;
+            }
+            if (!g->batch_pending.empty()) launch_pending_batches(g); // this job must stay behind them
+        }
+        if (device && g->backlog.empty()) {
             const int rc = start_device_generation(g, job, false, &err);
             if (rc == 0) {
                 delete job;
@@ -1527,6 +1600,7 @@ const char *group_schedule(Group *g, FimoWorldsMeta_Fence *const *wait_on, size_
             }
         }
     }
+    while (!g->batch_pending.empty()) g->backlog.push_back(g->batch_pending.front()), g->batch_pending.pop_front(); // earlier generations first
     g->backlog.push_back(job);
     if (!g->dispatcher_running) {
         if (g->dispatcher.joinable()) g->dispatcher.join();
@@ -1619,7 +1693,7 @@ bool builtin_create(const void *factory, FimoWorldsMeta_SystemContext *context, 
     state->stats_peers = nullptr;
     if (state->device < 0) return false; // built-in systems exist on the device only
     if (m->type->builtin_id == FIMO_B200_BUILTIN_CULL || m->type->builtin_id == FIMO_B200_BUILTIN_CULL_WAABB) {
-        state->scratch = dev::hbm_alloc(state->device, 64);
+        state->scratch = dev::hbm_alloc(state->device, dev::kBuiltinScratchBytes);
         if (!state->scratch) return false;
     }
     return true;
@@ -2010,6 +2084,12 @@ FimoUSize fimo_b200_group_executor_describe(FimoWorldsMeta_SystemGroup *group, c
         buffer[n] = 0;
     }
     return g->plan_text.size();
+}
+
+uint64_t fimo_b200_group_kernels_launched(FimoWorldsMeta_SystemGroup *group) {
+    Group *g = (Group *)group;
+    std::lock_guard<std::mutex> lock(g->m);
+    return g->executor_dev ? dev::executor_kernels_launched(g->executor_dev) : 0;
 }
 
 void *fimo_b200_group_stream(FimoWorldsMeta_SystemGroup *group) {

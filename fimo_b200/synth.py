@@ -469,6 +469,9 @@ class WorldStepRig:
         self.lib.fimo_b200_group_executor_describe(self.group.handle, buf, 512)
         return buf.value.decode()
 
+    def kernels_launched(self) -> int:
+        return int(self.lib.fimo_b200_group_kernels_launched(self.group.handle))
+
     def device_ms(self) -> tuple[float, int]:
         n = C.c_uint64(0)
         ms = self.lib.fimo_b200_group_device_ms(self.group.handle, C.byref(n))

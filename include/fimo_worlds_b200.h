@@ -850,7 +850,11 @@ typedef struct FimoB200_ExecutorInfo {
     uint32_t kernel_launches_per_generation;
     uint64_t edges;                      /* dependency edges between nodes */
     uint64_t algorithmic_bytes_per_step; /* live-in read once + live-out written once, 0 if unknown */
-    uint64_t reserved[4];
+    /* > 1: the executor is ONE fused world-step node able to step several generations per launch; plain generations
+     * scheduled while two launches are already on the stream then leave together, up to this many per launch
+     * (FIMO_B200_GENS caps it).  Results, generation numbers and fences are unchanged; only launch boundaries go. */
+    uint64_t max_generations_per_launch;
+    uint64_t reserved[3];
 } FimoB200_ExecutorInfo;
 FIMO_B200_EXPORT FimoStatus fimo_b200_group_executor_info(FimoWorldsMeta_SystemGroup *group,
                                                           FimoB200_ExecutorInfo *info);
@@ -859,6 +863,9 @@ FIMO_B200_EXPORT FimoStatus fimo_b200_group_executor_info(FimoWorldsMeta_SystemG
  * fimo_b200_group_executor_info first (it compiles a dirty group).  Returns the length of the full text; at most
  * buffer_len - 1 characters + NUL are written. */
 FIMO_B200_EXPORT FimoUSize fimo_b200_group_executor_describe(FimoWorldsMeta_SystemGroup *group, char *buffer, FimoUSize buffer_len);
+
+/* Kernel launches of all generations of this group enqueued so far (copies and host nodes not counted). */
+FIMO_B200_EXPORT uint64_t fimo_b200_group_kernels_launched(FimoWorldsMeta_SystemGroup *group);
 
 /* The CUDA stream (cudaStream_t) generations of this group are enqueued on. */
 FIMO_B200_EXPORT void *fimo_b200_group_stream(FimoWorldsMeta_SystemGroup *group);

@@ -233,6 +233,64 @@ def test_baseline_configs_at_full_size_match_oracle(oracle, product, monkeypatch
     assert st[abi.STAT_VISIBLE] == counts.sum()
 
 
+QUEUED_CASES = [
+    # (dag, worlds, entities, depth, queued generations, FIMO_B200_GENS or None)
+    ("chain3", 1200, 2048, 4, 37, None),   # 3 worlds per CTA: generations queued behind two launches share launches (up to 16 each)
+    ("chain3", 600, 2048, 4, 21, "3"),     # T = 256: 3 worlds x 8 chunks per CTA; at most 3 generations per launch
+    ("dag8", 1300, 1280, 4, 19, None),     # persistent grid + tail grid of one-world CTAs (10 chunks each), both looping over generations
+    ("dag16", 700, 1024, 4, 9, None),      # prev_copy stays a node of its own: two nodes, one launch per generation
+    ("chain3", 592, 256, 4, 12, None),     # 2 chunks per CTA < ring + 2: the plan refuses multi-generation launches
+]
+
+
+@pytest.mark.parametrize("dag,W,E,D,K,gens", QUEUED_CASES)
+def test_queued_generations_share_launches_and_match_oracle(oracle, product, monkeypatch, dag, W, E, D, K, gens):
+    """K generations scheduled back to back without waiting: once two launches are on the stream the following plain
+    generations leave together in ONE launch (the ring runs across generation boundaries, every generation publishes
+    its own statistics).  Same bit-exact bar after K generations; every generation's statistics land in the ring; the
+    generation counter advances by one per schedule and the last fence fires after all of them."""
+    import torch
+
+    monkeypatch.setenv("FIMO_B200_TEAM", "1")
+    if gens:
+        monkeypatch.setenv("FIMO_B200_GENS", gens)
+    data = synth.generate(W, E, D, dag=dag)
+    ref = synth.WorldStepRig(oracle, W, E, D, data={k: v.copy() for k, v in data.items()}, dag=dag)
+    per_step = []
+    try:
+        for _ in range(K):
+            ref.step(1)
+            per_step.append(ref.stats().copy())
+        want = ref.download()
+    finally:
+        ref.close()
+    ring = torch.zeros((K, abi.STAT_WORDS), dtype=torch.int64, device="cuda")
+    opts = synth.RigOptions(stats_ring=ring.data_ptr(), stats_ring_slots=K)
+    rig = synth.WorldStepRig(product, W, E, D, data={k: v.copy() for k, v in data.items()}, options=opts, dag=dag)
+    try:
+        info = rig.executor_info()
+        before = rig.kernels_launched()
+        rig.schedule(K)
+        rig.wait()
+        launched = rig.kernels_launched() - before
+        got = rig.download()
+        snapshots = ring.cpu().numpy().astype(np.uint64)
+    finally:
+        rig.close()
+    expect_multi = dag != "dag16" and E * 1 >= 5 * 128 and W >= 592
+    assert (info.max_generations_per_launch > 1) == expect_multi, info.max_generations_per_launch
+    if gens:
+        assert info.max_generations_per_launch == int(gens)
+    if expect_multi:
+        assert launched < info.kernel_launches_per_generation * K, (launched, K)  # some generations shared a launch
+    else:
+        assert launched == info.kernel_launches_per_generation * K
+    problems = synth.compare_outputs(got, want, FLOAT_RTOL)
+    assert not problems, "\n".join(problems)
+    for g in range(K):
+        assert np.array_equal(snapshots[g][:5], per_step[g][:5]), (g, snapshots[g], per_step[g])
+
+
 def test_generations_pipeline_and_fences(product):
     """schedule is asynchronous; K queued generations run in order; the signal fence fires after the last."""
     rig = synth.WorldStepRig(product, 32, 256, 4)
