@@ -172,6 +172,7 @@ struct WorldStepPlan {
     uint32_t teams = 0;         // worlds in flight = grid / team
     uint32_t kernels = 1;       // launches per generation (team mode adds the list-compaction kernel, a tail grid one launch)
     uint32_t max_gens = 1;      // generations ONE launch may step (> 1: one-CTA-per-world plans with enough chunks per CTA)
+    uint32_t block_worlds = 0x40000000u; // worlds a CTA steps through all generations of a launch before it moves on (PipeArgs)
     // One CTA per world: the persistent grid steps worlds [0, tail_first) in whole rounds, a second grid launched
     // beside it steps [tail_first, n_worlds) one world per CTA as slots free up (tail_first == n_worlds: no tail).
     uint32_t grid = 0, tail_first = 0;

@@ -185,23 +185,14 @@ struct StatsSink { // where one cull's batch statistics go (the DAGs have up to 
     uint32_t ring_slots = 0;
     const PeerTable *peers = nullptr;   // fimo_b200_group_stats_peers_bind
 };
-// Accumulator blocks in `scratch`, one per generation a launch steps (a multi-generation launch lets CTAs drift apart
-// by whole generations, so each generation gets its own sums and its own ticket): slot s at scratch[8 s ..]:
-// [0] visible, [1] mask sum, [2] worlds, [4] ticket.  Behind them scratch[kStatGlobals + 0] counts the generations
-// published since the system was created (ring / inbox slot index) and [kStatGlobals + 1] the generations published
-// within the running launch (finalisers run in generation order).
+// Accumulator blocks in `scratch`, one per generation a launch steps (a CTA of a multi-generation launch is in any
+// generation at any time, so each generation gets its own sums): slot s at scratch[8 s ..]: [0] visible, [1] mask
+// sum, [2] worlds; scratch[4] (slot 0's spare word) is the launch's completion ticket.  Behind them
+// scratch[kStatGlobals] counts the generations published since the system was created (ring / inbox row index).
 constexpr int kStatSlots = 16;
 constexpr int kStatGlobals = kStatSlots * 8;
 constexpr size_t kStatScratchBytes = (kStatGlobals + 8) * 8;
 static_assert(kStatScratchBytes <= kBuiltinScratchBytes, "built-in scratch block too small");
-__device__ __forceinline__ unsigned long long ld_acquire_gpu_u64(const unsigned long long *p) {
-    unsigned long long v;
-    asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
-    return v;
-}
-__device__ __forceinline__ void st_release_gpu_u64(unsigned long long *p, unsigned long long v) {
-    asm volatile("st.release.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
-}
 // The three steps of publishing: every CTA adds its sums (fire-and-forget reductions), draws a ticket behind a fence,
 // and the CTA that drew the last one turns the accumulators into the published words and re-arms them.
 __device__ __forceinline__ void stats_contribute(const StatsSink &a, uint32_t slot, unsigned long long visible, unsigned long long mask_sum,
@@ -217,8 +208,20 @@ __device__ __forceinline__ bool stats_last_ticket(const StatsSink &a, uint32_t s
     __threadfence();
     return true;
 }
-// `ordered`: this sink carries the launch's publication order (the first sink of a pair); generation `slot` of the
-// launch is published only after generation slot - 1 has been (their finalisers may be different CTAs).
+// The words of generation `gen` into every rank's inbox (our own included), tagged with the generation.
+__device__ __forceinline__ void stats_store_peers(const StatsSink &a, const uint4 &peers /* nranks, rank, slots */, unsigned long long gen,
+                                                  const unsigned long long (&words)[5], const unsigned long long (&rest)[FIMO_B200_STAT_WORDS - 5]) {
+    const unsigned long long tag = ((gen + 1) & 0xFFFFFFFFull) << 32;
+    const unsigned long long at = ((gen % peers.z) * kStatsMaxRanks + peers.y) * 16ull;
+    for (uint32_t r = 0; r < peers.x; r++) {
+        unsigned long long *dst = a.peers->inbox[r] + at;
+        for (int i = 0; i < FIMO_B200_STAT_WORDS; i++) {
+            const unsigned long long w = i < 5 ? words[i] : rest[i - 5];
+            st_relaxed_sys(dst + 2 * i, tag | (w & 0xFFFFFFFFull));
+            st_relaxed_sys(dst + 2 * i + 1, tag | (w >> 32));
+        }
+    }
+}
 template <bool kGroupStats>
 __device__ __forceinline__ void stats_finalize(const StatsSink &a, uint32_t slot) {
     // This runs on the kernel's critical path (the last CTA, after everyone else has left): the loads that do not
@@ -248,18 +251,7 @@ __device__ __forceinline__ void stats_finalize(const StatsSink &a, uint32_t slot
         for (int i = 0; i < 5; i++) row[i] = words[i];
         for (int i = 5; i < FIMO_B200_STAT_WORDS; i++) row[i] = rest[i - 5];
     }
-    if (a.peers) { // the same words into every rank's inbox (our own included), tagged with the generation
-        const unsigned long long tag = ((gen + 1) & 0xFFFFFFFFull) << 32;
-        const unsigned long long at = ((gen % peers.z) * kStatsMaxRanks + peers.y) * 16ull;
-        for (uint32_t r = 0; r < peers.x; r++) {
-            unsigned long long *dst = a.peers->inbox[r] + at;
-            for (int i = 0; i < FIMO_B200_STAT_WORDS; i++) {
-                const unsigned long long w = i < 5 ? words[i] : rest[i - 5];
-                st_relaxed_sys(dst + 2 * i, tag | (w & 0xFFFFFFFFull));
-                st_relaxed_sys(dst + 2 * i + 1, tag | (w >> 32));
-            }
-        }
-    }
+    if (a.peers) stats_store_peers(a, peers, gen, words, rest);
     if (kGroupStats) {
         uint32_t *g = a.gstats;
         for (int i = 0; i < FIMO_B200_GSTAT_WORDS; i++) g[i] = 0u;
@@ -271,45 +263,100 @@ __device__ __forceinline__ void stats_finalize(const StatsSink &a, uint32_t slot
         }
     }
 }
-// Generations of one launch are published in order: the finaliser of generation `slot` waits for slot - 1's.
-__device__ __forceinline__ void stats_order_enter(const StatsSink &a, uint32_t slot) {
-    if (slot == 0) return;
-    while (ld_acquire_gpu_u64(a.scratch + kStatGlobals + 1) != slot) __nanosleep(100);
-}
-__device__ __forceinline__ void stats_order_leave(const StatsSink &a, uint32_t slot, bool last_of_launch) {
-    atomicExch(&a.scratch[slot * 8 + 4], 0ull); // re-arm the ticket
-    if (slot == 0 && last_of_launch) return;    // single-generation launch: nothing to order
-    st_release_gpu_u64(a.scratch + kStatGlobals + 1, last_of_launch ? 0ull : (unsigned long long)slot + 1ull);
-}
 template <bool kGroupStats>
 __device__ __forceinline__ bool publish_stats_to(const StatsSink &a, unsigned long long visible, unsigned long long mask_sum,
-                                                 unsigned long long worlds, unsigned long long n_ctas, uint32_t slot = 0, bool last_of_launch = true) {
-    stats_contribute(a, slot, visible, mask_sum, worlds);
-    if (!stats_last_ticket(a, slot, n_ctas)) return false;
-    stats_order_enter(a, slot);
-    stats_finalize<kGroupStats>(a, slot);
-    stats_order_leave(a, slot, last_of_launch);
+                                                 unsigned long long worlds, unsigned long long n_ctas) {
+    stats_contribute(a, 0, visible, mask_sum, worlds);
+    if (!stats_last_ticket(a, 0, n_ctas)) return false;
+    stats_finalize<kGroupStats>(a, 0);
+    atomicExch(&a.scratch[4], 0ull); // re-arm the ticket
     return true;
 }
-// Two culls published by one kernel (the 16-system set): one fence and one ticket (the first sink's) for both.
+// A launch that stepped `gens` generations (world_step.cu): ONE warp publishes them all.  Lane g adds the CTA's sums of
+// generation g to that generation's accumulators; one fence and ONE ticket per CTA and launch; the warp of the CTA
+// that drew the last ticket turns every generation's accumulators into its published words — `stats` (and the group
+// statistics) end up holding the last generation's, every generation gets its own row in the snapshot ring and in the
+// peers' inboxes, the step counter advances by every generation's worlds.  kPair: two culls (the 16-system set) share
+// the fence and the ticket (the first sink's).
 template <bool kGroupStats>
-__device__ __forceinline__ bool publish_stats_pair(const StatsSink &a, const StatsSink &b, unsigned long long visible_a,
-                                                   unsigned long long mask_sum_a, unsigned long long visible_b, unsigned long long mask_sum_b,
-                                                   unsigned long long worlds, unsigned long long n_ctas, uint32_t slot = 0, bool last_of_launch = true) {
-    stats_contribute(a, slot, visible_a, mask_sum_a, worlds);
-    stats_contribute(b, slot, visible_b, mask_sum_b, worlds);
-    if (!stats_last_ticket(a, slot, n_ctas)) return false;
-    stats_order_enter(a, slot);
-    stats_finalize<kGroupStats>(a, slot);
-    stats_finalize<kGroupStats>(b, slot);
-    stats_order_leave(a, slot, last_of_launch);
+__device__ __forceinline__ void stats_finalize_launch(const StatsSink &a, uint32_t gens, int lane) {
+    const bool mine = (uint32_t)lane < gens;
+    const unsigned long long steps_before = a.stats[FIMO_B200_STAT_STEPS];
+    unsigned long long gen0 = 0, rest[FIMO_B200_STAT_WORDS - 5] = {};
+    uint4 peers = make_uint4(0u, 0u, 1u, 0u);
+    if (a.peers) peers = *(const uint4 *)a.peers;
+    if (a.ring || a.peers) {
+        gen0 = a.scratch[kStatGlobals];
+        for (int i = 5; i < FIMO_B200_STAT_WORDS; i++) rest[i - 5] = a.stats[i];
+    }
+    const unsigned long long v = mine ? atomicExch(&a.scratch[lane * 8 + 0], 0ull) : 0ull;
+    const unsigned long long m = mine ? atomicExch(&a.scratch[lane * 8 + 1], 0ull) : 0ull;
+    const unsigned long long n = mine ? atomicExch(&a.scratch[lane * 8 + 2], 0ull) : 0ull;
+    unsigned long long steps = n; // inclusive prefix over the generations: the step counter after generation `lane`
+#pragma unroll
+    for (int d = 1; d < kStatSlots; d <<= 1) {
+        const unsigned long long up = __shfl_up_sync(kFull, steps, d);
+        if (lane >= d) steps += up;
+    }
+    unsigned long long words[5];
+    words[FIMO_B200_STAT_VISIBLE] = v;
+    words[FIMO_B200_STAT_ENTITIES] = n * (unsigned long long)a.entities;
+    words[FIMO_B200_STAT_MASK_SUM] = m;
+    words[FIMO_B200_STAT_WORLDS] = n;
+    words[FIMO_B200_STAT_STEPS] = steps_before + steps;
+    const bool last = (uint32_t)lane + 1 == gens;
+    if (last) {
+        for (int i = 0; i < 5; i++) a.stats[i] = words[i];
+        if (a.ring || a.peers) a.scratch[kStatGlobals] = gen0 + gens;
+    }
+    // a ring / inbox with fewer rows than the launch has generations keeps the latest ones
+    if (mine && a.ring && (uint32_t)lane + a.ring_slots >= gens) {
+        unsigned long long *row = a.ring + ((gen0 + lane) % a.ring_slots) * FIMO_B200_STAT_WORDS;
+        for (int i = 0; i < 5; i++) row[i] = words[i];
+        for (int i = 5; i < FIMO_B200_STAT_WORDS; i++) row[i] = rest[i - 5];
+    }
+    if (mine && a.peers && (uint32_t)lane + peers.z >= gens) stats_store_peers(a, peers, gen0 + lane, words, rest);
+    if (kGroupStats && mine) {
+        int keys[6];
+        for (int i = 0; i < 6; i++) {
+            const int empty = i < 3 ? float_key(FIMO_B200_BOUNDS_EMPTY_MIN) : float_key(-FIMO_B200_BOUNDS_EMPTY_MIN);
+            keys[i] = atomicExch(a.bounds_keys + lane * 6 + i, empty); // every generation's accumulators are re-armed
+        }
+        if (last) {
+            uint32_t *g = a.gstats;
+            for (int i = 0; i < FIMO_B200_GSTAT_WORDS; i++) g[i] = 0u;
+            g[FIMO_B200_GSTAT_VISIBLE_LO] = (uint32_t)(v & 0xFFFFFFFFull), g[FIMO_B200_GSTAT_VISIBLE_LO + 1] = (uint32_t)(v >> 32);
+            g[FIMO_B200_GSTAT_WORLDS_LO] = (uint32_t)(n & 0xFFFFFFFFull), g[FIMO_B200_GSTAT_WORLDS_LO + 1] = (uint32_t)(n >> 32);
+            for (int i = 0; i < 6; i++) g[FIMO_B200_GSTAT_BOUNDS + i] = __float_as_uint(key_float(keys[i]));
+        }
+    }
+}
+template <bool kGroupStats, bool kPair>
+__device__ __forceinline__ bool publish_stats_launch(const StatsSink &a, const StatsSink &b, const unsigned long long *vis_a, const unsigned long long *mask_a,
+                                                     const unsigned long long *vis_b, const unsigned long long *mask_b, uint32_t gens,
+                                                     unsigned long long worlds, unsigned long long n_ctas, int lane) {
+    if ((uint32_t)lane < gens) {
+        stats_contribute(a, lane, vis_a[lane], mask_a[lane], worlds);
+        if (kPair) stats_contribute(b, lane, vis_b[lane], mask_b[lane], worlds);
+    }
+    __threadfence();
+    __syncwarp();
+    unsigned long long ticket = 0;
+    if (lane == 0) ticket = atomicAdd(&a.scratch[4], 1ull);
+    ticket = __shfl_sync(kFull, ticket, 0);
+    if (ticket != n_ctas - 1) return false;
+    __threadfence();
+    stats_finalize_launch<kGroupStats>(a, gens, lane);
+    if (kPair) stats_finalize_launch<kGroupStats>(b, gens, lane);
+    __syncwarp();
+    if (lane == 0) atomicExch(&a.scratch[4], 0ull); // re-arm the ticket
     return true;
 }
 template <bool kGroupStats = false>
 __device__ __forceinline__ bool publish_stats(const StepArgs &a, unsigned long long visible, unsigned long long mask_sum,
-                                              unsigned long long worlds, unsigned long long n_ctas, uint32_t slot = 0, bool last_of_launch = true) {
+                                              unsigned long long worlds, unsigned long long n_ctas) {
     return publish_stats_to<kGroupStats>(StatsSink{a.stats, a.scratch, a.gstats, a.bounds_keys, a.entities, a.ring, a.ring_slots, a.peers}, visible,
-                                         mask_sum, worlds, n_ctas, slot, last_of_launch);
+                                         mask_sum, worlds, n_ctas);
 }
 __device__ __forceinline__ bool publish_stats(const StepArgs &a, unsigned long long visible, unsigned long long mask_sum,
                                               unsigned long long worlds) {

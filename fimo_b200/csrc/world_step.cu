@@ -118,11 +118,16 @@ struct PipeArgs {
     uint32_t stages;   // ring depth (chunks)
     uint32_t lvl_cap;  // parent matrices kept in shared memory: entities [0, lvl_cap) of a world
     uint32_t chunks;   // chunks per world = ceil(E / T)
-    // Generations this launch steps (1..kStatSlots).  A world belongs to one CTA, so generation g + 1 of a CTA's worlds
-    // needs nothing but that CTA's own generation g: the ring simply runs on across generation boundaries (behind a
-    // bulk-group wait that orders a chunk's loads after the stores of its previous generation) and every generation
-    // publishes its own statistics.  One-CTA-per-world plans only.
+    // Generations this launch steps (1..kStatSlots).  A world belongs to one CTA, so generation g + 1 of a world needs
+    // nothing but that CTA's own generation g of it.  A CTA therefore walks its worlds in BLOCKS of `block_worlds`
+    // consecutive worlds and steps a block through ALL generations before it moves on (block, generation, world,
+    // chunk): the block's state — written by generation g, read back by generation g + 1 a few microseconds later —
+    // stays in L2, so HBM sees a world's inputs once and its final outputs once per launch instead of once per
+    // generation.  The ring runs straight across world, generation and block boundaries; a chunk's loads are ordered
+    // behind the stores of its previous generation by a bulk-group wait (the block holds at least stages + 2 chunks).
+    // Every generation still writes every output and accumulates its own statistics.  One-CTA-per-world plans only.
     uint32_t gens;
+    uint32_t block_worlds;
     uint32_t team;     // CTAs that step one world together (1 = a world belongs to one CTA)
     uint32_t teams;    // gridDim.x / team
     // The worlds this launch steps: [world_first, world_end).  One generation of a one-CTA-per-world plan is two
@@ -189,6 +194,33 @@ struct Walk {
     }
 };
 
+// Position of a CTA in its work: world k (of my_worlds), chunk c, generation g, inside the block of worlds [b0, b1).
+// Order: block, generation, world, chunk.  The TMA thread runs two cursors (loads, and stores `stages` behind), the
+// compute threads one; all three advance identically.
+struct Cursor {
+    uint32_t k, c, g, b0, b1;
+    __device__ __forceinline__ uint32_t block_end(const PipeArgs &pa, const Walk &wk, uint32_t from) const {
+        return wk.my_worlds - from >= 2 * pa.block_worlds ? from + pa.block_worlds : wk.my_worlds; // a short last block joins its neighbour
+    }
+    __device__ __forceinline__ Cursor(const PipeArgs &pa, const Walk &wk) : k(0), c(wk.rank), g(0), b0(0), b1(0) { b1 = block_end(pa, wk, 0); }
+    // the world visited after world k's visit ends (k itself again in the next generation if the block is one world); my_worlds: none
+    __device__ __forceinline__ uint32_t next_world(const PipeArgs &pa, const Walk &wk) const {
+        if (k + 1 < b1) return k + 1;
+        if (g + 1 < pa.gens) return b0;
+        return b1; // first world of the next block, or my_worlds
+    }
+    __device__ __forceinline__ void advance(const PipeArgs &pa, const Walk &wk) {
+        if ((c += pa.team) < pa.chunks) return;
+        c = wk.rank;
+        if (++k < b1) return;
+        if (++g < pa.gens) {
+            k = b0;
+            return;
+        }
+        g = 0, b0 = b1, b1 = block_end(pa, wk, b0);
+    }
+};
+
 // The TMA warp (one elected thread): loads chunk inputs into the ring and stores the finished chunk's
 // outputs, which the compute threads leave in the same ring stage (world matrices over planes 0-11, new
 // positions over 12-14).
@@ -196,9 +228,9 @@ template <int T, int kSet>
 __device__ __forceinline__ void tma_warp(const PipeArgs &pa, const Walk &wk, float *ring, uint64_t *full, uint64_t *done) {
     constexpr int kIn = SetTraits<kSet>::kIn, kStage = SetTraits<kSet>::kStage;
     const StepArgs &a = pa.a;
-    const uint32_t E = a.entities, N = pa.stages, nc = pa.chunks, G = pa.team, total = wk.total, all = wk.total * pa.gens;
-    uint32_t k = 0, c = wk.rank, s = 0, round = 0; // position of the chunk being loaded
-    uint32_t sk = 0, sc = wk.rank;                  // position of the chunk being stored (N behind)
+    const uint32_t E = a.entities, N = pa.stages, all = wk.total * pa.gens;
+    uint32_t s = 0, round = 0;
+    Cursor ld(pa, wk), st_(pa, wk); // the chunk being loaded; the chunk being stored (N behind)
     auto store_chunk = [&](uint32_t stage, uint32_t wk_, uint32_t wc) {
         const uint64_t w = wk.first_world + (uint64_t)wk_ * pa.teams;
         const uint32_t first = wc * T, bytes = min((uint32_t)T, E - first) * 4u;
@@ -227,21 +259,21 @@ __device__ __forceinline__ void tma_warp(const PipeArgs &pa, const Walk &wk, flo
     for (uint32_t it = 0; it < all; it++) {
         if (it >= N) { // the stage still holds chunk it-N: wait for its outputs, drain them, then reuse it
             mbar_wait(&done[s], (round - 1) & 1u);
-            store_chunk(s, sk, sc);
-            if ((sc += G) >= nc) sc = wk.rank, sk = sk + 1 == wk.my_worlds ? 0 : sk + 1;
+            store_chunk(s, st_.k, st_.c);
+            st_.advance(pa, wk);
             bulk_wait_read_all();
         }
-        // A later generation reads what the previous one stored: bulk group it - total (this chunk, one generation ago)
-        // must have completed.  Groups 0 .. it - N are committed and total >= N + 2 (world_step_max_gens), so "all but
-        // the two most recent" covers it — and those stores were issued a whole generation ago, so this never waits.
-        if (it >= total) bulk_wait_all_but_2();
-        const uint64_t w = wk.first_world + (uint64_t)k * pa.teams;
-        const uint32_t first = c * T, bytes = min((uint32_t)T, E - first) * 4u; // multiple of 16 (E % 4 == 0)
+        // A later generation reads what the previous one stored: the bulk group of this chunk one generation ago must
+        // have COMPLETED.  That group lies a whole block (>= N + 2 chunks, world_step_plan) back and groups up to
+        // it - N are committed, so "all but the two most recent" covers it.
+        if (ld.g > 0) bulk_wait_all_but_2();
+        const uint64_t w = wk.first_world + (uint64_t)ld.k * pa.teams;
+        const uint32_t first = ld.c * T, bytes = min((uint32_t)T, E - first) * 4u; // multiple of 16 (E % 4 == 0)
         float *st = ring + (size_t)s * kStage * T;
         mbar_expect_tx(&full[s], bytes * kIn);
 #pragma unroll
         for (int p = 0; p < kIn; p++) bulk_load(st + p * T, plane_src(a, p, w, E) + first, bytes, &full[s]);
-        if ((c += G) >= nc) c = wk.rank, k = k + 1 == wk.my_worlds ? 0 : k + 1;
+        ld.advance(pa, wk);
         if (++s == N) s = 0, round++;
     }
     // drain the last min(N, all) chunks
@@ -249,8 +281,8 @@ __device__ __forceinline__ void tma_warp(const PipeArgs &pa, const Walk &wk, flo
     uint32_t ds = all < N ? 0 : s, dround = all < N ? 0 : round - 1;
     for (uint32_t j = 0; j < tail; j++) {
         mbar_wait(&done[ds], dround & 1u);
-        store_chunk(ds, sk, sc);
-        if ((sc += G) >= nc) sc = wk.rank, sk = sk + 1 == wk.my_worlds ? 0 : sk + 1;
+        store_chunk(ds, st_.k, st_.c);
+        st_.advance(pa, wk);
         if (++ds == N) ds = 0, dround++;
     }
     bulk_wait_all();
@@ -305,11 +337,15 @@ __global__ void __launch_bounds__(T + 32, kMinBlocks) k_world_step_pipe(const Pi
     float4 *s_pre = (float4 *)(done + N);                         // team mode: [2][T][3] parent rows prefetched from L2
     __shared__ __align__(16) WorldConst s_c[2];
     __shared__ __align__(16) uint32_t s_cnt[2][4]; // per-warp visible counts of a chunk, one byte per warp
-    __shared__ unsigned long long s_sum;
+    // this CTA's sums per generation of the launch (one-CTA-per-world plans): visible entities (thread 0), mask words
+    // (lane 0 of every warp), batch bounds as float keys (threads 0-5); published by warp 0 when the CTA is done
+    constexpr int kGens = kTeam ? 1 : kStatSlots;
+    __shared__ unsigned long long s_gen_vis[kGens], s_gen_mask[kGens];
+    __shared__ unsigned long long s_gen_vis2[kSet == 2 ? kGens : 1], s_gen_mask2[kSet == 2 ? kGens : 1];
+    __shared__ int s_gen_bounds[kSet >= 1 ? kGens : 1][6], s_gen_vbounds[kSet == 2 ? kGens : 1][6];
     __shared__ int s_bounds[2][6]; // kSet >= 1: bounds of the current world as float keys (min xyz, max xyz), by world parity
     __shared__ int s_vbounds[2][6]; // kSet 2: the same over the entities `cull` found visible (vis_bounds)
     __shared__ __align__(16) uint32_t s_cnt2[2][4]; // kSet 2: per-warp counts of cull2
-    __shared__ unsigned long long s_sum2;
     static_assert(!(kTeam && kSet == 2), "the 16-system set is fused for one-CTA-per-world plans only");
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -320,8 +356,14 @@ __global__ void __launch_bounds__(T + 32, kMinBlocks) k_world_step_pipe(const Pi
     const int kEmptyKey = tid % 6 < 3 ? float_key(FIMO_B200_BOUNDS_EMPTY_MIN) : float_key(-FIMO_B200_BOUNDS_EMPTY_MIN);
     if (kSet >= 1 && tid < 12) s_bounds[tid / 6][tid % 6] = kEmptyKey;
     if (kSet == 2 && tid < 12) s_vbounds[tid / 6][tid % 6] = kEmptyKey;
-    int cta_bounds_key = kEmptyKey; // threads 0-5: bounds over every world this CTA stepped (kTeam = false)
-    int cta_vbounds_key = kEmptyKey;
+    if (!kTeam && tid < kGens) {
+        s_gen_vis[tid] = 0, s_gen_mask[tid] = 0;
+        if (kSet == 2) s_gen_vis2[tid] = 0, s_gen_mask2[tid] = 0;
+    }
+    if (!kTeam && kSet >= 1 && tid < kGens * 6) {
+        s_gen_bounds[tid / 6][tid % 6] = kEmptyKey;
+        if (kSet == 2) s_gen_vbounds[tid / 6][tid % 6] = kEmptyKey;
+    }
     const uint32_t levels = a.levels;
     const Walk wk(pa);
     const uint32_t my_worlds = wk.my_worlds, total = wk.total * (kTeam ? 1u : pa.gens); // chunks of every generation of the launch
@@ -331,8 +373,6 @@ __global__ void __launch_bounds__(T + 32, kMinBlocks) k_world_step_pipe(const Pi
             mbar_init(&full[s], 1);
             mbar_init(&done[s], kWarps);
         }
-        s_sum = 0;
-        s_sum2 = 0;
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncthreads();
@@ -377,13 +417,12 @@ __global__ void __launch_bounds__(T + 32, kMinBlocks) k_world_step_pipe(const Pi
     consumer_sync<T>();
 
     uint32_t next_const = 0;
-    unsigned long long cta_visible = 0, warp_mask_sum = 0; // thread 0 / lane 0 of each warp
-    unsigned long long cta_visible2 = 0, warp_mask_sum2 = 0; // kSet 2: cull2
+    unsigned long long warp_mask_sum = 0, warp_mask_sum2 = 0; // lane 0 of each warp: mask words of the current world visit (kSet 2: cull2's)
     uint32_t running = 0;                                   // visible entities of the current world so far
     uint32_t running2 = 0;
-    uint32_t k = 0, c = wk.rank, s = 0, parity = 0, l_lo = 0;
-    uint32_t kk = 0;  // worlds begun so far, over all generations of the launch: parity of the double-buffered per-world state
-    uint32_t gen = 0; // generation of the launch being stepped
+    uint32_t s = 0, parity = 0, l_lo = 0;
+    uint32_t kk = 0;  // world visits begun so far: parity of the double-buffered per-world state
+    Cursor cur(pa, wk);
     // team mode: entities of level pend_level this CTA has finished but not yet announced.  Dependants only
     // care about a level being COMPLETE, so a CTA announces its share once, when it moves past the level.
     int pend_level = -1;
@@ -396,7 +435,6 @@ __global__ void __launch_bounds__(T + 32, kMinBlocks) k_world_step_pipe(const Pi
     };
     bool pre_have = false; // team mode: this thread's parent row of the current chunk is (being) prefetched into s_pre
     int ready_upto = -1; // team mode: levels [0, ready_upto] of the current world are known to be complete
-    uint64_t w = wk.first_world;
     uint32_t *mask_out = nullptr, *list_out = nullptr;
     float4 *rows = nullptr;
     uint32_t *lvl_done = nullptr;
@@ -409,10 +447,13 @@ __global__ void __launch_bounds__(T + 32, kMinBlocks) k_world_step_pipe(const Pi
     if (kTimingBuild && pa.timing && tid == 0) asm volatile("mov.u64 %0, %globaltimer;" : "=l"(tm_wall0));
     for (uint32_t it = 0; it < total; it++) {
         const WorldConst &wc = s_c[kk & 1];
-        const bool more_worlds = k + 1 < my_worlds || (!kTeam && gen + 1 < pa.gens); // this CTA steps another world after this one
-        if (c == wk.rank) { // a new world begins
+        const uint32_t k = cur.k, c = cur.c, gen = cur.g;
+        const uint64_t w = wk.first_world + (uint64_t)k * pa.teams;
+        const uint32_t next_k = cur.next_world(pa, wk);
+        const bool more_worlds = next_k < my_worlds; // this CTA visits another world (or this one again, a generation on) afterwards
+        if (c == wk.rank) { // a world visit begins
             if (kTeam && it != 0) consumer_sync<T>(); // its constants were published during the previous world
-            if (more_worlds) next_const = const_word(k + 1 < my_worlds ? w + pa.teams : (uint64_t)wk.first_world);
+            if (more_worlds) next_const = const_word(wk.first_world + (uint64_t)next_k * pa.teams);
             running = 0, running2 = 0, l_lo = 0, ready_upto = -1;
             mask_out = uptr(a.vis_mask, w);
             list_out = uptr(a.vis_list, w);
@@ -667,52 +708,28 @@ __global__ void __launch_bounds__(T + 32, kMinBlocks) k_world_step_pipe(const Pi
         if (world_ends) {
             if (!kTeam && tid == 0) {
                 uptr(a.vis_count, w)[0] = running;
-                cta_visible += running;
-                if (kSet == 2) uptr(a.vis_count2, w)[0] = running2, cta_visible2 += running2;
+                s_gen_vis[gen] += running;
+                if (kSet == 2) uptr(a.vis_count2, w)[0] = running2, s_gen_vis2[gen] += running2;
+            }
+            if (!kTeam && lane == 0) { // mask words of this world visit join its generation's sum
+                atomicAdd(&s_gen_mask[gen], warp_mask_sum), warp_mask_sum = 0;
+                if (kSet == 2) atomicAdd(&s_gen_mask2[gen], warp_mask_sum2), warp_mask_sum2 = 0;
             }
             if (kSet >= 1 && !kTeam && tid < 6) { // after this chunk's barrier: every warp's keys are in
                 const int key = s_bounds[kk & 1][tid];
                 fptr(a.wbounds, w)[tid] = key_float(key);
-                cta_bounds_key = tid < 3 ? min(cta_bounds_key, key) : max(cta_bounds_key, key);
+                s_gen_bounds[gen][tid] = tid < 3 ? min(s_gen_bounds[gen][tid], key) : max(s_gen_bounds[gen][tid], key);
                 s_bounds[kk & 1][tid] = kEmptyKey;
                 if (kSet == 2) {
                     const int vkey = s_vbounds[kk & 1][tid];
                     fptr(a.vbounds, w)[tid] = key_float(vkey);
-                    cta_vbounds_key = tid < 3 ? min(cta_vbounds_key, vkey) : max(cta_vbounds_key, vkey);
+                    s_gen_vbounds[gen][tid] = tid < 3 ? min(s_gen_vbounds[gen][tid], vkey) : max(s_gen_vbounds[gen][tid], vkey);
                     s_vbounds[kk & 1][tid] = kEmptyKey;
                 }
             }
-            c = wk.rank, k++, kk++, w += pa.teams;
-            if (!kTeam && k == my_worlds) { // this CTA's share of generation `gen` is done: publish it, go round again
-                if (lane == 0) atomicAdd(&s_sum, warp_mask_sum), warp_mask_sum = 0;
-                if (kSet == 2 && lane == 0) atomicAdd(&s_sum2, warp_mask_sum2), warp_mask_sum2 = 0;
-                if (kSet >= 1 && tid < 6) {
-                    if (tid < 3) atomicMin(a.bounds_keys + gen * 6 + tid, cta_bounds_key);
-                    else atomicMax(a.bounds_keys + gen * 6 + tid, cta_bounds_key);
-                    cta_bounds_key = kEmptyKey;
-                    if (kSet == 2) {
-                        if (tid < 3) atomicMin(a.bounds_keys2 + gen * 6 + tid, cta_vbounds_key);
-                        else atomicMax(a.bounds_keys2 + gen * 6 + tid, cta_vbounds_key);
-                        cta_vbounds_key = kEmptyKey;
-                    }
-                }
-                consumer_sync<T>();
-                if (tid == 0) { // the other warps go on with the next generation's first chunk meanwhile
-                    const unsigned long long sum = s_sum, sum2 = s_sum2;
-                    s_sum = 0, s_sum2 = 0; // next added to after the next chunk's barrier at the earliest
-                    const bool last_gen = gen + 1 == pa.gens;
-                    if (kSet == 2)
-                        publish_stats_pair<true>(StatsSink{a.stats, a.scratch, a.gstats, a.bounds_keys, a.entities, a.ring, a.ring_slots, a.peers},
-                                                 StatsSink{a.stats2, a.scratch2, a.gstats2, a.bounds_keys2, a.entities}, cta_visible, sum,
-                                                 cta_visible2, sum2, my_worlds, (unsigned long long)pa.stat_ctas, gen, last_gen);
-                    else publish_stats<kSet >= 1>(a, cta_visible, sum, my_worlds, (unsigned long long)pa.stat_ctas, gen, last_gen);
-                    cta_visible = 0, cta_visible2 = 0;
-                }
-                k = 0, w = wk.first_world, gen++;
-            }
-        } else {
-            c += G;
+            kk++;
         }
+        cur.advance(pa, wk);
         if (++s == N) s = 0, parity ^= 1u;
         pre_have = pre_next;
     }
@@ -735,13 +752,25 @@ __global__ void __launch_bounds__(T + 32, kMinBlocks) k_world_step_pipe(const Pi
             row[0] = smid, row[1] = tm_wall0, row[2] = wall1, row[3] = (unsigned long long)total, row[4] = tm_entry;
         }
     }
-    if (!kTeam && my_worlds == 0 && tid == 0) { // a CTA without worlds still draws its ticket in every generation
-        for (uint32_t g = 0; g < pa.gens; g++) {
+    if (!kTeam) { // publish every generation of the launch: batch bounds first, then warp 0 with one ticket for all of them
+        consumer_sync<T>(); // the per-generation sums in shared memory are complete
+        if (kSet >= 1 && tid < 6 && my_worlds) {
+            for (uint32_t g = 0; g < pa.gens; g++) {
+                if (tid < 3) atomicMin(a.bounds_keys + g * 6 + tid, s_gen_bounds[g][tid]);
+                else atomicMax(a.bounds_keys + g * 6 + tid, s_gen_bounds[g][tid]);
+                if (kSet == 2) {
+                    if (tid < 3) atomicMin(a.bounds_keys2 + g * 6 + tid, s_gen_vbounds[g][tid]);
+                    else atomicMax(a.bounds_keys2 + g * 6 + tid, s_gen_vbounds[g][tid]);
+                }
+            }
+        }
+        if (warp == 0) {
+            const StatsSink sink{a.stats, a.scratch, a.gstats, a.bounds_keys, a.entities, a.ring, a.ring_slots, a.peers};
             if (kSet == 2)
-                publish_stats_pair<true>(StatsSink{a.stats, a.scratch, a.gstats, a.bounds_keys, a.entities, a.ring, a.ring_slots, a.peers},
-                                         StatsSink{a.stats2, a.scratch2, a.gstats2, a.bounds_keys2, a.entities}, 0, 0, 0, 0, 0,
-                                         (unsigned long long)pa.stat_ctas, g, g + 1 == pa.gens);
-            else publish_stats<kSet >= 1>(a, 0, 0, 0, (unsigned long long)pa.stat_ctas, g, g + 1 == pa.gens);
+                publish_stats_launch<true, true>(sink, StatsSink{a.stats2, a.scratch2, a.gstats2, a.bounds_keys2, a.entities}, s_gen_vis, s_gen_mask,
+                                                 s_gen_vis2, s_gen_mask2, pa.gens, my_worlds, (unsigned long long)pa.stat_ctas, lane);
+            else publish_stats_launch<kSet >= 1, false>(sink, sink, s_gen_vis, s_gen_mask, s_gen_vis, s_gen_mask, pa.gens, my_worlds,
+                                                        (unsigned long long)pa.stat_ctas, lane);
         }
     }
     if (kTimingBuild && !kTeam && pa.timing && tid == 0 && pa.trace_base + blockIdx.x < kTimingCtas) { // statistics published: thread 0 leaves
@@ -837,7 +866,7 @@ struct TailLaunch {
 
 constexpr size_t kSmemPerSm = 227 * 1024;  // usable by CTAs on sm_100a
 constexpr size_t kSmemPerCtaReserve = 1024; // the hardware reserves 1 KB per resident CTA
-constexpr size_t static_smem(uint32_t set) { return set == 2 ? 1024 : 896; } // WorldConst x2, counts, sums, bounds keys (see -Xptxas -v)
+constexpr size_t static_smem(uint32_t set) { return set == 2 ? 2304 : set == 1 ? 1536 : 1152; } // WorldConst x2, counts, per-generation sums and bounds keys (see -Xptxas -v)
 
 size_t ring_bytes(uint32_t set, int T, uint32_t stages) {
     return (size_t)stages * (set == 2 ? SetTraits<2>::kStage : set == 1 ? SetTraits<1>::kStage : SetTraits<0>::kStage) * T * 4;
@@ -1029,10 +1058,16 @@ bool world_step_plan(const WorldStepViews &v, int device, WorldStepPlan &plan) {
     // Multi-generation launches (PipeArgs::gens): every CTA — the tail grid's one-world CTAs included — must have at
     // least stages + 2 chunks per generation, so that a chunk's previous-generation stores are covered by the TMA
     // thread's "all but the two most recent bulk groups" wait.
-    plan.max_gens = 1;
+    plan.max_gens = 1, plan.block_worlds = 0x40000000u; // one block: plain world order
     if (plan.team == 1 && plan.grid) {
         const uint64_t persist = plan.tail_first, min_worlds = plan.tail_first < W ? 1 : persist / plan.grid;
-        if (min_worlds >= 1 && min_worlds * chunks >= (uint64_t)plan.stages + 2) plan.max_gens = kStatSlots;
+        const uint64_t block = ((uint64_t)plan.stages + 2 + chunks - 1) / chunks; // fewest worlds that hold stages + 2 chunks
+        if (min_worlds >= block) plan.max_gens = kStatSlots, plan.block_worlds = (uint32_t)block;
+        // FIMO_B200_BLOCK=n: at least n worlds per block (A/B runs; 0 = all of a CTA's worlds, i.e. generation-major order)
+        if (const char *env = std::getenv("FIMO_B200_BLOCK")) {
+            const uint64_t want = std::strtoull(env, nullptr, 10);
+            plan.block_worlds = want == 0 ? 0x40000000u : (uint32_t)std::min<uint64_t>(std::max<uint64_t>(want, block), 0x40000000u);
+        }
     }
     if (const char *env = std::getenv("FIMO_B200_GENS")) plan.max_gens = std::min<uint32_t>(plan.max_gens, (uint32_t)std::max(1, std::atoi(env)));
     plan.rows = hbm_shared(device, (size_t)W * E * 48);
@@ -1124,6 +1159,7 @@ FimoStatus world_step_launch(const WorldStepViews &v, const WorldStepPlan &plan,
         a.dt = plane_of(v.dt, FIMO_B200_SCOPE_WORLD, 1, 1, W, "dt");
         pa.stages = plan.stages;
         pa.gens = gens;
+        pa.block_worlds = plan.block_worlds;
         pa.lvl_cap = plan.lvl_cap;
         pa.chunks = (uint32_t)((E + plan.threads - 1) / plan.threads);
         pa.rows = (float4 *)plan.rows.get();
