@@ -155,6 +155,7 @@ struct WorldStepViews {
     const FimoB200_ResourceView *damp = nullptr, *sleep_eps = nullptr, *campos = nullptr, *lod_dist2 = nullptr, *frustum2 = nullptr,
                                 *sleep = nullptr, *lod = nullptr, *vis_mask2 = nullptr, *vis_list2 = nullptr, *vis_count2 = nullptr,
                                 *stats2 = nullptr, *vbounds = nullptr, *gstats2 = nullptr;
+    const FimoB200_ResourceView *prev_world = nullptr; // set 2, optional: prev_copy (X: prev_world, S: world) is a member too
     void *scratch2 = nullptr; // cull2's statistics accumulator block (its BuiltinState)
     void *stats_ring = nullptr; // FimoB200_GroupDeviceExt::stats_ring (per-generation snapshots of `stats`)
     uint32_t stats_ring_slots = 0;

@@ -135,7 +135,7 @@ struct StepArgs {
     int *bounds_keys;     // [kStatSlots][6] batch bounds as float_key accumulators (one set per generation of a launch), then [n_worlds][6] per-world ones (team mode)
     // the fused 16-system DAG (kSet = 2) additionally uses:
     Plane damp, sleep_eps, campos, lod_dist2, frustum2;     // per-world constants
-    Plane sleep, lod, vis_mask2, vis_list2, vis_count2, vbounds;
+    Plane sleep, lod, vis_mask2, vis_list2, vis_count2, vbounds, prev_world;
     unsigned long long *stats2, *scratch2; // cull2's statistics and its accumulator block
     uint32_t *gstats2;                     // group_stats2
     int *bounds_keys2;                     // [kStatSlots][6] batch bounds of the visible entities (float keys)

@@ -46,8 +46,10 @@ template <> struct SetTraits<1> {
 // kSet 2: set 1 with vel_clamp plus six more systems of the 16-system DAG that only touch data the kernel already
 // holds: angvel_damp (angvel *= damp, written back: planes 22-24), sleep_flags (bit per entity from the clamped
 // velocity), lod (u32 per entity from the world AABB centre), cull2 (second frustum: mask2 / list2 / count2 /
-// stats2), vis_bounds (bounds over the VISIBLE entities of cull) and group_stats2.  prev_copy stays a separate
-// node in front of the kernel (it reads the world matrices this kernel overwrites).
+// stats2), vis_bounds (bounds over the VISIBLE entities of cull) and group_stats2 — and, as a runtime option
+// (kPipePrevCopy), prev_copy: every thread copies its entity's OLD world matrix (12 coalesced plane loads through L2,
+// 12 plane stores) before the chunk's new matrices leave the stage, i.e. before the R/W conflict the reference
+// resolves by ordering prev_copy in front of propagate (SystemGroup.zig:264-336) can arise.
 template <> struct SetTraits<2> {
     static constexpr int kIn = 21, kOut = 25, kStage = 25;
 };
@@ -151,6 +153,7 @@ struct PipeArgs {
 constexpr uint32_t kTimingCtas = 4096;      // timing build: CTAs whose (smid, loop start ns, loop end ns, chunks, entry ns, exit ns) are recorded
 constexpr uint32_t kTimingRow = 6;
 constexpr uint32_t kPipeVelClamp = 8u;         // kSet 1: vel_clamp sits between forces and integrate_lin
+constexpr uint32_t kPipePrevCopy = 16u;        // kSet 2: prev_copy is a member too (prev_world = the matrices this generation overwrites)
 constexpr uint32_t kPipePublishPerChunk = 2u; // FIMO_B200_PUBLISH=chunk: announce level progress after every chunk
 constexpr uint32_t kPipePrefetchBlocking = 4u; // FIMO_B200_PREFETCH=2: wait for the next chunk's inputs before this chunk's math
 constexpr uint32_t kPipeNoPrefetch = 1u; // FIMO_B200_PREFETCH=0: parent rows are loaded where they are used
@@ -440,6 +443,8 @@ __global__ void __launch_bounds__(T + 32, kMinBlocks) k_world_step_pipe(const Pi
     uint32_t *lvl_done = nullptr;
     float *waabb_out = nullptr;
     uint32_t *mask2_out = nullptr, *list2_out = nullptr, *sleep_out = nullptr, *lod_out = nullptr;
+    const float *world_old = nullptr; // kSet 2 + prev_copy
+    float *prev_out = nullptr;
 
     long long tm_input = 0, tm_level = 0, tm_pre = 0, tm_gather = 0, tm_prefetched = 0;
     const long long tm_begin = (kTimingBuild && pa.timing && tid == 0) ? clock64() : 0;
@@ -463,6 +468,7 @@ __global__ void __launch_bounds__(T + 32, kMinBlocks) k_world_step_pipe(const Pi
             if (kSet == 2) {
                 mask2_out = uptr(a.vis_mask2, w), list2_out = uptr(a.vis_list2, w);
                 sleep_out = uptr(a.sleep, w), lod_out = uptr(a.lod, w);
+                if (pa.flags & kPipePrevCopy) world_old = fptr(a.world, w), prev_out = fptr(a.prev_world, w);
             }
         }
         const uint32_t first = c * T;
@@ -601,6 +607,15 @@ __global__ void __launch_bounds__(T + 32, kMinBlocks) k_world_step_pipe(const Pi
                 if (kSet >= 1) {
                     st[15 * T] = vx, st[16 * T] = vy, st[17 * T] = vz;
                     st[18 * T] = rx, st[19 * T] = ry, st[20 * T] = rz, st[21 * T] = rw;
+                }
+                if (kSet == 2 && (pa.flags & kPipePrevCopy)) {
+                    // prev_copy: this entity's matrix of the previous generation (the chunk's new ones are still in the
+                    // stage; the bulk store that overwrites `world` is issued only after every warp has arrived on done[s])
+                    float old[12];
+#pragma unroll
+                    for (int i = 0; i < 12; i++) old[i] = __ldcg(world_old + (uint64_t)i * E + e);
+#pragma unroll
+                    for (int i = 0; i < 12; i++) prev_out[(uint64_t)i * E + e] = old[i];
                 }
             }
             if (kTeam) {
@@ -1203,6 +1218,7 @@ FimoStatus world_step_launch(const WorldStepViews &v, const WorldStepPlan &plan,
             a.scratch2 = (unsigned long long *)v.scratch2;
             a.gstats2 = (uint32_t *)v.gstats2->device_ptr;
             a.bounds_keys2 = (int *)plan.bounds2.get();
+            if (v.prev_world) a.prev_world = plane_of(v.prev_world, FIMO_B200_SCOPE_ENTITY, 12, E, W, "prev_world"), pa.flags |= kPipePrevCopy;
         }
         const int key = plan.threads * 100 + (int)plan.blocks_per_sm * 10 + (int)plan.set;
         struct TimingReport { // prints the accumulated ticks every 16th launch, after the launch below has been enqueued

@@ -1012,6 +1012,13 @@ bool build_device_executor(Group *g, const char **err) {
                         views16.scratch2 = ((dev::BuiltinState *)c2->state)->scratch;
                         fused16 = fused;
                         for (Member *m : {md, msl, ml, c2, mvb, ms2}) fused16.push_back(m);
+                        // prev_copy (X: prev_world, S: world), ordered in front of propagate by the R/W conflict on `world`:
+                        // inside the kernel every thread copies its entity's old matrix before the chunk's new ones are stored
+                        Member *mpc = by_id(FIMO_B200_BUILTIN_PREV_COPY, [&](Member *m) { return arity(m, 1, 1) && m->type->shared[0] == world; });
+                        if (mpc && mpc->order < mp->order && !std::getenv("FIMO_B200_NO_PREV_FUSION")) {
+                            views16.prev_world = view_of(g, mpc->type->exclusive[0]);
+                            fused16.push_back(mpc);
+                        }
                     }
                 }
             }

@@ -288,8 +288,12 @@ class WorldStepRig:
 
     def __init__(self, lib: abi.WorldsLib, n_worlds: int, entities: int, depth: int, world0: int = 0,
                  options: RigOptions | None = None, data: dict[str, np.ndarray] | None = None, pool: abi.Pool | None = None,
-                 post_step=None, dag: str = "chain3", host_systems: bool = False):
-        assert dag in DAGS and not (host_systems and dag != "chain3")
+                 post_step=None, dag: str = "chain3", host_systems: bool = False, wind: tuple | None = None):
+        """wind = (path of examples/wind_system/libwind_system.so, "between" | "front"): also registers that library's
+        third-party system (X: vel, S: pos, wind, dt; a device entry point with builtin_id 0 on the product, a plain
+        `system_run` on a CPU implementation) in the 8-system DAG — between `forces` and `integrate_lin`, or in front
+        of `forces`."""
+        assert dag in DAGS and not (host_systems and dag != "chain3") and not (wind and dag != "dag8")
         self.lib, self.W, self.E, self.depth, self.dag = lib, n_worlds, entities, depth, dag
         self.opt = options or RigOptions()
         self.on_device = lib.is_product
@@ -303,7 +307,17 @@ class WorldStepRig:
         if self.on_device:
             batch = abi.WorldBatchExt(abi.ExtHeader(abi.STYPE_WORLD_BATCH, 0, None), n_worlds, entities, self.opt.device, 0)
         self.world = World.init(lib, "synthetic-batch", pool=pool, batch=batch)
-        for name, (scope, comps, _dtype) in layout_for(dag).items():
+        layout = layout_for(dag)
+        if wind:
+            layout["wind"] = (abi.SCOPE_WORLD, 4, np.float32)
+            if "wind" not in self.host:  # direction xyz per world (counter-based like everything else), shear
+                wi = (np.arange(n_worlds, dtype=np.uint32) + np.uint32(world0))
+                w4 = np.empty((n_worlds, 4, 1), dtype=np.float32)
+                for k in range(3):
+                    w4[:, k, 0] = _uniform(SEED, wi, np.zeros(n_worlds, np.uint32), 40 + k, -3.0, 3.0)
+                w4[:, 3, 0] = np.float32(0.01)
+                self.host["wind"] = w4
+        for name, (scope, comps, _dtype) in layout.items():
             if name == "level_start":
                 comps = depth + 1
             arr = self.host[name]
@@ -341,8 +355,12 @@ class WorldStepRig:
         else:
             # 8-system fan-out / fan-in DAG: forces -> integrate_lin || integrate_ang -> propagate ->
             # world_aabb -> { cull || bounds_reduce } -> group_stats
-            forces = sysdef("forces", abi.BUILTIN_FORCES, [R["vel"]], [R["gravity"], R["dt"]])
-            integrate = sysdef("integrate_lin", abi.BUILTIN_INTEGRATE, [R["pos"]], [R["vel"], R["dt"]], before=[forces])
+            wind_sys = self._wind_system(wind[0]) if wind and wind[1] == "front" else None
+            forces = sysdef("forces", abi.BUILTIN_FORCES, [R["vel"]], [R["gravity"], R["dt"]], before=[wind_sys] if wind_sys else ())
+            if wind and wind[1] == "between":
+                wind_sys = self._wind_system(wind[0], before=[forces])
+            integrate = sysdef("integrate_lin", abi.BUILTIN_INTEGRATE, [R["pos"]], [R["vel"], R["dt"]],
+                               before=[forces, wind_sys] if wind and wind[1] == "between" else [forces])
             integrate_ang = sysdef("integrate_ang", abi.BUILTIN_INTEGRATE_ANG, [R["rot"]], [R["angvel"], R["dt"]])
             propagate = sysdef("propagate", abi.BUILTIN_PROPAGATE, [R["world"]],
                                [R["pos"], R["rot"], R["scale"], R["parent"], R["level_start"]], before=[integrate, integrate_ang])
@@ -354,6 +372,8 @@ class WorldStepRig:
             gstats = sysdef("group_stats", abi.BUILTIN_GROUP_STATS, [R["gstats"]], [R["vis_count"], R["wbounds"]],
                             before=[cull, bounds])
             self.systems = [forces, integrate, integrate_ang, propagate, world_aabb, cull, bounds, gstats]
+            if wind_sys is not None:
+                self.systems.insert(0 if wind[1] == "front" else 1, wind_sys)
             if dag == "dag16":
                 # 8 more systems; where no `before` is given the order follows from resource conflicts alone
                 # (W/W, R/W, W/R in rank-then-add order, SystemGroup.zig:264-336):
@@ -420,6 +440,30 @@ class WorldStepRig:
         counted = System.register(self.lib, "host_census", run=run_census, exclusive=[census], shared=[R["vis_count"]], before=[cull])
         self._registered += [camera, counted]
         return [camera, counted]
+
+    def _wind_system(self, path: str, before=()):
+        """The third-party system of examples/wind_system: its library fills the descriptor (factory, state size,
+        create / destroy / run) and, on the product, the device extension with ITS entry point (builtin_id 0)."""
+        windlib = C.CDLL(path)
+        windlib.wind_fill_descriptor.argtypes = [C.c_void_p, C.c_void_p, C.c_float]
+        windlib.wind_fill_descriptor.restype = None
+        windlib.wind_counters.argtypes = [C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
+        windlib.wind_bind_futex_wake.argtypes = [C.c_void_p]
+        windlib.wind_bind_futex_wake(C.cast(self.lib.fimo_tasks_futex_wake, C.c_void_p))
+        desc = abi.SystemDescriptor()
+        ext = abi.SystemDeviceExt() if self.on_device else None
+        windlib.wind_fill_descriptor(C.byref(desc), C.byref(ext) if ext is not None else None, 1.25)
+        self.windlib = windlib
+        R = self.resources
+        system = System.register(self.lib, "wind", exclusive=[R["vel"]], shared=[R["pos"], R["wind"], R["dt"]], before=before,
+                                 descriptor=desc, keep=[desc, ext, windlib])
+        self._registered.append(system)
+        return system
+
+    def wind_counters(self) -> tuple[int, int]:
+        d, h = C.c_uint64(0), C.c_uint64(0)
+        self.windlib.wind_counters(C.byref(d), C.byref(h))
+        return int(d.value), int(h.value)
 
     def census(self):
         """The host resource `host_census` writes (locked shared, copied out)."""

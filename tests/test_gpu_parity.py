@@ -125,7 +125,7 @@ def test_tail_grid_matches_oracle(oracle, product, monkeypatch, dag, W, E, D, st
     kw = {} if dag == "chain3" else {"dag": dag}
     got, want, info = run_both(oracle, product, W, E, D, steps, synth.RigOptions(fused=True, graph=graph), **kw)
     assert info.fused_world_step == 1
-    assert info.kernel_launches_per_generation == (2 if dag != "dag16" else 3)  # + prev_copy outside the fused kernel
+    assert info.kernel_launches_per_generation == 2 and info.nodes == 1  # dag16: prev_copy is inside the fused kernel too
     problems = synth.compare_outputs(got, want, FLOAT_RTOL)
     assert not problems, "\n".join(problems)
     st = got["stats"].reshape(-1).view(np.uint64)
@@ -208,9 +208,9 @@ FULL_SIZE_CASES = [
     ("C2", "chain3", 4096, 1024, 4, 16, 1),    # BASELINE configs[1]: grid 586 x 7 worlds per CTA
     ("C3", "dag8", 256, 65536, 8, 4, 2),        # configs[2]: CTA teams per world + list compaction
     ("C4-per-gpu", "chain3", 4096, 4096, 4, 4, 1),  # configs[3] = 32768 x 4k over 8 GPUs: the shard one GPU steps
-    ("C5-per-gpu", "dag16", 1024, 1024, 4, 16, None),  # configs[4]: 16-system DAG, 1 M entities per GPU
+    ("C5-per-gpu", "dag16", 1024, 1024, 4, 16, 1),  # configs[4]: 16-system DAG, 1 M entities per GPU: ONE kernel for all 16 systems
     ("dag8-4096", "dag8", 4096, 1024, 4, 4, 2),  # persistent grid + tail grid at bench size
-    ("dag16-4096", "dag16", 4096, 1024, 4, 3, None),
+    ("dag16-4096", "dag16", 4096, 1024, 4, 3, 1),
 ]
 
 
@@ -238,7 +238,7 @@ QUEUED_CASES = [
     ("chain3", 1200, 2048, 4, 37, None),   # 3 worlds per CTA: generations queued behind two launches share launches (up to 16 each)
     ("chain3", 600, 2048, 4, 21, "3"),     # T = 256: 3 worlds x 8 chunks per CTA; at most 3 generations per launch
     ("dag8", 1300, 1280, 4, 19, None),     # persistent grid + tail grid of one-world CTAs (10 chunks each), both looping over generations
-    ("dag16", 700, 1024, 4, 9, None),      # prev_copy stays a node of its own: two nodes, one launch per generation
+    ("dag16", 700, 1024, 4, 13, None),     # all 16 systems in the kernel, prev_copy included (reads the previous generation's matrices)
     ("chain3", 592, 256, 4, 12, None),     # 2 chunks per CTA < ring + 2: the plan refuses multi-generation launches
 ]
 
@@ -277,7 +277,7 @@ def test_queued_generations_share_launches_and_match_oracle(oracle, product, mon
         snapshots = ring.cpu().numpy().astype(np.uint64)
     finally:
         rig.close()
-    expect_multi = dag != "dag16" and E * 1 >= 5 * 128 and W >= 592
+    expect_multi = E >= 5 * 128 and W >= 592
     assert (info.max_generations_per_launch > 1) == expect_multi, info.max_generations_per_launch
     if gens:
         assert info.max_generations_per_launch == int(gens)
@@ -621,6 +621,47 @@ def test_trace_sink_reports_every_device_generation(product):
     assert all(0.0 < e[2] < 50.0 and 0 < e[3] <= e[4] for e in events)
 
 
+WIND_LIB = __import__("os").path.join(__import__("os").path.dirname(__import__("os").path.dirname(__import__("os").path.abspath(__file__))),
+                                      "examples", "wind_system", "libwind_system.so")
+
+
+@pytest.mark.parametrize("placement,mode", [("between", "fused"), ("between", "graph"), ("between", "streams"),
+                                            ("front", "fused"), ("front", "graph"), ("front", "streams")])
+@pytest.mark.parametrize("W,E,D,steps", [(24, 1024, 4, 5), (700, 260, 5, 3)])
+def test_user_device_system_through_device_entry(oracle, product, placement, mode, W, E, D, steps):
+    """A system the library has never heard of (examples/wind_system, its own .so; builtin_id 0) registered through the
+    unchanged SystemDescriptor + the device extension on `next` (systems.h:51-114): its `device_entry` launches its
+    kernel on the generation's stream — captured into the CUDA graph, or launched live — ordered against the built-ins by
+    `before` edges and resource conflicts only.  "between": after `forces`, before `integrate_lin` — the fused set is no
+    longer convex, so every system runs as its own node; "front": in front of `forces` — the 8 built-ins still fuse
+    AROUND it (2 nodes).  Same math as its host `system_run` on the oracle: every output bit-exact."""
+    data = synth.generate(W, E, D, dag="dag8")
+    ref = synth.WorldStepRig(oracle, W, E, D, data={k: v.copy() for k, v in data.items()}, dag="dag8", wind=(WIND_LIB, placement))
+    try:
+        ref.step(steps)
+        want = ref.download()
+        assert ref.wind_counters() == (0, steps)  # the CPU path ran system_run
+    finally:
+        ref.close()
+    opts = synth.RigOptions(fused=(mode == "fused"), graph=(mode != "streams"))
+    dev = synth.WorldStepRig(product, W, E, D, data={k: v.copy() for k, v in data.items()}, options=opts, dag="dag8", wind=(WIND_LIB, placement))
+    try:
+        info = dev.executor_info()
+        dev.step(steps)
+        got = dev.download()
+        launches, host_runs = dev.wind_counters()
+    finally:
+        dev.close()
+    assert info.systems == 9 and info.device_systems == 9 and host_runs == 0  # its system_run is never called on the product
+    if mode == "fused" and placement == "front" and E % 4 == 0:
+        assert info.fused_world_step == 1 and info.nodes == 2
+    else:
+        assert info.fused_world_step == 0 and info.nodes == 9
+    assert launches == (steps if mode == "streams" else 0)  # live launches per generation; under capture the graph replays the kernel
+    problems = synth.compare_outputs(got, want, FLOAT_RTOL)
+    assert not problems, "\n".join(problems)
+
+
 DAG_CASES = [
     # (dag, worlds, entities, depth, steps)
     ("dag8", 1, 1024, 4, 8),
@@ -649,11 +690,11 @@ def test_system_dags_match_oracle(oracle, product, monkeypatch, dag, W, E, D, st
     n = 8 if dag == "dag8" else 16
     assert info.systems == n and info.device_systems == n
     if fused and E % 4 == 0:
-        # dag16: 15 systems inside the world-step kernel + prev_copy in front of it (2 nodes); with CTA teams (few,
-        # large worlds) the 8-system core + vel_clamp is fused and seven systems stay graph nodes (8 nodes)
-        assert info.fused_world_step == 1 and info.nodes in ((1,) if dag == "dag8" else (2, 8))
+        # dag16: all 16 systems inside the world-step kernel (1 node); with CTA teams (few, large worlds) the 8-system
+        # core + vel_clamp is fused and seven systems stay graph nodes (8 nodes)
+        assert info.fused_world_step == 1 and info.nodes in ((1,) if dag == "dag8" else (1, 8))
         if dag == "dag16" and (mode == "fused-one-cta-per-world" or W >= 300):
-            assert info.nodes == 2
+            assert info.nodes == 1
     else:
         assert info.fused_world_step == 0 and info.nodes == n and info.edges >= n - 1
     assert info.uses_cuda_graph == (0 if mode == "streams" else 1)
