@@ -656,7 +656,7 @@ bool executor_launch_batch(Executor *ex, uint32_t gens, void (*done)(void *), vo
     bool launched = ok(cudaEventRecord(c.start, ex->stream), "cudaEventRecord");
     launched = launched && ex->nodes[0].launch_gens(&info, gens) == FIMO_STATUS_OK; // a plain launch: the generation count is a kernel argument
     launched = ok(cudaEventRecord(c.end, ex->stream), "cudaEventRecord") && launched;
-    ex->kernels_launched.fetch_add(ex->kernels, std::memory_order_relaxed); // one launch of the node's kernels for all `gens` generations
+    ex->kernels_launched.fetch_add(ex->nodes[0].kernels_gens, std::memory_order_relaxed); // one launch for all `gens` generations
     for (uint32_t i = 0; i < gens; i++) {
         Completion one = c;
         one.user = users[i];

@@ -37,6 +37,7 @@ struct Node {
     // with nothing between them (executor_launch_batch).
     std::function<FimoStatus(const FimoB200_LaunchInfo *, uint32_t gens)> launch_gens;
     uint32_t max_gens = 1;
+    uint32_t kernels_gens = 1; // kernel launches of one launch_gens call
 };
 
 struct Executor;
@@ -177,6 +178,7 @@ struct WorldStepPlan {
     // One CTA per world: the persistent grid steps worlds [0, tail_first) in whole rounds, a second grid launched
     // beside it steps [tail_first, n_worlds) one world per CTA as slots free up (tail_first == n_worlds: no tail).
     uint32_t grid = 0, tail_first = 0;
+    uint32_t grid_all = 0;      // the persistent grid over ALL worlds (multi-generation launches do without the tail grid)
     std::shared_ptr<void> tail;     // side stream + fork / join events of the tail grid
     size_t smem = 0;            // dynamic shared memory per CTA
     std::shared_ptr<void> rows;     // HBM: [n_worlds][E] 48-byte parent rows (parents outside the window)

@@ -990,15 +990,26 @@ bool world_step_plan(const WorldStepViews &v, int device, WorldStepPlan &plan) {
     double window_coverage = 1.0;
     if (!planned) {
         static const struct { int T; uint32_t blocks, stages; } kCandidates[] = {{128, 4, 3}, {256, 3, 3}, {256, 2, 3}, {512, 1, 3}};
-        double best = -1.0;
+        // ... but not at any price: a window that holds 90 % of the best coverage on offer with more CTAs per SM beats the
+        // full window with fewer (4096-entity worlds: (256, 2) at 0.92 coverage 0.968 of the HBM peak, (512, 1) at 1.0
+        // coverage 0.921; profiles/r2f_sweep.txt).
+        double best = -1.0, chosen = -1.0;
         for (const auto &cand : kCandidates) {
             WorldStepPlan trial = plan;
             if (!make_plan(trial, cand.T, cand.blocks, cand.stages, parents, E)) continue;
-            const double coverage = parents ? std::min(1.0, (double)trial.lvl_cap / (double)parents) : 1.0;
-            if (coverage > best + 1e-9) best = coverage, plan = trial;
+            best = std::max(best, parents ? std::min(1.0, (double)trial.lvl_cap / (double)parents) : 1.0);
         }
         if (best < 0.0) return false;
-        window_coverage = best;
+        for (const auto &cand : kCandidates) { // in order of decreasing CTAs per SM
+            WorldStepPlan trial = plan;
+            if (!make_plan(trial, cand.T, cand.blocks, cand.stages, parents, E)) continue;
+            const double coverage = parents ? std::min(1.0, (double)trial.lvl_cap / (double)parents) : 1.0;
+            if (coverage >= 0.9 * best) {
+                chosen = coverage, plan = trial;
+                break;
+            }
+        }
+        window_coverage = chosen;
     }
     // Few worlds (or a forced team size): CTA teams, with the geometry that suits them (no window needed).
     const char *team_var = std::getenv("FIMO_B200_TEAM"); // force the team size (1 = one CTA per world)
@@ -1037,7 +1048,7 @@ bool world_step_plan(const WorldStepViews &v, int device, WorldStepPlan &plan) {
         // Persistent grid with an even share of worlds per CTA: a ragged tail costs more than idle CTA slots on an
         // HBM-bound kernel.
         const uint64_t per_cta = std::max<uint64_t>((W + slots - 1) / slots, 1);
-        plan.grid = (uint32_t)((W + per_cta - 1) / per_cta), plan.tail_first = (uint32_t)W;
+        plan.grid = plan.grid_all = (uint32_t)((W + per_cta - 1) / per_cta), plan.tail_first = (uint32_t)W;
         // CTAs do not all run at the same speed.  On the 8-system set whole groups of SMs (by %smid, the same ones every
         // launch) step their chunks 5-16 % slower than the rest, so with an even static share the kernel ends with its
         // slowest CTA, 1.23x the mean (profiles/r1zc_cta_trace.txt).  There the last round of worlds is not assigned
@@ -1074,8 +1085,8 @@ bool world_step_plan(const WorldStepViews &v, int device, WorldStepPlan &plan) {
     // least stages + 2 chunks per generation, so that a chunk's previous-generation stores are covered by the TMA
     // thread's "all but the two most recent bulk groups" wait.
     plan.max_gens = 1, plan.block_worlds = 0x40000000u; // one block: plain world order
-    if (plan.team == 1 && plan.grid) {
-        const uint64_t persist = plan.tail_first, min_worlds = plan.tail_first < W ? 1 : persist / plan.grid;
+    if (plan.team == 1 && plan.grid_all) { // multi-generation launches always use the one persistent grid (no tail grid)
+        const uint64_t min_worlds = W / plan.grid_all;
         const uint64_t block = ((uint64_t)plan.stages + 2 + chunks - 1) / chunks; // fewest worlds that hold stages + 2 chunks
         if (min_worlds >= block) plan.max_gens = kStatSlots, plan.block_worlds = (uint32_t)block;
         // FIMO_B200_BLOCK=n: at least n worlds per block (A/B runs; 0 = all of a CTA's worlds, i.e. generation-major order)
@@ -1134,9 +1145,12 @@ FimoStatus launch_pipe(PipeArgs &pa, const WorldStepPlan &plan, uint64_t W, cons
     }
     auto kernel = k_world_step_pipe<T, kBlocks, false, kSet>;
     if (!allow_smem(kernel, plan.smem)) return check_launch("world_step (shared memory opt-in)");
-    const unsigned grid = plan.grid, tail_ctas = (unsigned)(W - plan.tail_first); // two worlds per tail CTA: measured slower
+    // The tail grid evens out ONE generation's slowest CTAs; a multi-generation launch amortises that tail over its
+    // generations anyway (dag8 4096 x 1024: 0.974 with, 0.975 without), so it uses the one persistent grid.
+    const bool use_tail = plan.tail_first < W && pa.gens == 1;
+    const unsigned grid = use_tail ? plan.grid : plan.grid_all, tail_ctas = use_tail ? (unsigned)(W - plan.tail_first) : 0u;
     pa.team = 1, pa.teams = grid;
-    pa.world_first = 0, pa.world_end = plan.tail_first, pa.stat_ctas = grid + tail_ctas, pa.trace_base = 0;
+    pa.world_first = 0, pa.world_end = use_tail ? plan.tail_first : (uint32_t)W, pa.stat_ctas = grid + tail_ctas, pa.trace_base = 0;
     if (!tail_ctas) {
         kernel<<<grid, T + 32, plan.smem, stream>>>(pa);
         return check_launch("world_step");

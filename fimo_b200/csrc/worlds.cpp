@@ -1586,6 +1586,21 @@ const char *group_schedule(Group *g, FimoWorldsMeta_Fence *const *wait_on, size_
                 device = g->has_device_systems;
             }
         }
+        // FIMO_B200_GENS_HOLD=n (profiling aid: under ncu every launch is synchronous, so nothing ever queues up): hold
+        // plain generations until n are pending or one carries a fence, then launch them together
+        static const size_t hold = [] { const char *e = std::getenv("FIMO_B200_GENS_HOLD"); return e ? (size_t)std::strtoull(e, nullptr, 10) : 0; }();
+        if (hold > 1 && device && dev::executor_max_gens(g->executor_dev) > 1 && batchable(g, job) &&
+            g->compiled_epoch == g->world->resource_epoch.load(std::memory_order_acquire)) {
+            g->batch_pending.push_back(job);
+            if (g->batch_pending.size() >= std::min<size_t>(hold, dev::executor_max_gens(g->executor_dev)) || job->signal) {
+                if (g->in_flight == 0) {
+                    std::vector<void *> blobs(g->resources.size());
+                    world_lock_resources(g->world, g->resources.data(), g->resources.size(), nullptr, 0, blobs.data());
+                }
+                launch_pending_batches(g);
+            }
+            return nullptr;
+        }
         if (device && dev::executor_max_gens(g->executor_dev) > 1 && g->in_flight != 0 &&
             g->compiled_epoch == g->world->resource_epoch.load(std::memory_order_acquire)) {
             if (batchable(g, job) && (g->launches_in_flight >= 2 || !g->batch_pending.empty())) {
