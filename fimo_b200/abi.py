@@ -84,7 +84,9 @@ class CommandBufferEntry(C.Structure):
     _fields_ = [("type", c_int32), ("payload", CommandBufferEntryPayload)]
 
 
-ENTRY_ABORT_ON_ERROR, ENTRY_ENQUEUE_TASK, ENTRY_WAIT_ON_BARRIER, ENTRY_WAIT_ON_COMMAND_INDIRECT = 0, 4, 6, 8
+# command_buffer.h:44-54
+(ENTRY_ABORT_ON_ERROR, ENTRY_SET_MIN_STACK_SIZE, ENTRY_SELECT_WORKER, ENTRY_SELECT_ANY_WORKER, ENTRY_ENQUEUE_TASK,
+ ENTRY_ENQUEUE_COMMAND_BUFFER, ENTRY_WAIT_ON_BARRIER, ENTRY_WAIT_ON_COMMAND_BUFFER, ENTRY_WAIT_ON_COMMAND_INDIRECT) = range(9)
 
 
 class CommandBuffer(C.Structure):
@@ -362,6 +364,8 @@ COMMON_SYMBOLS = [
     ("fimo_worlds_b200_fence_wait", None, [POINTER(Fence)]),
     ("fimo_worlds_b200_fence_signal", None, [POINTER(Fence)]),
     ("fimo_tasks_create_worker_pool", FimoStatus, [POINTER(PoolConfig), POINTER(Pool)]),
+    ("fimo_tasks_abort", None, []),
+    ("fimo_tasks_worker_id", c_bool, [POINTER(c_size_t)]),
 ]
 
 class TraceEvent(C.Structure):  # FimoB200_TraceEvent

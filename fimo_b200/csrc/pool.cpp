@@ -14,10 +14,18 @@
 //   wait_on_barrier: until all earlier entries completed                 (:339-348)
 //   enqueue_command_buffer: child buffer, completes the entry when done  (:315-337)
 //   wait_on_command_buffer: until another buffer's handle completed      (:350-388)
+//   select_worker / select_any_worker: the following tasks run on that worker's thread only (:236-268; an index
+//       outside the pool aborts the entry); set_min_stack_size is accepted and has no effect (tasks own a whole thread)
+//   abort_on_error + errors (:459-513): a task errors by calling the `abort` symbol (Worker.zig:115-122,
+//       symbols.zig:97); with the setting on, every entry not yet issued is skipped — its task / child buffer gets its
+//       on_abort and on_deinit hooks — up to an abort_on_error=false entry, and the buffer ends aborted; an aborted
+//       child buffer or awaited handle propagates the same way; malformed entries (offset out of range, unknown worker
+//       or type) abort instead of panicking; wait_on_command_indirect(0) is a no-op (:397).
 // Tasks run on OS threads (boost.context is an un-vendored network dependency of the reference,
 // modules/fimo_tasks/build.zig.zon:8-11); a task that parks on the futex keeps the pool's thread
 // budget through BlockingScope.
 #include <algorithm>
+#include <csetjmp>
 #include <deque>
 #include <thread>
 
@@ -31,6 +39,7 @@ struct WorkItem {
     Cmd *cmd;
     size_t entry;
     FimoTasksMeta_Task *task;
+    ptrdiff_t worker = -1; // >= 0: only that worker thread may run it (select_worker)
 };
 
 struct Pool {
@@ -43,6 +52,7 @@ struct Pool {
     std::mutex m;
     std::condition_variable cv;
     std::deque<WorkItem> queue;
+    std::vector<std::deque<WorkItem>> pinned; // per regular worker: tasks enqueued under select_worker
     size_t runnable = 0;     // threads that are not parked inside a task
     size_t idle = 0;         // runnable threads waiting for work
     size_t live_threads = 0; // regular + spare threads still alive
@@ -54,6 +64,8 @@ namespace {
 
 std::atomic<size_t> g_pool_ids{1};
 thread_local Pool *t_pool = nullptr;
+thread_local ptrdiff_t t_worker = -1;       // index of this regular worker thread in its pool (-1: spare / foreign thread)
+thread_local std::jmp_buf *t_abort = nullptr; // where `abort` unwinds to while a task body runs
 
 enum : uint8_t { kPending = 0, kRunning = 1, kDone = 2 };
 
@@ -70,7 +82,8 @@ struct Cmd {
     size_t issue = 0;    // next entry to issue
     size_t finished = 0; // entries completed
     bool abort_on_error = false;
-    bool failed = false;
+    bool failed = false; // has_error in the reference
+    ptrdiff_t worker = -1; // select_worker state
     bool finalized = false;
     int outcome = 0; // 0 running, 1 completed, 2 aborted (under m)
     std::atomic<int> outcome_published{0};
@@ -86,23 +99,29 @@ void cmd_unref(Cmd *c) {
     if (c->refs.fetch_sub(1, std::memory_order_acq_rel) == 1) delete c;
 }
 
-void worker_main(Pool *p, bool spare);
+void worker_main(Pool *p, bool spare, ptrdiff_t index);
 
 // Called with p->m held.
 void spawn_spare_locked(Pool *p) {
     p->runnable++;
     p->live_threads++;
-    std::thread(worker_main, p, true).detach();
+    std::thread(worker_main, p, true, (ptrdiff_t)-1).detach();
 }
 
 void push_task(Pool *p, WorkItem w) {
     std::lock_guard<std::mutex> g(p->m);
+    if (w.worker >= 0) { // pinned: only that thread takes it
+        p->pinned[(size_t)w.worker].push_back(w);
+        p->cv.notify_all();
+        return;
+    }
     p->queue.push_back(w);
     if (p->idle > 0) p->cv.notify_one();
     else if (p->runnable < p->worker_count) spawn_spare_locked(p); // every regular thread is busy or parked
 }
 
 void resume(Cmd *c, ptrdiff_t done_entry, bool child_aborted);
+extern const FimoTasksMeta_CommandBufferHandleVTable g_handle_vtable;
 
 Cmd *cmd_create(Pool *p, FimoTasksMeta_CommandBuffer *cb) {
     Cmd *c = new Cmd();
@@ -114,17 +133,64 @@ Cmd *cmd_create(Pool *p, FimoTasksMeta_CommandBuffer *cb) {
     return c;
 }
 
+// Entry.abort (pkgs/fimo_tasks_meta/src/command_buffer.zig:56-70) + Entry.deinit: an entry that will never be issued.
+void abort_entry(const FimoTasksMeta_CommandBufferEntry &e) {
+    if (e.type == FIMO_TASKS_META_COMMAND_BUFFER_ENTRY_TYPE_ENQUEUE_TASK) {
+        FimoTasksMeta_Task *t = e.payload.enqueue_task;
+        if (t->on_abort) t->on_abort(t);
+        if (t->on_deinit) t->on_deinit(t);
+    } else if (e.type == FIMO_TASKS_META_COMMAND_BUFFER_ENTRY_TYPE_ENQUEUE_COMMAND_BUFFER) {
+        FimoTasksMeta_CommandBuffer *b = e.payload.enqueue_command_buffer;
+        if (b->on_abort) b->on_abort(b);
+        if (b->on_deinit) b->on_deinit(b);
+    }
+}
+void mark_processed(Cmd *c) {
+    c->state[c->issue] = kDone;
+    c->finished++;
+    c->issue++;
+}
+// CommandBuffer.zig:490-513.  c->m held.
+void abort_forward(Cmd *c) {
+    if (!c->abort_on_error) return;
+    const FimoTasksMeta_CommandBuffer *cb = c->cb;
+    while (c->issue < cb->entries_len) {
+        const FimoTasksMeta_CommandBufferEntry &e = cb->entries[c->issue];
+        if (e.type == FIMO_TASKS_META_COMMAND_BUFFER_ENTRY_TYPE_ABORT_ON_ERROR) {
+            c->abort_on_error = e.payload.abort_on_error;
+            mark_processed(c);
+            if (!c->abort_on_error) break;
+        } else {
+            abort_entry(e);
+            mark_processed(c);
+        }
+    }
+    c->failed = c->abort_on_error;
+}
+// :459-466: the entry being issued is malformed.
+void abort_current_and_forward(Cmd *c) {
+    abort_entry(c->cb->entries[c->issue]);
+    mark_processed(c);
+    abort_forward(c);
+}
+// :468-488: entry `index` (already issued) ended in error.
+void abort_from_index(Cmd *c, size_t index) {
+    if (!c->abort_on_error) return;
+    const FimoTasksMeta_CommandBuffer *cb = c->cb;
+    if (c->issue == cb->entries_len) {
+        c->failed = true;
+        return;
+    }
+    for (size_t i = index; i < c->issue; i++) // did the setting change between that entry and now?
+        if (cb->entries[i].type == FIMO_TASKS_META_COMMAND_BUFFER_ENTRY_TYPE_ABORT_ON_ERROR && !cb->entries[i].payload.abort_on_error) return;
+    abort_forward(c);
+}
+
 // Issues entries until one blocks.  c->m is held.  Returns true when the buffer is complete.
 bool advance_locked(Cmd *c) {
     const FimoTasksMeta_CommandBuffer *cb = c->cb;
     while (c->issue < cb->entries_len) {
         const size_t idx = c->issue;
-        if (c->failed) { // aborted buffers skip what was not issued yet (CommandBuffer.zig:459-513)
-            c->state[idx] = kDone;
-            c->finished++;
-            c->issue++;
-            continue;
-        }
         const FimoTasksMeta_CommandBufferEntry &e = cb->entries[idx];
         bool done_now = true;
         switch (e.type) {
@@ -132,12 +198,20 @@ bool advance_locked(Cmd *c) {
                 c->abort_on_error = e.payload.abort_on_error;
                 break;
             case FIMO_TASKS_META_COMMAND_BUFFER_ENTRY_TYPE_SET_MIN_STACK_SIZE:
+                break; // a task owns a whole OS thread here: every size is honoured
             case FIMO_TASKS_META_COMMAND_BUFFER_ENTRY_TYPE_SELECT_WORKER:
+                if (e.payload.select_worker >= c->pool->worker_count) { // CommandBuffer.zig:243-254
+                    abort_current_and_forward(c);
+                    continue;
+                }
+                c->worker = (ptrdiff_t)e.payload.select_worker;
+                break;
             case FIMO_TASKS_META_COMMAND_BUFFER_ENTRY_TYPE_SELECT_ANY_WORKER:
-                break; // fiber stack sizes and worker pinning do not apply to thread-run tasks
+                c->worker = -1;
+                break;
             case FIMO_TASKS_META_COMMAND_BUFFER_ENTRY_TYPE_ENQUEUE_TASK:
                 c->state[idx] = kRunning;
-                push_task(c->pool, WorkItem{c, idx, e.payload.enqueue_task});
+                push_task(c->pool, WorkItem{c, idx, e.payload.enqueue_task, c->worker});
                 done_now = false;
                 break;
             case FIMO_TASKS_META_COMMAND_BUFFER_ENTRY_TYPE_ENQUEUE_COMMAND_BUFFER: {
@@ -156,23 +230,39 @@ bool advance_locked(Cmd *c) {
                 break;
             case FIMO_TASKS_META_COMMAND_BUFFER_ENTRY_TYPE_WAIT_ON_COMMAND_BUFFER: {
                 Cmd *other = (Cmd *)e.payload.wait_on_command_buffer.data;
-                std::lock_guard<std::mutex> link(g_link_lock);
-                if (other->outcome_published.load(std::memory_order_acquire) == 0) {
-                    if (std::find(other->blocked_on_me.begin(), other->blocked_on_me.end(), c) == other->blocked_on_me.end()) {
-                        c->refs.fetch_add(1, std::memory_order_relaxed);
-                        other->blocked_on_me.push_back(c);
-                    }
-                    return false;
+                if (e.payload.wait_on_command_buffer.vtable != &g_handle_vtable || other->pool != c->pool) { // :357-381
+                    abort_current_and_forward(c);
+                    continue;
                 }
-                break;
+                int outcome;
+                {
+                    std::lock_guard<std::mutex> link(g_link_lock);
+                    outcome = other->outcome_published.load(std::memory_order_acquire);
+                    if (outcome == 0) {
+                        if (std::find(other->blocked_on_me.begin(), other->blocked_on_me.end(), c) == other->blocked_on_me.end()) {
+                            c->refs.fetch_add(1, std::memory_order_relaxed);
+                            other->blocked_on_me.push_back(c);
+                        }
+                        return false;
+                    }
+                }
+                mark_processed(c);
+                if (outcome == 2) abort_forward(c); // :385-387
+                continue;
             }
             case FIMO_TASKS_META_COMMAND_BUFFER_ENTRY_TYPE_WAIT_ON_COMMAND_INDIRECT: {
                 const size_t k = e.payload.wait_on_command_indirect;
-                if (k == 0 || k > idx) panic("wait_on_command_indirect out of range");
+                if (k == 0) break; // :397
+                if (k > idx) {     // :398-408
+                    abort_current_and_forward(c);
+                    continue;
+                }
                 if (c->state[idx - k] != kDone) return false;
                 break;
             }
-            default: panic("unknown command buffer entry");
+            default: // :413-421
+                abort_current_and_forward(c);
+                continue;
         }
         if (done_now) {
             c->state[idx] = kDone;
@@ -224,10 +314,10 @@ void resume(Cmd *c, ptrdiff_t done_entry, bool child_aborted) {
     bool complete;
     {
         std::lock_guard<std::mutex> g(c->m);
-        if (done_entry >= 0) {
+        if (done_entry >= 0) { // completeTask (CommandBuffer.zig:127-148): a task or child buffer has ended, possibly in error
             c->state[(size_t)done_entry] = kDone;
             c->finished++;
-            if (child_aborted && c->abort_on_error) c->failed = true;
+            if (child_aborted) abort_from_index(c, (size_t)done_entry);
         }
         complete = advance_locked(c);
     }
@@ -240,27 +330,39 @@ void pool_destroy_if_last_thread_locked(Pool *p, std::unique_lock<std::mutex> &g
     if (last) delete p;
 }
 
-void worker_main(Pool *p, bool spare) {
+void worker_main(Pool *p, bool spare, ptrdiff_t index) {
     t_pool = p;
+    t_worker = index;
     std::unique_lock<std::mutex> g(p->m);
     for (;;) {
         if (spare && p->runnable > p->worker_count) break; // parked threads came back: retire
-        if (p->queue.empty()) {
+        std::deque<WorkItem> *from = index >= 0 && !p->pinned[(size_t)index].empty() ? &p->pinned[(size_t)index] : &p->queue;
+        if (from->empty()) {
             if (p->stopping || spare) break;
             p->idle++;
             p->cv.wait(g);
             p->idle--;
             continue;
         }
-        WorkItem w = p->queue.front();
-        p->queue.pop_front();
+        WorkItem w = from->front();
+        from->pop_front();
         g.unlock();
         if (w.task) {
-            // Task.zig:56-67, Worker.zig:225-248,306-321: body, completion hooks, completion report.
-            w.task->on_start(w.task);
-            if (w.task->on_complete) w.task->on_complete(w.task);
+            // Task.zig:56-67, Worker.zig:225-248,306-335: body, then the completion OR the abort hook (the task called
+            // the `abort` symbol: fimo_tasks_abort unwinds to here), deinit, completion report with is_error.
+            std::jmp_buf unwind;
+            t_abort = &unwind;
+            volatile bool is_error = false;
+            if (setjmp(unwind) == 0) w.task->on_start(w.task);
+            else is_error = true;
+            t_abort = nullptr;
+            if (is_error) {
+                if (w.task->on_abort) w.task->on_abort(w.task);
+            } else if (w.task->on_complete) {
+                w.task->on_complete(w.task);
+            }
             if (w.task->on_deinit) w.task->on_deinit(w.task);
-            resume(w.cmd, (ptrdiff_t)w.entry, false);
+            resume(w.cmd, (ptrdiff_t)w.entry, is_error);
         } else {
             resume(w.cmd, -1, false); // first advance of a child command buffer
         }
@@ -330,7 +432,7 @@ FimoTasksMeta_CommandBufferHandleCompletionStatus h_wait_on(void *d) {
     return c->outcome == 1 ? FIMO_TASKS_META_COMMAND_BUFFER_HANDLE_COMPLETION_STATUS_COMPLETED
                            : FIMO_TASKS_META_COMMAND_BUFFER_HANDLE_COMPLETION_STATUS_ABORTED;
 }
-const FimoTasksMeta_CommandBufferHandleVTable g_handle_vtable = {h_acquire, h_release, h_owner_pool, h_wait_on};
+extern const FimoTasksMeta_CommandBufferHandleVTable g_handle_vtable = {h_acquire, h_release, h_owner_pool, h_wait_on};
 
 FimoStatus vt_enqueue_buffer(void *d, FimoTasksMeta_CommandBuffer *buffer, FimoTasksMeta_CommandBufferHandle *handle) {
     // Pool.zig:820-842
@@ -366,7 +468,8 @@ Pool *pool_create(const char *label, size_t label_len, size_t workers) {
     p->worker_count = workers;
     p->runnable = workers;
     p->live_threads = workers;
-    for (size_t i = 0; i < workers; i++) std::thread(worker_main, p, false).detach();
+    p->pinned.resize(workers);
+    for (size_t i = 0; i < workers; i++) std::thread(worker_main, p, false, (ptrdiff_t)i).detach();
     return p;
 }
 
@@ -394,4 +497,16 @@ extern "C" FimoStatus fimo_tasks_create_worker_pool(const FimoTasksMeta_PoolConf
     }
     *pool = fb::pool_handle(fb::pool_create(config->label, config->label_len, config->worker_count));
     return FIMO_STATUS_OK;
+}
+
+// `abort` of fimo-tasks (symbols.zig:94-99; Worker.zig:115-122): ends the calling task in error.  Never returns.
+extern "C" void fimo_tasks_abort(void) {
+    if (!fb::t_abort) fb::panic("fimo_tasks_abort called outside a task");
+    std::longjmp(*fb::t_abort, 1);
+}
+// `worker_id` (symbols.zig:60-65): the index of the calling worker thread in its pool.
+extern "C" bool fimo_tasks_worker_id(FimoTasksMeta_PoolWorker *id) {
+    if (fb::t_worker < 0) return false;
+    *id = (FimoTasksMeta_PoolWorker)fb::t_worker;
+    return true;
 }

@@ -749,6 +749,15 @@ FIMO_B200_EXPORT void fimo_worlds_b200_fence_signal(FimoWorldsMeta_Fence *fence)
 FIMO_B200_EXPORT FimoStatus fimo_tasks_create_worker_pool(const FimoTasksMeta_PoolConfig *config,
                                                           FimoTasksMeta_Pool *pool);
 
+/* `abort` of fimo-tasks (symbols.zig:94-99; modules/fimo_tasks/src/Worker.zig:115-122): ends the calling
+ * task in error and never returns.  The task's on_abort hook runs instead of on_complete, and its command
+ * buffer applies abort_on_error (modules/fimo_tasks/src/CommandBuffer.zig:127-148,468-513).  Calling it
+ * outside a task of this library's pools is a contract violation. */
+FIMO_B200_EXPORT void fimo_tasks_abort(void);
+/* `worker_id` of fimo-tasks (symbols.zig:60-65): index of the calling worker inside its pool; false on any
+ * other thread.  Tasks enqueued after a select_worker entry observe exactly that index. */
+FIMO_B200_EXPORT bool fimo_tasks_worker_id(FimoTasksMeta_PoolWorker *id);
+
 /* ------------------------------------------------------------------------- */
 /* Device-side helpers (product library only; absent from the CPU oracle)     */
 /* ------------------------------------------------------------------------- */

@@ -8,12 +8,18 @@
 //   CommandBuffer.zig:390-411  wait_on_command_indirect (documented meaning, command_buffer.h:83-85;
 //                              NOT the double markStatus of SURVEY.md §5 quirk 1)
 //   CommandBuffer.zig:127-148,445-457  completeTask / progressCompleted
+//   CommandBuffer.zig:236-268  select_worker / select_any_worker (private queue per worker, Worker.zig:58-76)
+//   CommandBuffer.zig:459-513  abortCurrentAndForward / abortFromIndex / abortForward;
+//                              command_buffer.zig:56-70 Entry.abort; Worker.zig:115-122 abortTask (`abort` symbol)
 //   Worker.zig:250-411         worker run loop (task fetch, run, report completion)
 // Difference from the reference, stated once: tasks run on OS threads, not on stackful fibers
 // (boost.context is an un-vendored network dependency, modules/fimo_tasks/build.zig.zon:8-11).
+// `abort` unwinds the task with longjmp where the reference switches away from the fiber for good.
 // A task that blocks therefore blocks its thread; the pool compensates by keeping
 // `worker_count` runnable threads (pool_blocking_enter/exit), which is what a parked fiber
 // achieves in the reference.
+#include <algorithm>
+#include <csetjmp>
 #include <deque>
 #include <memory>
 #include <string>
@@ -29,6 +35,8 @@ std::atomic<size_t> g_next_pool_id{1};
 thread_local Pool *t_pool = nullptr;      // pool owning this thread (worker or event loop)
 thread_local bool t_is_worker = false;    // true on worker threads only
 thread_local bool t_is_spare = false;     // compensation thread
+thread_local ptrdiff_t t_worker = -1;     // index of a regular worker thread
+thread_local std::jmp_buf *t_abort = nullptr;
 } // namespace
 
 struct RtBuffer;
@@ -43,6 +51,7 @@ struct RtBuffer {
     size_t completed_index = 0; // all entries below are processed
     bool abort_on_error = false;
     bool has_error = false;
+    ptrdiff_t worker = -1; // select_worker state (CommandBuffer.zig:34)
     bool in_process_list = false;
     RtBuffer *parent = nullptr; // set for enqueue_command_buffer children
     size_t parent_entry = 0;
@@ -58,6 +67,7 @@ struct Msg {
     enum Kind { enqueue, task_done, wake } kind;
     RtBuffer *rb;
     size_t entry;
+    bool is_error = false;
 };
 
 struct WorkItem {
@@ -84,6 +94,7 @@ struct Pool {
     std::mutex q_m;
     std::condition_variable q_cv;
     std::deque<WorkItem> queue;
+    std::vector<std::deque<WorkItem>> private_queue; // Worker.zig:58-76, one per regular worker
     bool stop_workers = false;
     size_t runnable = 0;       // threads currently able to run tasks
     size_t threads_total = 0;  // live worker + spare threads
@@ -105,27 +116,40 @@ static void rb_unref(RtBuffer *rb) {
 }
 
 // ---- worker threads (Worker.zig:250-411) ---------------------------------------
-static void worker_main(Pool *p, bool spare) {
+static void worker_main(Pool *p, bool spare, ptrdiff_t index) {
     t_pool = p;
     t_is_worker = true;
     t_is_spare = spare;
+    t_worker = index;
     std::unique_lock<std::mutex> g(p->q_m);
     for (;;) {
         // A compensation thread retires as soon as the pool is back at its thread budget.
         if (spare && p->runnable > p->worker_count) break;
-        if (p->queue.empty()) {
+        // Worker.zig:262-280: the private queue first, then the pool's global queue.
+        std::deque<WorkItem> *from = &p->queue;
+        if (index >= 0 && !p->private_queue[(size_t)index].empty()) from = &p->private_queue[(size_t)index];
+        if (from->empty()) {
             if (p->stop_workers) break;
             p->q_cv.wait(g);
             continue;
         }
-        WorkItem w = p->queue.front();
-        p->queue.pop_front();
+        WorkItem w = from->front();
+        from->pop_front();
         g.unlock();
-        // Task.zig:56-67 / Worker.taskEntry: run the task body, then its completion hooks.
-        w.task->on_start(w.task);
-        if (w.task->on_complete) w.task->on_complete(w.task);
+        // Task.zig:56-67 / Worker.taskEntry: run the task body, then its completion (or abort) hook.
+        std::jmp_buf unwind;
+        volatile bool is_error = false;
+        t_abort = &unwind;
+        if (setjmp(unwind) == 0) w.task->on_start(w.task);
+        else is_error = true; // Worker.zig:115-122 abortTask
+        t_abort = nullptr;
+        if (is_error) {
+            if (w.task->on_abort) w.task->on_abort(w.task);
+        } else if (w.task->on_complete) {
+            w.task->on_complete(w.task);
+        }
         if (w.task->on_deinit) w.task->on_deinit(w.task);
-        post(p, Msg{Msg::task_done, w.rb, w.entry}); // Worker.zig:306-321 "complete" message
+        post(p, Msg{Msg::task_done, w.rb, w.entry, is_error}); // Worker.zig:306-335 "complete" message
         g.lock();
     }
     p->runnable--;
@@ -140,7 +164,7 @@ void pool_blocking_enter() {
     if (p->runnable < p->worker_count && !p->stop_workers) {
         p->runnable++;
         p->threads_total++;
-        std::thread(worker_main, p, true).detach();
+        std::thread(worker_main, p, true, (ptrdiff_t)-1).detach();
     }
 }
 
@@ -166,9 +190,66 @@ static void progress_completed(RtBuffer *rb) {
 }
 
 static void finish_buffer(Pool *p, RtBuffer *rb);
+extern const FimoTasksMeta_CommandBufferHandleVTable g_handle_vtable;
 
-static void complete_entry(Pool *p, RtBuffer *rb, size_t entry) {
+// command_buffer.zig:56-70 Entry.abort, then Entry.deinit: the entry will never be issued.
+static void abort_entry(const FimoTasksMeta_CommandBufferEntry &e) {
+    if (e.type == FIMO_TASKS_META_COMMAND_BUFFER_ENTRY_TYPE_ENQUEUE_TASK) {
+        FimoTasksMeta_Task *t = e.payload.enqueue_task;
+        if (t->on_abort) t->on_abort(t);
+        if (t->on_deinit) t->on_deinit(t);
+    } else if (e.type == FIMO_TASKS_META_COMMAND_BUFFER_ENTRY_TYPE_ENQUEUE_COMMAND_BUFFER) {
+        FimoTasksMeta_CommandBuffer *b = e.payload.enqueue_command_buffer;
+        if (b->on_abort) b->on_abort(b);
+        if (b->on_deinit) b->on_deinit(b);
+    }
+}
+
+// CommandBuffer.zig:490-513
+static void abort_forward(RtBuffer *rb) {
+    if (!rb->abort_on_error) return;
+    const FimoTasksMeta_CommandBuffer *cb = rb->buffer;
+    while (rb->entry_index < cb->entries_len) {
+        const FimoTasksMeta_CommandBufferEntry &e = cb->entries[rb->entry_index];
+        rb->status[rb->entry_index] = EntryStatus::processed;
+        rb->entry_index++;
+        if (e.type == FIMO_TASKS_META_COMMAND_BUFFER_ENTRY_TYPE_ABORT_ON_ERROR) {
+            rb->abort_on_error = e.payload.abort_on_error;
+            if (!rb->abort_on_error) break;
+        } else {
+            abort_entry(e);
+        }
+    }
+    rb->has_error = rb->abort_on_error;
+}
+
+// CommandBuffer.zig:459-466: the entry at entry_index is malformed.
+static void abort_current_and_forward(RtBuffer *rb) {
+    abort_entry(rb->buffer->entries[rb->entry_index]);
+    rb->status[rb->entry_index] = EntryStatus::processed;
+    rb->entry_index++;
+    abort_forward(rb);
+}
+
+// CommandBuffer.zig:468-488: the already-issued entry `index` ended in error.
+static void abort_from_index(RtBuffer *rb, size_t index) {
+    if (!rb->abort_on_error) return;
+    const FimoTasksMeta_CommandBuffer *cb = rb->buffer;
+    if (rb->entry_index == cb->entries_len) {
+        rb->has_error = true;
+        return;
+    }
+    for (size_t i = index; i < rb->entry_index; i++) {
+        const FimoTasksMeta_CommandBufferEntry &e = cb->entries[i];
+        if (e.type == FIMO_TASKS_META_COMMAND_BUFFER_ENTRY_TYPE_ABORT_ON_ERROR && !e.payload.abort_on_error) return;
+    }
+    abort_forward(rb);
+}
+
+// CommandBuffer.zig:127-148 completeTask
+static void complete_entry(Pool *p, RtBuffer *rb, size_t entry, bool is_error) {
     rb->status[entry] = EntryStatus::processed;
+    if (is_error) abort_from_index(rb, entry);
     progress_completed(rb);
     enqueue_process(p, rb);
 }
@@ -185,18 +266,30 @@ static bool process_buffer(Pool *p, RtBuffer *rb) {
                 rb->status[idx] = EntryStatus::processed;
                 break;
             case FIMO_TASKS_META_COMMAND_BUFFER_ENTRY_TYPE_SET_MIN_STACK_SIZE:
+                // Stack sizes have no meaning for OS-thread tasks: every request is satisfiable.
+                rb->status[idx] = EntryStatus::processed;
+                break;
             case FIMO_TASKS_META_COMMAND_BUFFER_ENTRY_TYPE_SELECT_WORKER:
+                if (e.payload.select_worker >= p->worker_count) { // :243-254
+                    abort_current_and_forward(rb);
+                    continue;
+                }
+                rb->worker = (ptrdiff_t)e.payload.select_worker;
+                rb->status[idx] = EntryStatus::processed;
+                break;
             case FIMO_TASKS_META_COMMAND_BUFFER_ENTRY_TYPE_SELECT_ANY_WORKER:
-                // Stack sizes and worker pinning have no meaning for OS-thread tasks.
+                rb->worker = -1;
                 rb->status[idx] = EntryStatus::processed;
                 break;
             case FIMO_TASKS_META_COMMAND_BUFFER_ENTRY_TYPE_ENQUEUE_TASK: {
                 rb->status[idx] = EntryStatus::running_task;
                 {
                     std::lock_guard<std::mutex> g(p->q_m);
-                    p->queue.push_back(WorkItem{rb, idx, e.payload.enqueue_task});
+                    const WorkItem w{rb, idx, e.payload.enqueue_task};
+                    if (rb->worker >= 0) p->private_queue[(size_t)rb->worker].push_back(w);
+                    else p->queue.push_back(w);
                 }
-                p->q_cv.notify_one();
+                p->q_cv.notify_all();
                 break;
             }
             case FIMO_TASKS_META_COMMAND_BUFFER_ENTRY_TYPE_ENQUEUE_COMMAND_BUFFER: {
@@ -218,27 +311,42 @@ static bool process_buffer(Pool *p, RtBuffer *rb) {
                 break;
             case FIMO_TASKS_META_COMMAND_BUFFER_ENTRY_TYPE_WAIT_ON_COMMAND_BUFFER: {
                 RtBuffer *other = (RtBuffer *)e.payload.wait_on_command_buffer.data;
-                bool other_done;
+                if (e.payload.wait_on_command_buffer.vtable != &g_handle_vtable || other->owner != p) { // :357-381
+                    abort_current_and_forward(rb);
+                    continue;
+                }
+                int other_done;
                 {
                     std::lock_guard<std::mutex> g(other->m);
-                    other_done = other->done != 0;
+                    other_done = other->done;
                 }
                 if (!other_done) {
-                    if (other->owner != p) panic("wait_on_command_buffer across pools is not restated");
-                    other->buffer_waiters.push_back(rb);
+                    auto &w = other->buffer_waiters;
+                    if (std::find(w.begin(), w.end(), rb) == w.end()) w.push_back(rb);
                     return false;
                 }
                 rb->status[idx] = EntryStatus::processed;
-                break;
+                rb->entry_index++;
+                if (other_done == 2) abort_forward(rb); // :385-387
+                continue;
             }
             case FIMO_TASKS_META_COMMAND_BUFFER_ENTRY_TYPE_WAIT_ON_COMMAND_INDIRECT: {
                 const size_t k = e.payload.wait_on_command_indirect;
-                if (k == 0 || k > idx) panic("wait_on_command_indirect out of range");
+                if (k == 0) { // :397
+                    rb->status[idx] = EntryStatus::processed;
+                    break;
+                }
+                if (k > idx) { // :398-408
+                    abort_current_and_forward(rb);
+                    continue;
+                }
                 if (rb->status[idx - k] != EntryStatus::processed) return false; // error.Block
                 rb->status[idx] = EntryStatus::processed;
                 break;
             }
-            default: panic("unknown command buffer entry");
+            default: // :413-421
+                abort_current_and_forward(rb);
+                continue;
         }
         rb->entry_index++;
     }
@@ -269,7 +377,7 @@ static void finish_buffer(Pool *p, RtBuffer *rb) {
     rb->cv.notify_all();
     if (on_deinit) on_deinit(cb);
     for (RtBuffer *w : waiters) enqueue_process(p, w);
-    if (parent) complete_entry(p, parent, parent_entry);
+    if (parent) complete_entry(p, parent, parent_entry, err);
     p->active_buffers--;
     rb_unref(rb);
 }
@@ -293,7 +401,7 @@ static void event_loop(Pool *p) {
                     p->active_buffers++;
                     enqueue_process(p, m.rb);
                     break;
-                case Msg::task_done: complete_entry(p, m.rb, m.entry); break;
+                case Msg::task_done: complete_entry(p, m.rb, m.entry, m.is_error); break;
                 case Msg::wake: break;
             }
         }
@@ -372,7 +480,7 @@ static FimoTasksMeta_CommandBufferHandleCompletionStatus h_wait_on(void *d) {
     return rb->done == 1 ? FIMO_TASKS_META_COMMAND_BUFFER_HANDLE_COMPLETION_STATUS_COMPLETED
                          : FIMO_TASKS_META_COMMAND_BUFFER_HANDLE_COMPLETION_STATUS_ABORTED;
 }
-static const FimoTasksMeta_CommandBufferHandleVTable g_handle_vtable = {h_acquire, h_release, h_owner_pool, h_wait_on};
+extern const FimoTasksMeta_CommandBufferHandleVTable g_handle_vtable = {h_acquire, h_release, h_owner_pool, h_wait_on};
 
 static FimoStatus vt_enqueue_buffer(void *d, FimoTasksMeta_CommandBuffer *buffer,
                                     FimoTasksMeta_CommandBufferHandle *handle) {
@@ -411,7 +519,8 @@ Pool *pool_create(const char *label, size_t label_len, size_t workers) {
     p->worker_count = workers;
     p->runnable = workers;
     p->threads_total = workers;
-    for (size_t i = 0; i < workers; i++) p->threads.emplace_back(worker_main, p, false);
+    p->private_queue.resize(workers);
+    for (size_t i = 0; i < workers; i++) p->threads.emplace_back(worker_main, p, false, (ptrdiff_t)i);
     p->event_thread = std::thread(event_loop, p);
     p->event_thread.detach();
     return p;
@@ -427,4 +536,16 @@ extern "C" FimoStatus fimo_tasks_create_worker_pool(const FimoTasksMeta_PoolConf
     }
     *pool = oracle::pool_handle(oracle::pool_create(config->label, config->label_len, config->worker_count));
     return FIMO_STATUS_OK;
+}
+
+// symbols.zig:94-99 `abort`; Worker.zig:115-122
+extern "C" void fimo_tasks_abort(void) {
+    if (!oracle::t_abort) oracle::panic("fimo_tasks_abort called outside a task");
+    std::longjmp(*oracle::t_abort, 1);
+}
+// symbols.zig:60-65 `worker_id`
+extern "C" bool fimo_tasks_worker_id(FimoTasksMeta_PoolWorker *id) {
+    if (oracle::t_worker < 0) return false;
+    *id = (FimoTasksMeta_PoolWorker)oracle::t_worker;
+    return true;
 }

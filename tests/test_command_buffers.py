@@ -1,0 +1,323 @@
+"""Command buffer entry set of the pool behind the path.
+
+The reference holds no test of its own for the interpreter in modules/fimo_tasks/src/CommandBuffer.zig, so the cases below are
+written from its code: in-order issue (:150-201), nested buffers (:315-337), wait_on_command_buffer (:350-388),
+wait_on_command_indirect (:390-411), select_worker (:236-268) and the three abort functions (:459-513) driven by the `abort`
+symbol (Worker.zig:115-122).  Every case runs on the CPU oracle and on the product's pool (host code, no GPU needed) and the
+two must report the same per-entry outcome.
+"""
+import ctypes as C
+import os
+import subprocess
+import time
+
+import pytest
+
+from fimo_b200 import abi, library
+from fimo_b200.worlds import create_pool
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(HERE)
+
+START, COMPLETE, ABORT, DEINIT, B_COMPLETE, B_ABORT, B_DEINIT = range(1, 8)
+COMPLETED, ABORTED = 0, 1  # command_buffer.h:118-121
+
+
+class Event(C.Structure):
+    _fields_ = [("id", C.c_int32), ("kind", C.c_int32), ("worker", C.c_int64)]
+
+
+class Log(C.Structure):
+    _fields_ = [("n", C.c_size_t), ("gate", C.c_int), ("cap", C.c_size_t), ("events", C.POINTER(Event))]
+
+
+class HandleVTable(C.Structure):
+    _fields_ = [("acquire", C.CFUNCTYPE(None, C.c_void_p)), ("release", C.CFUNCTYPE(None, C.c_void_p)),
+                ("owner_pool", C.CFUNCTYPE(abi.Pool, C.c_void_p)), ("wait_on", C.CFUNCTYPE(C.c_int32, C.c_void_p))]
+
+
+@pytest.fixture(scope="module")
+def helper():
+    out_dir = os.path.join(HERE, "helpers", "_build")
+    os.makedirs(out_dir, exist_ok=True)
+    so = os.path.join(out_dir, "libcmdbuf_helper.so")
+    src = os.path.join(HERE, "helpers", "cmdbuf_helper.c")
+    if not os.path.exists(so) or os.path.getmtime(so) < os.path.getmtime(src):
+        subprocess.run(["gcc", "-std=c11", "-O1", "-shared", "-fPIC", "-I", os.path.join(ROOT, "include"), src, "-o", so], check=True)
+    dll = C.CDLL(so)
+    dll.helper_sizeof_task.restype = dll.helper_sizeof_buffer.restype = dll.helper_event_count.restype = C.c_size_t
+    dll.helper_task_init.argtypes = [C.c_void_p, C.POINTER(Log), C.c_int32, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p]
+    dll.helper_buffer_init.argtypes = [C.c_void_p, C.POINTER(Log), C.c_int32, C.POINTER(abi.CommandBufferEntry), C.c_size_t]
+    dll.helper_open_gate.argtypes = [C.POINTER(Log)]
+    dll.helper_event_count.argtypes = [C.POINTER(Log)]
+    return dll
+
+
+@pytest.fixture(scope="module", params=["oracle", "product"])
+def lib(request, oracle):
+    return oracle if request.param == "oracle" else library.load()
+
+
+class Rig:
+    """Builds helper tasks and buffers from a small description and collects the event log."""
+
+    def __init__(self, lib, helper, workers=4):
+        self.lib, self.h = lib, helper
+        self.pool = create_pool(lib, "cmdbuf", workers)
+        self.events = (Event * 256)()
+        self.log = Log(0, 0, 256, self.events)
+        self.keep = []
+        self.abort_fn = C.cast(lib.fimo_tasks_abort, C.c_void_p)
+        self.worker_id_fn = C.cast(lib.fimo_tasks_worker_id, C.c_void_p)
+
+    def task(self, ident, abort=False, gate=False):
+        mem = C.create_string_buffer(self.h.helper_sizeof_task())
+        self.h.helper_task_init(mem, C.byref(self.log), ident, int(abort), int(gate), self.abort_fn, self.worker_id_fn)
+        self.keep.append(mem)
+        return ("task", mem)
+
+    def buffer(self, ident, *items):
+        """items: ("task", mem) | ("buffer", mem) | ("aoe", bool) | ("barrier",) | ("indirect", k) | ("worker", i) | ("any",)
+        | ("stack", n) | ("wait", handle) | ("raw", type)"""
+        entries = (abi.CommandBufferEntry * max(len(items), 1))()
+        for e, item in zip(entries, items):
+            kind = item[0]
+            if kind == "task":
+                e.type, e.payload.enqueue_task = abi.ENTRY_ENQUEUE_TASK, C.cast(item[1], C.POINTER(abi.Task))
+            elif kind == "buffer":
+                e.type, e.payload.enqueue_command_buffer = abi.ENTRY_ENQUEUE_COMMAND_BUFFER, C.addressof(item[1])
+            elif kind == "aoe":
+                e.type, e.payload.abort_on_error = abi.ENTRY_ABORT_ON_ERROR, item[1]
+            elif kind == "barrier":
+                e.type = abi.ENTRY_WAIT_ON_BARRIER
+            elif kind == "indirect":
+                e.type, e.payload.wait_on_command_indirect = abi.ENTRY_WAIT_ON_COMMAND_INDIRECT, item[1]
+            elif kind == "worker":
+                e.type, e.payload.select_worker = abi.ENTRY_SELECT_WORKER, item[1]
+            elif kind == "any":
+                e.type = abi.ENTRY_SELECT_ANY_WORKER
+            elif kind == "stack":
+                e.type, e.payload.set_min_stack_size = abi.ENTRY_SET_MIN_STACK_SIZE, item[1]
+            elif kind == "wait":
+                e.type, e.payload.wait_on_command_buffer = abi.ENTRY_WAIT_ON_COMMAND_BUFFER, item[1]
+            elif kind == "raw":
+                e.type = item[1]
+            else:
+                raise ValueError(kind)
+        mem = C.create_string_buffer(self.h.helper_sizeof_buffer())
+        self.h.helper_buffer_init(mem, C.byref(self.log), ident, entries, len(items))
+        self.keep += [entries, mem]
+        return ("buffer", mem)
+
+    def enqueue(self, buf):
+        handle = abi.CommandBufferHandle()
+        self.lib.check(self.pool.enqueue_buffer(C.cast(buf[1], C.POINTER(abi.CommandBuffer)).contents, handle))
+        return handle
+
+    @staticmethod
+    def wait(handle):
+        vt = C.cast(handle.vtable, C.POINTER(HandleVTable)).contents
+        status = vt.wait_on(handle.data)
+        return status
+
+    @staticmethod
+    def release(handle):
+        C.cast(handle.vtable, C.POINTER(HandleVTable)).contents.release(handle.data)
+
+    def settle(self, expected_events):
+        """Deinit hooks of a buffer run after its handle is signalled: wait for the log to reach its final length."""
+        deadline = time.time() + 10
+        while self.h.helper_event_count(C.byref(self.log)) < expected_events and time.time() < deadline:
+            time.sleep(0.001)
+        time.sleep(0.01)
+        n = self.h.helper_event_count(C.byref(self.log))
+        assert n == expected_events, self.trace()
+        return self.trace()
+
+    def trace(self):
+        n = min(self.h.helper_event_count(C.byref(self.log)), 256)
+        return [(self.events[i].id, self.events[i].kind, self.events[i].worker) for i in range(n)]
+
+    def close(self):
+        self.pool.unref()
+
+
+def kinds(trace, ident):
+    return [k for (i, k, _w) in trace if i == ident]
+
+
+def index(trace, ident, kind):
+    return next(n for n, (i, k, _w) in enumerate(trace) if i == ident and k == kind)
+
+
+RAN, SKIPPED, ERRORED = [START, COMPLETE, DEINIT], [ABORT, DEINIT], [START, ABORT, DEINIT]
+B_OK, B_FAILED = [B_COMPLETE, B_DEINIT], [B_ABORT, B_DEINIT]
+
+
+@pytest.fixture
+def rig(lib, helper):
+    r = Rig(lib, helper)
+    yield r
+    r.close()
+
+
+def test_nested_buffer_completes_its_entry_in_the_parent(rig):
+    child = rig.buffer(101, rig.task(1), rig.task(2))
+    parent = rig.buffer(100, rig.task(0), child, ("barrier",), rig.task(3))
+    h = rig.enqueue(parent)
+    assert rig.wait(h) == COMPLETED
+    t = rig.settle(4 * 3 + 2 * 2)
+    rig.release(h)
+    for ident in range(4):
+        assert kinds(t, ident) == RAN
+    assert kinds(t, 101) == B_OK and kinds(t, 100) == B_OK
+    # the barrier holds task 3 back until the child BUFFER (not only its tasks) has completed
+    assert index(t, 3, START) > index(t, 101, B_COMPLETE)
+    assert index(t, 3, START) > index(t, 0, COMPLETE)
+    assert index(t, 100, B_COMPLETE) > index(t, 3, COMPLETE)
+
+
+def test_wait_on_command_buffer_orders_two_buffers(rig):
+    first = rig.buffer(100, rig.task(0, gate=True))
+    h_first = rig.enqueue(first)
+    second = rig.buffer(101, ("wait", h_first), rig.task(1))
+    h_second = rig.enqueue(second)
+    time.sleep(0.02)
+    assert kinds(rig.trace(), 1) == []  # still behind the gated buffer
+    rig.h.helper_open_gate(C.byref(rig.log))
+    assert rig.wait(h_second) == COMPLETED and rig.wait(h_first) == COMPLETED
+    t = rig.settle(2 * 3 + 2 * 2)
+    assert index(t, 1, START) > index(t, 100, B_COMPLETE)
+    rig.release(h_first)
+    rig.release(h_second)
+
+
+def test_wait_on_command_indirect(rig):
+    # offset 0 is a no-op (CommandBuffer.zig:397); offset 2 waits for task 0 only, so task 2 may start while task 1 is gated
+    buf = rig.buffer(100, ("indirect", 0), rig.task(0), rig.task(1, gate=True), ("indirect", 2), rig.task(2))
+    h = rig.enqueue(buf)
+    deadline = time.time() + 10
+    while COMPLETE not in kinds(rig.trace(), 2) and time.time() < deadline:
+        time.sleep(0.001)
+    t = rig.trace()
+    assert COMPLETE in kinds(t, 2) and COMPLETE not in kinds(t, 1)
+    rig.h.helper_open_gate(C.byref(rig.log))
+    assert rig.wait(h) == COMPLETED
+    rig.settle(3 * 3 + 2)
+    rig.release(h)
+
+
+def test_task_abort_skips_the_rest_of_the_buffer(rig):
+    buf = rig.buffer(100, ("aoe", True), rig.task(0, abort=True), ("barrier",), rig.task(1), rig.buffer(101, rig.task(2)))
+    h = rig.enqueue(buf)
+    assert rig.wait(h) == ABORTED
+    t = rig.settle(3 + 2 + 2 + 2)
+    rig.release(h)
+    assert kinds(t, 0) == ERRORED and kinds(t, 1) == SKIPPED
+    assert kinds(t, 101) == B_FAILED  # the never-issued child buffer gets on_abort + on_deinit (command_buffer.zig:56-70)
+    assert kinds(t, 2) == []          # ... and its own entries are not touched
+    assert kinds(t, 100) == B_FAILED
+
+
+def test_abort_stops_at_an_abort_on_error_false_entry(rig):
+    buf = rig.buffer(100, ("aoe", True), rig.task(0, abort=True), ("barrier",), rig.task(1), ("aoe", False), rig.task(2))
+    h = rig.enqueue(buf)
+    assert rig.wait(h) == COMPLETED  # abortForward leaves has_error = abort_on_error = false (CommandBuffer.zig:512)
+    t = rig.settle(3 + 2 + 3 + 2)
+    rig.release(h)
+    assert kinds(t, 0) == ERRORED and kinds(t, 1) == SKIPPED and kinds(t, 2) == RAN and kinds(t, 100) == B_OK
+
+
+def test_errors_are_ignored_without_abort_on_error(rig):
+    buf = rig.buffer(100, rig.task(0, abort=True), ("barrier",), rig.task(1))
+    h = rig.enqueue(buf)
+    assert rig.wait(h) == COMPLETED
+    t = rig.settle(3 + 3 + 2)
+    rig.release(h)
+    assert kinds(t, 0) == ERRORED and kinds(t, 1) == RAN and kinds(t, 100) == B_OK
+
+
+def test_setting_changed_after_the_failing_entry_was_issued(rig):
+    # abortFromIndex (:476-485): the error arrives when abort_on_error is on again, but an `off` entry lies between the
+    # failing task and the issue cursor, so nothing is aborted
+    buf = rig.buffer(100, ("aoe", True), rig.task(0, abort=True, gate=True), ("aoe", False), ("aoe", True), ("barrier",), rig.task(1))
+    h = rig.enqueue(buf)
+    time.sleep(0.02)
+    rig.h.helper_open_gate(C.byref(rig.log))
+    assert rig.wait(h) == COMPLETED
+    t = rig.settle(3 + 3 + 2)
+    rig.release(h)
+    assert kinds(t, 0) == ERRORED and kinds(t, 1) == RAN
+
+
+def test_error_in_the_last_entry_aborts_the_buffer(rig):
+    buf = rig.buffer(100, ("aoe", True), rig.task(0), rig.task(1, abort=True))
+    h = rig.enqueue(buf)
+    assert rig.wait(h) == ABORTED
+    t = rig.settle(3 + 3 + 2)
+    rig.release(h)
+    assert kinds(t, 0) == RAN and kinds(t, 1) == ERRORED and kinds(t, 100) == B_FAILED
+
+
+def test_aborted_child_buffer_aborts_the_parent(rig):
+    child = rig.buffer(101, ("aoe", True), rig.task(1, abort=True))
+    parent = rig.buffer(100, ("aoe", True), child, ("barrier",), rig.task(2))
+    h = rig.enqueue(parent)
+    assert rig.wait(h) == ABORTED
+    t = rig.settle(3 + 2 + 2 + 2)
+    rig.release(h)
+    assert kinds(t, 1) == ERRORED and kinds(t, 101) == B_FAILED and kinds(t, 2) == SKIPPED and kinds(t, 100) == B_FAILED
+
+
+def test_waiting_on_an_aborted_buffer_aborts_the_waiter(rig):
+    first = rig.buffer(100, ("aoe", True), rig.task(0, abort=True, gate=True))
+    h_first = rig.enqueue(first)
+    second = rig.buffer(101, ("aoe", True), ("wait", h_first), rig.task(1))
+    h_second = rig.enqueue(second)
+    rig.h.helper_open_gate(C.byref(rig.log))
+    assert rig.wait(h_first) == ABORTED and rig.wait(h_second) == ABORTED
+    t = rig.settle(3 + 2 + 2 + 2)
+    assert kinds(t, 1) == SKIPPED and kinds(t, 101) == B_FAILED
+    # an already-aborted handle gives the same result (:385-387 on the fast path)
+    third = rig.buffer(102, ("aoe", True), ("wait", h_first), rig.task(2))
+    h_third = rig.enqueue(third)
+    assert rig.wait(h_third) == ABORTED
+    t = rig.settle(3 + 2 + 2 + 2 + 2 + 2)
+    assert kinds(t, 2) == SKIPPED
+    for h in (h_first, h_second, h_third):
+        rig.release(h)
+
+
+@pytest.mark.parametrize("bad", [("indirect", 7), ("worker", 99), ("raw", 42)], ids=["indirect-out-of-range", "unknown-worker", "unknown-entry"])
+def test_malformed_entries_abort_instead_of_panicking(rig, bad):
+    # CommandBuffer.zig:243-254, :398-408, :413-421
+    buf = rig.buffer(100, ("aoe", True), rig.task(0), ("barrier",), bad, rig.task(1))
+    h = rig.enqueue(buf)
+    assert rig.wait(h) == ABORTED
+    t = rig.settle(3 + 2 + 2)
+    rig.release(h)
+    assert kinds(t, 0) == RAN and kinds(t, 1) == SKIPPED and kinds(t, 100) == B_FAILED
+    # without abort_on_error the malformed entry is dropped and the buffer goes on
+    buf = rig.buffer(200, bad, rig.task(10))
+    h = rig.enqueue(buf)
+    assert rig.wait(h) == COMPLETED
+    t = rig.settle(3 + 2 + 2 + 3 + 2)
+    rig.release(h)
+    assert kinds(t, 10) == RAN and kinds(t, 200) == B_OK
+
+
+def test_select_worker_pins_the_following_tasks(rig):
+    buf = rig.buffer(100, ("stack", 1 << 16), ("worker", 2), rig.task(0), rig.task(1), ("worker", 1), rig.task(2), ("any",), rig.task(3))
+    h = rig.enqueue(buf)
+    assert rig.wait(h) == COMPLETED
+    t = rig.settle(4 * 3 + 2)
+    rig.release(h)
+    worker_of = {i: w for (i, k, w) in t if k == START}
+    assert worker_of[0] == 2 and worker_of[1] == 2 and worker_of[2] == 1
+    assert 0 <= worker_of[3] < 4
+    assert index(t, 1, START) > index(t, 0, COMPLETE)  # one worker: its tasks run one after the other
+
+
+def test_worker_id_is_false_outside_the_pool(lib):
+    w = C.c_size_t(123)
+    assert lib.fimo_tasks_worker_id(C.byref(w)) is False and w.value == 123
