@@ -376,6 +376,65 @@ class TraceEvent(C.Structure):  # FimoB200_TraceEvent
 TraceSinkFn = C.CFUNCTYPE(None, c_void_p, POINTER(TraceEvent))
 
 
+# fimo tracing subscriber events (fimo_std/tracing.h:35-56,72-204) the bridge emits
+class Instant(C.Structure):
+    _fields_ = [("secs", c_uint64), ("nanos", c_uint32)]
+
+
+class TracingEventInfo(C.Structure):
+    _fields_ = [("name", c_char_p), ("target", c_char_p), ("scope", c_char_p), ("file_name", c_char_p),
+                ("line_number", C.c_int32), ("level", C.c_int32)]
+
+
+class TracingCallStackEvent(C.Structure):  # create / destroy call stack
+    _fields_ = [("event", c_uint32), ("time", Instant), ("stack", c_void_p)]
+
+
+class TracingEnterSpan(C.Structure):  # also log_message (same layout: info instead of span)
+    _fields_ = [("event", c_uint32), ("time", Instant), ("stack", c_void_p), ("span", POINTER(TracingEventInfo)),
+                ("message", c_void_p), ("message_length", c_size_t)]
+
+
+class TracingExitSpan(C.Structure):
+    _fields_ = [("event", c_uint32), ("time", Instant), ("stack", c_void_p), ("is_unwinding", C.c_bool)]
+
+
+class TracingDeclareEventInfo(C.Structure):
+    _fields_ = [("event", c_uint32), ("info", POINTER(TracingEventInfo))]
+
+
+TracingOnEventFn = C.CFUNCTYPE(None, c_void_p, POINTER(c_uint32))
+
+
+class TracingSubscriber(C.Structure):
+    _fields_ = [("ptr", c_void_p), ("on_event", TracingOnEventFn)]
+
+
+(TRACING_EVENT_CREATE_CALL_STACK, TRACING_EVENT_DESTROY_CALL_STACK, TRACING_EVENT_ENTER_SPAN, TRACING_EVENT_EXIT_SPAN,
+ TRACING_EVENT_LOG_MESSAGE, TRACING_EVENT_DECLARE_EVENT_INFO) = 4, 5, 9, 10, 11, 12
+
+
+def decode_tracing_event(ptr):
+    """(kind, dict) of one subscriber event, read through the struct its tag names."""
+    kind = ptr[0]
+    if kind in (TRACING_EVENT_CREATE_CALL_STACK, TRACING_EVENT_DESTROY_CALL_STACK):
+        e = C.cast(ptr, POINTER(TracingCallStackEvent)).contents
+        return kind, {"ns": e.time.secs * 10**9 + e.time.nanos, "stack": e.stack}
+    if kind in (TRACING_EVENT_ENTER_SPAN, TRACING_EVENT_LOG_MESSAGE):
+        e = C.cast(ptr, POINTER(TracingEnterSpan)).contents
+        info = e.span.contents
+        return kind, {"ns": e.time.secs * 10**9 + e.time.nanos, "stack": e.stack, "info": C.addressof(info),
+                      "name": info.name.decode(), "target": info.target.decode(), "scope": info.scope.decode(), "level": info.level,
+                      "message": C.string_at(e.message, e.message_length).decode()}
+    if kind == TRACING_EVENT_EXIT_SPAN:
+        e = C.cast(ptr, POINTER(TracingExitSpan)).contents
+        return kind, {"ns": e.time.secs * 10**9 + e.time.nanos, "stack": e.stack, "is_unwinding": bool(e.is_unwinding)}
+    if kind == TRACING_EVENT_DECLARE_EVENT_INFO:
+        e = C.cast(ptr, POINTER(TracingDeclareEventInfo)).contents
+        return kind, {"info": C.addressof(e.info.contents), "name": e.info.contents.name.decode()}
+    return kind, {}
+
+
 # device-side helpers: product library only
 PRODUCT_SYMBOLS = [
     ("fimo_b200_builtin_system", FimoStatus, [c_uint32, POINTER(SystemDescriptor), POINTER(SystemDeviceExt)]),
@@ -392,6 +451,7 @@ PRODUCT_SYMBOLS = [
     ("fimo_b200_group_schedule_io", FimoStatus, [c_void_p, c_void_p, c_size_t, c_void_p, c_size_t, c_void_p, c_size_t, POINTER(Fence)]),
     ("fimo_b200_group_schedule_readback", FimoStatus, [c_void_p, c_void_p, c_size_t, c_void_p, c_void_p, c_size_t, POINTER(Fence)]),
     ("fimo_worlds_b200_set_trace_sink", None, [TraceSinkFn, c_void_p]),
+    ("fimo_worlds_b200_trace_subscribe", FimoStatus, [POINTER(TracingSubscriber), c_size_t]),
     ("fimo_b200_host_alloc", c_void_p, [c_size_t]),
     ("fimo_b200_host_free", None, [c_void_p]),
     ("fimo_b200_group_stats_peers_open", FimoStatus, [c_void_p, c_uint32, c_void_p]),

@@ -57,6 +57,12 @@ struct BlockingScope {
     BlockingScope &operator=(const BlockingScope &) = delete;
 };
 
+// ---- tracing.cpp ------------------------------------------------------------------------------
+// fimo tracing subscribers attached with fimo_worlds_b200_trace_subscribe (tracing.zig:387-565).
+bool trace_bridge_active();
+void trace_bridge_generation(const void *group, const FimoB200_TraceEvent &event);
+void trace_bridge_group_destroyed(const void *group);
+
 // Reader/writer lock with try-lock; may be released by a different thread than the one that
 // acquired it (a device generation locks on the scheduling thread and unlocks on the
 // completion thread).  Writer-preferring like sync/RwLock.zig.

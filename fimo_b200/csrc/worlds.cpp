@@ -1295,6 +1295,7 @@ void dispatcher_main(Group *g);
 
 std::atomic<FimoB200_trace_sink> g_trace_sink{nullptr};
 std::atomic<void *> g_trace_user{nullptr};
+bool tracing_wanted() { return g_trace_sink.load(std::memory_order_relaxed) || trace_bridge_active(); }
 int64_t monotonic_ns() {
     return std::chrono::duration_cast<std::chrono::nanoseconds>(std::chrono::steady_clock::now().time_since_epoch()).count();
 }
@@ -1304,14 +1305,16 @@ void device_generation_done(void *user) {
     // SystemGroup.run (:477-486) and the Job cleanup (Job.zig:234-247).
     std::unique_ptr<DeviceDone> done((DeviceDone *)user);
     Group *g = done->group;
-    if (FimoB200_trace_sink sink = g_trace_sink.load(std::memory_order_acquire)) { // before the group may be destroyed
+    FimoB200_trace_sink sink = g_trace_sink.load(std::memory_order_acquire);
+    if (sink || trace_bridge_active()) { // before the group may be destroyed
         FimoB200_TraceEvent ev{};
         ev.group_label = g->label.data(), ev.group_label_len = g->label.size();
         ev.generation = done->generation;
         ev.device_ms = dev::executor_last_generation_ms(g->executor_dev);
         ev.host_enqueue_ns = done->enqueue_ns, ev.host_complete_ns = monotonic_ns();
         ev.kernels = g->info.kernel_launches_per_generation, ev.fused_world_step = g->info.fused_world_step;
-        sink(g_trace_user.load(std::memory_order_acquire), &ev);
+        if (sink) sink(g_trace_user.load(std::memory_order_acquire), &ev);
+        trace_bridge_generation(g, ev); // fimo tracing subscribers (tracing.cpp)
     }
     size_t gen;
     {
@@ -1403,7 +1406,7 @@ int start_device_generation(Group *g, Job *job, bool blocking, const char **err)
     }
     g->in_flight++;
     g->launches_in_flight++;
-    DeviceDone *done = new DeviceDone{g, job->signal, (uint64_t)job->generation, g_trace_sink.load(std::memory_order_relaxed) ? monotonic_ns() : 0};
+    DeviceDone *done = new DeviceDone{g, job->signal, (uint64_t)job->generation, tracing_wanted() ? monotonic_ns() : 0};
     if (g->stats_x) dev::stats_exchange_before_launch(g->stats_x, dev::executor_stream(g->executor_dev), 1);
     if (!dev::executor_launch(g->executor_dev, &device_generation_done, done, ups.data(), ups.size(), downs.data(), downs.size(),
                               job->has_readback ? &rb : nullptr)) {
@@ -1440,7 +1443,7 @@ void launch_pending_batches(Group *g) {
         return;
     }
     const uint32_t max_gens = dev::executor_max_gens(g->executor_dev);
-    const int64_t now = g_trace_sink.load(std::memory_order_relaxed) ? monotonic_ns() : 0;
+    const int64_t now = tracing_wanted() ? monotonic_ns() : 0;
     while (!g->batch_pending.empty()) {
         const uint32_t n = (uint32_t)std::min<size_t>(g->batch_pending.size(), max_gens);
         std::vector<void *> users(n);
@@ -1484,10 +1487,19 @@ void run_host_generation(Group *g, Job *job) {
     buffer.entries = g->entries.data();
     buffer.entries_len = g->entries.size();
     FimoTasksMeta_CommandBufferHandle handle{};
+    const int64_t t_enqueue = trace_bridge_active() ? monotonic_ns() : 0;
     if (g->executor.vtable->enqueue_buffer(g->executor.data, &buffer, &handle) != FIMO_STATUS_OK)
         panic("enqueue of the systems buffer failed");
     handle.vtable->wait_on(handle.data);
     handle.vtable->release(handle.data);
+    if (t_enqueue) { // a host generation is a span too: the systems buffer between enqueue and completion (kernels = 0)
+        FimoB200_TraceEvent ev{};
+        ev.group_label = g->label.data(), ev.group_label_len = g->label.size();
+        ev.generation = (uint64_t)job->generation;
+        ev.host_enqueue_ns = t_enqueue, ev.host_complete_ns = monotonic_ns();
+        ev.device_ms = (double)(ev.host_complete_ns - t_enqueue) / 1.0e6;
+        trace_bridge_generation(g, ev);
+    }
     size_t gen;
     {
         std::lock_guard<std::mutex> lock(g->m);
@@ -1666,6 +1678,7 @@ void group_destroy(Group *g) {
         g->backlog_cv.notify_all();
     }
     if (g->dispatcher.joinable()) g->dispatcher.join();
+    trace_bridge_group_destroyed(g); // its call stack ends (tracing.cpp)
     if (g->executor_dev) dev::executor_destroy(g->executor_dev);
     dev::stats_exchange_destroy(g->stats_x);
     g->world->groups.fetch_sub(1, std::memory_order_relaxed);

@@ -849,6 +849,101 @@ typedef struct FimoB200_TraceEvent {
 typedef void (*FimoB200_trace_sink)(void *user, const FimoB200_TraceEvent *event);
 FIMO_B200_EXPORT void fimo_worlds_b200_set_trace_sink(FimoB200_trace_sink sink, void *user);
 
+/* The same information as fimo tracing events.  A fimo tracing *subscriber* (pkgs/fimo_std/include/fimo_std/
+ * tracing.h:199-204; tracing.zig:562-565: `{data, on_event(data, *const Event)}`) receives extern structs that
+ * start with the `Event` tag (tracing.zig:387-554, tracing.h:72-192).  The structs below are byte-identical
+ * mirrors of the ones the bridge emits (tests/golden/abi_layout.json pins them against the reference header), so
+ * the module shim can hand the context's own subscribers — the `.ftrdb` writer included — to
+ * fimo_worlds_b200_trace_subscribe and device generations show up as spans:
+ *
+ *   first generation of a group : declare_event_info(span id), create_call_stack(stack = one token per group)
+ *   every generation            : enter_span(time = device start, stack, span id, message
+ *                                 "<label> generation <n>: <k> kernels, <t> ms on device"),
+ *                                 [log_message per kernel-level record when the executor collected one],
+ *                                 exit_span(time = device end, stack, is_unwinding = false)
+ *   unsubscribe / group destroy : destroy_call_stack(stack)
+ *
+ * Times are FimoInstant on the host's monotonic clock (the clock fimo_instant_now reads, time.zig:363-420):
+ * exit = the completion thread's observation of the end event, enter = exit - device time between the two CUDA
+ * events that bracket the generation.  Events of one group are delivered in generation order from the completion
+ * thread, never from inside a CUDA callback. */
+typedef FimoI32 FimoTracingLevel; /* tracing.h:18-25 */
+enum {
+    FIMO_TRACING_LEVEL_OFF = 0,
+    FIMO_TRACING_LEVEL_ERROR = 1,
+    FIMO_TRACING_LEVEL_WARN = 2,
+    FIMO_TRACING_LEVEL_INFO = 3,
+    FIMO_TRACING_LEVEL_DEBUG = 4,
+    FIMO_TRACING_LEVEL_TRACE = 5,
+};
+typedef struct FimoTracingEventInfo { /* tracing.h:35-56 */
+    const char *name;
+    const char *target;
+    const char *scope;
+    const char *file_name;
+    FimoI32 line_number;
+    FimoTracingLevel level;
+} FimoTracingEventInfo;
+typedef uint32_t FimoTracingEvent; /* tracing.h:72-94, tracing.zig:389-411 */
+enum {
+    FIMO_TRACING_EVENT_START = 0,
+    FIMO_TRACING_EVENT_FINISH = 1,
+    FIMO_TRACING_EVENT_REGISTER_THREAD = 2,
+    FIMO_TRACING_EVENT_UNREGISTER_THREAD = 3,
+    FIMO_TRACING_EVENT_CREATE_CALL_STACK = 4,
+    FIMO_TRACING_EVENT_DESTROY_CALL_STACK = 5,
+    FIMO_TRACING_EVENT_UNBLOCK_CALL_STACK = 6,
+    FIMO_TRACING_EVENT_SUSPEND_CALL_STACK = 7,
+    FIMO_TRACING_EVENT_RESUME_CALL_STACK = 8,
+    FIMO_TRACING_EVENT_ENTER_SPAN = 9,
+    FIMO_TRACING_EVENT_EXIT_SPAN = 10,
+    FIMO_TRACING_EVENT_LOG_MESSAGE = 11,
+    FIMO_TRACING_EVENT_DECLARE_EVENT_INFO = 12,
+};
+typedef struct FimoTracingEventCreateCallStack { /* tracing.h:137-141 */
+    FimoTracingEvent event;
+    FimoInstant time;
+    void *stack;
+} FimoTracingEventCreateCallStack;
+typedef struct FimoTracingEventDestroyCallStack { /* tracing.h:143-147 */
+    FimoTracingEvent event;
+    FimoInstant time;
+    void *stack;
+} FimoTracingEventDestroyCallStack;
+typedef struct FimoTracingEventEnterSpan { /* tracing.h:169-176 */
+    FimoTracingEvent event;
+    FimoInstant time;
+    void *stack;
+    const FimoTracingEventInfo *span;
+    const char *message;
+    FimoUSize message_length;
+} FimoTracingEventEnterSpan;
+typedef struct FimoTracingEventExitSpan { /* tracing.h:178-183 */
+    FimoTracingEvent event;
+    FimoInstant time;
+    void *stack;
+    bool is_unwinding;
+} FimoTracingEventExitSpan;
+typedef struct FimoTracingEventLogMessage { /* tracing.h:185-192 */
+    FimoTracingEvent event;
+    FimoInstant time;
+    void *stack;
+    const FimoTracingEventInfo *info;
+    const char *message;
+    FimoUSize message_length;
+} FimoTracingEventLogMessage;
+typedef struct FimoTracingEventDeclareEventInfo { /* tracing.zig:505-508 */
+    FimoTracingEvent event;
+    const FimoTracingEventInfo *info;
+} FimoTracingEventDeclareEventInfo;
+typedef struct FimoTracingSubscriber { /* tracing.h:199-204 */
+    void *ptr;
+    void (*on_event)(void *data, const FimoTracingEvent *event);
+} FimoTracingSubscriber;
+/* Attaches up to 8 subscribers (copied); NULL / 0 detaches all of them (each live group's call stack is destroyed
+ * first).  Independent of fimo_worlds_b200_set_trace_sink. */
+FIMO_B200_EXPORT FimoStatus fimo_worlds_b200_trace_subscribe(const FimoTracingSubscriber *subscribers, FimoUSize count);
+
 /* What the DAG compiler produced for the group's current system set. */
 typedef struct FimoB200_ExecutorInfo {
     uint32_t systems;          /* member systems */

@@ -52,6 +52,14 @@ STRUCTS = {
     "FimoWorldsMeta_WorldDescriptor": ["next", "label", "label_len", "pool"],
     "FimoDuration": ["secs", "nanos"],
     "FimoInstant": ["secs", "nanos"],
+    # tracing subscriber events the bridge emits (fimo_std/tracing.h:35-56,137-147,169-204)
+    "FimoTracingEventInfo": ["name", "target", "scope", "file_name", "line_number", "level"],
+    "FimoTracingEventCreateCallStack": ["event", "time", "stack"],
+    "FimoTracingEventDestroyCallStack": ["event", "time", "stack"],
+    "FimoTracingEventEnterSpan": ["event", "time", "stack", "span", "message", "message_length"],
+    "FimoTracingEventExitSpan": ["event", "time", "stack", "is_unwinding"],
+    "FimoTracingEventLogMessage": ["event", "time", "stack", "info", "message", "message_length"],
+    "FimoTracingSubscriber": ["ptr", "on_event"],
 }
 # enumerators / constants whose VALUES are part of the ABI
 CONSTANTS = [
@@ -71,6 +79,10 @@ CONSTANTS = [
     "FIMO_WORLDS_META_SYSTEM_DEPENDENCY_FLAGS_WEAK", "FIMO_WORLDS_META_SYSTEM_DEPENDENCY_FLAGS_IGNORE_DEFERRED",
     "FIMO_WORLDS_META_SYSTEM_ALLOCATOR_STRATEGY_TRANSIENT", "FIMO_WORLDS_META_SYSTEM_ALLOCATOR_STRATEGY_SINGLE_GENERATION",
     "FIMO_WORLDS_META_SYSTEM_ALLOCATOR_STRATEGY_MULTI_GENERATION", "FIMO_WORLDS_META_SYSTEM_ALLOCATOR_STRATEGY_SYSTEM_PERSISTENT",
+    "FIMO_TRACING_EVENT_CREATE_CALL_STACK", "FIMO_TRACING_EVENT_DESTROY_CALL_STACK", "FIMO_TRACING_EVENT_ENTER_SPAN",
+    "FIMO_TRACING_EVENT_EXIT_SPAN", "FIMO_TRACING_EVENT_LOG_MESSAGE", "FIMO_TRACING_EVENT_DECLARE_EVENT_INFO",
+    "FIMO_TRACING_LEVEL_OFF", "FIMO_TRACING_LEVEL_ERROR", "FIMO_TRACING_LEVEL_WARN", "FIMO_TRACING_LEVEL_INFO",
+    "FIMO_TRACING_LEVEL_DEBUG", "FIMO_TRACING_LEVEL_TRACE",
 ]
 
 
@@ -122,7 +134,7 @@ def reference_layout() -> dict:
                       "atomic_compare_exchange_weak_explicit(&fence->state, &(FimoU8){FIMO_WORLDS_META_FENCE_UNSIGNALED},", text)
         open(jobs, "w").write(text)
         incs = [tmp, os.path.join(REF, "pkgs/fimo_std/include"), os.path.join(REF, "pkgs/fimo_tasks_meta/include")]
-        return layout_of(incs, ["fimo_std/time.h", "fimo_tasks_meta/package.h", "fimo_worlds_meta/jobs.h",
+        return layout_of(incs, ["fimo_std/time.h", "fimo_std/tracing.h", "fimo_tasks_meta/package.h", "fimo_worlds_meta/jobs.h",
                                 "fimo_worlds_meta/resources.h", "fimo_worlds_meta/systems.h", "fimo_worlds_meta/worlds.h"])
     finally:
         shutil.rmtree(tmp, ignore_errors=True)
