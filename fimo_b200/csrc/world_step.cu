@@ -88,6 +88,37 @@ __device__ __forceinline__ void bulk_load(void *dst, const void *src, uint32_t b
                  : "memory");
 }
 
+// L2 eviction priorities (createpolicy): team mode streams 3.3 GB per step through the 126 MB L2 while the 48-byte
+// parent rows (58 MB, re-read a few tens of microseconds after they are written) must stay in it — the streamed chunk
+// inputs and outputs are marked evict_first, the rows evict_last.
+__device__ __forceinline__ uint64_t l2_evict_first() {
+    uint64_t p;
+    asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(p));
+    return p;
+}
+__device__ __forceinline__ uint64_t l2_evict_last() {
+    uint64_t p;
+    asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(p));
+    return p;
+}
+__device__ __forceinline__ void bulk_load_hint(void *dst, const void *src, uint32_t bytes, uint64_t *bar, uint64_t policy) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;" ::"r"(smem_addr(dst)),
+                 "l"(src), "r"(bytes), "r"(smem_addr(bar)), "l"(policy)
+                 : "memory");
+}
+__device__ __forceinline__ void bulk_store_hint(void *dst, const void *src, uint32_t bytes, uint64_t policy) {
+    asm volatile("cp.async.bulk.global.shared::cta.bulk_group.L2::cache_hint [%0], [%1], %2, %3;" ::"l"(dst), "r"(smem_addr(src)), "r"(bytes), "l"(policy)
+                 : "memory");
+}
+__device__ __forceinline__ void st_row_hint(float4 *dst, const float4 &v, uint64_t policy) {
+    asm volatile("st.global.L2::cache_hint.v4.f32 [%0], {%1, %2, %3, %4}, %5;" ::"l"(dst), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w), "l"(policy) : "memory");
+}
+__device__ __forceinline__ float4 ld_row_hint(const float4 *src, uint64_t policy) {
+    float4 v;
+    asm volatile("ld.global.cg.L2::cache_hint.v4.f32 {%0, %1, %2, %3}, [%4], %5;" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(src), "l"(policy) : "memory");
+    return v;
+}
+
 // 1-D bulk async copy shared -> global (TMA engine), tracked by the issuing thread's bulk async-group.
 __device__ __forceinline__ void bulk_store(void *dst, const void *src, uint32_t bytes) {
     asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst), "r"(smem_addr(src)), "r"(bytes) : "memory");
@@ -157,6 +188,7 @@ constexpr uint32_t kPipePrevCopy = 16u;        // kSet 2: prev_copy is a member 
 constexpr uint32_t kPipePublishPerChunk = 2u; // FIMO_B200_PUBLISH=chunk: announce level progress after every chunk
 constexpr uint32_t kPipePrefetchBlocking = 4u; // FIMO_B200_PREFETCH=2: wait for the next chunk's inputs before this chunk's math
 constexpr uint32_t kPipeNoPrefetch = 1u; // FIMO_B200_PREFETCH=0: parent rows are loaded where they are used
+constexpr uint32_t kPipeNoL2Hints = 32u; // FIMO_B200_L2_HINTS=0: team mode without L2 eviction priorities (A/B runs)
 
 // Per-world constants, double-buffered in shared memory (world k uses buffer k & 1): the compute threads
 // fetch world k+1's words into a register while world k is being stepped and publish them before the last
@@ -227,10 +259,19 @@ struct Cursor {
 // The TMA warp (one elected thread): loads chunk inputs into the ring and stores the finished chunk's
 // outputs, which the compute threads leave in the same ring stage (world matrices over planes 0-11, new
 // positions over 12-14).
-template <int T, int kSet>
+template <int T, int kSet, bool kHint>
 __device__ __forceinline__ void tma_warp(const PipeArgs &pa, const Walk &wk, float *ring, uint64_t *full, uint64_t *done) {
     constexpr int kIn = SetTraits<kSet>::kIn, kStage = SetTraits<kSet>::kStage;
     const StepArgs &a = pa.a;
+    const uint64_t stream_policy = kHint ? l2_evict_first() : 0ull; // kHint (team mode): streamed data leaves L2 first
+    auto bulk_store = [&](void *dst, const void *src, uint32_t bytes) {
+        if (kHint && !(pa.flags & kPipeNoL2Hints)) bulk_store_hint(dst, src, bytes, stream_policy);
+        else fb::dev::bulk_store(dst, src, bytes);
+    };
+    auto bulk_load = [&](void *dst, const void *src, uint32_t bytes, uint64_t *bar) {
+        if (kHint && !(pa.flags & kPipeNoL2Hints)) bulk_load_hint(dst, src, bytes, bar, stream_policy);
+        else fb::dev::bulk_load(dst, src, bytes, bar);
+    };
     const uint32_t E = a.entities, N = pa.stages, all = wk.total * pa.gens;
     uint32_t s = 0, round = 0;
     Cursor ld(pa, wk), st_(pa, wk); // the chunk being loaded; the chunk being stored (N behind)
@@ -309,6 +350,9 @@ __device__ __forceinline__ bool mbar_test(uint64_t *bar, uint32_t parity) {
 __device__ __forceinline__ void cp_async16(void *dst, const void *src) {
     asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_addr(dst)), "l"(src) : "memory");
 }
+__device__ __forceinline__ void cp_async16_hint(void *dst, const void *src, uint64_t policy) {
+    asm volatile("cp.async.cg.shared.global.L2::cache_hint [%0], [%1], 16, %2;" ::"r"(smem_addr(dst)), "l"(src), "l"(policy) : "memory");
+}
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 __device__ __forceinline__ void cp_async_wait_all_but_latest() { asm volatile("cp.async.wait_group 1;" ::: "memory"); }
 
@@ -381,7 +425,7 @@ __global__ void __launch_bounds__(T + 32, kMinBlocks) k_world_step_pipe(const Pi
     __syncthreads();
 
     if (warp == kWarps) {
-        if (lane == 0) tma_warp<T, kSet>(pa, wk, ring, full, done);
+        if (lane == 0) tma_warp<T, kSet, kTeam>(pa, wk, ring, full, done);
         return;
     }
 
@@ -440,7 +484,10 @@ __global__ void __launch_bounds__(T + 32, kMinBlocks) k_world_step_pipe(const Pi
     int ready_upto = -1; // team mode: levels [0, ready_upto] of the current world are known to be complete
     uint32_t *mask_out = nullptr, *list_out = nullptr;
     float4 *rows = nullptr;
-    uint32_t *lvl_done = nullptr;
+    uint32_t *lvl_done = nullptr, *lvl_prev = nullptr;
+    int guard_upto = -1; // team mode: rows of levels [0, guard_upto] of the PREVIOUS world are known to have no readers left
+    const uint64_t row_policy = kTeam ? l2_evict_last() : 0ull;
+    const bool l2_hints = kTeam && !(pa.flags & kPipeNoL2Hints);
     float *waabb_out = nullptr;
     uint32_t *mask2_out = nullptr, *list2_out = nullptr, *sleep_out = nullptr, *lod_out = nullptr;
     const float *world_old = nullptr; // kSet 2 + prev_copy
@@ -462,8 +509,14 @@ __global__ void __launch_bounds__(T + 32, kMinBlocks) k_world_step_pipe(const Pi
             running = 0, running2 = 0, l_lo = 0, ready_upto = -1;
             mask_out = uptr(a.vis_mask, w);
             list_out = uptr(a.vis_list, w);
-            rows = pa.rows ? pa.rows + w * (uint64_t)E * 3 : nullptr;
-            if (kTeam) lvl_done = pa.lvl_done + w * kMaxLevels;
+            // team mode: ONE rows buffer per team, reused by every world the team steps, so the rows' footprint
+            // (teams x parents x 48 B) fits L2 and a dirty row line is overwritten in place instead of written back
+            rows = pa.rows ? pa.rows + (kTeam ? (uint64_t)wk.team_id : w) * (uint64_t)E * 3 : nullptr;
+            if (kTeam) {
+                lvl_prev = lvl_done; // the world this team stepped before (nullptr: none): its readers guard row reuse
+                lvl_done = pa.lvl_done + w * kMaxLevels;
+                guard_upto = -1;
+            }
             if (kSet >= 1) waabb_out = fptr(a.waabb, w);
             if (kSet == 2) {
                 mask2_out = uptr(a.vis_mask2, w), list2_out = uptr(a.vis_list2, w);
@@ -510,7 +563,8 @@ __global__ void __launch_bounds__(T + 32, kMinBlocks) k_world_step_pipe(const Pi
                     if (nfirst + tid < E && np != kRoot) {
                         const float4 *src = rows + (uint64_t)np * 3;
                         float4 *dst = s_pre + ((size_t)((it + 1) & 1) * T + tid) * 3;
-                        cp_async16(dst, src), cp_async16(dst + 1, src + 1), cp_async16(dst + 2, src + 2);
+                        if (l2_hints) cp_async16_hint(dst, src, row_policy), cp_async16_hint(dst + 1, src + 1, row_policy), cp_async16_hint(dst + 2, src + 2, row_policy);
+                        else cp_async16(dst, src), cp_async16(dst + 1, src + 1), cp_async16(dst + 2, src + 2);
                     }
                     pre_next = true;
                 }
@@ -519,17 +573,29 @@ __global__ void __launch_bounds__(T + 32, kMinBlocks) k_world_step_pipe(const Pi
             if (kTimingBuild && pa.timing && tid == 0) tm_pre += clock64() - t_pre0, tm_prefetched += pre_next ? 1 : 0;
         }
         for (uint32_t l = l_lo; l <= l_hi; l++) {
-            if (kTeam && l >= 1 && ready_upto < (int)l - 1) {
-                flush_pending(lvl_done); // our own share of level l-1 (same chunk) counts too
-                // every entity of level l-1 — in whichever CTA's chunk — must be visible in `rows`
+            // Row reuse across worlds: this chunk overwrites the team's rows of level l, which level l + 1 of the
+            // PREVIOUS world read.  That level must be complete (it almost always is: the wait returns at once).
+            const bool guard = kTeam && lvl_prev && l + 1 < levels && guard_upto < (int)l;
+            if (kTeam && ((l >= 1 && ready_upto < (int)l - 1) || guard)) {
+                const bool wait_level = l >= 1 && ready_upto < (int)l - 1;
+                if (wait_level) flush_pending(lvl_done); // our own share of level l-1 (same chunk) counts too
                 if (tid == 0) {
-                    const uint32_t need = wc.ls[l] - wc.ls[l - 1];
                     const long long t_lv0 = (kTimingBuild && pa.timing) ? clock64() : 0;
-                    while (ld_acquire_gpu(lvl_done + (l - 1)) < need) __nanosleep(64);
+                    if (guard) {
+                        const WorldConst &pc = s_c[(kk + 1) & 1]; // the previous world's constants are still in the other buffer
+                        const uint32_t need_prev = pc.ls[l + 2] - pc.ls[l + 1];
+                        while (ld_acquire_gpu(lvl_prev + (l + 1)) < need_prev) __nanosleep(64);
+                    }
+                    // every entity of level l-1 — in whichever CTA's chunk — must be visible in `rows`
+                    if (wait_level) {
+                        const uint32_t need = wc.ls[l] - wc.ls[l - 1];
+                        while (ld_acquire_gpu(lvl_done + (l - 1)) < need) __nanosleep(64);
+                    }
                     if (kTimingBuild && pa.timing) tm_level += clock64() - t_lv0;
                 }
                 consumer_sync<T>();
-                ready_upto = (int)l - 1;
+                if (wait_level) ready_upto = (int)l - 1;
+                if (guard) guard_upto = (int)l;
             }
             if (valid && l_me == l) {
                 const float dt = wc.dt;
@@ -571,7 +637,8 @@ __global__ void __launch_bounds__(T + 32, kMinBlocks) k_world_step_pipe(const Pi
                     } else { // beyond the shared-memory window: the parent's row comes back through L2
                         const float4 *row = rows + (uint64_t)p * 3;
                         const long long t_g0 = (kTimingBuild && pa.timing && tid == 0) ? clock64() : 0;
-                        r0 = __ldcg(row), r1 = __ldcg(row + 1), r2 = __ldcg(row + 2);
+                        if (l2_hints) r0 = ld_row_hint(row, row_policy), r1 = ld_row_hint(row + 1, row_policy), r2 = ld_row_hint(row + 2, row_policy);
+                        else r0 = __ldcg(row), r1 = __ldcg(row + 1), r2 = __ldcg(row + 2);
                         if (kTimingBuild && pa.timing && tid == 0) tm_gather += (long long)(r0.x != r1.x) * 0 + clock64() - t_g0;
                     }
                     const float P[12] = {r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, r1.w, r2.x, r2.y, r2.z, r2.w};
@@ -596,9 +663,15 @@ __global__ void __launch_bounds__(T + 32, kMinBlocks) k_world_step_pipe(const Pi
                 }
                 if (may_be_parent) { // 48-byte rows: three 128-bit stores, conflict-free in shared memory
                     float4 *row = (!kTeam && e < cap) ? s_win + 3 * e : rows + (uint64_t)e * 3;
-                    row[0] = make_float4(Wm[0], Wm[1], Wm[2], Wm[3]);
-                    row[1] = make_float4(Wm[4], Wm[5], Wm[6], Wm[7]);
-                    row[2] = make_float4(Wm[8], Wm[9], Wm[10], Wm[11]);
+                    if (l2_hints) {
+                        st_row_hint(row, make_float4(Wm[0], Wm[1], Wm[2], Wm[3]), row_policy);
+                        st_row_hint(row + 1, make_float4(Wm[4], Wm[5], Wm[6], Wm[7]), row_policy);
+                        st_row_hint(row + 2, make_float4(Wm[8], Wm[9], Wm[10], Wm[11]), row_policy);
+                    } else {
+                        row[0] = make_float4(Wm[0], Wm[1], Wm[2], Wm[3]);
+                        row[1] = make_float4(Wm[4], Wm[5], Wm[6], Wm[7]);
+                        row[2] = make_float4(Wm[8], Wm[9], Wm[10], Wm[11]);
+                    }
                 }
                 // outputs replace this thread's own (now dead) column of the stage; the TMA warp stores them
 #pragma unroll
@@ -619,11 +692,11 @@ __global__ void __launch_bounds__(T + 32, kMinBlocks) k_world_step_pipe(const Pi
                 }
             }
             if (kTeam) {
-                if (l + 1 < levels) { // this chunk's share of level l is (being) written to `rows`
+                { // this chunk's share of level l is done (rows written, or — last level — rows read)
                     if (pend_level != (int)l) flush_pending(lvl_done);
                     pend_level = (int)l;
                     pend_count += min(last, wc.ls[l + 1] - 1) - max(first, wc.ls[l]) + 1;
-                    if (pa.flags & kPipePublishPerChunk) flush_pending(lvl_done);
+                    if ((pa.flags & kPipePublishPerChunk) && l + 1 < levels) flush_pending(lvl_done);
                 }
             } else if (l < l_hi) {
                 consumer_sync<T>(); // the next level of this chunk reads what this one wrote
@@ -1096,7 +1169,8 @@ bool world_step_plan(const WorldStepViews &v, int device, WorldStepPlan &plan) {
         }
     }
     if (const char *env = std::getenv("FIMO_B200_GENS")) plan.max_gens = std::min<uint32_t>(plan.max_gens, (uint32_t)std::max(1, std::atoi(env)));
-    plan.rows = hbm_shared(device, (size_t)W * E * 48);
+    // parent rows beyond the window: per world; team mode: per TEAM (reused world after world, L2-resident)
+    plan.rows = hbm_shared(device, (size_t)(plan.team > 1 ? plan.teams : W) * E * 48);
     return plan.rows != nullptr;
 }
 
@@ -1201,6 +1275,8 @@ FimoStatus world_step_launch(const WorldStepViews &v, const WorldStepPlan &plan,
         pa.flags = kPipePrefetchBlocking; // FIMO_B200_PREFETCH=0 / 1 (only if already landed) / 2 (default)
         if (const char *env = std::getenv("FIMO_B200_PREFETCH"))
             pa.flags = (pa.flags & ~kPipePrefetchBlocking) | (env[0] == '0' ? kPipeNoPrefetch : (env[0] == '2' ? kPipePrefetchBlocking : 0u));
+        if (const char *env = std::getenv("FIMO_B200_L2_HINTS"))
+            if (env[0] == '0') pa.flags |= kPipeNoL2Hints;
         if (const char *env = std::getenv("FIMO_B200_PUBLISH"))
             if (env[0] == 'c') pa.flags |= kPipePublishPerChunk;
         if (plan.set >= 1) {

@@ -289,7 +289,10 @@ static bool process_buffer(Pool *p, RtBuffer *rb) {
                     if (rb->worker >= 0) p->private_queue[(size_t)rb->worker].push_back(w);
                     else p->queue.push_back(w);
                 }
-                p->q_cv.notify_all();
+                // a pinned task must reach ITS worker (one shared condition variable: wake all); any worker can
+                // take a task of the global queue (wake one — waking all 16 per task cost the CPU arm 2-7x)
+                if (rb->worker >= 0) p->q_cv.notify_all();
+                else p->q_cv.notify_one();
                 break;
             }
             case FIMO_TASKS_META_COMMAND_BUFFER_ENTRY_TYPE_ENQUEUE_COMMAND_BUFFER: {
