@@ -255,7 +255,13 @@ def roofline_of(rig, np, abi, synth, dag, W, E, D, kernel_ms, step_ms, peak, pea
             "kernel_ms": round(kernel_ms, 5), "step_ms": round(step_ms, 5), "peak_source": peak_src,
             "traffic_source": traffic_src,
             "note": "frac: algorithmic bytes / average per-generation device time (CUDA events around each generation); "
-                    "frac_step: the same bytes / ms_per_step (gaps between generations included), per GPU"}
+                    "frac_step: the same bytes / ms_per_step (gaps between generations included), per GPU. `traffic` = ncu DRAM bytes per "
+                    "GENERATION (per launch / generations in the launch). When queued generations share a launch (max_generations_per_launch "
+                    "> 1) a block of worlds stays in the 126 MB L2 from one generation to the next, so DRAM traffic falls far below the "
+                    "algorithmic bytes and the kernel is bounded by L2 -> SM delivery and instruction issue, not by HBM: frac then says how "
+                    "the step compares with streaming its algorithmic bytes at the HBM copy peak (it may exceed 1), and "
+                    "one_generation_per_launch is the HBM-bound figure",
+            "max_generations_per_launch": int(info.max_generations_per_launch)}
 
 
 def measure_config(lib, np, torch, abi, synth, dag, W, E, D, K, WU, windows, peak, peak_src, gate: bool) -> dict:
@@ -429,6 +435,16 @@ def run_b200(args) -> None:
             "configs[2]": measure_config(lib, np, torch, abi, synth, "dag8", 256, 65536, 8, 20, 5, 3, peak, peak_src, not args.no_parity_gate),
             "configs[4] per-GPU shape": measure_config(lib, np, torch, abi, synth, "dag16", 1024, 1024, 4, 20, 5, 3, peak, peak_src, not args.no_parity_gate),
         }
+        # the same workload with ONE generation per launch (FIMO_B200_GENS=1, read when the plan is made): every generation then
+        # streams its whole state through HBM, which is what `bound: hbm` describes; the default lets queued generations share a launch
+        os.environ["FIMO_B200_GENS"] = "1"
+        try:
+            one = measure_config(lib, np, torch, abi, synth, args.dag, W, E, D, K, WU, 3, peak, peak_src, False)
+        finally:
+            del os.environ["FIMO_B200_GENS"]
+        line["roofline"]["one_generation_per_launch"] = {
+            "value": one["value"], "ms_per_step": one["ms_per_step"], "gpu_launches": one["gpu_launches"],
+            "achieved": one["roofline"]["achieved"], "frac": one["roofline"]["frac"], "frac_step": one["roofline"]["frac_step"]}
         for name, cfg in line["other_configs"].items():
             if "parity" in cfg and not cfg["parity"]["ok"]:
                 print(f"bench.py: PARITY GATE FAILED for {name} — no bench line:\n" + "\n".join(cfg["parity"]["problems"]), file=sys.stderr, flush=True)

@@ -681,15 +681,6 @@ __global__ void __launch_bounds__(T + 32, kMinBlocks) k_world_step_pipe(const Pi
                     st[15 * T] = vx, st[16 * T] = vy, st[17 * T] = vz;
                     st[18 * T] = rx, st[19 * T] = ry, st[20 * T] = rz, st[21 * T] = rw;
                 }
-                if (kSet == 2 && (pa.flags & kPipePrevCopy)) {
-                    // prev_copy: this entity's matrix of the previous generation (the chunk's new ones are still in the
-                    // stage; the bulk store that overwrites `world` is issued only after every warp has arrived on done[s])
-                    float old[12];
-#pragma unroll
-                    for (int i = 0; i < 12; i++) old[i] = __ldcg(world_old + (uint64_t)i * E + e);
-#pragma unroll
-                    for (int i = 0; i < 12; i++) prev_out[(uint64_t)i * E + e] = old[i];
-                }
             }
             if (kTeam) {
                 { // this chunk's share of level l is done (rows written, or — last level — rows read)
@@ -701,6 +692,16 @@ __global__ void __launch_bounds__(T + 32, kMinBlocks) k_world_step_pipe(const Pi
             } else if (l < l_hi) {
                 consumer_sync<T>(); // the next level of this chunk reads what this one wrote
             }
+        }
+        // prev_copy (kSet 2): this entity's matrix of the previous generation.  The twelve loads are issued HERE — the
+        // matrix registers are dead, the chunk's new matrices sit in the stage — and consumed only after the cull
+        // compaction below, which covers their L2 latency (they were the kernel's top stall: 34 % long_scoreboard).  The
+        // bulk store that overwrites `world` cannot pass them: a warp arrives on done[s] only after its prev_copy stores.
+        float old_w[kSet == 2 ? 12 : 1];
+        const bool copy_prev = kSet == 2 && (pa.flags & kPipePrevCopy) && valid;
+        if (kSet == 2 && copy_prev) {
+#pragma unroll
+            for (int i = 0; i < 12; i++) old_w[i] = __ldcg(world_old + (uint64_t)i * E + e);
         }
         fence_async_smem();
         const unsigned ballot = __ballot_sync(kFull, vis);
@@ -754,7 +755,7 @@ __global__ void __launch_bounds__(T + 32, kMinBlocks) k_world_step_pipe(const Pi
             // mask word + ordered compaction
             uint32_t *cnt = s_cnt[it & 1];
             if (lane == 0) {
-                mbar_arrive(&done[s]);
+                if (kSet != 2) mbar_arrive(&done[s]);
                 if ((e >> 5) < a.mask_words) mask_out[e >> 5] = ballot;
                 warp_mask_sum += ballot;
                 ((uint8_t *)cnt)[warp] = (uint8_t)__popc(ballot);
@@ -791,6 +792,12 @@ __global__ void __launch_bounds__(T + 32, kMinBlocks) k_world_step_pipe(const Pi
                 }
                 if (vis2) list2_out[running2 + before2 + __popc(ballot2 & ((1u << lane) - 1u))] = e;
                 running2 += chunk_total2;
+                if (copy_prev) {
+#pragma unroll
+                    for (int i = 0; i < 12; i++) prev_out[(uint64_t)i * E + e] = old_w[i];
+                }
+                __syncwarp(); // every lane's old matrix has been consumed: the stage (and `world`) may be drained
+                if (lane == 0) mbar_arrive(&done[s]);
             }
         }
         if (world_ends) {

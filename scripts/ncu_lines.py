@@ -85,5 +85,6 @@ for r, (_, li, _) in zip(body, line_of):
     tot_s += s
 print(f"total warp instructions {tot_i}, samples {tot_s}")
 src_cache = {}
-for key, (n, s) in sorted(agg.items(), key=lambda kv: -kv[1][0])[:top]:
+by = 1 if os.environ.get("BY_SAMPLES") else 0
+for key, (n, s) in sorted(agg.items(), key=lambda kv: -kv[1][by])[:top]:
     print(f"  {n:10d} {100.0 * n / max(tot_i, 1):5.1f}%  samples {100.0 * s / max(tot_s, 1):5.1f}%  {key}")
