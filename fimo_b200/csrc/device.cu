@@ -565,6 +565,37 @@ __global__ void __launch_bounds__(128) k_readback_pack(const uint32_t *__restric
         if (at + i < capacity) dst_list[at + i] = src_list[i];
 }
 
+// Batches of up to kFusedPackWorlds worlds: ONE kernel.  CTA w sums the counts of the worlds before it itself (at most
+// 64 coalesced L2 loads per thread) instead of waiting for a single-CTA scan kernel in front — one launch boundary and
+// one serial 1-CTA kernel fewer per step on the e2e path.
+constexpr uint32_t kFusedPackWorlds = 8192;
+__global__ void __launch_bounds__(128) k_readback_scan_pack(const uint32_t *__restrict__ count, const uint32_t *__restrict__ mask,
+                                                            const uint32_t *__restrict__ list, uint32_t W, uint32_t mask_words, uint32_t entities,
+                                                            uint32_t capacity, unsigned long long generation, uint32_t *__restrict__ out) {
+    __shared__ uint32_t s_warp[4];
+    const uint32_t w = blockIdx.x, tid = threadIdx.x;
+    uint32_t mine = 0;
+    for (uint32_t i = tid; i < w; i += 128) mine += __ldcg(count + i);
+    mine = __reduce_add_sync(0xFFFFFFFFu, mine);
+    if ((tid & 31) == 0) s_warp[tid >> 5] = mine;
+    __syncthreads();
+    const uint32_t at = s_warp[0] + s_warp[1] + s_warp[2] + s_warp[3], n = __ldcg(count + w);
+    if (tid == 0) {
+        out[8 + w] = n, out[8 + W + w] = at;
+        if (w == W - 1) {
+            const uint32_t total = at + n;
+            out[0] = total, out[1] = W, out[2] = mask_words, out[3] = capacity, out[4] = total > capacity ? 1u : 0u;
+            out[5] = (uint32_t)(generation & 0xFFFFFFFFull), out[6] = (uint32_t)(generation >> 32), out[7] = entities;
+        }
+    }
+    uint32_t *dst_mask = out + 8 + 2ull * W + (uint64_t)w * mask_words;
+    uint32_t *dst_list = out + 8 + 2ull * W + (uint64_t)W * mask_words;
+    const uint32_t *src_mask = mask + (uint64_t)w * mask_words, *src_list = list + (uint64_t)w * entities;
+    for (uint32_t i = tid; i < mask_words; i += 128) dst_mask[i] = src_mask[i];
+    for (uint32_t i = tid; i < n; i += 128)
+        if (at + i < capacity) dst_list[at + i] = src_list[i];
+}
+
 bool enqueue_readback(Executor *ex, const Readback &rb, cudaEvent_t landed) {
     const uint64_t fixed_words = 8 + 2 * rb.n_worlds + rb.n_worlds * rb.mask_words;
     if (rb.host_bytes < fixed_words * 4 || rb.n_worlds > 0xFFFFFFFFull) return false;
@@ -589,10 +620,15 @@ bool enqueue_readback(Executor *ex, const Readback &rb, cudaEvent_t landed) {
     const int slot = (int)(ex->rb_count & 1);
     uint32_t *out = (uint32_t *)ex->rb_staging[slot];
     if (ex->rb_count >= 2 && !ok(cudaStreamWaitEvent(ex->stream, ex->rb_drained[slot], 0), "cudaStreamWaitEvent")) return false;
-    k_readback_scan<<<1, kScanThreads, 0, ex->stream>>>(rb.count, (uint32_t)rb.n_worlds, (uint32_t)rb.mask_words, (uint32_t)rb.entities, (uint32_t)capacity,
-                                                        rb.generation, out);
-    k_readback_pack<<<(unsigned)rb.n_worlds, 128, 0, ex->stream>>>(rb.mask, rb.list, (uint32_t)rb.n_worlds, (uint32_t)rb.mask_words, (uint32_t)rb.entities,
-                                                                    (uint32_t)capacity, out);
+    if (rb.n_worlds <= kFusedPackWorlds && !std::getenv("FIMO_B200_READBACK_TWO_KERNELS")) {
+        k_readback_scan_pack<<<(unsigned)rb.n_worlds, 128, 0, ex->stream>>>(rb.count, rb.mask, rb.list, (uint32_t)rb.n_worlds, (uint32_t)rb.mask_words,
+                                                                             (uint32_t)rb.entities, (uint32_t)capacity, rb.generation, out);
+    } else {
+        k_readback_scan<<<1, kScanThreads, 0, ex->stream>>>(rb.count, (uint32_t)rb.n_worlds, (uint32_t)rb.mask_words, (uint32_t)rb.entities, (uint32_t)capacity,
+                                                            rb.generation, out);
+        k_readback_pack<<<(unsigned)rb.n_worlds, 128, 0, ex->stream>>>(rb.mask, rb.list, (uint32_t)rb.n_worlds, (uint32_t)rb.mask_words, (uint32_t)rb.entities,
+                                                                        (uint32_t)capacity, out);
+    }
     bool queued = ok(cudaGetLastError(), "k_readback_pack");
     queued = queued && ok(cudaEventRecord(ex->rb_packed[slot], ex->stream), "cudaEventRecord");
     queued = queued && ok(cudaStreamWaitEvent(ex->readback_stream, ex->rb_packed[slot], 0), "cudaStreamWaitEvent");
