@@ -11,7 +11,6 @@ run() { # N, tag, extra args
 for n in 1 2 4 8; do run $n c2 --no-cpu-baseline --no-other-configs; done
 run 8 c4 --entities 4096 --no-e2e
 run 8 c5 --dag dag16 --worlds 1024 --no-e2e
-run 4 c5 --dag dag16 --worlds 1024 --no-e2e
 run 8 c2nccl --stats nccl --no-e2e
 for f in gpurun_out/r2k_*.json; do python - "$f" <<'PY'
 import json, sys
