@@ -161,11 +161,32 @@ def run_reference(args) -> None:
 # clocks sampled DURING the timed region
 # ------------------------------------------------------------------------------------------------
 class ClockSampler:
+    """SM clock and throttle reasons of one GPU, sampled DURING the timed region: NVML in-process (a thread every 2 ms plus one
+    explicit sample per timed window while its generations are in flight — a 2 ms window would otherwise fall between two
+    `nvidia-smi -lms 100` lines), nvidia-smi as the fallback."""
     Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
          "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
 
     def __init__(self, device: int):
-        self.rows, self.proc = [], None
+        self.rows, self.proc, self.nvml, self.handle, self.stop = [], None, None, None, False
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            visible = os.environ.get("CUDA_VISIBLE_DEVICES")
+            index = int(visible.split(",")[device]) if visible and all(v.strip().isdigit() for v in visible.split(",")) else device
+            try:  # NVML enumerates in PCI order, CUDA need not: match the device by its PCI address
+                import torch
+                pr = torch.cuda.get_device_properties(device)
+                self.handle = pynvml.nvmlDeviceGetHandleByPciBusId(("%08x:%02x:%02x.0" % (pr.pci_domain_id, pr.pci_bus_id, pr.pci_device_id)).encode())
+            except Exception:
+                self.handle = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.nvml = pynvml
+            self.sm_max = int(pynvml.nvmlDeviceGetMaxClockInfo(self.handle, pynvml.NVML_CLOCK_SM))
+            self.sample()
+            threading.Thread(target=self._poll, daemon=True).start()
+            return
+        except Exception:
+            self.nvml = None
         try:
             self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100",
                                           "-i", str(device)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
@@ -173,11 +194,36 @@ class ClockSampler:
         except Exception:
             self.proc = None
 
+    def sample(self) -> None:
+        """One NVML sample now (called with a window's generations in flight)."""
+        if self.nvml is None:
+            return
+        n = self.nvml
+        try:
+            sm = int(n.nvmlDeviceGetClockInfo(self.handle, n.NVML_CLOCK_SM))
+            bits = int(n.nvmlDeviceGetCurrentClocksEventReasons(self.handle)) if hasattr(n, "nvmlDeviceGetCurrentClocksEventReasons") \
+                else int(n.nvmlDeviceGetCurrentClocksThrottleReasons(self.handle))
+            flag = lambda name, old: bits & int(getattr(n, name, getattr(n, old, 0)))  # noqa: E731
+            row = ["0", str(sm), str(self.sm_max), "", "",
+                   "Active" if flag("nvmlClocksEventReasonHwSlowdown", "nvmlClocksThrottleReasonHwSlowdown") else "Not Active",
+                   "Active" if flag("nvmlClocksEventReasonHwThermalSlowdown", "nvmlClocksThrottleReasonHwThermalSlowdown") else "Not Active",
+                   "Active" if flag("nvmlClocksEventReasonSwThermalSlowdown", "nvmlClocksThrottleReasonSwThermalSlowdown") else "Not Active",
+                   "Active" if flag("nvmlClocksEventReasonSwPowerCap", "nvmlClocksThrottleReasonSwPowerCap") else "Not Active"]
+            self.rows.append((time.time(), row))
+        except Exception:
+            pass
+
+    def _poll(self):
+        while not self.stop:
+            self.sample()
+            time.sleep(0.002)
+
     def _read(self):
         for line in self.proc.stdout:
             self.rows.append((time.time(), [c.strip() for c in line.split(",")]))
 
     def summary(self, t0: float, t1: float) -> dict:
+        self.stop = True
         if self.proc is not None:
             self.proc.terminate()
         rows = [r for t, r in self.rows if t0 <= t <= t1 + 0.15] or [r for _, r in self.rows[-3:]]
@@ -186,7 +232,7 @@ class ClockSampler:
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
         reasons = sorted({n for r in rows if len(r) >= 9 for n, v in zip(names, r[5:9]) if v.lower().startswith("active")})
         return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": reasons,
-                "samples": len(rows)}
+                "samples": len(rows), "source": "nvml" if self.nvml is not None else "nvidia-smi"}
 
 
 # ------------------------------------------------------------------------------------------------
@@ -212,7 +258,7 @@ def parity_gate(lib, data, W, E, D, dag, options, steps: int = 2) -> dict:
 # ------------------------------------------------------------------------------------------------
 # device-resident measurement of one configuration
 # ------------------------------------------------------------------------------------------------
-def timed_windows(rig, K: int, windows: int, barrier, reduce_max=None):
+def timed_windows(rig, K: int, windows: int, barrier, reduce_max=None, sampler=None):
     """`windows` x exactly K generations, each bracketed by barrier + synchronize; per window (span_ms, kernel_ms)."""
     spans, kernels, walls = [], [], []
     timed_windows.launches = []  # kernel launches inside each window, counted by the executor
@@ -223,6 +269,8 @@ def timed_windows(rig, K: int, windows: int, barrier, reduce_max=None):
         launched0 = rig.kernels_launched()
         t0 = time.perf_counter()
         rig.schedule(K)
+        if sampler is not None:
+            sampler.sample()  # the window's generations are in flight
         rig.wait()
         barrier()
         walls.append(1e3 * (time.perf_counter() - t0))
@@ -360,7 +408,7 @@ def run_b200(args) -> None:
     sampler = ClockSampler(local_rank)
     time.sleep(0.25)
     t0 = time.time()
-    spans, kernels, walls = timed_windows(rig, K, R, barrier, reduce_max)
+    spans, kernels, walls = timed_windows(rig, K, R, barrier, reduce_max, sampler)
     window_launches = list(timed_windows.launches)
     t1 = time.time()
     clocks = sampler.summary(t0, t1)

@@ -188,6 +188,7 @@ constexpr uint32_t kPipePrevCopy = 16u;        // kSet 2: prev_copy is a member 
 constexpr uint32_t kPipePublishPerChunk = 2u; // FIMO_B200_PUBLISH=chunk: announce level progress after every chunk
 constexpr uint32_t kPipePrefetchBlocking = 4u; // FIMO_B200_PREFETCH=2: wait for the next chunk's inputs before this chunk's math
 constexpr uint32_t kPipeNoPrefetch = 1u; // FIMO_B200_PREFETCH=0: parent rows are loaded where they are used
+constexpr uint32_t kParSlots = 4; // team mode: depth of the parent-plane look-ahead ring
 constexpr uint32_t kPipeNoL2Hints = 32u; // FIMO_B200_L2_HINTS=0: team mode without L2 eviction priorities (A/B runs)
 
 // Per-world constants, double-buffered in shared memory (world k uses buffer k & 1): the compute threads
@@ -260,7 +261,8 @@ struct Cursor {
 // outputs, which the compute threads leave in the same ring stage (world matrices over planes 0-11, new
 // positions over 12-14).
 template <int T, int kSet, bool kHint>
-__device__ __forceinline__ void tma_warp(const PipeArgs &pa, const Walk &wk, float *ring, uint64_t *full, uint64_t *done) {
+__device__ __forceinline__ void tma_warp(const PipeArgs &pa, const Walk &wk, float *ring, uint64_t *full, uint64_t *done, uint32_t *s_par,
+                                         uint64_t *pfull) {
     constexpr int kIn = SetTraits<kSet>::kIn, kStage = SetTraits<kSet>::kStage;
     const StepArgs &a = pa.a;
     const uint64_t stream_policy = kHint ? l2_evict_first() : 0ull; // kHint (team mode): streamed data leaves L2 first
@@ -318,6 +320,13 @@ __device__ __forceinline__ void tma_warp(const PipeArgs &pa, const Walk &wk, flo
 #pragma unroll
         for (int p = 0; p < kIn; p++) bulk_load(st + p * T, plane_src(a, p, w, E) + first, bytes, &full[s]);
         ld.advance(pa, wk);
+        if (kHint && it + 1 < all) { // team mode: parent indices of chunk it + 1, a whole ring turn before its stage is loaded
+            // slot (it + 1) % kParSlots last held chunk it - 3, read while chunk it - 4 was computed: long done (done[s] of it - N)
+            const uint64_t nw = wk.first_world + (uint64_t)ld.k * pa.teams;
+            const uint32_t nfirst = ld.c * T, nbytes = min((uint32_t)T, E - nfirst) * 4u, slot = (it + 1) % kParSlots;
+            mbar_expect_tx(&pfull[slot], nbytes);
+            fb::dev::bulk_load(s_par + (size_t)slot * T, uptr(a.parent, nw) + nfirst, nbytes, &pfull[slot]);
+        }
         if (++s == N) s = 0, round++;
     }
     // drain the last min(N, all) chunks
@@ -382,6 +391,10 @@ __global__ void __launch_bounds__(T + 32, kMinBlocks) k_world_step_pipe(const Pi
     uint64_t *full = (uint64_t *)(s_win + (size_t)3 * cap);       // [N] inputs have landed
     uint64_t *done = full + N;                                    // [N] outputs are in the stage
     float4 *s_pre = (float4 *)(done + N);                         // team mode: [2][T][3] parent rows prefetched from L2
+    // team mode: the parent-index plane of the chunk AFTER the one being loaded, one ring slot ahead of the stage ring
+    // ([kParSlots][T] + kParSlots mbarriers), so that the row prefetch for chunk i + 1 never waits for that chunk's stage
+    uint32_t *s_par = (uint32_t *)(s_pre + (size_t)2 * T * 3);
+    uint64_t *pfull = (uint64_t *)(s_par + (size_t)kParSlots * T);
     __shared__ __align__(16) WorldConst s_c[2];
     __shared__ __align__(16) uint32_t s_cnt[2][4]; // per-warp visible counts of a chunk, one byte per warp
     // this CTA's sums per generation of the launch (one-CTA-per-world plans): visible entities (thread 0), mask words
@@ -420,12 +433,14 @@ __global__ void __launch_bounds__(T + 32, kMinBlocks) k_world_step_pipe(const Pi
             mbar_init(&full[s], 1);
             mbar_init(&done[s], kWarps);
         }
+        if (kTeam)
+            for (uint32_t s = 0; s < kParSlots; s++) mbar_init(&pfull[s], 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncthreads();
 
     if (warp == kWarps) {
-        if (lane == 0) tma_warp<T, kSet, kTeam>(pa, wk, ring, full, done);
+        if (lane == 0) tma_warp<T, kSet, kTeam>(pa, wk, ring, full, done, kTeam ? s_par : nullptr, kTeam ? pfull : nullptr);
         return;
     }
 
@@ -555,11 +570,10 @@ __global__ void __launch_bounds__(T + 32, kMinBlocks) k_world_step_pipe(const Pi
                 uint32_t nl = l_hi;
                 while (nl + 1 < levels && nfirst >= wc.ls[nl + 1]) nl++;
                 const bool single = !(nl + 1 < levels && nlast >= wc.ls[nl + 1]);
-                const uint32_t ns = s + 1 == N ? 0 : s + 1;
-                const uint32_t npar = ns == 0 ? parity ^ 1u : parity;
+                const uint32_t slot = (it + 1) % kParSlots, spar = ((it + 1) / kParSlots) & 1u;
                 if (single && nl >= 1 && l_lo == nl && ready_upto >= (int)nl - 1 &&
-                    ((pa.flags & kPipePrefetchBlocking) ? (mbar_wait(&full[ns], npar), true) : mbar_test(&full[ns], npar))) {
-                    const uint32_t np = __float_as_uint(ring[(size_t)ns * kStage * T + 11 * T + tid]);
+                    ((pa.flags & kPipePrefetchBlocking) ? (mbar_wait(&pfull[slot], spar), true) : mbar_test(&pfull[slot], spar))) {
+                    const uint32_t np = s_par[(size_t)slot * T + tid];
                     if (nfirst + tid < E && np != kRoot) {
                         const float4 *src = rows + (uint64_t)np * 3;
                         float4 *dst = s_pre + ((size_t)((it + 1) & 1) * T + tid) * 3;
@@ -1119,7 +1133,9 @@ bool world_step_plan(const WorldStepViews &v, int device, WorldStepPlan &plan) {
     if (plan.team <= 1) plan.team = 1, plan.teams = 0;
     if (plan.team > 1) { // no window: every parent row goes through L2
         plan.lvl_cap = 0;
-        plan.smem = ring_bytes(plan.set, plan.threads, plan.stages) + (size_t)plan.stages * 16 + (size_t)2 * plan.threads * 48;
+        plan.stages = std::min<uint32_t>(plan.stages, kParSlots - 1); // the parent look-ahead ring runs one slot ahead of the stage ring
+        plan.smem = ring_bytes(plan.set, plan.threads, plan.stages) + (size_t)plan.stages * 16 + (size_t)2 * plan.threads * 48 +
+                    (size_t)kParSlots * plan.threads * 4 + (size_t)kParSlots * 8; // + parent-plane look-ahead ring
         plan.kernels = 2;
         plan.lvl_done = hbm_shared(device, (size_t)W * kMaxLevels * 4);
         if (!plan.lvl_done) return false;
