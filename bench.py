@@ -336,6 +336,29 @@ def measure_config(lib, np, torch, abi, synth, dag, W, E, D, K, WU, windows, pea
     return out
 
 
+def bind_to_gpu_numa_node(torch, device: int):
+    """One process per GPU: run this rank's threads (and so first-touch its pinned buffers) on the CPUs of the NUMA node the GPU's
+    PCIe root hangs off.  With several ranks reading back megabytes per step, host buffers on the far socket put every D2H on the
+    inter-socket link.  Returns what was done, for the bench line; None when the topology is unknown or the node has no allowed CPU."""
+    try:
+        pr = torch.cuda.get_device_properties(device)
+        bdf = "%04x:%02x:%02x.0" % (pr.pci_domain_id, pr.pci_bus_id, pr.pci_device_id)
+        node = int(open(f"/sys/bus/pci/devices/{bdf}/numa_node").read().strip())
+        if node < 0:
+            return None
+        cpus = set()
+        for part in open(f"/sys/devices/system/node/node{node}/cpulist").read().strip().split(","):
+            lo, _, hi = part.partition("-")
+            cpus.update(range(int(lo), int(hi or lo) + 1))
+        allowed = cpus & os.sched_getaffinity(0)
+        if not allowed or os.environ.get("FIMO_B200_NO_NUMA_BIND"):
+            return {"node": node, "bound": False, "cpus_allowed_on_node": len(allowed)}
+        os.sched_setaffinity(0, allowed)
+        return {"node": node, "bound": True, "cpus": len(allowed)}
+    except Exception:
+        return None
+
+
 # ------------------------------------------------------------------------------------------------
 # the CUDA arm
 # ------------------------------------------------------------------------------------------------
@@ -352,6 +375,7 @@ def run_b200(args) -> None:
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device — the B200 path has no CPU fallback (use --impl reference for the CPU arm)")
     torch.cuda.set_device(local_rank)
+    numa = bind_to_gpu_numa_node(torch, local_rank) if world_size > 1 else None  # before any library thread or pinned buffer exists
     distributed = world_size > 1
     if distributed:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
@@ -474,6 +498,8 @@ def run_b200(args) -> None:
         line["e2e_full_state"] = e2e["full_state"]
     if global_stats is not None:
         line["global_stats"] = global_stats
+    if numa is not None:
+        line["config"]["numa"] = numa
     if distributed:
         dist.barrier()  # every rank has finished storing into its peers' inboxes before anyone tears down
     rig.close()
