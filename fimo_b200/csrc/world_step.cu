@@ -321,9 +321,9 @@ __device__ __forceinline__ void tma_warp(const PipeArgs &pa, const Walk &wk, flo
         for (int p = 0; p < kIn; p++) bulk_load(st + p * T, plane_src(a, p, w, E) + first, bytes, &full[s]);
         ld.advance(pa, wk);
         if (kHint && it + 1 < all) { // team mode: parent indices of chunk it + 1, a whole ring turn before its stage is loaded
-            // slot (it + 1) % kParSlots last held chunk it - 3, read while chunk it - 4 was computed: long done (done[s] of it - N)
+            // slot it % kParSlots last held chunk it - 3's indices, read while chunk it - 4 was computed: long done (done[s] of it - N)
             const uint64_t nw = wk.first_world + (uint64_t)ld.k * pa.teams;
-            const uint32_t nfirst = ld.c * T, nbytes = min((uint32_t)T, E - nfirst) * 4u, slot = (it + 1) % kParSlots;
+            const uint32_t nfirst = ld.c * T, nbytes = min((uint32_t)T, E - nfirst) * 4u, slot = it % kParSlots; // use it / kParSlots of that slot
             mbar_expect_tx(&pfull[slot], nbytes);
             fb::dev::bulk_load(s_par + (size_t)slot * T, uptr(a.parent, nw) + nfirst, nbytes, &pfull[slot]);
         }
@@ -570,7 +570,7 @@ __global__ void __launch_bounds__(T + 32, kMinBlocks) k_world_step_pipe(const Pi
                 uint32_t nl = l_hi;
                 while (nl + 1 < levels && nfirst >= wc.ls[nl + 1]) nl++;
                 const bool single = !(nl + 1 < levels && nlast >= wc.ls[nl + 1]);
-                const uint32_t slot = (it + 1) % kParSlots, spar = ((it + 1) / kParSlots) & 1u;
+                const uint32_t slot = it % kParSlots, spar = (it / kParSlots) & 1u; // loaded by the TMA thread's iteration `it`
                 if (single && nl >= 1 && l_lo == nl && ready_upto >= (int)nl - 1 &&
                     ((pa.flags & kPipePrefetchBlocking) ? (mbar_wait(&pfull[slot], spar), true) : mbar_test(&pfull[slot], spar))) {
                     const uint32_t np = s_par[(size_t)slot * T + tid];

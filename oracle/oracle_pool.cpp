@@ -12,14 +12,20 @@
 //   CommandBuffer.zig:459-513  abortCurrentAndForward / abortFromIndex / abortForward;
 //                              command_buffer.zig:56-70 Entry.abort; Worker.zig:115-122 abortTask (`abort` symbol)
 //   Worker.zig:250-411         worker run loop (task fetch, run, report completion)
-// Difference from the reference, stated once: tasks run on OS threads, not on stackful fibers
-// (boost.context is an un-vendored network dependency, modules/fimo_tasks/build.zig.zon:8-11).
-// `abort` unwinds the task with longjmp where the reference switches away from the fiber for good.
-// A task that blocks therefore blocks its thread; the pool compensates by keeping
-// `worker_count` runnable threads (pool_blocking_enter/exit), which is what a parked fiber
-// achieves in the reference.
+//   Worker.zig:225-248,284-321 taskEntry / switch to the task's context and back; Task.zig:56-67 ensureReady;
+//   Pool.zig:100-170           StackAllocator (cached stacks); context.zig:67-100,477-535 make/jump context, mmap +
+//                              guard page
+// Every task runs as a STACKFUL FIBER, as in the reference: a stack from the pool's cache (8 MiB + one guard page,
+// mmap'd and mprotect'ed once, FimoTasks.zig:32), a fresh context made on it, one switch in and one switch out
+// (boost.context's fcontext is an un-vendored network dependency, modules/fimo_tasks/build.zig.zon:8-11; the two
+// routines below restate its x86-64 SysV switch: callee-saved registers + MXCSR / x87 control word + stack pointer).
+// `abort` switches away from the fiber for good (Worker.zig:115-122).  Difference that remains, stated once: a task
+// that BLOCKS (futex wait) blocks its OS thread instead of parking the fiber; the pool compensates by keeping
+// `worker_count` runnable threads (pool_blocking_enter/exit), which is what a parked fiber achieves in the reference.
+#include <sys/mman.h>
+#include <unistd.h>
+
 #include <algorithm>
-#include <csetjmp>
 #include <deque>
 #include <memory>
 #include <string>
@@ -27,6 +33,72 @@
 #include <vector>
 
 #include "oracle_internal.h"
+
+// ---- stackful fibers (context.zig:67-100: make_fcontext / jump_fcontext) ---------------------------------------
+// fiber_switch(&save_sp, load_sp): pushes the callee-saved state of the running context, stores its stack pointer,
+// adopts `load_sp` and pops that context's state.  A new fiber's stack is primed so that the first switch "returns"
+// into fiber_trampoline with the Fiber* in r12.
+extern "C" void oracle_fiber_switch(void **save_sp, void *load_sp);
+extern "C" void oracle_fiber_trampoline();
+asm(R"(
+    .text
+    .globl oracle_fiber_switch
+    .type oracle_fiber_switch, @function
+oracle_fiber_switch:
+    pushq %rbp
+    pushq %rbx
+    pushq %r12
+    pushq %r13
+    pushq %r14
+    pushq %r15
+    subq $8, %rsp
+    stmxcsr (%rsp)
+    fnstcw 4(%rsp)
+    movq %rsp, (%rdi)
+    movq %rsi, %rsp
+    ldmxcsr (%rsp)
+    fldcw 4(%rsp)
+    addq $8, %rsp
+    popq %r15
+    popq %r14
+    popq %r13
+    popq %r12
+    popq %rbx
+    popq %rbp
+    ret
+    .size oracle_fiber_switch, .-oracle_fiber_switch
+    .globl oracle_fiber_trampoline
+    .type oracle_fiber_trampoline, @function
+oracle_fiber_trampoline:
+    movq %r12, %rdi
+    call oracle_fiber_main
+    ud2
+    .size oracle_fiber_trampoline, .-oracle_fiber_trampoline
+)");
+
+namespace oracle {
+struct Stack { // context.zig:477-535: [guard page | usable]; grows down from memory + size
+    void *memory = nullptr;
+    size_t size = 0;
+};
+constexpr size_t kStackSize = 8u << 20; // FimoTasks.zig:32 default_stack_size
+
+struct Fiber {
+    FimoTasksMeta_Task *task = nullptr;
+    void *sp = nullptr;        // the fiber's saved stack pointer while it is switched out
+    void *worker_sp = nullptr; // the worker's, while the fiber runs
+    bool aborted = false;
+};
+
+thread_local Fiber *t_fiber = nullptr; // the fiber running on this thread
+} // namespace oracle
+
+extern "C" void oracle_fiber_main(oracle::Fiber *f) { // Worker.taskEntry (:225-248)
+    f->task->on_start(f->task);
+    void *dead;
+    oracle_fiber_switch(&dead, f->worker_sp); // completeTask: back to the worker for good
+    __builtin_unreachable();
+}
 
 namespace oracle {
 
@@ -36,7 +108,7 @@ thread_local Pool *t_pool = nullptr;      // pool owning this thread (worker or 
 thread_local bool t_is_worker = false;    // true on worker threads only
 thread_local bool t_is_spare = false;     // compensation thread
 thread_local ptrdiff_t t_worker = -1;     // index of a regular worker thread
-thread_local std::jmp_buf *t_abort = nullptr;
+
 } // namespace
 
 struct RtBuffer;
@@ -95,6 +167,7 @@ struct Pool {
     std::condition_variable q_cv;
     std::deque<WorkItem> queue;
     std::vector<std::deque<WorkItem>> private_queue; // Worker.zig:58-76, one per regular worker
+    std::vector<Stack> stack_cache; // Pool.zig:100-170 StackAllocator free list (guarded by q_m)
     bool stop_workers = false;
     size_t runnable = 0;       // threads currently able to run tasks
     size_t threads_total = 0;  // live worker + spare threads
@@ -135,14 +208,36 @@ static void worker_main(Pool *p, bool spare, ptrdiff_t index) {
         }
         WorkItem w = from->front();
         from->pop_front();
+        // StackAllocator.allocate (Pool.zig:112-121): a cached stack, else a fresh mapping with its guard page
+        Stack stack;
+        if (!p->stack_cache.empty()) stack = p->stack_cache.back(), p->stack_cache.pop_back();
         g.unlock();
-        // Task.zig:56-67 / Worker.taskEntry: run the task body, then its completion (or abort) hook.
-        std::jmp_buf unwind;
-        volatile bool is_error = false;
-        t_abort = &unwind;
-        if (setjmp(unwind) == 0) w.task->on_start(w.task);
-        else is_error = true; // Worker.zig:115-122 abortTask
-        t_abort = nullptr;
+        if (!stack.memory) {
+            const size_t page = (size_t)sysconf(_SC_PAGESIZE);
+            stack.size = kStackSize + page;
+            stack.memory = mmap(nullptr, stack.size, PROT_READ | PROT_WRITE, MAP_PRIVATE | MAP_ANONYMOUS | MAP_STACK, -1, 0);
+            if (stack.memory == MAP_FAILED || mprotect(stack.memory, page, PROT_NONE) != 0) panic("fiber stack allocation failed");
+        }
+        // Task.ensureReady (Task.zig:56-67): a fresh context on the stack; Worker.run (:284-300): switch to it.  The task
+        // body runs on the fiber; it comes back by finishing (taskEntry -> completeTask) or through `abort`.
+        Fiber fiber;
+        fiber.task = w.task;
+        {
+            uintptr_t top = ((uintptr_t)stack.memory + stack.size) & ~(uintptr_t)15;
+            void **sp = (void **)top;
+            *--sp = (void *)&oracle_fiber_trampoline;      // "return address" of the first switch: rsp is 16-byte aligned at the trampoline's `call`
+            *--sp = nullptr;                               // rbp
+            *--sp = nullptr;                               // rbx
+            *--sp = &fiber;                                // r12 = Fiber*
+            *--sp = nullptr, *--sp = nullptr, *--sp = nullptr; // r13, r14, r15
+            uint32_t *csr = (uint32_t *)(--sp);            // MXCSR + x87 control word: the defaults
+            csr[0] = 0x1F80u, csr[1] = 0x037Fu;
+            fiber.sp = sp;
+        }
+        t_fiber = &fiber;
+        oracle_fiber_switch(&fiber.worker_sp, fiber.sp);
+        t_fiber = nullptr;
+        const bool is_error = fiber.aborted; // Worker.zig:115-122 abortTask
         if (is_error) {
             if (w.task->on_abort) w.task->on_abort(w.task);
         } else if (w.task->on_complete) {
@@ -151,6 +246,7 @@ static void worker_main(Pool *p, bool spare, ptrdiff_t index) {
         if (w.task->on_deinit) w.task->on_deinit(w.task);
         post(p, Msg{Msg::task_done, w.rb, w.entry, is_error}); // Worker.zig:306-335 "complete" message
         g.lock();
+        p->stack_cache.push_back(stack); // StackAllocator.deallocate (:123-130): back to the cache
     }
     p->runnable--;
     p->threads_total--;
@@ -543,8 +639,12 @@ extern "C" FimoStatus fimo_tasks_create_worker_pool(const FimoTasksMeta_PoolConf
 
 // symbols.zig:94-99 `abort`; Worker.zig:115-122
 extern "C" void fimo_tasks_abort(void) {
-    if (!oracle::t_abort) oracle::panic("fimo_tasks_abort called outside a task");
-    std::longjmp(*oracle::t_abort, 1);
+    oracle::Fiber *f = oracle::t_fiber;
+    if (!f) oracle::panic("fimo_tasks_abort called outside a task");
+    f->aborted = true;
+    void *dead;
+    oracle_fiber_switch(&dead, f->worker_sp); // the fiber is never resumed; its stack goes back to the cache
+    __builtin_unreachable();
 }
 // symbols.zig:60-65 `worker_id`
 extern "C" bool fimo_tasks_worker_id(FimoTasksMeta_PoolWorker *id) {
