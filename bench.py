@@ -126,7 +126,7 @@ def cpu_arm(worlds: int, entities: int, depth: int, steps: int, warmup: int, dag
         "value": worlds * steps / seconds, "unit": UNIT, "cores": cores, "kind": "port",
         "sample": f"{worlds} worlds x {entities} entities, depth {depth}, {dag}, {steps} steps, one World+SystemGroup "
                   f"per world on one shared {cores}-thread pool, {CPU_QUEUE_DEPTH} generations queued per group at a time (oracle "
-                  f"restatement of fimo_worlds/fimo_tasks, gcc -O3 -mavx2 -mfma; the reference itself needs zig + boost.context and cannot be built here)",
+                  f"restatement of fimo_worlds/fimo_tasks: one event-loop thread per pool, every task a stackful fiber on a cached 8 MiB stack; gcc -O3 -mavx2 -mfma; the reference itself needs zig + boost.context and cannot be built here)",
         "seconds": seconds, "steps": steps, "ms_per_step": 1e3 * seconds / steps,
     }
 
