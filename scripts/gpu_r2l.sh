@@ -1,7 +1,7 @@
 #!/bin/bash
 # Round-2 call: team mode with the parent-plane look-ahead ring (C3), prefetch-mode A/B now that rows are L2-resident.
 mkdir -p gpurun_out
-timeout 600 python -m pytest tests -m gpu -x -q --timeout 200 --timeout-method=thread > gpurun_out/r2l_pytest.log 2>&1; echo "pytest rc=$?"; tail -3 gpurun_out/r2l_pytest.log
+timeout 400 python -m pytest tests -m gpu -x -q --timeout 100 --timeout-method=thread > gpurun_out/r2l_pytest.log 2>&1; echo "pytest rc=$?"; tail -3 gpurun_out/r2l_pytest.log
 S="--steps 20 --warmup 5 --no-cpu-baseline --no-e2e --no-other-configs"
 C3="--dag dag8 --worlds 256 --entities 65536 --depth 8"
 timeout 120 python bench.py $S $C3 > gpurun_out/r2l_bench_c3.json 2>/dev/null; echo "c3 rc=$?"
