@@ -1071,7 +1071,7 @@ bool world_step_plan(const WorldStepViews &v, int device, WorldStepPlan &plan) {
         unsigned blocks = 0, stages = 0;
         unsigned long long cap = parents;
         if (std::sscanf(env, "%d,%u,%u,%llu", &T, &blocks, &stages, &cap) >= 3 && (T == 128 || T == 256 || T == 512) &&
-            blocks >= 1 && blocks <= 6 && stages >= 2 && stages <= 16 && (v.set == 0 || blocks <= 4) &&
+            blocks >= 1 && blocks <= 6 && stages >= 2 && stages <= 16 && (v.set == 0 || blocks <= 4 || (v.set == 1 && blocks == 5 && T == 128)) &&
             make_plan(plan, T, blocks, stages, cap, E))
             planned = true;
         else
@@ -1374,6 +1374,7 @@ FimoStatus world_step_launch(const WorldStepViews &v, const WorldStepPlan &plan,
         case 25630: return launch_pipe<256, 3, 0>(pa, plan, W, info);
         case 51210: return launch_pipe<512, 1, 0>(pa, plan, W, info);
         case 12841: case 12831: case 12821: case 12811: return launch_pipe<128, 4, 1>(pa, plan, W, info);
+        case 12851: return launch_pipe<128, 5, 1>(pa, plan, W, info);
         case 25611: case 25621: return launch_pipe<256, 2, 1>(pa, plan, W, info);
         case 25631: return launch_pipe<256, 3, 1>(pa, plan, W, info);
         case 51211: return launch_pipe<512, 1, 1>(pa, plan, W, info);
