@@ -339,6 +339,9 @@ __device__ __forceinline__ void tma_warp(const PipeArgs &pa, const Walk &wk, flo
         if (++ds == N) ds = 0, dround++;
     }
     bulk_wait_all();
+    if (kHint && all > 1) { // the compute warps need not have waited for the last parent-plane loads: none may land after the CTA is gone
+        for (uint32_t j = all - 1 > kParSlots ? all - 1 - kParSlots : 0; j + 1 < all; j++) mbar_wait(&pfull[j % kParSlots], (j / kParSlots) & 1u);
+    }
 }
 
 // non-blocking probe of an mbarrier phase
