@@ -482,7 +482,7 @@ __global__ void __launch_bounds__(T + 32, kMinBlocks) k_world_step_pipe(const Pi
     consumer_sync<T>();
 
     uint32_t next_const = 0;
-    unsigned long long warp_mask_sum = 0, warp_mask_sum2 = 0; // lane 0 of each warp: mask words of the current world visit (kSet 2: cull2's)
+    unsigned long long warp_mask_sum = 0; // lane 0 of each warp: mask words of the current world visit (kSet 2 adds them to shared memory per chunk)
     uint32_t running = 0;                                   // visible entities of the current world so far
     uint32_t running2 = 0;
     uint32_t s = 0, parity = 0, l_lo = 0;
@@ -774,11 +774,12 @@ __global__ void __launch_bounds__(T + 32, kMinBlocks) k_world_step_pipe(const Pi
             if (lane == 0) {
                 if (kSet != 2) mbar_arrive(&done[s]);
                 if ((e >> 5) < a.mask_words) mask_out[e >> 5] = ballot;
-                warp_mask_sum += ballot;
+                if (kSet == 2) atomicAdd(&s_gen_mask[gen], (unsigned long long)ballot); // set 2 runs at the register cap: no per-thread 64-bit accumulators
+                else warp_mask_sum += ballot;
                 ((uint8_t *)cnt)[warp] = (uint8_t)__popc(ballot);
                 if (kSet == 2) {
                     if ((e >> 5) < a.mask_words) mask2_out[e >> 5] = ballot2, sleep_out[e >> 5] = ballot_sleep;
-                    warp_mask_sum2 += ballot2;
+                    atomicAdd(&s_gen_mask2[gen], (unsigned long long)ballot2);
                     ((uint8_t *)s_cnt2[it & 1])[warp] = (uint8_t)__popc(ballot2);
                 }
             }
@@ -824,8 +825,7 @@ __global__ void __launch_bounds__(T + 32, kMinBlocks) k_world_step_pipe(const Pi
                 if (kSet == 2) uptr(a.vis_count2, w)[0] = running2, s_gen_vis2[gen] += running2;
             }
             if (!kTeam && lane == 0) { // mask words of this world visit join its generation's sum
-                atomicAdd(&s_gen_mask[gen], warp_mask_sum), warp_mask_sum = 0;
-                if (kSet == 2) atomicAdd(&s_gen_mask2[gen], warp_mask_sum2), warp_mask_sum2 = 0;
+                if (kSet != 2) atomicAdd(&s_gen_mask[gen], warp_mask_sum), warp_mask_sum = 0;
             }
             if (kSet >= 1 && !kTeam && tid < 6) { // after this chunk's barrier: every warp's keys are in
                 const int key = s_bounds[kk & 1][tid];
