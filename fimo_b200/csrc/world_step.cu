@@ -174,6 +174,7 @@ struct PipeArgs {
     // Team mode: entities of (world, level) whose matrices are visible in `rows` — the dataflow counters the
     // CTAs of a team synchronise on ([n_worlds][kMaxLevels], zeroed by the compaction kernel).
     uint32_t *lvl_done;
+    uint32_t poll_ns; // team mode: pause between two polls of a level counter (FIMO_B200_POLL_NS, default 64)
     // FIMO_B200_TIMING=1 (debug, plain stream launches only): thread 0 of every CTA accumulates clock64 ticks spent
     // [0] waiting for chunk inputs, [1] waiting for a level to complete, [2] in the whole chunk loop, [3] chunks,
     // [4] prefetch section (team mode), [5] thread 0 waiting for its parent row, [6] chunks whose rows were prefetched,
@@ -606,7 +607,8 @@ __global__ void __launch_bounds__(T + 32, kMinBlocks) k_world_step_pipe(const Pi
                     // every entity of level l-1 — in whichever CTA's chunk — must be visible in `rows`
                     if (wait_level) {
                         const uint32_t need = wc.ls[l] - wc.ls[l - 1];
-                        while (ld_acquire_gpu(lvl_done + (l - 1)) < need) __nanosleep(64);
+                        while (ld_acquire_gpu(lvl_done + (l - 1)) < need)
+                            if (pa.poll_ns) __nanosleep(pa.poll_ns);
                     }
                     if (kTimingBuild && pa.timing) tm_level += clock64() - t_lv0;
                 }
@@ -1301,6 +1303,8 @@ FimoStatus world_step_launch(const WorldStepViews &v, const WorldStepPlan &plan,
         pa.flags = kPipePrefetchBlocking; // FIMO_B200_PREFETCH=0 / 1 (only if already landed) / 2 (default)
         if (const char *env = std::getenv("FIMO_B200_PREFETCH"))
             pa.flags = (pa.flags & ~kPipePrefetchBlocking) | (env[0] == '0' ? kPipeNoPrefetch : (env[0] == '2' ? kPipePrefetchBlocking : 0u));
+        pa.poll_ns = 64;
+        if (const char *env = std::getenv("FIMO_B200_POLL_NS")) pa.poll_ns = (uint32_t)std::min(std::max(std::atoi(env), 0), 100000);
         if (const char *env = std::getenv("FIMO_B200_L2_HINTS"))
             if (env[0] == '0') pa.flags |= kPipeNoL2Hints;
         if (const char *env = std::getenv("FIMO_B200_PUBLISH"))

@@ -527,6 +527,7 @@ static void event_loop(Pool *p) {
         p->q_cv.notify_all();
         std::this_thread::yield();
     }
+    for (const Stack &st : p->stack_cache) munmap(st.memory, st.size); // StackAllocator.deinit: every cached stack goes back
     delete p;
 }
 
