@@ -558,7 +558,7 @@ def run_e2e(rig, torch, np, abi, W, E, K, distributed, dist, world_size, f_vis) 
         return t, v
 
     keep = []
-    DEPTH = 4
+    DEPTH = max(1, int(os.environ.get("FIMO_B200_E2E_DEPTH", "4")))  # steps in flight (A/B: more depth hides host jitter, costs latency)
     in_slots, out_slots, rb_slots, fences = [], [], [], [Fence(rig.lib) for _ in range(DEPTH)]
     capacity = int(1.15 * f_vis * W * E) + 1024  # list entries the read-back buffer holds (measured visible fraction + 15 %)
     rb_words = rig.readback_words(capacity)
