@@ -57,7 +57,7 @@ def parse_args():
     p.add_argument("--no-cpu-baseline", action="store_true")
     p.add_argument("--no-e2e", action="store_true")
     p.add_argument("--no-parity-gate", action="store_true", help="skip the K=2 full-size check against the oracle (sweeps only)")
-    p.add_argument("--no-other-configs", action="store_true", help="skip the short configs[2] / configs[4]-shape measurements")
+    p.add_argument("--no-other-configs", action="store_true", help="skip the short configs[2] / configs[3]-shape / configs[4]-shape measurements")
     p.add_argument("--stats", default="peers", choices=["peers", "nccl"], help="transport of the statistics exchange (N > 1)")
     p.add_argument("--stats-bucket", type=int, default=8, help="NCCL transport: generations per all-reduce")
     p.add_argument("--cpu-steps", type=int, default=0, help="steps of the CPU arm (0 = sized for ~15 s)")
@@ -507,6 +507,7 @@ def run_b200(args) -> None:
         # the other single-GPU BASELINE shapes, short, so that the driver's record carries them (not bench lines of their own)
         line["other_configs"] = {
             "configs[2]": measure_config(lib, np, torch, abi, synth, "dag8", 256, 65536, 8, 20, 5, 3, peak, peak_src, not args.no_parity_gate),
+            "configs[3] per-GPU shape": measure_config(lib, np, torch, abi, synth, "chain3", 4096, 4096, 4, 20, 5, 3, peak, peak_src, not args.no_parity_gate),
             "configs[4] per-GPU shape": measure_config(lib, np, torch, abi, synth, "dag16", 1024, 1024, 4, 20, 5, 3, peak, peak_src, not args.no_parity_gate),
         }
         # the same workload with ONE generation per launch (FIMO_B200_GENS=1, read when the plan is made): every generation then
