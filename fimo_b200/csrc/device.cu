@@ -123,6 +123,13 @@ struct Executor {
     size_t rb_bytes = 0;
     cudaEvent_t rb_packed[2] = {nullptr, nullptr}, rb_drained[2] = {nullptr, nullptr};
     uint64_t rb_count = 0;
+    // Shadow mode (the executor is one fused world-step node that can write its cull outputs twice, Node::launch_shadow):
+    // generation g leaves a second copy of mask / list / count in shadow set g & 1, the pack reads THAT copy on
+    // `readback_stream` beside generation g + 1 (which overwrites the resources) and `rb_ready[s]` orders it behind its
+    // generation; generation g + 2 waits for `rb_packed[s]` before it overwrites the set.
+    CullShadow rb_shadow[2] = {{nullptr, nullptr, nullptr}, {nullptr, nullptr, nullptr}};
+    size_t rb_shadow_words[3] = {0, 0, 0};
+    cudaEvent_t rb_ready[2] = {nullptr, nullptr};
     // Host memory that queued device -> host copies have yet to write.  An upload that reads such memory (a result fed
     // back as the next step's input without waiting) must stay in stream order behind that copy: it is not staged.
     struct HostRange {
@@ -383,6 +390,9 @@ void executor_destroy(Executor *ex) {
         if (ex->rb_packed[i]) cudaEventDestroy(ex->rb_packed[i]);
         if (ex->rb_drained[i]) cudaEventDestroy(ex->rb_drained[i]);
         if (ex->rb_staging[i]) cudaFree(ex->rb_staging[i]);
+        if (ex->rb_ready[i]) cudaEventDestroy(ex->rb_ready[i]);
+        for (uint32_t *q : {ex->rb_shadow[i].mask, ex->rb_shadow[i].list, ex->rb_shadow[i].count})
+            if (q) cudaFree(q);
     }
     cudaStreamDestroy(ex->stream);
     delete ex;
@@ -596,7 +606,10 @@ __global__ void __launch_bounds__(128) k_readback_scan_pack(const uint32_t *__re
         if (at + i < capacity) dst_list[at + i] = src_list[i];
 }
 
-bool enqueue_readback(Executor *ex, const Readback &rb, cudaEvent_t landed) {
+// Before the generation is enqueued: stream, events, staging slots (and, in shadow mode, the shadow sets) exist; returns
+// the slot this step uses.  Shadow mode: the generation about to be launched overwrites shadow set `slot`, which the
+// pack of two steps ago read on the read-back stream.
+bool readback_prepare(Executor *ex, const Readback &rb, bool shadow, int *slot_out) {
     const uint64_t fixed_words = 8 + 2 * rb.n_worlds + rb.n_worlds * rb.mask_words;
     if (rb.host_bytes < fixed_words * 4 || rb.n_worlds > 0xFFFFFFFFull) return false;
     const uint64_t capacity = std::min<uint64_t>(rb.host_bytes / 4 - fixed_words, rb.n_worlds * rb.entities);
@@ -605,7 +618,8 @@ bool enqueue_readback(Executor *ex, const Readback &rb, cudaEvent_t landed) {
         if (!ok(cudaStreamCreateWithFlags(&ex->readback_stream, cudaStreamNonBlocking), "cudaStreamCreate")) return false;
         for (int i = 0; i < 2; i++)
             if (!ok(cudaEventCreateWithFlags(&ex->rb_packed[i], cudaEventDisableTiming), "cudaEventCreate") ||
-                !ok(cudaEventCreateWithFlags(&ex->rb_drained[i], cudaEventDisableTiming), "cudaEventCreate"))
+                !ok(cudaEventCreateWithFlags(&ex->rb_drained[i], cudaEventDisableTiming), "cudaEventCreate") ||
+                !ok(cudaEventCreateWithFlags(&ex->rb_ready[i], cudaEventDisableTiming), "cudaEventCreate"))
                 return false;
     }
     if (bytes > ex->rb_bytes) { // (re)size the slots: cold path, drains what is in flight
@@ -617,21 +631,54 @@ bool enqueue_readback(Executor *ex, const Readback &rb, cudaEvent_t landed) {
         }
         ex->rb_bytes = bytes, ex->rb_count = 0;
     }
-    const int slot = (int)(ex->rb_count & 1);
-    uint32_t *out = (uint32_t *)ex->rb_staging[slot];
-    if (ex->rb_count >= 2 && !ok(cudaStreamWaitEvent(ex->stream, ex->rb_drained[slot], 0), "cudaStreamWaitEvent")) return false;
-    if (rb.n_worlds <= kFusedPackWorlds && !std::getenv("FIMO_B200_READBACK_TWO_KERNELS")) {
-        k_readback_scan_pack<<<(unsigned)rb.n_worlds, 128, 0, ex->stream>>>(rb.count, rb.mask, rb.list, (uint32_t)rb.n_worlds, (uint32_t)rb.mask_words,
-                                                                             (uint32_t)rb.entities, (uint32_t)capacity, rb.generation, out);
-    } else {
-        k_readback_scan<<<1, kScanThreads, 0, ex->stream>>>(rb.count, (uint32_t)rb.n_worlds, (uint32_t)rb.mask_words, (uint32_t)rb.entities, (uint32_t)capacity,
-                                                            rb.generation, out);
-        k_readback_pack<<<(unsigned)rb.n_worlds, 128, 0, ex->stream>>>(rb.mask, rb.list, (uint32_t)rb.n_worlds, (uint32_t)rb.mask_words, (uint32_t)rb.entities,
-                                                                        (uint32_t)capacity, out);
+    if (shadow) {
+        const size_t want[3] = {(size_t)(rb.n_worlds * rb.mask_words), (size_t)(rb.n_worlds * rb.entities), (size_t)rb.n_worlds};
+        if (want[0] > ex->rb_shadow_words[0] || want[1] > ex->rb_shadow_words[1] || want[2] > ex->rb_shadow_words[2]) { // cold path
+            if (!ok(cudaStreamSynchronize(ex->readback_stream), "cudaStreamSynchronize") || !ok(cudaStreamSynchronize(ex->stream), "cudaStreamSynchronize")) return false;
+            for (int i = 0; i < 2; i++) {
+                uint32_t **set[3] = {&ex->rb_shadow[i].mask, &ex->rb_shadow[i].list, &ex->rb_shadow[i].count};
+                for (int k = 0; k < 3; k++) {
+                    if (*set[k]) cudaFree(*set[k]);
+                    *set[k] = nullptr;
+                    if (!ok(cudaMalloc((void **)set[k], std::max<size_t>(want[k], 1) * 4), "cudaMalloc (read-back shadow)")) return false;
+                }
+            }
+            for (int k = 0; k < 3; k++) ex->rb_shadow_words[k] = want[k];
+            ex->rb_count = 0;
+        }
     }
-    bool queued = ok(cudaGetLastError(), "k_readback_pack");
-    queued = queued && ok(cudaEventRecord(ex->rb_packed[slot], ex->stream), "cudaEventRecord");
-    queued = queued && ok(cudaStreamWaitEvent(ex->readback_stream, ex->rb_packed[slot], 0), "cudaStreamWaitEvent");
+    const int slot = (int)(ex->rb_count & 1);
+    // the staging slot (in-stream pack) or the shadow set (pack beside the next generation) of two steps ago is free again
+    if (ex->rb_count >= 2 && !ok(cudaStreamWaitEvent(ex->stream, shadow ? ex->rb_packed[slot] : ex->rb_drained[slot], 0), "cudaStreamWaitEvent")) return false;
+    *slot_out = slot;
+    return true;
+}
+
+// Behind the generation: scan + pack into the staging slot, one copy-engine transfer to the host, `landed`.
+bool enqueue_readback(Executor *ex, const Readback &rb, cudaEvent_t landed, int slot, bool shadow) {
+    const uint64_t fixed_words = 8 + 2 * rb.n_worlds + rb.n_worlds * rb.mask_words;
+    const uint64_t capacity = std::min<uint64_t>(rb.host_bytes / 4 - fixed_words, rb.n_worlds * rb.entities);
+    const size_t bytes = (size_t)(fixed_words + capacity) * 4;
+    uint32_t *out = (uint32_t *)ex->rb_staging[slot];
+    cudaStream_t pack_stream = shadow ? ex->readback_stream : ex->stream;
+    const uint32_t *count = shadow ? ex->rb_shadow[slot].count : rb.count, *mask = shadow ? ex->rb_shadow[slot].mask : rb.mask,
+                   *list = shadow ? ex->rb_shadow[slot].list : rb.list;
+    bool queued = true;
+    if (shadow) // the pack waits for its generation only; the staging slot's previous transfer precedes it on the same stream
+        queued = ok(cudaEventRecord(ex->rb_ready[slot], ex->stream), "cudaEventRecord") &&
+                 ok(cudaStreamWaitEvent(ex->readback_stream, ex->rb_ready[slot], 0), "cudaStreamWaitEvent");
+    if (rb.n_worlds <= kFusedPackWorlds && !std::getenv("FIMO_B200_READBACK_TWO_KERNELS")) {
+        k_readback_scan_pack<<<(unsigned)rb.n_worlds, 128, 0, pack_stream>>>(count, mask, list, (uint32_t)rb.n_worlds, (uint32_t)rb.mask_words,
+                                                                              (uint32_t)rb.entities, (uint32_t)capacity, rb.generation, out);
+    } else {
+        k_readback_scan<<<1, kScanThreads, 0, pack_stream>>>(count, (uint32_t)rb.n_worlds, (uint32_t)rb.mask_words, (uint32_t)rb.entities, (uint32_t)capacity,
+                                                             rb.generation, out);
+        k_readback_pack<<<(unsigned)rb.n_worlds, 128, 0, pack_stream>>>(mask, list, (uint32_t)rb.n_worlds, (uint32_t)rb.mask_words, (uint32_t)rb.entities,
+                                                                         (uint32_t)capacity, out);
+    }
+    queued = ok(cudaGetLastError(), "k_readback_pack") && queued;
+    queued = queued && ok(cudaEventRecord(ex->rb_packed[slot], pack_stream), "cudaEventRecord");
+    if (!shadow) queued = queued && ok(cudaStreamWaitEvent(ex->readback_stream, ex->rb_packed[slot], 0), "cudaStreamWaitEvent");
     queued = queued && ok(cudaMemcpyAsync(rb.host, out, bytes, cudaMemcpyDeviceToHost, ex->readback_stream), "cudaMemcpyAsync D2H (read-back)");
     queued = queued && ok(cudaEventRecord(ex->rb_drained[slot], ex->readback_stream), "cudaEventRecord");
     queued = queued && ok(cudaEventRecord(landed, ex->readback_stream), "cudaEventRecord");
@@ -657,15 +704,24 @@ bool executor_launch(Executor *ex, void (*done)(void *), void *user, const Copy 
     // staging pays only when an earlier generation is still running for the PCIe leg to hide behind, and is only
     // correct when no queued result copy has yet to write the memory this upload reads
     bool launched = enqueue_copies(ex->stream, uploads, n_up, true, busy && !feedback ? ex : nullptr); // this generation's inputs, in stream order in front of it
+    // read-back: the pack runs beside the NEXT generation when the executor is one fused world-step node that can leave a
+    // second copy of its cull outputs (FIMO_B200_READBACK_IN_STREAM=1: pack in stream order, A/B)
+    const bool shadow = readback && ex->nodes.size() == 1 && ex->nodes[0].launch_shadow && !std::getenv("FIMO_B200_READBACK_IN_STREAM");
+    int rb_slot = 0;
+    if (readback) launched = readback_prepare(ex, *readback, shadow, &rb_slot) && launched;
     launched = ok(cudaEventRecord(c.start, ex->stream), "cudaEventRecord") && launched;
     if (launched) {
-        if (ex->use_graph) launched = ok(cudaGraphLaunch(ex->graph_exec, ex->stream), "cudaGraphLaunch");
+        if (shadow) {
+            FimoB200_LaunchInfo info = ex->info;
+            info.stream = ex->stream, info.flags = 0u; // a plain launch: the shadow set alternates from step to step
+            launched = ex->nodes[0].launch_shadow(&info, &ex->rb_shadow[rb_slot]) == FIMO_STATUS_OK;
+        } else if (ex->use_graph) launched = ok(cudaGraphLaunch(ex->graph_exec, ex->stream), "cudaGraphLaunch");
         else launched = replay(ex, false);
     }
     launched = ok(cudaEventRecord(c.end, ex->stream), "cudaEventRecord") && launched;
     ex->kernels_launched.fetch_add(ex->kernels, std::memory_order_relaxed);
     if (launched) launched = enqueue_copies(ex->stream, downloads, n_down, false); // its results, behind it
-    if (readback) launched = launched && enqueue_readback(ex, *readback, c.landed);
+    if (readback) launched = launched && enqueue_readback(ex, *readback, c.landed, rb_slot, shadow);
     if (c.landed && (!readback || !launched)) launched = ok(cudaEventRecord(c.landed, ex->stream), "cudaEventRecord") && launched;
     if (!launched) c.done = nullptr; // the caller reports the failure itself
     completer().post(c);

@@ -38,6 +38,12 @@ struct Node {
     std::function<FimoStatus(const FimoB200_LaunchInfo *, uint32_t gens)> launch_gens;
     uint32_t max_gens = 1;
     uint32_t kernels_gens = 1; // kernel launches of one launch_gens call
+    // Optional: one generation that ALSO writes the cull outputs (mask words, ordered list, count: the layout of the
+    // resources) to a shadow set — read-back generations, so that the pack of generation g can run beside generation g + 1.
+    std::function<FimoStatus(const FimoB200_LaunchInfo *, const struct CullShadow *)> launch_shadow;
+};
+struct CullShadow {
+    uint32_t *mask, *list, *count; // HBM: [n_worlds][mask_words], [n_worlds][entities], [n_worlds]
 };
 
 struct Executor;
@@ -189,7 +195,8 @@ struct WorldStepPlan {
 };
 bool world_step_plan(const WorldStepViews &v, int device, WorldStepPlan &plan); // false: not fusable
 FimoStatus world_step_launch(const WorldStepViews &v, const WorldStepPlan &plan, void *cull_scratch,
-                             const FimoB200_LaunchInfo *info, uint32_t gens = 1);
+                             const FimoB200_LaunchInfo *info, uint32_t gens = 1, const CullShadow *shadow = nullptr);
+bool world_step_supports_shadow(const WorldStepPlan &plan); // one-CTA-per-world pipelined plans
 const char *world_step_kernel_name(const WorldStepPlan &plan); // which kernel world_step_launch picks
 std::string world_step_describe(const WorldStepPlan &plan, uint64_t n_worlds); // ... and with which geometry
 // v1: one CTA per world, whole world's matrices in shared memory, loads through registers (kernels.cu)

@@ -174,6 +174,10 @@ struct PipeArgs {
     // Team mode: entities of (world, level) whose matrices are visible in `rows` — the dataflow counters the
     // CTAs of a team synchronise on ([n_worlds][kMaxLevels], zeroed by the compaction kernel).
     uint32_t *lvl_done;
+    // Read-back generations (fimo_b200_group_schedule_readback): a second copy of the cull outputs — mask words, ordered list,
+    // count; the layout of the resources — goes to this shadow set, so that the pack of generation g can run beside generation
+    // g + 1 (which overwrites the resources themselves).  nullptr: none.  One-CTA-per-world plans only.
+    uint32_t *rb_mask, *rb_list, *rb_count;
     uint32_t poll_ns; // team mode: pause between two polls of a level counter (FIMO_B200_POLL_NS, default 64)
     // FIMO_B200_TIMING=1 (debug, plain stream launches only): thread 0 of every CTA accumulates clock64 ticks spent
     // [0] waiting for chunk inputs, [1] waiting for a level to complete, [2] in the whole chunk loop, [3] chunks,
@@ -384,7 +388,9 @@ __device__ __forceinline__ void red_release_gpu_add(uint32_t *p, uint32_t v) {
 //                parents travel through `rows` in L2, and a CTA starts level l of a chunk once the (world, l-1)
 //                counter says every entity of level l-1 is visible — dataflow, no team-wide barrier.  Only the
 //                mask leaves this kernel; k_compact_lists derives list, count and statistics from it.
-template <int T, int kMinBlocks, bool kTeam, int kSet>
+// kShadow: the cull outputs are written twice (PipeArgs::rb_*).  A variant of its own: the three extra predicated stores cost
+// the plain kernel 3 % at C2 when they were a run-time option.
+template <int T, int kMinBlocks, bool kTeam, int kSet, bool kShadow = false>
 __global__ void __launch_bounds__(T + 32, kMinBlocks) k_world_step_pipe(const PipeArgs pa) {
     constexpr int kStage = SetTraits<kSet>::kStage;
     extern __shared__ __align__(128) unsigned char smem_raw[];
@@ -775,7 +781,10 @@ __global__ void __launch_bounds__(T + 32, kMinBlocks) k_world_step_pipe(const Pi
             uint32_t *cnt = s_cnt[it & 1];
             if (lane == 0) {
                 if (kSet != 2) mbar_arrive(&done[s]);
-                if ((e >> 5) < a.mask_words) mask_out[e >> 5] = ballot;
+                if ((e >> 5) < a.mask_words) {
+                    mask_out[e >> 5] = ballot;
+                    if (kShadow) pa.rb_mask[w * a.vis_mask.world_words + (e >> 5)] = ballot;
+                }
                 if (kSet == 2) atomicAdd(&s_gen_mask[gen], (unsigned long long)ballot); // set 2 runs at the register cap: no per-thread 64-bit accumulators
                 else warp_mask_sum += ballot;
                 ((uint8_t *)cnt)[warp] = (uint8_t)__popc(ballot);
@@ -797,7 +806,11 @@ __global__ void __launch_bounds__(T + 32, kMinBlocks) k_world_step_pipe(const Pi
                 before = __dp4a(word & below, 0x01010101u, before);
                 chunk_total = __dp4a(word, 0x01010101u, chunk_total);
             }
-            if (vis) list_out[running + before + __popc(ballot & ((1u << lane) - 1u))] = e;
+            if (vis) {
+                const uint32_t at = running + before + __popc(ballot & ((1u << lane) - 1u));
+                list_out[at] = e;
+                if (kShadow) pa.rb_list[w * a.vis_list.world_words + at] = e;
+            }
             running += chunk_total;
             if (kSet == 2) { // cull2's ordered list, same scan on its own count bytes
                 const uint32_t *cnt2 = s_cnt2[it & 1];
@@ -823,6 +836,7 @@ __global__ void __launch_bounds__(T + 32, kMinBlocks) k_world_step_pipe(const Pi
         if (world_ends) {
             if (!kTeam && tid == 0) {
                 uptr(a.vis_count, w)[0] = running;
+                if (kShadow) pa.rb_count[w * a.vis_count.world_words] = running;
                 s_gen_vis[gen] += running;
                 if (kSet == 2) uptr(a.vis_count2, w)[0] = running2, s_gen_vis2[gen] += running2;
             }
@@ -1245,7 +1259,8 @@ FimoStatus launch_pipe(PipeArgs &pa, const WorldStepPlan &plan, uint64_t W, cons
         return check_launch("compact_lists");
         }
     }
-    auto kernel = k_world_step_pipe<T, kBlocks, false, kSet>;
+    const bool shadow = pa.rb_mask && pa.rb_list && pa.rb_count; // read-back generation: second copy of the cull outputs
+    auto kernel = shadow ? k_world_step_pipe<T, kBlocks, false, kSet, true> : k_world_step_pipe<T, kBlocks, false, kSet, false>;
     if (!allow_smem(kernel, plan.smem)) return check_launch("world_step (shared memory opt-in)");
     // The tail grid evens out ONE generation's slowest CTAs; a multi-generation launch amortises that tail over its
     // generations anyway (dag8 4096 x 1024: 0.974 with, 0.975 without), so it uses the one persistent grid.
@@ -1274,8 +1289,11 @@ FimoStatus launch_pipe(PipeArgs &pa, const WorldStepPlan &plan, uint64_t W, cons
 }
 } // namespace
 
+bool world_step_supports_shadow(const WorldStepPlan &plan) { return plan.threads != 0 && plan.team == 1; }
+
 FimoStatus world_step_launch(const WorldStepViews &v, const WorldStepPlan &plan, void *cull_scratch,
-                             const FimoB200_LaunchInfo *info, uint32_t gens) {
+                             const FimoB200_LaunchInfo *info, uint32_t gens, const CullShadow *shadow) {
+    if (shadow && (!world_step_supports_shadow(plan) || gens != 1)) return fail("world_step plan (shadow cull outputs)");
     if (plan.threads == 0) return gens == 1 ? world_step_launch_v1(v, cull_scratch, info) : FIMO_STATUS_ERROR;
     const uint64_t W = info->n_worlds, E = info->entities_per_world;
     if (W == 0 || E == 0) return FIMO_STATUS_OK;
@@ -1294,6 +1312,7 @@ FimoStatus world_step_launch(const WorldStepViews &v, const WorldStepPlan &plan,
         pa.lvl_cap = plan.lvl_cap;
         pa.chunks = (uint32_t)((E + plan.threads - 1) / plan.threads);
         pa.rows = (float4 *)plan.rows.get();
+        if (shadow) pa.rb_mask = shadow->mask, pa.rb_list = shadow->list, pa.rb_count = shadow->count;
         pa.lvl_done = (uint32_t *)plan.lvl_done.get();
         static unsigned long long *timing_buf = nullptr; // debug only (FIMO_B200_TIMING=1 with plain stream launches)
         static int timing_launches = 0;

@@ -1100,6 +1100,10 @@ bool build_device_executor(Group *g, const char **err) {
             node.launch_gens = [views, plan, scratch](const FimoB200_LaunchInfo *info, uint32_t gens) {
                 return dev::world_step_launch(views, plan, scratch, info, gens);
             };
+            if (dev::world_step_supports_shadow(plan))
+                node.launch_shadow = [views, plan, scratch](const FimoB200_LaunchInfo *info, const dev::CullShadow *shadow) {
+                    return dev::world_step_launch(views, plan, scratch, info, 1, shadow);
+                };
             node.max_gens = plan.max_gens;
             node.kernels = plan.kernels;
             nodes.push_back(std::move(node));
