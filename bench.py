@@ -637,7 +637,7 @@ def run_e2e(rig, torch, np, abi, W, E, K, distributed, dist, world_size, f_vis) 
             "result": f"what cull produces: per-world visible counts + offsets, visibility masks, ordered visible lists packed back to back "
                       f"({last['total']} entries of a {capacity}-entry buffer)",
             "api": "fimo_b200_group_schedule_readback: one C-ABI call per step = H2D of the step's inputs (staged beside the running generation) "
-                   "+ one generation + device-side pack of the cull outputs + ONE copy-engine D2H beside the next generation + completion fence; "
+                   "+ one generation (the fused kernel leaves a second copy of its cull outputs) + scan-and-pack of that copy and ONE copy-engine D2H, both on the read-back stream beside the next generation + completion fence; "
                    f"{DEPTH} steps in flight, every result waited for inside the timed region",
             "in_flight": DEPTH}
 
