@@ -474,14 +474,23 @@ def test_schedule_io_result_fed_back_through_host_memory(oracle, product):
     assert not problems, "\n".join(problems)
 
 
+@pytest.mark.parametrize("pack", ["beside-next-generation", "in-stream"])
 @pytest.mark.parametrize("W,E,D,K,margin", [(24, 1024, 4, 7, 1.0), (700, 96, 4, 5, 1.0), (3, 8192, 8, 4, 1.0), (24, 1024, 4, 3, 0.5)])
-def test_readback_returns_what_cull_produces(oracle, product, W, E, D, K, margin):
+def test_readback_returns_what_cull_produces(oracle, product, monkeypatch, W, E, D, K, margin, pack):
     """fimo_b200_group_schedule_readback: every step uploads its frusta and gets back, in ONE packed pinned buffer, the
     per-world visible counts, their exclusive offsets, the masks and the ordered visible lists back to back — all K
     steps queued before the first wait, each with its own buffer; every buffer equals the oracle's outputs of that
-    step.  margin < 1: the list does not fit -> `truncated`, the prefix that fits is still exact."""
+    step.  margin < 1: the list does not fit -> `truncated`, the prefix that fits is still exact.
+    pack: one-CTA-per-world plans leave a second copy of the cull outputs and pack it on the read-back stream beside the
+    next generation (default); "in-stream" packs from the resources in stream order (what CTA-team plans always do).  Either
+    way the resources themselves hold the last step's outputs afterwards."""
     import ctypes as C
     from fimo_b200.worlds import Fence
+
+    if pack == "in-stream":
+        monkeypatch.setenv("FIMO_B200_READBACK_IN_STREAM", "1")
+    else:
+        monkeypatch.delenv("FIMO_B200_READBACK_IN_STREAM", raising=False)
 
     data = synth.generate(W, E, D)
     frusta = [synth.generate(W, E, D, world0=100 * (i + 1))["frustum"] for i in range(K)]
@@ -524,6 +533,11 @@ def test_readback_returns_what_cull_produces(oracle, product, W, E, D, K, margin
             full = np.concatenate([want[i]["vis_list"][w, 0, :counts[w]] for w in range(W)])
             assert rb["truncated"] == (1 if rb["total"] > capacity else 0)
             assert np.array_equal(rb["list"], full[:capacity]), i
+        last = rig.download(("vis_count", "vis_mask", "vis_list"))  # the resources, not the shadow copy
+        counts = want[-1]["vis_count"][:, 0, 0]
+        assert np.array_equal(last["vis_count"], want[-1]["vis_count"]) and np.array_equal(last["vis_mask"], want[-1]["vis_mask"])
+        for w in range(W):
+            assert np.array_equal(last["vis_list"][w, 0, :counts[w]], want[-1]["vis_list"][w, 0, :counts[w]])
     finally:
         rig.close()
         for ptr in locked:
