@@ -454,6 +454,7 @@ PRODUCT_SYMBOLS = [
     ("fimo_worlds_b200_trace_subscribe", FimoStatus, [POINTER(TracingSubscriber), c_size_t]),
     ("fimo_b200_host_alloc", c_void_p, [c_size_t]),
     ("fimo_b200_host_free", None, [c_void_p]),
+    ("fimo_b200_cull_pack_static", FimoStatus, [c_void_p, c_void_p, c_void_p, c_uint64, c_uint64, c_uint64, c_uint64, c_void_p, c_uint64, c_void_p]),
     ("fimo_b200_group_stats_peers_open", FimoStatus, [c_void_p, c_uint32, c_void_p]),
     ("fimo_b200_group_stats_peers_bind", FimoStatus, [c_void_p, c_void_p, c_uint32, c_uint32]),
     ("fimo_b200_stats_nccl_unique_id", FimoStatus, [c_void_p]),
@@ -474,6 +475,7 @@ class CullReadback(C.Structure):  # FimoB200_CullReadback
 
 
 READBACK_HEADER_WORDS = 8
+PACK_STATIC_MAX_BYTES, PACK_STATIC_MAX_WORLDS = 8 << 20, 8192  # fimo_b200_cull_pack_static's fixed staging area
 
 # CPU-oracle-only helpers (tests / bench cpu_baseline only)
 ORACLE_SYMBOLS = [

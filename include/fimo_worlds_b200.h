@@ -830,6 +830,50 @@ FIMO_B200_EXPORT FimoStatus fimo_b200_group_schedule_readback(FimoWorldsMeta_Sys
 FIMO_B200_EXPORT void *fimo_b200_host_alloc(FimoUSize bytes); /* page-locked host memory; NULL on failure */
 FIMO_B200_EXPORT void fimo_b200_host_free(void *ptr);
 
+/* The packed cull read-back for callers that must not allocate device memory.  No counterpart in the reference
+ * (it has neither a device nor a read-back; this is a B200-side convenience next to fimo_b200_group_schedule_readback).
+ *
+ * Who needs it: fimo_b200_group_schedule_readback packs into HBM staging slots that the library cudaMalloc's on
+ * first use and again whenever a larger buffer is asked for.  Some hosts cannot tolerate that: a frame loop in
+ * which cudaMalloc / cudaFree would stall every stream of the device behind their implicit synchronisation; an
+ * engine that claimed the whole HBM budget for its own pool at start-up, so that the driver has nothing left to
+ * hand out; a plug-in host that forbids driver allocations once it is past initialisation.  Such a caller owns the
+ * cull outputs already (its own device buffers, or the `device_ptr` of locked resource views) and only wants them
+ * packed.  This call uses no cudaMalloc, cudaFree or any other allocating routine, on any call.
+ *
+ * What it does, all queued on `stream` (NULL = the default stream) of the device that is CURRENT on the calling
+ * thread, to which every device pointer must belong:
+ *   1. clears the list part of the staging area (see "shared" below),
+ *   2. one kernel packs `vis_count[n_worlds]`, `vis_mask[n_worlds][mask_words]` and the first vis_count[w] entries
+ *      of every `vis_list[n_worlds][entities]` row into the layout documented at FimoB200_CullReadback
+ *      (header[8], counts, offsets, masks, lists back to back; `generation` is copied into the header),
+ *   3. one copy brings header + counts + offsets + masks + `capacity` list entries to `out`, which may be host
+ *      memory (page-locked if the copy is to be asynchronous) or device memory.  capacity = what fits in
+ *      `out_bytes`, at most n_worlds * entities; a longer list is cut there and header[4] (`truncated`) is set.
+ * It returns once the work is queued; `out` is valid when `stream` has reached that point.
+ *
+ * Limits: the staging area is a fixed array inside the library's device image — FIMO_B200_PACK_STATIC_MAX_BYTES
+ * (8 MiB) of HBM on every GPU that loads the library, held until the process exits.  A call whose packed size
+ * (4 * (8 + 2 n_worlds + n_worlds * mask_words + capacity) bytes) exceeds it, or with more than
+ * FIMO_B200_PACK_STATIC_MAX_WORLDS worlds, fails with FIMO_STATUS_ERROR and fimo_worlds_b200_last_error() ==
+ * "TooLarge" (the numbers go to stderr); nothing is queued.  Hand in a smaller `out_bytes` (a truncated list) or
+ * pack the batch in slices of worlds.
+ *
+ * Shared: every call on a device uses the same array, and it keeps what the previous call left there.  Step 1
+ * zeroes the list entries this call may copy out, so entries past the packed total read as 0 and never as another
+ * call's indices; everything else that is copied is rewritten by step 2.  Two calls that overlap on the GPU (two
+ * streams, two threads, two groups) race on the array: order them on one stream or with events.
+ *
+ * First call on a device: looks up the array's device address (cudaGetSymbolAddress, which also makes the driver
+ * load the kernel image and with it the array).  Make that first call during start-up, before any stream capture is
+ * begun on the thread. */
+#define FIMO_B200_PACK_STATIC_MAX_BYTES (8u << 20)
+#define FIMO_B200_PACK_STATIC_MAX_WORLDS 8192u
+FIMO_B200_EXPORT FimoStatus fimo_b200_cull_pack_static(const uint32_t *vis_count, const uint32_t *vis_mask,
+                                                       const uint32_t *vis_list, uint64_t n_worlds, uint64_t entities,
+                                                       uint64_t mask_words, uint64_t generation, void *out,
+                                                       uint64_t out_bytes, void *stream);
+
 /* Tracing bridge.  The reference records spans and events through the context's tracing
  * subsystem (pkgs/fimo_std/src/tracing.zig:387-554: enter_span / exit_span / log_message); device work has no
  * call stack there.  With a sink installed the completion thread reports every finished device generation —
