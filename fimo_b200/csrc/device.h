@@ -104,6 +104,10 @@ const void *stats_exchange_peer_table(StatsExchange *x); // HBM table the statis
 bool stats_nccl_unique_id(void *out);
 bool stats_exchange_nccl_bind(StatsExchange *x, const void *unique_id, uint32_t rank, uint32_t nranks, uint32_t bucket);
 void *stats_exchange_ring(StatsExchange *x, uint32_t *slots); // NCCL mode: the ring the kernel snapshots into
+// Generations ONE launch may step with this exchange bound: a launch writes its ring rows before any of its bucket
+// all-reduces can be enqueued, so in NCCL mode it must not reach around the ring into rows that are still waiting for
+// theirs — (blocks - 1) x bucket generations.  Unbounded (UINT32_MAX) otherwise.
+uint32_t stats_exchange_max_gens(StatsExchange *x);
 bool stats_exchange_before_launch(StatsExchange *x, void *stream, uint32_t n);
 bool stats_exchange_after_launch(StatsExchange *x, void *stream, uint32_t n);
 bool stats_exchange_read(StatsExchange *x, uint64_t generation, uint32_t mode, uint64_t *out);

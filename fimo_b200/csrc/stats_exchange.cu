@@ -226,6 +226,16 @@ bool reduce_upto(StatsExchange *x, uint64_t upto) {
 }
 } // namespace
 
+// A launch of n generations starting at generation `first` overwrites the rows of generations [first - slots,
+// first + n - slots).  All of those must already have had their all-reduce enqueued (generation < flushed, and
+// flushed > first - bucket) and before_launch must find the `reduced` event of every block the launch enters already
+// recorded: both hold exactly when n <= slots - bucket.
+uint32_t stats_exchange_max_gens(StatsExchange *x) {
+    if (!x) return UINT32_MAX;
+    std::lock_guard<std::mutex> lock(x->m);
+    return x->comm ? (kNcclBlocks - 1) * x->bucket : UINT32_MAX;
+}
+
 bool stats_exchange_before_launch(StatsExchange *x, void *stream, uint32_t n) {
     if (!x || !x->comm) return true;
     Guard guard(x->device);

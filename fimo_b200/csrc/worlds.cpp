@@ -1446,7 +1446,8 @@ void launch_pending_batches(Group *g) {
         g->backlog_cv.notify_one();
         return;
     }
-    const uint32_t max_gens = dev::executor_max_gens(g->executor_dev);
+    // with a NCCL statistics ring bound, a launch must not wrap the ring into rows whose all-reduce is still to come
+    const uint32_t max_gens = std::min(dev::executor_max_gens(g->executor_dev), dev::stats_exchange_max_gens(g->stats_x));
     const int64_t now = tracing_wanted() ? monotonic_ns() : 0;
     while (!g->batch_pending.empty()) {
         const uint32_t n = (uint32_t)std::min<size_t>(g->batch_pending.size(), max_gens);

@@ -1069,6 +1069,9 @@ FIMO_B200_EXPORT FimoStatus fimo_b200_group_stats_peers_open(FimoWorldsMeta_Syst
 FIMO_B200_EXPORT FimoStatus fimo_b200_group_stats_peers_bind(FimoWorldsMeta_SystemGroup *group, const void *handles,
                                                              uint32_t rank, uint32_t nranks);
 FIMO_B200_EXPORT FimoStatus fimo_b200_stats_nccl_unique_id(void *id_out); /* ncclGetUniqueId; rank 0 calls, broadcasts */
+/* The ring holds 4 * bucket generations.  Once bound, queued generations share a launch only up to 3 * bucket at a time
+ * (a launch writes its rows before its all-reduces can be enqueued, so it must not wrap into rows still waiting for
+ * theirs), and the last 3 * bucket generations stay readable. */
 FIMO_B200_EXPORT FimoStatus fimo_b200_group_stats_nccl_bind(FimoWorldsMeta_SystemGroup *group, const void *unique_id,
                                                             uint32_t rank, uint32_t nranks, uint32_t bucket);
 /* The statistics of `generation` summed over all ranks (8 u64 words).  PEERS: waits (bounded) until every rank's
