@@ -131,6 +131,18 @@ def cpu_arm(worlds: int, entities: int, depth: int, steps: int, warmup: int, dag
     }
 
 
+def config_of(worlds: int, entities: int, depth: int, dag: str) -> dict:
+    """The `config` object of BOTH arms (the driver compares them key for key): what is stepped, nothing about how."""
+    from fimo_b200 import synth
+
+    floor_mb = synth.dag_bytes_per_entity_step(dag, 0.0, 0.0) * worlds * entities / 1e6  # without the visible lists
+    return {"workload": f"{worlds} worlds x {entities} entities per GPU, depth-{depth} transform hierarchy, {DAG_TEXT[dag]}"
+                        + (", BASELINE.json configs[1]" if (worlds, entities, depth, dag) == (4096, 1024, 4, "chain3") else ""),
+            "dag": dag, "worlds_per_gpu": worlds, "entities_per_world": entities, "depth": depth,
+            "l2": ("inputs larger than L2 (state touched per step >= %.0f MB > 126 MB), no flush between steps" % floor_mb) if floor_mb > 126.0 else
+                  ("state touched per step >= %.0f MB (partly L2-resident between steps; no flush)" % floor_mb)}
+
+
 def run_reference(args) -> None:
     """The reference arm: the SAME config, steps and warm-up as the B200 arm wherever that ends within a few minutes —
     every world of the batch gets its own World + SystemGroup, as on the reference — else (over 8 M entities) a
@@ -146,11 +158,8 @@ def run_reference(args) -> None:
         "impl": "reference", "metric": METRIC, "value": base["value"], "unit": UNIT, "n_gpus": args.gpus,
         "steps": base["steps"], "warmup": warmup, "ms_per_step": base["ms_per_step"], "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": f"{args.worlds} worlds x {args.entities} entities per GPU, depth-{args.depth} transform hierarchy, {DAG_TEXT[args.dag]}"
-                               + (", BASELINE.json configs[1]" if (args.worlds, args.entities, args.depth, args.dag) == (4096, 1024, 4, "chain3") else "")
-                               + sampled,
-                   "dag": args.dag, "worlds_per_gpu": args.worlds, "entities_per_world": args.entities, "depth": args.depth,
-                   "same_config": worlds == args.worlds},
+        "config": config_of(args.worlds, args.entities, args.depth, args.dag),
+        "same_config": worlds == args.worlds, "sampled": sampled.lstrip("; ") or None,
         "cpu_baseline": {k: base[k] for k in ("value", "unit", "cores", "kind", "sample")},
         "e2e": {"value": base["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
@@ -236,23 +245,43 @@ class ClockSampler:
 
 
 # ------------------------------------------------------------------------------------------------
-# the parity gate: K = 2 generations of the benched workload, product vs oracle, bit for bit
+# the parity gate: the benched workload on the launch shape the timed windows use, product vs oracle, bit for bit
 # ------------------------------------------------------------------------------------------------
-def parity_gate(lib, data, W, E, D, dag, options, steps: int = 2) -> dict:
+def parity_gate(lib, data, W, E, D, dag, options, steps: int = 0) -> dict:
+    """Gates the path that is timed.  The timed windows schedule K generations back to back, and when the plan lets queued
+    generations share a launch (max_generations_per_launch > 1: grid over all worlds, block-of-worlds order, bulk-group
+    waits across generation boundaries, one statistics publish for the whole launch) almost all of them run that way —
+    two generations never do.  So the gate queues max_generations_per_launch + 4 generations without waiting, checks
+    that launches really were shared (fewer launches than one per generation; retried on a fresh rig if the host was too
+    slow to queue behind the first launches) and compares every written resource with the oracle."""
     from fimo_b200 import synth
     from oracle import loader
 
     t0 = time.time()
-    rig = synth.WorldStepRig(lib, W, E, D, data=data, options=options, dag=dag)  # uploads `data`, never writes it
-    try:
-        rig.step(steps)
-        got = rig.download()
-    finally:
-        rig.close()
-    want = synth.step_in_slices(loader.load(), {k: v.copy() for k, v in data.items()}, E, D, steps, dag=dag)
+    shared, launches, tries = False, 0, 0
+    while True:
+        tries += 1
+        rig = synth.WorldStepRig(lib, W, E, D, data=data, options=options, dag=dag)  # uploads `data`, never writes it
+        try:
+            info = rig.executor_info()
+            per_launch, per_generation = int(info.max_generations_per_launch), int(info.kernel_launches_per_generation)
+            K = steps or (per_launch + 4 if per_launch > 1 else 2)
+            before = rig.kernels_launched()
+            rig.step(K)  # K x schedule, ONE wait
+            launches = rig.kernels_launched() - before
+            got = rig.download()
+        finally:
+            rig.close()
+        shared = launches < K * per_generation
+        if shared or per_launch <= 1 or tries == 3:
+            break
+    want = synth.step_in_slices(loader.load(), {k: v.copy() for k, v in data.items()}, E, D, K, dag=dag)
     problems = synth.compare_outputs(got, want, 0.0)
-    return {"ok": not problems, "problems": problems[:4], "steps": steps, "seconds": round(time.time() - t0, 2),
-            "checked": f"{W} x {E}, {dag}: every written resource after {steps} generations, bit-exact vs the CPU oracle"}
+    return {"ok": not problems, "problems": problems[:4], "steps": K, "seconds": round(time.time() - t0, 2),
+            "kernel_launches": int(launches), "max_generations_per_launch": per_launch,
+            "covers_shared_launches": bool(shared) if per_launch > 1 else None,
+            "checked": f"{W} x {E}, {dag}: every written resource after {K} generations queued without waiting "
+                       f"({launches} kernel launches), bit-exact vs the CPU oracle"}
 
 
 # ------------------------------------------------------------------------------------------------
@@ -400,7 +429,7 @@ def run_b200(args) -> None:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return [float(v) for v in t.cpu()]
 
-    # ---- parity gate: this workload, this launch plan, 2 generations, against the oracle (rank 0's shard) -------------
+    # ---- parity gate: this workload, this launch plan and launch shape, against the oracle (rank 0's shard) ----------
     parity = None
     if not args.no_parity_gate:
         if rank == 0:
@@ -469,18 +498,15 @@ def run_b200(args) -> None:
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world_size, "steps": K, "warmup": WU,
         "ms_per_step": t_ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
         "data": "synthetic",
-        "config": {"workload": f"{W} worlds x {E} entities per GPU, depth-{D} transform hierarchy, {DAG_TEXT[args.dag]}"
-                               + (", BASELINE.json configs[1]" if default_config else ""),
-                   "dag": args.dag,
-                   "worlds_per_gpu": W, "entities_per_world": E, "depth": D, "executor": ("fused world-step kernel" if info.fused_world_step else "one kernel per system")
-                   + (" in a CUDA graph" if info.uses_cuda_graph else ", plain stream launches"),
-                   "l2": "inputs larger than L2 (state touched per step = %.0f MB > 126 MB)" % (alg_bytes / 1e6) if alg_bytes > 126e6 else
-                         "state touched per step = %.0f MB (partly L2-resident between steps; no flush)" % (alg_bytes / 1e6),
-                   "timing": f"{R} windows of exactly {K} generations, each bracketed by barrier + synchronize, device-timed (CUDA events on the "
-                             "group's stream), max over ranks; value = median window",
-                   "sharding": "worlds by global index, no data-path collective; every generation's statistics (64 B) exchanged by the product: "
-                               + ("peer stores over NVLink from the publishing CTA" if args.stats == "peers" else
-                                  f"ncclAllReduce on a library side stream, {args.stats_bucket} generations per collective")},
+        "config": config_of(W, E, D, args.dag),
+        "run": {"executor": ("fused world-step kernel" if info.fused_world_step else "one kernel per system")
+                            + (" in a CUDA graph" if info.uses_cuda_graph else ", plain stream launches"),
+                "state_touched_per_step_mb": round(alg_bytes / 1e6, 1),
+                "timing": f"{R} windows of exactly {K} generations, each bracketed by barrier + synchronize, device-timed (CUDA events on the "
+                          "group's stream), max over ranks; value = median window",
+                "sharding": "worlds by global index, no data-path collective; every generation's statistics (64 B) exchanged by the product: "
+                            + ("peer stores over NVLink from the publishing CTA" if args.stats == "peers" else
+                               f"ncclAllReduce on a library side stream, {args.stats_bucket} generations per collective")},
         "windows": {"n": R, "ms_per_step_median": t_ms / K, "ms_per_step_min": min(spans) / K, "ms_per_step_max": max(spans) / K,
                     "value_min": world_size * W * K / (max(spans) * 1e-3), "value_max": world_size * W * K / (min(spans) * 1e-3)},
         "wall_ms_per_step": statistics.median(walls) / K, "device_ms_per_step": kernel_ms,
@@ -491,7 +517,7 @@ def run_b200(args) -> None:
         "roofline": roofline, "clocks": clocks,
     }
     if parity is not None:
-        line["parity"] = {k: parity[k] for k in ("ok", "checked", "seconds")}
+        line["parity"] = {k: parity[k] for k in ("ok", "checked", "seconds", "steps", "kernel_launches", "covers_shared_launches")}
     if e2e is not None:
         line["e2e"] = e2e["headline"]
         line["e2e_constants_only"] = e2e["constants_only"]
@@ -499,7 +525,7 @@ def run_b200(args) -> None:
     if global_stats is not None:
         line["global_stats"] = global_stats
     if numa is not None:
-        line["config"]["numa"] = numa
+        line["run"]["numa"] = numa
     if distributed:
         dist.barrier()  # every rank has finished storing into its peers' inboxes before anyone tears down
     rig.close()
@@ -524,6 +550,12 @@ def run_b200(args) -> None:
             if "parity" in cfg and not cfg["parity"]["ok"]:
                 print(f"bench.py: PARITY GATE FAILED for {name} — no bench line:\n" + "\n".join(cfg["parity"]["problems"]), file=sys.stderr, flush=True)
                 raise SystemExit(3)
+        # the same figures as top-level scalars (a record that keeps only scalars still shows every BASELINE shape)
+        line["c2_one_gen_frac"], line["c2_one_gen_value"] = one["roofline"]["frac"], one["value"]
+        for key, name in (("c3", "configs[2]"), ("c4shape", "configs[3] per-GPU shape"), ("c5shape", "configs[4] per-GPU shape")):
+            cfg = line["other_configs"][name]
+            line[key + "_value"], line[key + "_frac"], line[key + "_frac_step"] = cfg["value"], cfg["roofline"]["frac"], cfg["roofline"]["frac_step"]
+            line[key + "_parity_ok"] = cfg["parity"]["ok"] if "parity" in cfg else None
     if rank == 0 and not args.no_cpu_baseline and world_size == 1:
         base = cpu_arm(max(1, min(CPU_SAMPLE_WORLDS, W, (CPU_SAMPLE_WORLDS * 1024) // max(E, 1))), E, D, args.cpu_steps, 2, args.dag, seconds_budget=10.0)
         line["cpu_baseline"] = {k: base[k] for k in ("value", "unit", "cores", "kind", "sample")}

@@ -237,7 +237,7 @@ QUEUED_CASES = [
     # (dag, worlds, entities, depth, queued generations, FIMO_B200_GENS or None)
     ("chain3", 1200, 2048, 4, 37, None),   # 3 worlds per CTA: generations queued behind two launches share launches (up to 16 each)
     ("chain3", 600, 2048, 4, 21, "3"),     # T = 256: 3 worlds x 8 chunks per CTA; at most 3 generations per launch
-    ("dag8", 1300, 1280, 4, 19, None),     # persistent grid + tail grid of one-world CTAs (10 chunks each), both looping over generations
+    ("dag8", 1300, 1280, 4, 19, None),     # 10 chunks per world; single launches use persistent + tail grid, shared launches one grid over all worlds (no tail grid)
     ("dag16", 700, 1024, 4, 13, None),     # all 16 systems in the kernel, prev_copy included (reads the previous generation's matrices)
     ("chain3", 592, 256, 4, 12, None),     # 2 chunks per CTA < ring + 2: the plan refuses multi-generation launches
 ]
