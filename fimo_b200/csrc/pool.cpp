@@ -23,7 +23,7 @@
 //       or type) abort instead of panicking; wait_on_command_indirect(0) is a no-op (:397).
 // Tasks run on OS threads (boost.context is an un-vendored network dependency of the reference,
 // modules/fimo_tasks/build.zig.zon:8-11); a task that parks on the futex keeps the pool's thread
-// budget through BlockingScope.
+// budget through BlockingScope, and while it is parked a stand-in thread serves the tasks pinned to its worker.
 #include <algorithm>
 #include <csetjmp>
 #include <deque>
@@ -53,6 +53,10 @@ struct Pool {
     std::condition_variable cv;
     std::deque<WorkItem> queue;
     std::vector<std::deque<WorkItem>> pinned; // per regular worker: tasks enqueued under select_worker
+    // Threads currently serving worker index i and not parked inside a task: 1 while the regular thread runs or idles,
+    // 0 while it is parked (BlockingScope) — then a stand-in spare adopts the index (worker_main) so that tasks pinned
+    // to i keep running, as they do in the reference where only the fiber parks (Worker.zig:58-76,262-280).
+    std::vector<size_t> active;
     size_t runnable = 0;     // threads that are not parked inside a task
     size_t idle = 0;         // runnable threads waiting for work
     size_t live_threads = 0; // regular + spare threads still alive
@@ -108,10 +112,19 @@ void spawn_spare_locked(Pool *p) {
     std::thread(worker_main, p, true, (ptrdiff_t)-1).detach();
 }
 
+// Called with p->m held: worker `index` has nobody running (its thread is parked inside a task) and has pinned work.
+void spawn_stand_in_locked(Pool *p, size_t index) {
+    p->active[index]++; // counted from here, so that nobody spawns a second one before this one has started
+    p->runnable++;
+    p->live_threads++;
+    std::thread(worker_main, p, true, (ptrdiff_t)index).detach();
+}
+
 void push_task(Pool *p, WorkItem w) {
     std::lock_guard<std::mutex> g(p->m);
-    if (w.worker >= 0) { // pinned: only that thread takes it
+    if (w.worker >= 0) { // pinned: only a thread serving that worker index takes it
         p->pinned[(size_t)w.worker].push_back(w);
+        if (p->active[(size_t)w.worker] == 0) spawn_stand_in_locked(p, (size_t)w.worker);
         p->cv.notify_all();
         return;
     }
@@ -334,8 +347,17 @@ void worker_main(Pool *p, bool spare, ptrdiff_t index) {
     t_pool = p;
     t_worker = index;
     std::unique_lock<std::mutex> g(p->m);
+    // A spare with an index is a stand-in: it serves ONLY the private queue of a worker whose thread is parked inside a
+    // task (fimo_tasks_worker_id reports that index), and leaves as soon as a parked thread of that index is back or
+    // the queue is empty.  The returning thread does not wait for it: for the rest of the stand-in's current task two
+    // tasks of one worker index run side by side, which fibers on one worker never do.
+    const bool stand_in = spare && index >= 0;
     for (;;) {
-        if (spare && p->runnable > p->worker_count) break; // parked threads came back: retire
+        if (stand_in) {
+            if (p->active[(size_t)index] > 1 || p->pinned[(size_t)index].empty()) break;
+        } else if (spare && p->runnable > p->worker_count) {
+            break; // parked threads came back: retire
+        }
         std::deque<WorkItem> *from = index >= 0 && !p->pinned[(size_t)index].empty() ? &p->pinned[(size_t)index] : &p->queue;
         if (from->empty()) {
             if (p->stopping || spare) break;
@@ -368,6 +390,7 @@ void worker_main(Pool *p, bool spare, ptrdiff_t index) {
         }
         g.lock();
     }
+    if (stand_in) p->active[(size_t)index]--;
     p->runnable--;
     pool_destroy_if_last_thread_locked(p, g);
 }
@@ -469,6 +492,7 @@ Pool *pool_create(const char *label, size_t label_len, size_t workers) {
     p->runnable = workers;
     p->live_threads = workers;
     p->pinned.resize(workers);
+    p->active.assign(workers, 1);
     for (size_t i = 0; i < workers; i++) std::thread(worker_main, p, false, (ptrdiff_t)i).detach();
     return p;
 }
@@ -478,6 +502,10 @@ BlockingScope::BlockingScope() {
     if (!p) return;
     std::lock_guard<std::mutex> g(p->m);
     p->runnable--;
+    if (t_worker >= 0) { // this worker index is about to have nobody running: its pinned tasks go to a stand-in
+        const size_t i = (size_t)t_worker;
+        if (--p->active[i] == 0 && !p->pinned[i].empty()) spawn_stand_in_locked(p, i);
+    }
     if (!p->queue.empty() && p->idle == 0 && p->runnable < p->worker_count) spawn_spare_locked(p);
 }
 BlockingScope::~BlockingScope() {
@@ -485,6 +513,7 @@ BlockingScope::~BlockingScope() {
     if (!p) return;
     std::lock_guard<std::mutex> g(p->m);
     p->runnable++;
+    if (t_worker >= 0) p->active[(size_t)t_worker]++; // a stand-in, if any, leaves after its current task
 }
 
 } // namespace fb

@@ -27,6 +27,10 @@ typedef struct {
     void (*abort_fn)(void);
     bool (*worker_id_fn)(FimoTasksMeta_PoolWorker *);
     int32_t id, should_abort, wait_gate;
+    /* set (before the gate opens) by helper_task_wait_on: the body then waits for that command buffer INSIDE the task */
+    void *wait_data;
+    const FimoTasksMeta_CommandBufferHandleVTable *wait_vtable;
+    _Atomic int32_t wait_status; /* -1 until the wait has returned, then the completion status */
 } HelperTask;
 
 typedef struct {
@@ -48,6 +52,7 @@ static void task_start(FimoTasksMeta_Task *t) {
     HelperTask *h = (HelperTask *)t;
     record(h->log, h->id, EV_TASK_START, h->worker_id_fn);
     while (h->wait_gate && !atomic_load(&h->log->gate)) sched_yield();
+    if (h->wait_vtable) atomic_store(&h->wait_status, (int32_t)h->wait_vtable->wait_on(h->wait_data));
     if (h->should_abort) h->abort_fn();
 }
 static void task_complete(FimoTasksMeta_Task *t) { record(((HelperTask *)t)->log, ((HelperTask *)t)->id, EV_TASK_COMPLETE, NULL); }
@@ -74,7 +79,16 @@ void helper_task_init(HelperTask *h, HelperLog *log, int32_t id, int32_t should_
     h->id = id;
     h->should_abort = should_abort;
     h->wait_gate = wait_gate;
+    h->wait_data = NULL;
+    h->wait_vtable = NULL;
+    atomic_store(&h->wait_status, -1);
 }
+
+void helper_task_wait_on(HelperTask *h, void *data, const FimoTasksMeta_CommandBufferHandleVTable *vtable) {
+    h->wait_data = data;
+    h->wait_vtable = vtable;
+}
+int32_t helper_task_wait_status(HelperTask *h) { return atomic_load(&h->wait_status); }
 
 void helper_buffer_init(HelperBuffer *b, HelperLog *log, int32_t id, FimoTasksMeta_CommandBufferEntry *entries, size_t n) {
     b->buffer.label = "helper";

@@ -49,6 +49,9 @@ def helper():
     dll.helper_task_init.argtypes = [C.c_void_p, C.POINTER(Log), C.c_int32, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p]
     dll.helper_buffer_init.argtypes = [C.c_void_p, C.POINTER(Log), C.c_int32, C.POINTER(abi.CommandBufferEntry), C.c_size_t]
     dll.helper_open_gate.argtypes = [C.POINTER(Log)]
+    dll.helper_task_wait_on.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
+    dll.helper_task_wait_status.argtypes = [C.c_void_p]
+    dll.helper_task_wait_status.restype = C.c_int32
     dll.helper_event_count.argtypes = [C.POINTER(Log)]
     return dll
 
@@ -316,6 +319,39 @@ def test_select_worker_pins_the_following_tasks(rig):
     assert worker_of[0] == 2 and worker_of[1] == 2 and worker_of[2] == 1
     assert 0 <= worker_of[3] < 4
     assert index(t, 1, START) > index(t, 0, COMPLETE)  # one worker: its tasks run one after the other
+
+
+def test_task_waits_for_a_buffer_pinned_to_its_own_worker(rig):
+    """A task pinned to worker 2 waits, inside its body, for a command buffer whose task is pinned to worker 2 as well.
+    In the reference only the fiber parks and worker 2 keeps draining its private queue (Worker.zig:58-76,262-280), so
+    the inner task runs and the outer one resumes.  A pool whose tasks own their threads must hand worker 2's queue to
+    somebody else while that thread is parked — or this never finishes."""
+    import threading
+
+    if rig.lib.is_oracle:
+        pytest.skip("the oracle's blocking waits hold their OS thread as well (oracle_pool.cpp header, 'Difference that remains') "
+                    "and it has no stand-in for a parked worker's private queue; it is not used for this case")
+    outer = rig.task(1, gate=True)
+    first = rig.enqueue(rig.buffer(100, ("worker", 2), outer))
+    deadline = time.time() + 10
+    while not any(i == 1 and k == START for (i, k, _w) in rig.trace()) and time.time() < deadline:
+        time.sleep(0.001)  # the outer task now occupies worker 2 (it spins on the gate)
+    second = rig.enqueue(rig.buffer(200, ("worker", 2), rig.task(2)))  # cannot start: its worker is busy
+    rig.h.helper_task_wait_on(outer[1], second.data, second.vtable)
+    rig.h.helper_open_gate(C.byref(rig.log))  # the outer task goes on to wait for `second`
+    result = []
+    waiter = threading.Thread(target=lambda: result.append(rig.wait(first)), daemon=True)
+    waiter.start()
+    waiter.join(20)
+    assert result == [COMPLETED], rig.trace()
+    t = rig.settle(2 * 3 + 2 * 2)
+    assert rig.h.helper_task_wait_status(outer[1]) == COMPLETED
+    rig.release(first)
+    rig.release(second)
+    assert kinds(t, 1) == RAN and kinds(t, 2) == RAN and kinds(t, 100) == B_OK and kinds(t, 200) == B_OK
+    worker_of = {i: w for (i, k, w) in t if k == START}
+    assert worker_of == {1: 2, 2: 2}  # both ran as worker 2
+    assert index(t, 1, START) < index(t, 2, START) < index(t, 2, COMPLETE) < index(t, 1, COMPLETE)
 
 
 def test_worker_id_is_false_outside_the_pool(lib):
