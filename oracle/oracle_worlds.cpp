@@ -14,6 +14,10 @@
 //    run_begin (task) / run_end (command buffer on_complete) because oracle tasks are OS
 //    threads, not fibers (see oracle_pool.cpp). Observable ordering is unchanged: generation
 //    g+1 starts after g ended; `signal` fires after the generation ended.
+//  * toposort records the systems it has visited (markers.put below).  The reference's sort reads `markers` but
+//    never writes it (SystemGroup.zig:214-246), so a system reached over two dependency paths would be appended
+//    twice into a task list sized for one entry per system; the contract (every system once per generation) is
+//    what is restated here.
 //  * MultiGenerationAllocator follows its documentation (4-generation ring), not the `& 4`
 //    typo of heap/MultiGenerationAllocator.zig:33.
 #include <algorithm>
